@@ -1,0 +1,181 @@
+/*
+ * b2gs.h — C ABI of libb2gs.so, the B200 (sm_100a) differentiable Gaussian-splatting
+ * hot path.  Plain C: raw device pointers, sizes, an opaque stream handle
+ * (cudaStream_t passed as void*), int status codes.  No torch types.
+ *
+ * Every entry point replaces one piece of the reference's native interface
+ * (paths relative to the reference tree; DGR = submodules/diff-gaussian-rasterization,
+ * CR = DGR/cuda_rasterizer, KNN = submodules/simple-knn, GS = gaussian_splatting):
+ *
+ *   b2gs_forward_plan + b2gs_forward_render
+ *        <- _C.rasterize_gaussians            DGR/rasterize_points.h:17-38, DGR/ext.cpp:16
+ *           CudaRasterizer::Rasterizer::forward   CR/rasterizer.h:35-61, CR/rasterizer_impl.cu:198-344
+ *   b2gs_backward
+ *        <- _C.rasterize_gaussians_backward   DGR/rasterize_points.h:40-64, DGR/ext.cpp:17
+ *           CudaRasterizer::Rasterizer::backward  CR/rasterizer.h:63-92, CR/rasterizer_impl.cu:348-455
+ *           + the [P,6] -> [6] tau reduction of DGR/diff_gaussian_rasterization/__init__.py:152
+ *   b2gs_mark_visible
+ *        <- _C.mark_visible                   DGR/rasterize_points.h:66-69, CR/rasterizer_impl.cu:141-153
+ *   b2gs_knn3_dist2
+ *        <- simple_knn._C.distCUDA2           KNN/spatial.cu:15-26, KNN/simple_knn.cu:185-221
+ *   b2gs_adam_step
+ *        <- torch.optim.Adam(eps=1e-15).step  GS/scene/gaussian_model.py:283, utils/slam_backend.py:307
+ *   b2gs_*_bytes
+ *        <- required<T>() / fromChunk         CR/rasterizer_impl.h:21-73, CR/rasterizer_impl.cu:155-194
+ *
+ * Ownership: the caller allocates every buffer (outputs, gradients, workspaces);
+ * the library never allocates or frees device memory and keeps no global state
+ * apart from a thread-local last-error string.  All work is enqueued on the
+ * given stream.  The only host synchronisation is in b2gs_forward_plan (it must
+ * return the instance count so the caller can size the binning workspace — the
+ * reference has the same sync at CR/rasterizer_impl.cu:284) and after every
+ * kernel when args->debug != 0 (CR/auxiliary.h:166-173).
+ *
+ * Matrix convention (identical to the reference): all 4x4 inputs
+ * are the transpose of the math matrix stored row-major, i.e. column-major math
+ * matrices: element (row r, col c) is m[4*c + r].
+ *
+ * Absent optional inputs are NULL pointers (reference: empty tensors whose
+ * data_ptr() is null, DGR/diff_gaussian_rasterization/__init__.py:214-228).
+ */
+#ifndef B2GS_H_INCLUDED
+#define B2GS_H_INCLUDED
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define B2GS_API __attribute__((visibility("default")))
+#else
+#define B2GS_API
+#endif
+
+#define B2GS_OK 0
+#define B2GS_ERR_INVALID 1   /* bad argument (message in b2gs_last_error) */
+#define B2GS_ERR_CUDA 2      /* a CUDA call / kernel failed */
+#define B2GS_ERR_WORKSPACE 3 /* a workspace is too small */
+
+#define B2GS_TILE 16         /* tile edge in pixels (CR/config.h:16-17) */
+
+/* Arguments shared by forward and backward: the 13 fields of
+ * GaussianRasterizationSettings plus the per-Gaussian inputs. */
+typedef struct B2gsScene {
+  int32_t P;               /* number of Gaussians */
+  int32_t D;               /* active SH degree 0..3 */
+  int32_t M;               /* SH coefficients per Gaussian in `shs` (0 when colors_precomp is used) */
+  int32_t W, H;            /* image size in pixels */
+  float tan_fovx, tan_fovy;
+  float scale_modifier;
+  int32_t prefiltered;     /* CR/auxiliary.h:155-160: trap if a culled point shows up */
+  int32_t debug;           /* sync + check after every launch */
+  const float* bg;             /* device [3] */
+  const float* viewmatrix;     /* device [16] */
+  const float* projmatrix;     /* device [16] */
+  const float* projmatrix_raw; /* device [16]; backward only (may be NULL in forward) */
+  const float* campos;         /* device [3] */
+  const float* means3D;        /* device [P,3] */
+  const float* shs;            /* device [P,M,3] or NULL */
+  const float* colors_precomp; /* device [P,3] or NULL */
+  const float* opacities;      /* device [P] */
+  const float* scales;         /* device [P,3] or NULL */
+  const float* rotations;      /* device [P,4] (r,x,y,z) or NULL */
+  const float* cov3D_precomp;  /* device [P,6] or NULL */
+} B2gsScene;
+
+/* Workspaces.  Layout is private to the library; the same three buffers must be
+ * handed back, unmodified, to b2gs_backward. */
+typedef struct B2gsWorkspace {
+  void* geom;   size_t geom_bytes;    /* >= b2gs_geom_bytes(P) */
+  void* image;  size_t image_bytes;   /* >= b2gs_image_bytes(W,H) */
+  void* binning; size_t binning_bytes;/* >= b2gs_binning_bytes(R,W,H); may be NULL in forward_plan */
+} B2gsWorkspace;
+
+typedef struct B2gsForwardOut {
+  float* color;      /* device [3,H,W] */
+  float* depth;      /* device [1,H,W] */
+  float* opacity;    /* device [1,H,W] */
+  int32_t* radii;    /* device [P] */
+  int32_t* n_touched;/* device [P]; zero-filled by the library */
+} B2gsForwardOut;
+
+typedef struct B2gsBackwardIO {
+  const float* dL_dcolor;  /* device [3,H,W] */
+  const float* dL_ddepth;  /* device [1,H,W] */
+  const int32_t* radii;    /* device [P], from the forward */
+  /* outputs: every row is written by the library (zeros for culled Gaussians);
+   * pointers marked optional may be NULL to skip that output. */
+  float* dL_dmeans3D;   /* [P,3] */
+  float* dL_dmeans2D;   /* [P,3] (z always 0; x,y scaled by W/2, H/2 — CR/backward.cu:643-644) */
+  float* dL_dopacity;   /* [P] */
+  float* dL_dcolors;    /* [P,3] optional: gradient wrt colors_precomp */
+  float* dL_dsh;        /* [P,M,3] optional: gradient wrt shs */
+  float* dL_dscales;    /* [P,3] optional */
+  float* dL_drotations; /* [P,4] optional */
+  float* dL_dcov3D;     /* [P,6] optional */
+  float* dL_dtau;       /* [6] = (rho(3), theta(3)), already summed over Gaussians */
+  void* scratch; size_t scratch_bytes; /* >= b2gs_backward_scratch_bytes(P) */
+} B2gsBackwardIO;
+
+B2GS_API int b2gs_version(void);
+B2GS_API const char* b2gs_last_error(void);
+
+B2GS_API size_t b2gs_geom_bytes(int32_t P);
+B2GS_API size_t b2gs_image_bytes(int32_t W, int32_t H);
+B2GS_API size_t b2gs_binning_bytes(int64_t R, int32_t W, int32_t H);
+B2GS_API size_t b2gs_backward_scratch_bytes(int32_t P);
+
+/* Phase 1: per-Gaussian preprocessing, depth ordering, instance offsets.
+ * Writes out->radii, zero-fills out->n_touched, returns the number of
+ * (Gaussian,tile) instances in *num_rendered (synchronises the stream). */
+B2GS_API int b2gs_forward_plan(const B2gsScene* scene, const B2gsWorkspace* ws,
+                      const B2gsForwardOut* out, void* stream, int64_t* num_rendered);
+
+/* Phase 2: instance emission, tile binning, tile ranges, alpha blending. */
+B2GS_API int b2gs_forward_render(const B2gsScene* scene, const B2gsWorkspace* ws,
+                        const B2gsForwardOut* out, int64_t num_rendered, void* stream);
+
+B2GS_API int b2gs_backward(const B2gsScene* scene, const B2gsWorkspace* ws, int64_t num_rendered,
+                  const B2gsBackwardIO* io, void* stream);
+
+/* present[i] = 1 if view-space z > 0.2 (CR/auxiliary.h:139-164). */
+B2GS_API int b2gs_mark_visible(int32_t P, const float* means3D, const float* viewmatrix,
+                      const float* projmatrix, uint8_t* present, void* stream);
+
+/* Parity/debug helper: materialise the reference's sorted 64-bit key list
+ * (tile<<32 | depth bits), the sorted Gaussian ids and the tile ranges from the
+ * library's private workspaces.  keys[R], values[R], ranges[2*tiles]. */
+B2GS_API int b2gs_debug_export_binning(const B2gsScene* scene, const B2gsWorkspace* ws, int64_t num_rendered,
+                              uint64_t* keys, uint32_t* values, uint32_t* ranges, void* stream);
+/* Parity/debug helper: copy per-Gaussian forward state out of the geometry workspace.
+ * Any pointer may be NULL.  depths[P], means2D[P,2], conic_opacity[P,4], rgb[P,3], tiles_touched[P]. */
+B2GS_API int b2gs_debug_export_geom(const B2gsScene* scene, const B2gsWorkspace* ws, float* depths,
+                           float* means2D, float* conic_opacity, float* rgb,
+                           uint32_t* tiles_touched, void* stream);
+/* Parity/debug helper: final_T[N], n_contrib[N] from the image workspace. */
+B2GS_API int b2gs_debug_export_image(const B2gsScene* scene, const B2gsWorkspace* ws, float* final_T,
+                            uint32_t* n_contrib, void* stream);
+
+/* mean squared distance to the 3 nearest neighbours (exact). points [P,3] -> out [P]. */
+B2GS_API size_t b2gs_knn_bytes(int32_t P);
+B2GS_API int b2gs_knn3_dist2(const float* points, int32_t P, float* out, void* workspace,
+                    size_t workspace_bytes, void* stream);
+
+/* Fused Adam over a set of parameter segments (torch.optim.Adam semantics:
+ * no weight decay, no amsgrad, bias correction from `step`, 1-based).
+ * Segment s covers n[s] floats at param[s]/grad[s]/exp_avg[s]/exp_avg_sq[s]
+ * with learning rate lr[s].  All pointer arrays are HOST arrays of device pointers. */
+typedef struct B2gsAdamSegment {
+  float* param; const float* grad; float* exp_avg; float* exp_avg_sq;
+  int64_t n; float lr;
+} B2gsAdamSegment;
+B2GS_API int b2gs_adam_step(const B2gsAdamSegment* segments, int32_t num_segments, int64_t step,
+                   float beta1, float beta2, float eps, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B2GS_H_INCLUDED */

@@ -1,0 +1,208 @@
+// api.cu — the extern "C" surface of libb2gs.so (see include/b2gs.h).
+// Host orchestration replacing CudaRasterizer::Rasterizer::forward / ::backward
+// (CR/rasterizer_impl.cu:198-344, :348-455).  Stream-aware, re-entrant, no
+// allocations: all buffers come from the caller.
+#include "common.cuh"
+#include <stdarg.h>
+#include <string.h>
+
+namespace b2gs {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int cuda_fail(cudaError_t e, const char* what, const char* file, int line) {
+  set_error("CUDA error '%s' (%d) at %s:%d in %s", cudaGetErrorString(e), (int)e, file, line, what);
+  return B2GS_ERR_CUDA;
+}
+
+static int check_scene(const B2gsScene* s, bool backward) {
+  if (!s) { set_error("scene is NULL"); return B2GS_ERR_INVALID; }
+  if (s->P < 0 || s->W <= 0 || s->H <= 0) {
+    set_error("bad sizes P=%d W=%d H=%d", s->P, s->W, s->H);
+    return B2GS_ERR_INVALID;
+  }
+  if (s->P == 0) return B2GS_OK;
+  if (!s->means3D || !s->opacities || !s->viewmatrix || !s->projmatrix || !s->bg) {
+    set_error("means3D/opacities/viewmatrix/projmatrix/bg must be non-NULL");
+    return B2GS_ERR_INVALID;
+  }
+  if ((s->shs == nullptr) == (s->colors_precomp == nullptr)) {
+    // message of DGR/diff_gaussian_rasterization/__init__.py:209
+    set_error("Please provide excatly one of either SHs or precomputed colors!");
+    return B2GS_ERR_INVALID;
+  }
+  const bool has_sr = s->scales != nullptr && s->rotations != nullptr;
+  if (has_sr == (s->cov3D_precomp != nullptr) || ((s->scales != nullptr) != (s->rotations != nullptr))) {
+    // message of DGR/diff_gaussian_rasterization/__init__.py:212
+    set_error("Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!");
+    return B2GS_ERR_INVALID;
+  }
+  if (s->shs) {
+    if (!s->campos) { set_error("campos must be non-NULL when SHs are used"); return B2GS_ERR_INVALID; }
+    if (s->D < 0 || s->D > 3 || (s->D + 1) * (s->D + 1) > s->M) {
+      set_error("SH degree %d needs %d coefficients, shs has M=%d", s->D, (s->D + 1) * (s->D + 1), s->M);
+      return B2GS_ERR_INVALID;
+    }
+  }
+  if (backward && !s->projmatrix_raw) {
+    set_error("projmatrix_raw must be non-NULL in backward");
+    return B2GS_ERR_INVALID;
+  }
+  return B2GS_OK;
+}
+
+}  // namespace b2gs
+
+using namespace b2gs;
+
+extern "C" int b2gs_version(void) { return 100; }
+extern "C" const char* b2gs_last_error(void) { return g_err; }
+
+extern "C" size_t b2gs_geom_bytes(int32_t P) {
+  size_t t = 0;
+  carve_geom(nullptr, P, &t);
+  return t;
+}
+extern "C" size_t b2gs_image_bytes(int32_t W, int32_t H) {
+  size_t t = 0;
+  carve_image(nullptr, W, H, &t);
+  return t;
+}
+extern "C" size_t b2gs_binning_bytes(int64_t R, int32_t W, int32_t H) {
+  (void)W; (void)H;
+  size_t t = 0;
+  carve_bin(nullptr, R, &t);
+  return t;
+}
+extern "C" size_t b2gs_backward_scratch_bytes(int32_t P) {
+  const size_t blocks = ((size_t)(P > 0 ? P : 1) + 255) / 256;
+  return align_up(((size_t)(P > 0 ? P : 1) * ACC_STRIDE + blocks * 8) * sizeof(float), 256);
+}
+
+extern "C" int b2gs_forward_plan(const B2gsScene* scene, const B2gsWorkspace* ws,
+                                 const B2gsForwardOut* out, void* stream, int64_t* num_rendered) {
+  int rc = check_scene(scene, false);
+  if (rc) return rc;
+  if (!ws || !out || !num_rendered) { set_error("NULL ws/out/num_rendered"); return B2GS_ERR_INVALID; }
+  *num_rendered = 0;
+  const B2gsScene& s = *scene;
+  if (s.P == 0) return B2GS_OK;
+  if (s.P >= (1 << 30)) { set_error("P too large"); return B2GS_ERR_INVALID; }
+  if (!out->radii || !out->n_touched) { set_error("radii/n_touched outputs must be non-NULL"); return B2GS_ERR_INVALID; }
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  size_t need = 0;
+  GeomWS g = carve_geom(ws->geom, s.P, &need);
+  if (!ws->geom || ws->geom_bytes < need) {
+    set_error("geometry workspace too small: %zu < %zu", ws->geom_bytes, need);
+    return B2GS_ERR_WORKSPACE;
+  }
+  B2GS_CUDA(cudaMemsetAsync(out->n_touched, 0, sizeof(int32_t) * (size_t)s.P, st));
+  rc = launch_preprocess_fwd(s, g, out->radii, st);
+  if (rc) return rc;
+  rc = launch_depth_order(s, g, st);
+  if (rc) return rc;
+  uint32_t R = 0;
+  B2GS_CUDA(cudaMemcpyAsync(&R, g.offsets + (s.P - 1), sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+  B2GS_CUDA(cudaStreamSynchronize(st));
+  *num_rendered = (int64_t)R;
+  return B2GS_OK;
+}
+
+extern "C" int b2gs_forward_render(const B2gsScene* scene, const B2gsWorkspace* ws,
+                                   const B2gsForwardOut* out, int64_t R, void* stream) {
+  int rc = check_scene(scene, false);
+  if (rc) return rc;
+  if (!ws || !out) { set_error("NULL ws/out"); return B2GS_ERR_INVALID; }
+  const B2gsScene& s = *scene;
+  if (!out->color || !out->depth || !out->opacity) { set_error("image outputs must be non-NULL"); return B2GS_ERR_INVALID; }
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  size_t need = 0;
+  ImageWS im = carve_image(ws->image, s.W, s.H, &need);
+  if (!ws->image || ws->image_bytes < need) {
+    set_error("image workspace too small: %zu < %zu", ws->image_bytes, need);
+    return B2GS_ERR_WORKSPACE;
+  }
+  if (s.P == 0) R = 0;
+  GeomWS g = carve_geom(ws->geom, s.P, nullptr);
+  BinWS b = carve_bin(ws->binning, R, &need);
+  if (R > 0 && (!ws->binning || ws->binning_bytes < need)) {
+    set_error("binning workspace too small: %zu < %zu", ws->binning_bytes, need);
+    return B2GS_ERR_WORKSPACE;
+  }
+  if (R >= ((int64_t)1 << 31)) { set_error("too many instances: %lld", (long long)R); return B2GS_ERR_INVALID; }
+  rc = launch_binning(s, g, im, b, R, st);
+  if (rc) return rc;
+  B2gsForwardOut o = *out;
+  return launch_render_fwd(s, g, im, b, o, st);
+}
+
+extern "C" int b2gs_backward(const B2gsScene* scene, const B2gsWorkspace* ws, int64_t R,
+                             const B2gsBackwardIO* io, void* stream) {
+  int rc = check_scene(scene, true);
+  if (rc) return rc;
+  if (!ws || !io) { set_error("NULL ws/io"); return B2GS_ERR_INVALID; }
+  const B2gsScene& s = *scene;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (!io->dL_dtau) { set_error("dL_dtau must be non-NULL"); return B2GS_ERR_INVALID; }
+  if (s.P == 0) {
+    B2GS_CUDA(cudaMemsetAsync(io->dL_dtau, 0, 6 * sizeof(float), st));
+    return B2GS_OK;
+  }
+  if (!io->dL_dcolor || !io->dL_ddepth || !io->radii || !io->dL_dmeans3D || !io->dL_dmeans2D ||
+      !io->dL_dopacity) {
+    set_error("backward: required pointer is NULL");
+    return B2GS_ERR_INVALID;
+  }
+  const size_t need = b2gs_backward_scratch_bytes(s.P);
+  if (!io->scratch || io->scratch_bytes < need) {
+    set_error("backward scratch too small: %zu < %zu", io->scratch_bytes, need);
+    return B2GS_ERR_WORKSPACE;
+  }
+  GeomWS g = carve_geom(ws->geom, s.P, nullptr);
+  ImageWS im = carve_image(ws->image, s.W, s.H, nullptr);
+  BinWS b = carve_bin(ws->binning, R, nullptr);
+  float* acc = reinterpret_cast<float*>(io->scratch);
+  B2GS_CUDA(cudaMemsetAsync(acc, 0, (size_t)s.P * ACC_STRIDE * sizeof(float), st));
+  if (R > 0) {
+    rc = launch_render_bwd(s, g, im, b, *io, acc, st);
+    if (rc) return rc;
+  }
+  return launch_preprocess_bwd(s, g, *io, acc, st);
+}
+
+namespace b2gs {
+__global__ void export_geom_kernel(int P, GeomWS g, float* depths, float* means2D, float* conic_o,
+                                   float* rgb, uint32_t* touched) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= P) return;
+  const bool vis = g.tiles_touched[i] != 0;
+  if (touched) touched[i] = g.tiles_touched[i];
+  float4 cd = vis ? g.rgbd[i] : make_float4(0, 0, 0, 0);
+  float4 co = vis ? g.conic_o[i] : make_float4(0, 0, 0, 0);
+  float2 p = vis ? g.xy[i] : make_float2(0, 0);
+  if (depths) depths[i] = cd.w;
+  if (means2D) { means2D[2 * i] = p.x; means2D[2 * i + 1] = p.y; }
+  if (conic_o) { conic_o[4 * i] = co.x; conic_o[4 * i + 1] = co.y; conic_o[4 * i + 2] = co.z; conic_o[4 * i + 3] = co.w; }
+  if (rgb) { rgb[3 * i] = cd.x; rgb[3 * i + 1] = cd.y; rgb[3 * i + 2] = cd.z; }
+}
+}  // namespace b2gs
+
+extern "C" int b2gs_debug_export_geom(const B2gsScene* scene, const B2gsWorkspace* ws, float* depths,
+                                      float* means2D, float* conic_opacity, float* rgb,
+                                      uint32_t* tiles_touched, void* stream) {
+  if (!scene || !ws) { set_error("NULL scene/ws"); return B2GS_ERR_INVALID; }
+  if (scene->P == 0) return B2GS_OK;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  GeomWS g = carve_geom(ws->geom, scene->P, nullptr);
+  export_geom_kernel<<<(scene->P + 255) / 256, 256, 0, st>>>(scene->P, g, depths, means2D,
+                                                             conic_opacity, rgb, tiles_touched);
+  B2GS_LAUNCH_CHECK(st, 1);
+  return B2GS_OK;
+}

@@ -1,0 +1,445 @@
+// preprocess_bwd.cu — fused per-Gaussian backward.
+// Replaces computeCov2DCUDA (CR/backward.cu:150-346), preprocessCUDA backward
+// (:418-539) with SH backward (:21-145) and cov3D backward (:350-413), and the
+// torch.sum over dL_dtau[P,6] (DGR/diff_gaussian_rasterization/__init__.py:152).
+//
+// One pass over the Gaussians: reads the packed 48 B accumulator row written by
+// render_bwd, recomputes the EWA intermediates (cov3D is recomputed from
+// scale/rotation instead of being stored and re-read), writes every per-Gaussian
+// gradient row exactly once (zeros for culled Gaussians, so the caller needs no
+// memset of the outputs), and reduces the pose gradient dL_dtau in-kernel:
+// warp shuffle -> shared -> one partial row per block -> a fixed-order final sum
+// (deterministic given the accumulator).
+#include "common.cuh"
+#include "gsmath.cuh"
+
+namespace b2gs {
+
+struct V3 { float x, y, z; };
+__device__ __forceinline__ V3 cross3(V3 a, V3 b) {
+  return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x};
+}
+
+// d|v|^-1 v / dv applied to dv (CR/auxiliary.h:107-118)
+__device__ __forceinline__ V3 dnormvdv3(V3 v, V3 dv) {
+  float sum2 = v.x * v.x + v.y * v.y + v.z * v.z;
+  float invsum32 = 1.0f / sqrtf(sum2 * sum2 * sum2);
+  V3 r;
+  r.x = ((+sum2 - v.x * v.x) * dv.x - v.y * v.x * dv.y - v.z * v.x * dv.z) * invsum32;
+  r.y = (-v.x * v.y * dv.x + (sum2 - v.y * v.y) * dv.y - v.z * v.y * dv.z) * invsum32;
+  r.z = (-v.x * v.z * dv.x - v.y * v.z * dv.y + (sum2 - v.z * v.z) * dv.z) * invsum32;
+  return r;
+}
+
+// SH backward for one Gaussian: writes dL_dsh rows [0, M), returns dL/d(mean) through
+// the view direction (CR/backward.cu:21-145).
+__device__ __forceinline__ V3 sh_backward(int deg, int M, const float* __restrict__ sh, V3 pos,
+                                          V3 campos, uint8_t clamp_bits, V3 dL_dRGB,
+                                          float* __restrict__ dL_dsh) {
+  V3 dir_orig = {pos.x - campos.x, pos.y - campos.y, pos.z - campos.z};
+  float len = sqrtf(dir_orig.x * dir_orig.x + dir_orig.y * dir_orig.y + dir_orig.z * dir_orig.z);
+  const float x = dir_orig.x / len, y = dir_orig.y / len, z = dir_orig.z / len;
+  dL_dRGB.x *= (clamp_bits & 1) ? 0.f : 1.f;
+  dL_dRGB.y *= (clamp_bits & 2) ? 0.f : 1.f;
+  dL_dRGB.z *= (clamp_bits & 4) ? 0.f : 1.f;
+  const float g[3] = {dL_dRGB.x, dL_dRGB.y, dL_dRGB.z};
+
+  float basis[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) basis[i] = 0.f;
+  basis[0] = B2GS_SH_C0;
+  float ddir[3] = {0.f, 0.f, 0.f};  // dL/d(dir)
+  if (deg > 0) {
+    basis[1] = -B2GS_SH_C1 * y;
+    basis[2] = B2GS_SH_C1 * z;
+    basis[3] = -B2GS_SH_C1 * x;
+    float xx = 0, yy = 0, zz = 0, xy = 0, yz = 0, xz = 0;
+    if (deg > 1) {
+      xx = x * x; yy = y * y; zz = z * z; xy = x * y; yz = y * z; xz = x * z;
+      basis[4] = B2GS_SH_C2_0 * xy;
+      basis[5] = B2GS_SH_C2_1 * yz;
+      basis[6] = B2GS_SH_C2_2 * (2.f * zz - xx - yy);
+      basis[7] = B2GS_SH_C2_3 * xz;
+      basis[8] = B2GS_SH_C2_4 * (xx - yy);
+      if (deg > 2) {
+        basis[9] = B2GS_SH_C3_0 * y * (3.f * xx - yy);
+        basis[10] = B2GS_SH_C3_1 * xy * z;
+        basis[11] = B2GS_SH_C3_2 * y * (4.f * zz - xx - yy);
+        basis[12] = B2GS_SH_C3_3 * z * (2.f * zz - 3.f * xx - 3.f * yy);
+        basis[13] = B2GS_SH_C3_4 * x * (4.f * zz - xx - yy);
+        basis[14] = B2GS_SH_C3_5 * z * (xx - yy);
+        basis[15] = B2GS_SH_C3_6 * x * (xx - 3.f * yy);
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      const float* s = sh + c;  // s[3*k] = coefficient k, channel c
+      float dx = -B2GS_SH_C1 * s[9];
+      float dy = -B2GS_SH_C1 * s[3];
+      float dz = B2GS_SH_C1 * s[6];
+      if (deg > 1) {
+        dx += B2GS_SH_C2_0 * y * s[12] + B2GS_SH_C2_2 * 2.f * -x * s[18] + B2GS_SH_C2_3 * z * s[21] +
+              B2GS_SH_C2_4 * 2.f * x * s[24];
+        dy += B2GS_SH_C2_0 * x * s[12] + B2GS_SH_C2_1 * z * s[15] + B2GS_SH_C2_2 * 2.f * -y * s[18] +
+              B2GS_SH_C2_4 * 2.f * -y * s[24];
+        dz += B2GS_SH_C2_1 * y * s[15] + B2GS_SH_C2_2 * 2.f * 2.f * z * s[18] + B2GS_SH_C2_3 * x * s[21];
+        if (deg > 2) {
+          dx += (B2GS_SH_C3_0 * s[27] * 3.f * 2.f * xy + B2GS_SH_C3_1 * s[30] * yz +
+                 B2GS_SH_C3_2 * s[33] * -2.f * xy + B2GS_SH_C3_3 * s[36] * -3.f * 2.f * xz +
+                 B2GS_SH_C3_4 * s[39] * (-3.f * xx + 4.f * zz - yy) +
+                 B2GS_SH_C3_5 * s[42] * 2.f * xz + B2GS_SH_C3_6 * s[45] * 3.f * (xx - yy));
+          dy += (B2GS_SH_C3_0 * s[27] * 3.f * (xx - yy) + B2GS_SH_C3_1 * s[30] * xz +
+                 B2GS_SH_C3_2 * s[33] * (-3.f * yy + 4.f * zz - xx) +
+                 B2GS_SH_C3_3 * s[36] * -3.f * 2.f * yz + B2GS_SH_C3_4 * s[39] * -2.f * xy +
+                 B2GS_SH_C3_5 * s[42] * -2.f * yz + B2GS_SH_C3_6 * s[45] * -3.f * 2.f * xy);
+          dz += (B2GS_SH_C3_1 * s[30] * xy + B2GS_SH_C3_2 * s[33] * 4.f * 2.f * yz +
+                 B2GS_SH_C3_3 * s[36] * 3.f * (2.f * zz - xx - yy) +
+                 B2GS_SH_C3_4 * s[39] * 4.f * 2.f * xz + B2GS_SH_C3_5 * s[42] * (xx - yy));
+        }
+      }
+      ddir[0] += dx * g[c];
+      ddir[1] += dy * g[c];
+      ddir[2] += dz * g[c];
+    }
+  }
+  const int active = (deg + 1) * (deg + 1);
+  for (int k = 0; k < M; ++k) {
+    const float bk = (k < active && k < 16) ? basis[k] : 0.f;
+    dL_dsh[3 * k + 0] = bk * g[0];
+    dL_dsh[3 * k + 1] = bk * g[1];
+    dL_dsh[3 * k + 2] = bk * g[2];
+  }
+  return dnormvdv3(dir_orig, V3{ddir[0], ddir[1], ddir[2]});
+}
+
+__global__ void __launch_bounds__(256)
+preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
+                      const int32_t* __restrict__ radii, const float* __restrict__ shs,
+                      const uint8_t* __restrict__ clamped, const float* __restrict__ scales,
+                      const float* __restrict__ rotations, float scale_modifier,
+                      const float* __restrict__ cov3D_precomp, const float* __restrict__ viewmatrix,
+                      const float* __restrict__ projmatrix, const float* __restrict__ projmatrix_raw,
+                      const float* __restrict__ campos_p, float h_x, float h_y, float tan_fovx,
+                      float tan_fovy, const float* __restrict__ acc,
+                      float* __restrict__ dL_dmeans3D, float* __restrict__ dL_dmeans2D,
+                      float* __restrict__ dL_dopacity, float* __restrict__ dL_dcolors,
+                      float* __restrict__ dL_dsh, float* __restrict__ dL_dscales,
+                      float* __restrict__ dL_drots, float* __restrict__ dL_dcov3D,
+                      float* __restrict__ tau_partials) {
+  __shared__ float s_view[16], s_proj[16];
+  __shared__ float s_tau[8][6];
+  if (threadIdx.x < 16) s_view[threadIdx.x] = viewmatrix[threadIdx.x];
+  else if (threadIdx.x < 32) s_proj[threadIdx.x - 16] = projmatrix[threadIdx.x - 16];
+  __syncthreads();
+  const float* view = s_view;
+  const float* proj = s_proj;
+
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  float tau[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  const bool live = idx < P && radii[idx] > 0;
+
+  if (idx < P && !live) {
+    // culled: every gradient row is zero (reference: torch::zeros, DGR/rasterize_points.cu:160-170)
+    dL_dmeans3D[3 * idx] = 0.f; dL_dmeans3D[3 * idx + 1] = 0.f; dL_dmeans3D[3 * idx + 2] = 0.f;
+    dL_dmeans2D[3 * idx] = 0.f; dL_dmeans2D[3 * idx + 1] = 0.f; dL_dmeans2D[3 * idx + 2] = 0.f;
+    dL_dopacity[idx] = 0.f;
+    if (dL_dcolors) { dL_dcolors[3 * idx] = 0.f; dL_dcolors[3 * idx + 1] = 0.f; dL_dcolors[3 * idx + 2] = 0.f; }
+    if (dL_dsh) for (int k = 0; k < 3 * M; ++k) dL_dsh[(size_t)idx * M * 3 + k] = 0.f;
+    if (dL_dscales) { dL_dscales[3 * idx] = 0.f; dL_dscales[3 * idx + 1] = 0.f; dL_dscales[3 * idx + 2] = 0.f; }
+    if (dL_drots) reinterpret_cast<float4*>(dL_drots)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (dL_dcov3D) for (int k = 0; k < 6; ++k) dL_dcov3D[6 * idx + k] = 0.f;
+  }
+
+  if (live) {
+    const float4* arow = reinterpret_cast<const float4*>(acc + (size_t)idx * ACC_STRIDE);
+    const float4 a0 = arow[0], a1 = arow[1], a2 = arow[2];
+    const float dmean2D_x = a0.x, dmean2D_y = a0.y;
+    const float3 dL_dconic = {a0.z, a0.w, a1.x};
+    const float dL_dop = a1.y;
+    const V3 dL_dcol = {a1.z, a1.w, a2.x};
+    const float dL_ddepth = a2.y;
+
+    const float3 mean = {means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]};
+    float cov6[6];
+    float4 q = make_float4(1.f, 0.f, 0.f, 0.f);
+    float sx = 0.f, sy = 0.f, sz = 0.f;
+    if (cov3D_precomp != nullptr) {
+#pragma unroll
+      for (int i = 0; i < 6; ++i) cov6[i] = cov3D_precomp[6 * idx + i];
+    } else {
+      q = reinterpret_cast<const float4*>(rotations)[idx];
+      sx = scales[3 * idx]; sy = scales[3 * idx + 1]; sz = scales[3 * idx + 2];
+      cov3d_from_scale_rot(sx, sy, sz, scale_modifier, q, cov6);
+    }
+
+    // ---------------- cov2D / conic backward (CR/backward.cu:150-346) ----------------
+    Ewa e;
+    ewa_setup(e, mean, h_x, h_y, tan_fovx, tan_fovy, cov6, view);
+    const float3 t = e.t;
+    const float x_grad_mul = (e.txtz < -e.limx || e.txtz > e.limx) ? 0.f : 1.f;
+    const float y_grad_mul = (e.tytz < -e.limy || e.tytz > e.limy) ? 0.f : 1.f;
+    const Mat3& J = e.J;
+    const Mat3& Wm = e.W;
+    const Mat3& T = e.T;
+    const Mat3& Vrk = e.Vrk;
+    Mat3 cov2D = ewa_cov2d(e);
+    const float a = cov2D.m[0][0] += 0.3f;
+    const float b = cov2D.m[0][1];
+    const float c = cov2D.m[1][1] += 0.3f;
+
+    const float denom = a * c - b * b;
+    float dL_da = 0, dL_db = 0, dL_dc = 0;
+    const float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
+    float dcov[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (denom2inv != 0) {
+      dL_da = denom2inv * (-c * c * dL_dconic.x + 2 * b * c * dL_dconic.y + (denom - a * c) * dL_dconic.z);
+      dL_dc = denom2inv * (-a * a * dL_dconic.z + 2 * a * b * dL_dconic.y + (denom - a * c) * dL_dconic.x);
+      dL_db = denom2inv * 2 * (b * c * dL_dconic.x - (denom + 2 * b * b) * dL_dconic.y + a * b * dL_dconic.z);
+
+      dcov[0] = (T.m[0][0] * T.m[0][0] * dL_da + T.m[0][0] * T.m[1][0] * dL_db + T.m[1][0] * T.m[1][0] * dL_dc);
+      dcov[3] = (T.m[0][1] * T.m[0][1] * dL_da + T.m[0][1] * T.m[1][1] * dL_db + T.m[1][1] * T.m[1][1] * dL_dc);
+      dcov[5] = (T.m[0][2] * T.m[0][2] * dL_da + T.m[0][2] * T.m[1][2] * dL_db + T.m[1][2] * T.m[1][2] * dL_dc);
+      dcov[1] = 2 * T.m[0][0] * T.m[0][1] * dL_da + (T.m[0][0] * T.m[1][1] + T.m[0][1] * T.m[1][0]) * dL_db + 2 * T.m[1][0] * T.m[1][1] * dL_dc;
+      dcov[2] = 2 * T.m[0][0] * T.m[0][2] * dL_da + (T.m[0][0] * T.m[1][2] + T.m[0][2] * T.m[1][0]) * dL_db + 2 * T.m[1][0] * T.m[1][2] * dL_dc;
+      dcov[4] = 2 * T.m[0][2] * T.m[0][1] * dL_da + (T.m[0][1] * T.m[1][2] + T.m[0][2] * T.m[1][1]) * dL_db + 2 * T.m[1][1] * T.m[1][2] * dL_dc;
+    }
+
+    // dL/dT (upper 2x3)
+    const float dL_dT00 = 2 * (T.m[0][0] * Vrk.m[0][0] + T.m[0][1] * Vrk.m[0][1] + T.m[0][2] * Vrk.m[0][2]) * dL_da +
+                          (T.m[1][0] * Vrk.m[0][0] + T.m[1][1] * Vrk.m[0][1] + T.m[1][2] * Vrk.m[0][2]) * dL_db;
+    const float dL_dT01 = 2 * (T.m[0][0] * Vrk.m[1][0] + T.m[0][1] * Vrk.m[1][1] + T.m[0][2] * Vrk.m[1][2]) * dL_da +
+                          (T.m[1][0] * Vrk.m[1][0] + T.m[1][1] * Vrk.m[1][1] + T.m[1][2] * Vrk.m[1][2]) * dL_db;
+    const float dL_dT02 = 2 * (T.m[0][0] * Vrk.m[2][0] + T.m[0][1] * Vrk.m[2][1] + T.m[0][2] * Vrk.m[2][2]) * dL_da +
+                          (T.m[1][0] * Vrk.m[2][0] + T.m[1][1] * Vrk.m[2][1] + T.m[1][2] * Vrk.m[2][2]) * dL_db;
+    const float dL_dT10 = 2 * (T.m[1][0] * Vrk.m[0][0] + T.m[1][1] * Vrk.m[0][1] + T.m[1][2] * Vrk.m[0][2]) * dL_dc +
+                          (T.m[0][0] * Vrk.m[0][0] + T.m[0][1] * Vrk.m[0][1] + T.m[0][2] * Vrk.m[0][2]) * dL_db;
+    const float dL_dT11 = 2 * (T.m[1][0] * Vrk.m[1][0] + T.m[1][1] * Vrk.m[1][1] + T.m[1][2] * Vrk.m[1][2]) * dL_dc +
+                          (T.m[0][0] * Vrk.m[1][0] + T.m[0][1] * Vrk.m[1][1] + T.m[0][2] * Vrk.m[1][2]) * dL_db;
+    const float dL_dT12 = 2 * (T.m[1][0] * Vrk.m[2][0] + T.m[1][1] * Vrk.m[2][1] + T.m[1][2] * Vrk.m[2][2]) * dL_dc +
+                          (T.m[0][0] * Vrk.m[2][0] + T.m[0][1] * Vrk.m[2][1] + T.m[0][2] * Vrk.m[2][2]) * dL_db;
+
+    const float dL_dJ00 = Wm.m[0][0] * dL_dT00 + Wm.m[0][1] * dL_dT01 + Wm.m[0][2] * dL_dT02;
+    const float dL_dJ02 = Wm.m[2][0] * dL_dT00 + Wm.m[2][1] * dL_dT01 + Wm.m[2][2] * dL_dT02;
+    const float dL_dJ11 = Wm.m[1][0] * dL_dT10 + Wm.m[1][1] * dL_dT11 + Wm.m[1][2] * dL_dT12;
+    const float dL_dJ12 = Wm.m[2][0] * dL_dT10 + Wm.m[2][1] * dL_dT11 + Wm.m[2][2] * dL_dT12;
+
+    const float tz = 1.f / t.z;
+    const float tz2 = tz * tz;
+    const float tz3 = tz2 * tz;
+
+    const float dL_dtx = x_grad_mul * -h_x * tz2 * dL_dJ02;
+    const float dL_dty = y_grad_mul * -h_y * tz2 * dL_dJ12;
+    const float dL_dtz = -h_x * tz2 * dL_dJ00 - h_y * tz2 * dL_dJ11 + (2 * h_x * t.x) * tz3 * dL_dJ02 +
+                         (2 * h_y * t.y) * tz3 * dL_dJ12;
+
+    // pose: rho gets dL/dt, theta gets (-[t]x)^T dL/dt = t x dL/dt  (t is the CLAMPED mean, quirk q4)
+    {
+      const V3 gt = {dL_dtx, dL_dty, dL_dtz};
+      const V3 th = cross3(V3{t.x, t.y, t.z}, gt);
+      tau[0] += gt.x; tau[1] += gt.y; tau[2] += gt.z;
+      tau[3] += th.x; tau[4] += th.y; tau[5] += th.z;
+    }
+
+    // dL/dmean through the covariance path (assign)
+    V3 dmean;
+    dmean.x = view[0] * dL_dtx + view[1] * dL_dty + view[2] * dL_dtz;
+    dmean.y = view[4] * dL_dtx + view[5] * dL_dty + view[6] * dL_dtz;
+    dmean.z = view[8] * dL_dtx + view[9] * dL_dty + view[10] * dL_dtz;
+
+    // pose through W (rotation columns), CR/backward.cu:299-343
+    {
+      const float dL_dW00 = J.m[0][0] * dL_dT00;
+      const float dL_dW01 = J.m[0][0] * dL_dT01;
+      const float dL_dW02 = J.m[0][0] * dL_dT02;
+      const float dL_dW10 = J.m[1][1] * dL_dT10;
+      const float dL_dW11 = J.m[1][1] * dL_dT11;
+      const float dL_dW12 = J.m[1][1] * dL_dT12;
+      const float dL_dW20 = J.m[0][2] * dL_dT00 + J.m[1][2] * dL_dT10;
+      const float dL_dW21 = J.m[0][2] * dL_dT01 + J.m[1][2] * dL_dT11;
+      const float dL_dW22 = J.m[0][2] * dL_dT02 + J.m[1][2] * dL_dT12;
+      const V3 c1 = {view[0], view[1], view[2]};
+      const V3 c2 = {view[4], view[5], view[6]};
+      const V3 c3 = {view[8], view[9], view[10]};
+      const V3 w1 = {dL_dW00, dL_dW10, dL_dW20};
+      const V3 w2 = {dL_dW01, dL_dW11, dL_dW21};
+      const V3 w3 = {dL_dW02, dL_dW12, dL_dW22};
+      const V3 k1 = cross3(c1, w1), k2 = cross3(c2, w2), k3 = cross3(c3, w3);
+      tau[3] += k1.x + k2.x + k3.x;
+      tau[4] += k1.y + k2.y + k3.y;
+      tau[5] += k1.z + k2.z + k3.z;
+    }
+
+    // ---------------- projection backward (CR/backward.cu:446-528) ----------------
+    const float4 m_hom = xform_point_4x4(mean, proj);
+    const float m_w = 1.0f / (m_hom.w + 0.0000001f);
+    {
+      const float mul1 = (proj[0] * mean.x + proj[4] * mean.y + proj[8] * mean.z + proj[12]) * m_w * m_w;
+      const float mul2 = (proj[1] * mean.x + proj[5] * mean.y + proj[9] * mean.z + proj[13]) * m_w * m_w;
+      dmean.x += (proj[0] * m_w - proj[3] * mul1) * dmean2D_x + (proj[1] * m_w - proj[3] * mul2) * dmean2D_y;
+      dmean.y += (proj[4] * m_w - proj[7] * mul1) * dmean2D_x + (proj[5] * m_w - proj[7] * mul2) * dmean2D_y;
+      dmean.z += (proj[8] * m_w - proj[11] * mul1) * dmean2D_x + (proj[9] * m_w - proj[11] * mul2) * dmean2D_y;
+    }
+    // camera-frame point p_C = R m + t
+    V3 p_C;
+    p_C.x = view[0] * mean.x + view[4] * mean.y + view[8] * mean.z + view[12];
+    p_C.y = view[1] * mean.x + view[5] * mean.y + view[9] * mean.z + view[13];
+    p_C.z = view[2] * mean.x + view[6] * mean.y + view[10] * mean.z + view[14];
+    {
+      const float alpha = 1.0f * m_w;
+      const float beta = -m_hom.x * m_w * m_w;
+      const float gamma = -m_hom.y * m_w * m_w;
+      const float pa = projmatrix_raw[0];
+      const float pb = projmatrix_raw[5];
+      const float pe = projmatrix_raw[11];
+      const V3 d1 = {alpha * pa, 0.f, beta * pe};
+      const V3 d2 = {0.f, alpha * pb, gamma * pe};
+      const V3 d1t = cross3(p_C, d1);
+      const V3 d2t = cross3(p_C, d2);
+      tau[0] += dmean2D_x * d1.x + dmean2D_y * d2.x;
+      tau[1] += dmean2D_x * d1.y + dmean2D_y * d2.y;
+      tau[2] += dmean2D_x * d1.z + dmean2D_y * d2.z;
+      tau[3] += dmean2D_x * d1t.x + dmean2D_y * d2t.x;
+      tau[4] += dmean2D_x * d1t.y + dmean2D_y * d2t.y;
+      tau[5] += dmean2D_x * d1t.z + dmean2D_y * d2t.z;
+    }
+    // depth = p_C.z
+    {
+      const float dL_dpCz = dL_ddepth;
+      dmean.x += dL_dpCz * view[2];
+      dmean.y += dL_dpCz * view[6];
+      dmean.z += dL_dpCz * view[10];
+      tau[2] += dL_dpCz;
+      tau[3] += dL_dpCz * p_C.y;
+      tau[4] += dL_dpCz * -p_C.x;
+    }
+
+    // ---------------- colour ----------------
+    if (shs != nullptr) {
+      const V3 campos = {campos_p[0], campos_p[1], campos_p[2]};
+      const V3 dm = sh_backward(D, M, shs + (size_t)idx * M * 3, V3{mean.x, mean.y, mean.z}, campos,
+                                clamped[idx], dL_dcol, dL_dsh + (size_t)idx * M * 3);
+      dmean.x += dm.x; dmean.y += dm.y; dmean.z += dm.z;
+      tau[0] += -dm.x; tau[1] += -dm.y; tau[2] += -dm.z;
+      if (dL_dcolors) { dL_dcolors[3 * idx] = dL_dcol.x; dL_dcolors[3 * idx + 1] = dL_dcol.y; dL_dcolors[3 * idx + 2] = dL_dcol.z; }
+    } else if (dL_dcolors) {
+      dL_dcolors[3 * idx] = dL_dcol.x; dL_dcolors[3 * idx + 1] = dL_dcol.y; dL_dcolors[3 * idx + 2] = dL_dcol.z;
+    }
+
+    // ---------------- cov3D -> scale, rotation (CR/backward.cu:350-413) ----------------
+    if (scales != nullptr && (dL_dscales || dL_drots)) {
+      const float r = q.x, x = q.y, y = q.z, z = q.w;
+      const Mat3 R = quat_to_Rcols(r, x, y, z);
+      Mat3 S = mat3_cols(1.f, 0.f, 0.f, 0.f, 1.f, 0.f, 0.f, 0.f, 1.f);
+      const float s0 = scale_modifier * sx, s1 = scale_modifier * sy, s2 = scale_modifier * sz;
+      S.m[0][0] = s0; S.m[1][1] = s1; S.m[2][2] = s2;
+      const Mat3 Mm = mat3_mul(S, R);
+      const Mat3 dL_dSigma = mat3_cols(dcov[0], 0.5f * dcov[1], 0.5f * dcov[2],
+                                       0.5f * dcov[1], dcov[3], 0.5f * dcov[4],
+                                       0.5f * dcov[2], 0.5f * dcov[4], dcov[5]);
+      Mat3 M2;
+#pragma unroll
+      for (int cc = 0; cc < 3; ++cc)
+#pragma unroll
+        for (int rr = 0; rr < 3; ++rr) M2.m[cc][rr] = 2.0f * Mm.m[cc][rr];
+      const Mat3 dL_dM = mat3_mul(M2, dL_dSigma);
+      const Mat3 Rt = mat3_transpose(R);
+      Mat3 dL_dMt = mat3_transpose(dL_dM);
+      if (dL_dscales) {
+        dL_dscales[3 * idx + 0] = Rt.m[0][0] * dL_dMt.m[0][0] + Rt.m[0][1] * dL_dMt.m[0][1] + Rt.m[0][2] * dL_dMt.m[0][2];
+        dL_dscales[3 * idx + 1] = Rt.m[1][0] * dL_dMt.m[1][0] + Rt.m[1][1] * dL_dMt.m[1][1] + Rt.m[1][2] * dL_dMt.m[1][2];
+        dL_dscales[3 * idx + 2] = Rt.m[2][0] * dL_dMt.m[2][0] + Rt.m[2][1] * dL_dMt.m[2][1] + Rt.m[2][2] * dL_dMt.m[2][2];
+      }
+#pragma unroll
+      for (int rr = 0; rr < 3; ++rr) {
+        dL_dMt.m[0][rr] *= s0;
+        dL_dMt.m[1][rr] *= s1;
+        dL_dMt.m[2][rr] *= s2;
+      }
+      if (dL_drots) {
+        float4 dq;
+        dq.x = 2 * z * (dL_dMt.m[0][1] - dL_dMt.m[1][0]) + 2 * y * (dL_dMt.m[2][0] - dL_dMt.m[0][2]) + 2 * x * (dL_dMt.m[1][2] - dL_dMt.m[2][1]);
+        dq.y = 2 * y * (dL_dMt.m[1][0] + dL_dMt.m[0][1]) + 2 * z * (dL_dMt.m[2][0] + dL_dMt.m[0][2]) + 2 * r * (dL_dMt.m[1][2] - dL_dMt.m[2][1]) - 4 * x * (dL_dMt.m[2][2] + dL_dMt.m[1][1]);
+        dq.z = 2 * x * (dL_dMt.m[1][0] + dL_dMt.m[0][1]) + 2 * r * (dL_dMt.m[2][0] - dL_dMt.m[0][2]) + 2 * z * (dL_dMt.m[1][2] + dL_dMt.m[2][1]) - 4 * y * (dL_dMt.m[2][2] + dL_dMt.m[0][0]);
+        dq.w = 2 * r * (dL_dMt.m[0][1] - dL_dMt.m[1][0]) + 2 * x * (dL_dMt.m[2][0] + dL_dMt.m[0][2]) + 2 * y * (dL_dMt.m[1][2] + dL_dMt.m[2][1]) - 4 * z * (dL_dMt.m[1][1] + dL_dMt.m[0][0]);
+        reinterpret_cast<float4*>(dL_drots)[idx] = dq;  // raw-quaternion gradient (quirk q3)
+      }
+    } else {
+      if (dL_dscales) { dL_dscales[3 * idx] = 0.f; dL_dscales[3 * idx + 1] = 0.f; dL_dscales[3 * idx + 2] = 0.f; }
+      if (dL_drots) reinterpret_cast<float4*>(dL_drots)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+
+    if (dL_dcov3D) {
+#pragma unroll
+      for (int k = 0; k < 6; ++k) dL_dcov3D[6 * idx + k] = dcov[k];
+    }
+    dL_dmeans3D[3 * idx] = dmean.x;
+    dL_dmeans3D[3 * idx + 1] = dmean.y;
+    dL_dmeans3D[3 * idx + 2] = dmean.z;
+    dL_dmeans2D[3 * idx] = dmean2D_x;
+    dL_dmeans2D[3 * idx + 1] = dmean2D_y;
+    dL_dmeans2D[3 * idx + 2] = 0.f;
+    dL_dopacity[idx] = dL_dop;
+  }
+
+  // ---- dL_dtau: warp -> block -> one partial row per block ----
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int k = 0; k < 6; ++k) {
+    float v = tau[k];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0) s_tau[warp][k] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x < 6) {
+    float v = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) v += s_tau[w][threadIdx.x];
+    tau_partials[(size_t)blockIdx.x * 8 + threadIdx.x] = v;
+  }
+}
+
+// fixed-order final sum of the per-block partials -> dL_dtau[6]
+__global__ void __launch_bounds__(256) tau_finalize_kernel(int blocks, const float* __restrict__ partials,
+                                                           float* __restrict__ dL_dtau) {
+  __shared__ float s[8][8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float v[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  for (int b = threadIdx.x; b < blocks; b += 256) {
+#pragma unroll
+    for (int k = 0; k < 6; ++k) v[k] += partials[(size_t)b * 8 + k];
+  }
+#pragma unroll
+  for (int k = 0; k < 6; ++k) {
+    float x = v[k];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+    if (lane == 0) s[warp][k] = x;
+  }
+  __syncthreads();
+  if (threadIdx.x < 6) {
+    float x = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) x += s[w][threadIdx.x];
+    dL_dtau[threadIdx.x] = x;
+  }
+}
+
+int launch_preprocess_bwd(const B2gsScene& s, const GeomWS& g, const B2gsBackwardIO& io,
+                          const float* acc, cudaStream_t st) {
+  const float focal_y = s.H / (2.0f * s.tan_fovy);
+  const float focal_x = s.W / (2.0f * s.tan_fovx);
+  const int blocks = (s.P + 255) / 256;
+  float* partials = const_cast<float*>(acc) + (size_t)s.P * ACC_STRIDE;  // scratch tail
+  preprocess_bwd_kernel<<<blocks, 256, 0, st>>>(
+      s.P, s.D, s.M, s.means3D, io.radii, s.shs, g.clamped, s.scales, s.rotations, s.scale_modifier,
+      s.cov3D_precomp, s.viewmatrix, s.projmatrix, s.projmatrix_raw, s.campos, focal_x, focal_y,
+      s.tan_fovx, s.tan_fovy, acc, io.dL_dmeans3D, io.dL_dmeans2D, io.dL_dopacity, io.dL_dcolors,
+      s.shs ? io.dL_dsh : nullptr, io.dL_dscales, io.dL_drotations, io.dL_dcov3D, partials);
+  B2GS_LAUNCH_CHECK(st, s.debug);
+  tau_finalize_kernel<<<1, 256, 0, st>>>(blocks, partials, io.dL_dtau);
+  B2GS_LAUNCH_CHECK(st, s.debug);
+  return B2GS_OK;
+}
+
+}  // namespace b2gs
