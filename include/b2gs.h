@@ -122,6 +122,9 @@ typedef struct B2gsBackwardIO {
 
 B2GS_API int b2gs_version(void);
 B2GS_API const char* b2gs_last_error(void);
+/* number of the library's own (hand-written) kernels launched so far in this process;
+ * CUB sort/scan launches are not counted. */
+B2GS_API uint64_t b2gs_kernel_launches(void);
 
 B2GS_API size_t b2gs_geom_bytes(int32_t P);
 B2GS_API size_t b2gs_image_bytes(int32_t W, int32_t H);

@@ -1,0 +1,115 @@
+"""ctypes binding of libb2gs.so (include/b2gs.h).
+
+The library is the product: if it is missing this module raises at import —
+there is no CPU or PyTorch fallback anywhere in the package.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libb2gs.so")
+
+c_float_p = C.c_void_p  # raw device pointers travel as integers
+
+
+class B2gsScene(C.Structure):
+    _fields_ = [
+        ("P", C.c_int32), ("D", C.c_int32), ("M", C.c_int32), ("W", C.c_int32), ("H", C.c_int32),
+        ("tan_fovx", C.c_float), ("tan_fovy", C.c_float), ("scale_modifier", C.c_float),
+        ("prefiltered", C.c_int32), ("debug", C.c_int32),
+        ("bg", C.c_void_p), ("viewmatrix", C.c_void_p), ("projmatrix", C.c_void_p),
+        ("projmatrix_raw", C.c_void_p), ("campos", C.c_void_p), ("means3D", C.c_void_p),
+        ("shs", C.c_void_p), ("colors_precomp", C.c_void_p), ("opacities", C.c_void_p),
+        ("scales", C.c_void_p), ("rotations", C.c_void_p), ("cov3D_precomp", C.c_void_p),
+    ]
+
+
+class B2gsWorkspace(C.Structure):
+    _fields_ = [
+        ("geom", C.c_void_p), ("geom_bytes", C.c_size_t),
+        ("image", C.c_void_p), ("image_bytes", C.c_size_t),
+        ("binning", C.c_void_p), ("binning_bytes", C.c_size_t),
+    ]
+
+
+class B2gsForwardOut(C.Structure):
+    _fields_ = [
+        ("color", C.c_void_p), ("depth", C.c_void_p), ("opacity", C.c_void_p),
+        ("radii", C.c_void_p), ("n_touched", C.c_void_p),
+    ]
+
+
+class B2gsBackwardIO(C.Structure):
+    _fields_ = [
+        ("dL_dcolor", C.c_void_p), ("dL_ddepth", C.c_void_p), ("radii", C.c_void_p),
+        ("dL_dmeans3D", C.c_void_p), ("dL_dmeans2D", C.c_void_p), ("dL_dopacity", C.c_void_p),
+        ("dL_dcolors", C.c_void_p), ("dL_dsh", C.c_void_p), ("dL_dscales", C.c_void_p),
+        ("dL_drotations", C.c_void_p), ("dL_dcov3D", C.c_void_p), ("dL_dtau", C.c_void_p),
+        ("scratch", C.c_void_p), ("scratch_bytes", C.c_size_t),
+    ]
+
+
+class B2gsAdamSegment(C.Structure):
+    _fields_ = [
+        ("param", C.c_void_p), ("grad", C.c_void_p), ("exp_avg", C.c_void_p),
+        ("exp_avg_sq", C.c_void_p), ("n", C.c_int64), ("lr", C.c_float),
+    ]
+
+
+# every symbol include/b2gs.h declares: name -> (restype, argtypes)
+SYMBOLS = {
+    "b2gs_version": (C.c_int, []),
+    "b2gs_last_error": (C.c_char_p, []),
+    "b2gs_kernel_launches": (C.c_uint64, []),
+    "b2gs_geom_bytes": (C.c_size_t, [C.c_int32]),
+    "b2gs_image_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
+    "b2gs_binning_bytes": (C.c_size_t, [C.c_int64, C.c_int32, C.c_int32]),
+    "b2gs_backward_scratch_bytes": (C.c_size_t, [C.c_int32]),
+    "b2gs_forward_plan": (C.c_int, [C.POINTER(B2gsScene), C.POINTER(B2gsWorkspace),
+                                    C.POINTER(B2gsForwardOut), C.c_void_p, C.POINTER(C.c_int64)]),
+    "b2gs_forward_render": (C.c_int, [C.POINTER(B2gsScene), C.POINTER(B2gsWorkspace),
+                                      C.POINTER(B2gsForwardOut), C.c_int64, C.c_void_p]),
+    "b2gs_backward": (C.c_int, [C.POINTER(B2gsScene), C.POINTER(B2gsWorkspace), C.c_int64,
+                                C.POINTER(B2gsBackwardIO), C.c_void_p]),
+    "b2gs_mark_visible": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                    C.c_void_p]),
+    "b2gs_debug_export_binning": (C.c_int, [C.POINTER(B2gsScene), C.POINTER(B2gsWorkspace), C.c_int64,
+                                            C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "b2gs_debug_export_geom": (C.c_int, [C.POINTER(B2gsScene), C.POINTER(B2gsWorkspace), C.c_void_p,
+                                         C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "b2gs_debug_export_image": (C.c_int, [C.POINTER(B2gsScene), C.POINTER(B2gsWorkspace), C.c_void_p,
+                                          C.c_void_p, C.c_void_p]),
+    "b2gs_knn_bytes": (C.c_size_t, [C.c_int32]),
+    "b2gs_knn3_dist2": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_size_t,
+                                  C.c_void_p]),
+    "b2gs_adam_step": (C.c_int, [C.POINTER(B2gsAdamSegment), C.c_int32, C.c_int64, C.c_float,
+                                 C.c_float, C.c_float, C.c_void_p]),
+}
+
+
+def _load():
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} not found: build it with `python monogs_dev_b200/build.py` "
+            "(there is no CPU fallback)")
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SYMBOLS.items():
+        fn = getattr(lib, name)  # AttributeError if the .so lacks a declared symbol
+        fn.restype = res
+        fn.argtypes = args
+    return lib
+
+
+lib = _load()
+
+
+def check(rc):
+    if rc != 0:
+        raise RuntimeError(f"libb2gs error {rc}: {lib.b2gs_last_error().decode()}")
+
+
+def ptr(t):
+    """device pointer of a tensor, or None (NULL) for absent / empty tensors."""
+    if t is None or t.numel() == 0:
+        return None
+    return t.data_ptr()

@@ -1,6 +1,6 @@
 """Build libb2gs.so (hand-written sm_100a CUDA + C ABI) in-tree with nvcc.
 
-    python -m monogs_dev_b200.build [--force]
+    python monogs_dev_b200/build.py [--force]
 
 Each .cu is compiled to an object (in parallel), then linked into
 monogs_dev_b200/libb2gs.so.  The CUDA runtime is linked statically so the

@@ -3,12 +3,16 @@
 // (CR/rasterizer_impl.cu:198-344, :348-455).  Stream-aware, re-entrant, no
 // allocations: all buffers come from the caller.
 #include "common.cuh"
+#include <atomic>
 #include <stdarg.h>
 #include <string.h>
 
 namespace b2gs {
 
 static thread_local char g_err[512] = "";
+static std::atomic<unsigned long long> g_launches{0};
+
+void note_launches(int n) { g_launches.fetch_add((unsigned long long)n, std::memory_order_relaxed); }
 
 void set_error(const char* fmt, ...) {
   va_list ap;
@@ -64,6 +68,7 @@ using namespace b2gs;
 
 extern "C" int b2gs_version(void) { return 100; }
 extern "C" const char* b2gs_last_error(void) { return g_err; }
+extern "C" uint64_t b2gs_kernel_launches(void) { return g_launches.load(std::memory_order_relaxed); }
 
 extern "C" size_t b2gs_geom_bytes(int32_t P) {
   size_t t = 0;

@@ -313,6 +313,7 @@ extern "C" int b2gs_knn3_dist2(const float* points, int32_t P, float* out, void*
   knn_bbox_kernel<<<blocks < 1184 ? blocks : 1184, 256, 0, st>>>(P, points, k.bbox);
   knn_morton_kernel<<<blocks, 256, 0, st>>>(P, points, k.bbox, k.morton, k.iota);
   B2GS_LAUNCH_CHECK(st, 0);
+  note_launches(2);
   size_t tb = k.temp_bytes;
   B2GS_CUDA(cub::DeviceRadixSort::SortPairs(k.temp, tb, (const uint32_t*)k.morton, k.morton_s,
                                             (const uint32_t*)k.iota, k.idx_s, P, 0, 30, st));
@@ -321,5 +322,6 @@ extern "C" int b2gs_knn3_dist2(const float* points, int32_t P, float* out, void*
   knn_parent_kernel<<<(k.n2 * 32 + 255) / 256, 256, 0, st>>>(k.n1, k.l1, k.l2);
   knn_search_kernel<<<(k.n0 + 7) / 8, 256, 0, st>>>(P, k.n0, k.n1, k.n2, k.pts, k.l0, k.l1, k.l2, out);
   B2GS_LAUNCH_CHECK(st, 0);
+  note_launches(3);
   return B2GS_OK;
 }

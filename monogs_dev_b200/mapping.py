@@ -1,0 +1,189 @@
+"""Keyframe mapping window: the one path sharded across GPUs.
+
+Host-side mirror of the reference's callers of the rasterizer:
+  render()                      gaussian_splatting/gaussian_renderer/__init__.py:24-153
+  GaussianModel (params/Adam)   gaussian_splatting/scene/gaussian_model.py:76-101,245-310
+  get_loss_mapping(_rgb/_rgbd)  utils/slam_utils.py:91-128
+  BackEnd.map() inner loop      utils/slam_backend.py:156-317
+  FrontEnd.tracking() loop      utils/slam_frontend.py:163-193, utils/slam_utils.py:56-88
+
+B200-first changes: all Gaussian parameters live in ONE packed fp32 arena (and their
+gradients / Adam moments in three more), so that
+  * the optimizer step is one fused kernel launch (libb2gs `b2gs_adam_step`),
+  * with N GPUs (one process per GPU, keyframes sharded rank-sticky) the per-Gaussian
+    gradients of all groups travel in ONE NCCL all-reduce over NVLink instead of six.
+The loss is a plain sum over views (utils/slam_backend.py:160-231), so keyframe sharding
+with a SUM all-reduce is exact up to fp32 summation order.
+"""
+import math
+
+import torch
+import torch.distributed as dist
+
+from .adam import FusedAdam
+from .rasterizer import GaussianRasterizationSettings, GaussianRasterizer
+
+_GROUPS = ("xyz", "f_dc", "f_rest", "opacity", "scaling", "rotation")
+
+
+class GaussianModel:
+    """Parameter container with the attribute surface render() and BackEnd.map() use.
+    Learning rates follow configs/rgbd/replica/base_config.yaml:64-80 with
+    spatial_lr_scale = 6.0 (slam.py:54)."""
+
+    def __init__(self, xyz, f_dc, f_rest, opacity, scaling, rotation, sh_degree=0,
+                 spatial_lr_scale=6.0, lrs=None):
+        dev = xyz.device
+        self.max_sh_degree = self.active_sh_degree = sh_degree
+        src = dict(xyz=xyz, f_dc=f_dc, f_rest=f_rest, opacity=opacity, scaling=scaling, rotation=rotation)
+        sizes = [src[k].numel() for k in _GROUPS]
+        offs, total = [], 0
+        for n in sizes:
+            offs.append(total)
+            total += (n + 3) // 4 * 4          # keep every segment 16 B aligned for float4 access
+        self.flat = torch.zeros(total, device=dev)
+        self.flat_grad = torch.zeros(total, device=dev)
+        self.flat_m = torch.zeros(total, device=dev)
+        self.flat_v = torch.zeros(total, device=dev)
+        self._params = {}
+        for k, o, n in zip(_GROUPS, offs, sizes):
+            view = self.flat[o:o + n].view(src[k].shape)
+            view.copy_(src[k])
+            p = torch.nn.Parameter(view)
+            p.grad = self.flat_grad[o:o + n].view(src[k].shape)
+            self._params[k] = p
+        lr = dict(xyz=0.00016 * spatial_lr_scale, f_dc=0.0025, f_rest=0.0025 / 20.0, opacity=0.05,
+                  scaling=0.001 * spatial_lr_scale, rotation=0.001)
+        lr.update(lrs or {})
+        self.optimizer = FusedAdam([dict(params=[self._params[k]], lr=lr[k], name=k) for k in _GROUPS],
+                                   lr=0.0, eps=1e-15)
+        for k, o, n in zip(_GROUPS, offs, sizes):   # Adam moments are views of the arenas too
+            st = self.optimizer.state[self._params[k]]
+            st["step"] = 0
+            st["exp_avg"] = self.flat_m[o:o + n].view(src[k].shape)
+            st["exp_avg_sq"] = self.flat_v[o:o + n].view(src[k].shape)
+
+    _xyz = property(lambda s: s._params["xyz"])
+    _features_dc = property(lambda s: s._params["f_dc"])
+    _features_rest = property(lambda s: s._params["f_rest"])
+    _opacity = property(lambda s: s._params["opacity"])
+    _scaling = property(lambda s: s._params["scaling"])
+    _rotation = property(lambda s: s._params["rotation"])
+
+    # activations (gaussian_model.py:76-101)
+    get_xyz = property(lambda s: s._xyz)
+    get_scaling = property(lambda s: torch.exp(s._scaling))
+    get_rotation = property(lambda s: torch.nn.functional.normalize(s._rotation))
+    get_opacity = property(lambda s: torch.sigmoid(s._opacity))
+    get_features = property(lambda s: torch.cat((s._features_dc, s._features_rest), dim=1))
+
+    def zero_grad(self):
+        self.flat_grad.zero_()
+
+
+def render(viewpoint_camera, pc, pipe=None, bg_color=None, scaling_modifier=1.0, override_color=None):
+    """Same contract as the reference's render(): returns the dict with keys render,
+    viewspace_points, visibility_filter, radii, depth, opacity, n_touched."""
+    screenspace_points = torch.zeros_like(pc.get_xyz, dtype=pc.get_xyz.dtype, requires_grad=True) + 0
+    try:
+        screenspace_points.retain_grad()
+    except Exception:
+        pass
+    cam = viewpoint_camera
+    rs = GaussianRasterizationSettings(
+        image_height=int(cam.image_height), image_width=int(cam.image_width),
+        tanfovx=math.tan(cam.FoVx * 0.5), tanfovy=math.tan(cam.FoVy * 0.5), bg=bg_color,
+        scale_modifier=scaling_modifier, viewmatrix=cam.world_view_transform,
+        projmatrix=cam.full_proj_transform, projmatrix_raw=cam.projection_matrix,
+        sh_degree=pc.active_sh_degree, campos=cam.camera_center, prefiltered=False, debug=False)
+    rasterizer = GaussianRasterizer(raster_settings=rs)
+    shs, colors = (pc.get_features, None) if override_color is None else (None, override_color)
+    rendered_image, radii, depth, opacity, n_touched = rasterizer(
+        means3D=pc.get_xyz, means2D=screenspace_points, shs=shs, colors_precomp=colors,
+        opacities=pc.get_opacity, scales=pc.get_scaling, rotations=pc.get_rotation,
+        cov3D_precomp=None, theta=cam.cam_rot_delta, rho=cam.cam_trans_delta)
+    return {"render": rendered_image, "viewspace_points": screenspace_points,
+            "visibility_filter": radii > 0, "radii": radii, "depth": depth, "opacity": opacity,
+            "n_touched": n_touched}
+
+
+def get_loss_mapping_rgbd(image, depth, viewpoint, gt_image, gt_depth, alpha=0.95,
+                          rgb_boundary_threshold=0.01):
+    """utils/slam_utils.py:91-96,113-128 (exposure affine + masked L1 rgb + masked L1 depth)."""
+    image_ab = torch.exp(viewpoint.exposure_a) * image + viewpoint.exposure_b
+    rgb_pixel_mask = (gt_image.sum(dim=0) > rgb_boundary_threshold).view(*depth.shape)
+    depth_pixel_mask = (gt_depth > 0.01).view(*depth.shape)
+    l1_rgb = torch.abs(image_ab * rgb_pixel_mask - gt_image * rgb_pixel_mask)
+    l1_depth = torch.abs(depth * depth_pixel_mask - gt_depth * depth_pixel_mask)
+    return alpha * l1_rgb.mean() + (1 - alpha) * l1_depth.mean()
+
+
+def get_loss_tracking_rgbd(image, depth, opacity, viewpoint, gt_image, gt_depth, alpha=0.95,
+                           rgb_boundary_threshold=0.01):
+    """utils/slam_utils.py:56-88 (grad_mask taken as all-ones)."""
+    image_ab = torch.exp(viewpoint.exposure_a) * image + viewpoint.exposure_b
+    rgb_pixel_mask = (gt_image.sum(dim=0) > rgb_boundary_threshold).view(1, *gt_image.shape[1:])
+    l1_rgb = (opacity * torch.abs(image_ab * rgb_pixel_mask - gt_image * rgb_pixel_mask)).mean()
+    depth_mask = (gt_depth > 0.01).view(*depth.shape) * (opacity > 0.95).view(*depth.shape)
+    l1_depth = torch.abs(depth * depth_mask - gt_depth * depth_mask)
+    return alpha * l1_rgb + (1 - alpha) * l1_depth.mean()
+
+
+def shard_views(num_views, rank, world):
+    """rank-sticky round-robin assignment of window keyframes."""
+    return [v for v in range(num_views) if v % world == rank]
+
+
+class MappingWindow:
+    """One BackEnd.map() iteration over a keyframe window, optionally data-parallel.
+
+    keyframes: list of dicts {cam, gt_image[3,H,W], gt_depth[1,H,W]} — every rank holds
+    the full list (only its shard's images are touched)."""
+
+    def __init__(self, gaussians, keyframes, bg, pose_lr=(0.003, 0.001, 0.01, 0.01),
+                 optimize_pose=True, group=None):
+        self.g, self.kfs, self.bg = gaussians, keyframes, bg
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.local = shard_views(len(keyframes), self.rank, self.world)
+        self.optimize_pose = optimize_pose
+        groups = []
+        for v in self.local:       # utils/slam_backend.py:434-471 (one Adam over the kf params)
+            cam = keyframes[v]["cam"]
+            if optimize_pose and v > 0:
+                groups += [dict(params=[cam.cam_rot_delta], lr=pose_lr[0]),
+                           dict(params=[cam.cam_trans_delta], lr=pose_lr[1])]
+            groups += [dict(params=[cam.exposure_a], lr=pose_lr[2]),
+                       dict(params=[cam.exposure_b], lr=pose_lr[3])]
+        self.kf_optimizer = FusedAdam(groups, lr=0.0, eps=1e-8) if groups else None
+        self.last = {}
+
+    def step(self):
+        g = self.g
+        loss = 0
+        stats = {}
+        for v in self.local:
+            kf = self.kfs[v]
+            pkg = render(kf["cam"], g, None, self.bg)
+            loss = loss + get_loss_mapping_rgbd(pkg["render"], pkg["depth"], kf["cam"],
+                                                kf["gt_image"], kf["gt_depth"])
+            stats[v] = pkg
+        if self.rank == 0:         # view-independent regulariser counted once (slam_backend.py:229-231)
+            scaling = g.get_scaling
+            loss = loss + 10 * torch.abs(scaling - scaling.mean(dim=1).view(-1, 1)).mean()
+        if torch.is_tensor(loss):
+            loss.backward()
+        if self.world > 1:         # ONE message for all six parameter groups
+            dist.all_reduce(g.flat_grad, op=dist.ReduceOp.SUM, group=self.group)
+        g.optimizer.step()
+        g.zero_grad()
+        if self.kf_optimizer is not None:
+            self.kf_optimizer.step()
+            self.kf_optimizer.zero_grad(set_to_none=True)
+            if self.optimize_pose:
+                for v in self.local:
+                    if v > 0:
+                        self.kfs[v]["cam"].update_pose()
+        self.last = stats
+        return loss.detach() if torch.is_tensor(loss) else torch.zeros((), device=g.flat.device)

@@ -1,0 +1,141 @@
+"""Shared test plumbing: build inputs for a synthetic scene, run the product path through
+the public Python API / C ABI, run the oracle, compare."""
+import ctypes as C
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+from monogs_dev_b200 import synthetic as syn  # noqa: E402
+from monogs_dev_b200 import _lib, rasterizer as rz  # noqa: E402
+from oracle import gs_oracle as O  # noqa: E402
+
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+
+def build_case(name, device="cpu", view=0, mode="sh", bg=(0.0, 0.0, 0.0), n_views=1, **kw):
+    """mode: 'sh' (shs + scales/rotations), 'precomp' (colors_precomp + cov3D_precomp)."""
+    sc = syn.make_scene(name, device=device, n_views=max(n_views, view + 1), **kw)
+    act = syn.activated(sc)
+    cam = sc.cameras[view]
+    rs = cam.settings(torch.tensor(bg, dtype=torch.float32, device=device), sh_degree=sc.sh_degree)
+    inp = dict(means3D=act["means3D"], opacities=act["opacities"])
+    if mode == "sh":
+        inp.update(shs=act["shs"], scales=act["scales"], rotations=act["rotations"])
+    else:
+        g = torch.Generator().manual_seed(99)
+        inp.update(colors_precomp=torch.rand(sc.P, 3, generator=g).to(device),
+                   cov3D_precomp=O.compute_cov3d(act["scales"].cpu(), 1.0, act["rotations"].cpu()).to(device))
+    gc, gd = syn.upstream_grads(sc, device=device)
+    return sc, rs, inp, gc, gd
+
+
+def run_oracle(rs, inp, gc=None, gd=None, dtype=torch.float32):
+    s = O.scene_from_settings(rs, inp["means3D"], inp["opacities"], shs=inp.get("shs"),
+                              colors_precomp=inp.get("colors_precomp"), scales=inp.get("scales"),
+                              rotations=inp.get("rotations"), cov3D_precomp=inp.get("cov3D_precomp"),
+                              dtype=dtype)
+    st = O.rasterize_forward(s)
+    bw = None
+    if gc is not None:
+        bw = O.rasterize_backward(s, st, gc.cpu().to(dtype), gd.cpu().to(dtype))
+    return s, st, bw
+
+
+def run_native(rs, inp, gc=None, gd=None):
+    """product path through the public API; returns outputs, grads (dict) and the RasterState."""
+    leaves = {k: v.detach().clone().requires_grad_(True) for k, v in inp.items()}
+    dev = inp["means3D"].device
+    means2D = torch.zeros_like(leaves["means3D"], requires_grad=True)
+    theta = torch.zeros(3, device=dev, requires_grad=True)
+    rho = torch.zeros(3, device=dev, requires_grad=True)
+    r = rz.GaussianRasterizer(rs)
+    color, radii, depth, opacity, n_touched = r(
+        means3D=leaves["means3D"], means2D=means2D, opacities=leaves["opacities"],
+        shs=leaves.get("shs"), colors_precomp=leaves.get("colors_precomp"),
+        scales=leaves.get("scales"), rotations=leaves.get("rotations"),
+        cov3D_precomp=leaves.get("cov3D_precomp"), theta=theta, rho=rho)
+    out = dict(color=color.detach(), radii=radii, depth=depth.detach(), opacity=opacity.detach(),
+               n_touched=n_touched, state=color.grad_fn.state if color.grad_fn is not None else None)
+    grads = None
+    if gc is not None:
+        torch.autograd.backward([color, depth], [gc, gd])
+        grads = dict(dL_dmeans3D=leaves["means3D"].grad, dL_dmeans2D=means2D.grad,
+                     dL_dopacity=leaves["opacities"].grad,
+                     dL_dtau=torch.cat([rho.grad.reshape(-1), theta.grad.reshape(-1)]))
+        for k, g in (("shs", "dL_dsh"), ("colors_precomp", "dL_dcolors"), ("scales", "dL_dscales"),
+                     ("rotations", "dL_drotations"), ("cov3D_precomp", "dL_dcov3D")):
+            if k in leaves:
+                grads[g] = leaves[k].grad
+    return out, grads
+
+
+def native_scene_struct(rs, inp, keep):
+    sh = inp.get("shs")
+    M = sh.size(1) if sh is not None else 0
+    return rz._scene_struct(rs, inp["means3D"].size(0), M, inp["means3D"], sh,
+                            inp.get("colors_precomp"), inp["opacities"], inp.get("scales"),
+                            inp.get("rotations"), inp.get("cov3D_precomp"), keep)
+
+
+def export_native(rs, inp, state):
+    """keys / sorted ids / ranges / per-Gaussian state from the library's private workspaces."""
+    lib = _lib.lib
+    dev = inp["means3D"].device
+    P = inp["means3D"].size(0)
+    W, H = rs.image_width, rs.image_height
+    R = state.num_rendered
+    keep = []
+    scene = native_scene_struct(rs, inp, keep)
+    ws = _lib.B2gsWorkspace(_lib.ptr(state.geom), state.geom.numel(), _lib.ptr(state.image),
+                            state.image.numel(), _lib.ptr(state.binning), state.binning.numel())
+    tiles = ((W + 15) // 16) * ((H + 15) // 16)
+    keys = torch.zeros(max(R, 1), dtype=torch.int64, device=dev)
+    vals = torch.zeros(max(R, 1), dtype=torch.int32, device=dev)
+    ranges = torch.zeros(tiles, 2, dtype=torch.int32, device=dev)
+    st = torch.cuda.current_stream().cuda_stream
+    _lib.check(lib.b2gs_debug_export_binning(C.byref(scene), C.byref(ws), R, keys.data_ptr(),
+                                             vals.data_ptr(), ranges.data_ptr(), st))
+    depths = torch.zeros(P, device=dev)
+    m2d = torch.zeros(P, 2, device=dev)
+    co = torch.zeros(P, 4, device=dev)
+    rgb = torch.zeros(P, 3, device=dev)
+    touched = torch.zeros(P, dtype=torch.int32, device=dev)
+    _lib.check(lib.b2gs_debug_export_geom(C.byref(scene), C.byref(ws), depths.data_ptr(),
+                                          m2d.data_ptr(), co.data_ptr(), rgb.data_ptr(),
+                                          touched.data_ptr(), st))
+    fT = torch.zeros(W * H, device=dev)
+    nc = torch.zeros(W * H, dtype=torch.int32, device=dev)
+    _lib.check(lib.b2gs_debug_export_image(C.byref(scene), C.byref(ws), fT.data_ptr(), nc.data_ptr(), st))
+    torch.cuda.synchronize()
+    return dict(keys=keys[:R], point_list=vals[:R], ranges=ranges, depths=depths, means2D=m2d,
+                conic_opacity=co, rgb=rgb, tiles_touched=touched, final_T=fT, n_contrib=nc)
+
+
+def rel_err(a, b):
+    """max |a-b| relative to the tensor's scale, and the element-wise mixed criterion."""
+    a, b = a.detach().double().cpu(), b.detach().double().cpu()
+    scale = float(b.abs().max()) if b.numel() else 0.0
+    if scale == 0.0:
+        return float(a.abs().max()) if a.numel() else 0.0
+    return float((a - b).abs().max()) / scale
+
+
+def assert_grad_close(a, b, tol=1e-4, name=""):
+    """|a-b| <= tol*|b| + tol*max|b| element-wise (north_star: 1e-4 relative/absolute,
+    absolute taken relative to the tensor's scale so that tiny gradients still count)."""
+    a, b = a.detach().double().cpu().reshape(-1), b.detach().double().cpu().reshape(-1)
+    assert a.shape == b.shape, f"{name}: shape {a.shape} vs {b.shape}"
+    scale = float(b.abs().max()) if b.numel() else 0.0
+    bad = (a - b).abs() > tol * b.abs() + tol * scale
+    assert not bool(bad.any()), (f"{name}: {int(bad.sum())}/{a.numel()} elements off, "
+                                 f"max err {float((a - b).abs().max()):.3e} at scale {scale:.3e}")
+
+
+def frac_bad(a, b, rtol, atol):
+    a, b = a.detach().double().cpu().reshape(-1), b.detach().double().cpu().reshape(-1)
+    return float(((a - b).abs() > atol + rtol * b.abs()).double().mean())
