@@ -126,6 +126,12 @@ B2GS_API const char* b2gs_last_error(void);
  * CUB sort/scan launches are not counted. */
 B2GS_API uint64_t b2gs_kernel_launches(void);
 
+/* Per-kernel timing: while enabled, every kernel (and CUB call) of the library is
+ * bracketed by CUDA events on its launching stream.  b2gs_profile_read synchronises,
+ * writes "name count total_ms" lines into buf and clears the records. */
+B2GS_API void b2gs_profile_enable(int on);
+B2GS_API int b2gs_profile_read(char* buf, int cap);
+
 B2GS_API size_t b2gs_geom_bytes(int32_t P);
 B2GS_API size_t b2gs_image_bytes(int32_t W, int32_t H);
 B2GS_API size_t b2gs_binning_bytes(int64_t R, int32_t W, int32_t H);

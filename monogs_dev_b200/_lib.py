@@ -61,6 +61,8 @@ SYMBOLS = {
     "b2gs_version": (C.c_int, []),
     "b2gs_last_error": (C.c_char_p, []),
     "b2gs_kernel_launches": (C.c_uint64, []),
+    "b2gs_profile_enable": (None, [C.c_int]),
+    "b2gs_profile_read": (C.c_int, [C.c_char_p, C.c_int]),
     "b2gs_geom_bytes": (C.c_size_t, [C.c_int32]),
     "b2gs_image_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
     "b2gs_binning_bytes": (C.c_size_t, [C.c_int64, C.c_int32, C.c_int32]),
@@ -106,6 +108,17 @@ lib = _load()
 def check(rc):
     if rc != 0:
         raise RuntimeError(f"libb2gs error {rc}: {lib.b2gs_last_error().decode()}")
+
+
+def profile_read():
+    """{kernel name: (launch count, total ms)} since the last read (needs b2gs_profile_enable(1))."""
+    buf = C.create_string_buffer(1 << 16)
+    n = lib.b2gs_profile_read(buf, len(buf))
+    out = {}
+    for line in buf.raw[:n].decode().splitlines():
+        name, cnt, ms = line.rsplit(" ", 2)
+        out[name] = (int(cnt), float(ms))
+    return out
 
 
 def ptr(t):

@@ -123,6 +123,7 @@ extern "C" int b2gs_adam_step(const B2gsAdamSegment* segments, int32_t num_segme
     t.num = k;
     if (chunks > 0) {
       if (chunks > 0x7fffffffLL) { set_error("b2gs_adam_step: too many elements"); return B2GS_ERR_INVALID; }
+      B2GS_PROF("adam", st);
       adam_kernel<<<(unsigned)chunks, 256, 0, st>>>(t, w1, beta2, w2, bc2_sqrt, eps);
       B2GS_LAUNCH_CHECK(st, 0);
     }

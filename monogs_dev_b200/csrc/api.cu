@@ -4,6 +4,10 @@
 // allocations: all buffers come from the caller.
 #include "common.cuh"
 #include <atomic>
+#include <mutex>
+#include <vector>
+#include <string>
+#include <map>
 #include <stdarg.h>
 #include <string.h>
 
@@ -13,6 +17,29 @@ static thread_local char g_err[512] = "";
 static std::atomic<unsigned long long> g_launches{0};
 
 void note_launches(int n) { g_launches.fetch_add((unsigned long long)n, std::memory_order_relaxed); }
+
+// ---- per-kernel event timing ------------------------------------------------------
+struct ProfRec { const char* name; cudaEvent_t a, b; };
+static std::mutex g_prof_mu;
+static bool g_prof_on = false;
+static std::vector<ProfRec> g_prof;
+
+ProfScope::ProfScope(const char* name, cudaStream_t stream) : slot(-1), st(stream) {
+  if (!g_prof_on) return;
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  if (g_prof.size() >= 200000) return;
+  ProfRec r;
+  r.name = name;
+  if (cudaEventCreate(&r.a) != cudaSuccess || cudaEventCreate(&r.b) != cudaSuccess) return;
+  cudaEventRecord(r.a, stream);
+  g_prof.push_back(r);
+  slot = (int)g_prof.size() - 1;
+}
+ProfScope::~ProfScope() {
+  if (slot < 0) return;
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  if (slot < (int)g_prof.size()) cudaEventRecord(g_prof[slot].b, st);
+}
 
 void set_error(const char* fmt, ...) {
   va_list ap;
@@ -69,6 +96,39 @@ using namespace b2gs;
 extern "C" int b2gs_version(void) { return 100; }
 extern "C" const char* b2gs_last_error(void) { return g_err; }
 extern "C" uint64_t b2gs_kernel_launches(void) { return g_launches.load(std::memory_order_relaxed); }
+
+extern "C" void b2gs_profile_enable(int on) {
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  g_prof_on = on != 0;
+}
+
+// Synchronises the device, folds all recorded scopes into per-name totals, writes
+// "name count total_ms\n" lines into buf, clears the records.  Returns bytes written.
+extern "C" int b2gs_profile_read(char* buf, int cap) {
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  cudaDeviceSynchronize();
+  std::map<std::string, std::pair<long long, double>> acc;
+  for (auto& r : g_prof) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, r.a, r.b) == cudaSuccess) {
+      auto& e = acc[r.name];
+      e.first += 1;
+      e.second += ms;
+    }
+    cudaEventDestroy(r.a);
+    cudaEventDestroy(r.b);
+  }
+  g_prof.clear();
+  cudaGetLastError();
+  int off = 0;
+  for (auto& kv : acc) {
+    int n = snprintf(buf + off, cap > off ? cap - off : 0, "%s %lld %.6f\n", kv.first.c_str(),
+                     kv.second.first, kv.second.second);
+    if (n < 0 || off + n >= cap) break;
+    off += n;
+  }
+  return off;
+}
 
 extern "C" size_t b2gs_geom_bytes(int32_t P) {
   size_t t = 0;

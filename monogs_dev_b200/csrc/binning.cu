@@ -97,13 +97,19 @@ BinWS carve_bin(void* base, int64_t R, size_t* total) {
 // ---- depth order + offsets -------------------------------------------------------
 int launch_depth_order(const B2gsScene& s, const GeomWS& g, cudaStream_t st) {
   size_t tb = g.temp_bytes;
-  B2GS_CUDA(cub::DeviceRadixSort::SortPairs(g.temp, tb, (const uint32_t*)g.depth_key, g.key_sorted,
-                                            (const uint32_t*)g.iota, g.id_sorted, s.P, 0, 32, st));
+  {
+    B2GS_PROF("depth_sort(cub)", st);
+    B2GS_CUDA(cub::DeviceRadixSort::SortPairs(g.temp, tb, (const uint32_t*)g.depth_key, g.key_sorted,
+                                              (const uint32_t*)g.iota, g.id_sorted, s.P, 0, 32, st));
+  }
   if (s.debug) B2GS_CUDA(cudaStreamSynchronize(st));
   TouchedInSortedOrder op{g.tiles_touched, g.id_sorted};
   TouchedIt it(CountIt(0), op);
   tb = g.temp_bytes;
-  B2GS_CUDA(cub::DeviceScan::InclusiveSum(g.temp, tb, it, g.offsets, s.P, st));
+  {
+    B2GS_PROF("offset_scan(cub)", st);
+    B2GS_CUDA(cub::DeviceScan::InclusiveSum(g.temp, tb, it, g.offsets, s.P, st));
+  }
   if (s.debug) B2GS_CUDA(cudaStreamSynchronize(st));
   return B2GS_OK;
 }
@@ -189,15 +195,22 @@ int launch_binning(const B2gsScene& s, const GeomWS& g, const ImageWS& im, const
   const uint32_t tiles = (uint32_t)gx * gy;
   B2GS_CUDA(cudaMemsetAsync(im.ranges, 0, sizeof(uint2) * tiles, st));
   if (R <= 0) return B2GS_OK;
-  emit_instances_kernel<<<(s.P + 255) / 256, 256, 0, st>>>(s.P, gx, g.id_sorted, g.offsets,
-                                                          g.tiles_touched, g.rect,
-                                                          b.tile_unsorted, b.id_unsorted);
-  B2GS_LAUNCH_CHECK(st, s.debug);
+  {
+    B2GS_PROF("emit_instances", st);
+    emit_instances_kernel<<<(s.P + 255) / 256, 256, 0, st>>>(s.P, gx, g.id_sorted, g.offsets,
+                                                            g.tiles_touched, g.rect,
+                                                            b.tile_unsorted, b.id_unsorted);
+    B2GS_LAUNCH_CHECK(st, s.debug);
+  }
   size_t tb = b.temp_bytes;
-  B2GS_CUDA(cub::DeviceRadixSort::SortPairs(b.temp, tb, (const uint32_t*)b.tile_unsorted,
-                                            b.tile_sorted, (const uint32_t*)b.id_unsorted,
-                                            b.point_list, (int)R, 0, tile_bits(tiles), st));
+  {
+    B2GS_PROF("tile_sort(cub)", st);
+    B2GS_CUDA(cub::DeviceRadixSort::SortPairs(b.temp, tb, (const uint32_t*)b.tile_unsorted,
+                                              b.tile_sorted, (const uint32_t*)b.id_unsorted,
+                                              b.point_list, (int)R, 0, tile_bits(tiles), st));
+  }
   if (s.debug) B2GS_CUDA(cudaStreamSynchronize(st));
+  B2GS_PROF("tile_ranges", st);
   tile_ranges_kernel<<<(uint32_t)((R + 255) / 256), 256, 0, st>>>((uint32_t)R, b.tile_sorted,
                                                                  im.ranges);
   B2GS_LAUNCH_CHECK(st, s.debug);

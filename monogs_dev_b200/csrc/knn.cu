@@ -320,6 +320,7 @@ extern "C" int b2gs_knn3_dist2(const float* points, int32_t P, float* out, void*
   knn_leaf_kernel<<<(k.n0 * 32 + 255) / 256, 256, 0, st>>>(P, points, k.idx_s, k.pts, k.l0);
   knn_parent_kernel<<<(k.n1 * 32 + 255) / 256, 256, 0, st>>>(k.n0, k.l0, k.l1);
   knn_parent_kernel<<<(k.n2 * 32 + 255) / 256, 256, 0, st>>>(k.n1, k.l1, k.l2);
+  B2GS_PROF("knn_search", st);
   knn_search_kernel<<<(k.n0 + 7) / 8, 256, 0, st>>>(P, k.n0, k.n1, k.n2, k.pts, k.l0, k.l1, k.l2, out);
   B2GS_LAUNCH_CHECK(st, 0);
   note_launches(3);

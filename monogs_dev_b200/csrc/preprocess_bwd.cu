@@ -103,7 +103,7 @@ __device__ __forceinline__ V3 sh_backward(int deg, int M, const float* __restric
     }
   }
   const int active = (deg + 1) * (deg + 1);
-  for (int k = 0; k < M; ++k) {
+  for (int k = 0; dL_dsh != nullptr && k < M; ++k) {
     const float bk = (k < active && k < 16) ? basis[k] : 0.f;
     dL_dsh[3 * k + 0] = bk * g[0];
     dL_dsh[3 * k + 1] = bk * g[1];
@@ -317,7 +317,8 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
     if (shs != nullptr) {
       const V3 campos = {campos_p[0], campos_p[1], campos_p[2]};
       const V3 dm = sh_backward(D, M, shs + (size_t)idx * M * 3, V3{mean.x, mean.y, mean.z}, campos,
-                                clamped[idx], dL_dcol, dL_dsh + (size_t)idx * M * 3);
+                                clamped[idx], dL_dcol,
+                                dL_dsh ? dL_dsh + (size_t)idx * M * 3 : nullptr);
       dmean.x += dm.x; dmean.y += dm.y; dmean.z += dm.z;
       tau[0] += -dm.x; tau[1] += -dm.y; tau[2] += -dm.z;
       if (dL_dcolors) { dL_dcolors[3 * idx] = dL_dcol.x; dL_dcolors[3 * idx + 1] = dL_dcol.y; dL_dcolors[3 * idx + 2] = dL_dcol.z; }
@@ -431,6 +432,7 @@ int launch_preprocess_bwd(const B2gsScene& s, const GeomWS& g, const B2gsBackwar
   const float focal_x = s.W / (2.0f * s.tan_fovx);
   const int blocks = (s.P + 255) / 256;
   float* partials = const_cast<float*>(acc) + (size_t)s.P * ACC_STRIDE;  // scratch tail
+  B2GS_PROF("preprocess_bwd", st);
   preprocess_bwd_kernel<<<blocks, 256, 0, st>>>(
       s.P, s.D, s.M, s.means3D, io.radii, s.shs, g.clamped, s.scales, s.rotations, s.scale_modifier,
       s.cov3D_precomp, s.viewmatrix, s.projmatrix, s.projmatrix_raw, s.campos, focal_x, focal_y,

@@ -170,6 +170,7 @@ int launch_preprocess_fwd(const B2gsScene& s, const GeomWS& g, int32_t* radii, c
   const float focal_x = s.W / (2.0f * s.tan_fovx);
   const int gx = (s.W + TILE - 1) / TILE, gy = (s.H + TILE - 1) / TILE;
   const int blocks = (s.P + 255) / 256;
+  B2GS_PROF("preprocess_fwd", st);
   preprocess_fwd_kernel<<<blocks, 256, 0, st>>>(
       s.P, s.D, s.M, s.means3D, s.scales, s.scale_modifier, s.rotations, s.opacities, s.shs,
       s.cov3D_precomp, s.colors_precomp, s.viewmatrix, s.projmatrix, s.campos, s.W, s.H,

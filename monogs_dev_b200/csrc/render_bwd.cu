@@ -190,6 +190,7 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
 int launch_render_bwd(const B2gsScene& s, const GeomWS& g, const ImageWS& im, const BinWS& b,
                       const B2gsBackwardIO& io, float* acc, cudaStream_t st) {
   const int gx = (s.W + TILE - 1) / TILE, gy = (s.H + TILE - 1) / TILE;
+  B2GS_PROF("render_bwd", st);
   render_bwd_kernel<<<gx * gy, 256, 0, st>>>(im.ranges, b.point_list, s.W, s.H, gx, s.bg, g.xy,
                                              g.conic_o, g.rgbd, im.final_T, im.n_contrib,
                                              io.dL_dcolor, io.dL_ddepth, acc);

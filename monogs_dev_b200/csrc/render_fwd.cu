@@ -115,6 +115,7 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
 int launch_render_fwd(const B2gsScene& s, const GeomWS& g, const ImageWS& im, const BinWS& b,
                       const B2gsForwardOut& out, cudaStream_t st) {
   const int gx = (s.W + TILE - 1) / TILE, gy = (s.H + TILE - 1) / TILE;
+  B2GS_PROF("render_fwd", st);
   render_fwd_kernel<<<gx * gy, 256, 0, st>>>(im.ranges, b.point_list, s.W, s.H, gx, g.xy, g.conic_o,
                                              g.rgbd, s.bg, im.final_T, im.n_contrib, out.color,
                                              out.depth, out.opacity, out.n_touched);

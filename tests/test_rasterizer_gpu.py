@@ -60,6 +60,10 @@ def test_native_vs_reference_ext(name, mode, kw):
     rbw = ref_ext.backward(rs, ref, gc, gd, inp["means3D"], shs=inp.get("shs"),
                            colors_precomp=inp.get("colors_precomp"), scales=inp.get("scales"),
                            rotations=inp.get("rotations"), cov3D_precomp=inp.get("cov3D_precomp"))
+    # the reference's own run-to-run noise (float atomics in its K7, CR/backward.cu:774-783)
+    rbw2 = ref_ext.backward(rs, ref, gc, gd, inp["means3D"], shs=inp.get("shs"),
+                            colors_precomp=inp.get("colors_precomp"), scales=inp.get("scales"),
+                            rotations=inp.get("rotations"), cov3D_precomp=inp.get("cov3D_precomp"))
     torch.cuda.synchronize()
     P, W, H = sc.P, sc.W, sc.H
     geom, rbin, rimg = ref_ext.decode_geom(ref, P), ref_ext.decode_binning(ref), ref_ext.decode_image(ref, W, H)
@@ -86,7 +90,9 @@ def test_native_vs_reference_ext(name, mode, kw):
         a, b = grads[k], rbw[k]
         if k == "dL_dcov3D" and "cov3D_precomp" not in inp:
             continue
-        assert_grad_close(a.reshape(b.shape) if k != "dL_dtau" else a, b, tol=1e-4, name=k)
+        noise = float((rbw2[k] - b).abs().max())
+        assert_grad_close(a.reshape(b.shape) if k != "dL_dtau" else a, b, tol=1e-4, name=k,
+                          extra_atol=4 * noise)
 
 
 def test_full_size_properties():
