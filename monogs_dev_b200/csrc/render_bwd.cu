@@ -13,9 +13,12 @@
 //              over all 32 lanes: 5+3+2+1+1 shuffles instead of 50) and the 10
 //              lanes that end up owning a total issue one red.global.add.f32 each
 //              into a packed 48 B accumulator row per splat.
+//   Before any per-pixel work each warp culls the staged batch against its own 8x4
+//   block (cull.cuh): one lane tests one splat, the warp walks the survivors' bit mask.
 //   Splats behind every pixel's last contributor are never staged: the block
 //   starts at max(n_contrib) over the tile, each warp at its own max.
 #include "common.cuh"
+#include "cull.cuh"
 
 namespace b2gs {
 
@@ -70,11 +73,12 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int tile = blockIdx.x;
   const int tile_x = tile % gx, tile_y = tile / gx;
-  const int px = tile_x * TILE + (warp & 1) * 8 + (lane & 7);
-  const int py = tile_y * TILE + (warp >> 1) * 4 + (lane >> 3);
+  const int bx = tile_x * TILE + (warp & 1) * 8, by = tile_y * TILE + (warp >> 1) * 4;
+  const int px = bx + (lane & 7), py = by + (lane >> 3);
   const bool inside = px < W && py < H;
   const int pix_id = W * py + px;
   const float pixfx = (float)px, pixfy = (float)py;
+  const float rx0 = (float)bx, ry0 = (float)by, rx1 = (float)(bx + 7), ry1 = (float)(by + 3);
 
   const uint2 range = ranges[tile];
 
@@ -124,65 +128,76 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     // entry j is at position tile_max-1-(base+j); this warp needs pos < warp_max
     int j0 = tile_max - base - warp_max;
     if (j0 < 0) j0 = 0;
-    for (int j = j0; j < cnt; ++j) {
-      const int pos = tile_max - 1 - (base + j);
-      const float2 p = s_xy[j];
-      const float4 co = s_co[j];
-      const float dx = p.x - pixfx, dy = p.y - pixfy;
-      const float power = -0.5f * (co.x * dx * dx + co.z * dy * dy) - co.y * dx * dy;
-      bool skip = !(pos < last_contributor);  // also false-inside lanes: last_contributor == 0
-      skip |= power > 0.0f;
-      const float G = expf(power);
-      const float alpha = fminf(0.99f, co.w * G);
-      skip |= alpha < 1.0f / 255.0f;
-      if (__all_sync(FULL, skip)) continue;
+    for (int c0 = j0 & ~31; c0 < cnt; c0 += 32) {
+      // one lane per splat: can it reach this warp's 8x4 block at all? (cull.cuh)
+      const int jj = c0 + lane;
+      const bool keep = jj >= j0 && jj < cnt &&
+                        splat_may_touch_rect(s_xy[jj], s_co[jj], rx0, ry0, rx1, ry1);
+      unsigned mask = __ballot_sync(FULL, keep);
+      while (mask) {
+        const int k = __ffs(mask) - 1;
+        mask &= mask - 1;
+        const int j = c0 + k;
+        const int pos = tile_max - 1 - (base + j);
+        const float2 p = s_xy[j];
+        const float4 co = s_co[j];
+        const float dx = p.x - pixfx, dy = p.y - pixfy;
+        const float power = -0.5f * (co.x * dx * dx + co.z * dy * dy) - co.y * dx * dy;
+        bool skip = !(pos < last_contributor);  // also false-inside lanes: last_contributor == 0
+        skip |= power > 0.0f;
+        const float G = expf(power);
+        const float alpha = fminf(0.99f, co.w * G);
+        skip |= alpha < 1.0f / 255.0f;
+        if (__all_sync(FULL, skip)) continue;
 
-      float v[10];
+        float v[10];
 #pragma unroll
-      for (int k = 0; k < 10; ++k) v[k] = 0.f;
-      if (!skip) {
-        const float4 cd = s_cd[j];
-        T = T / (1.f - alpha);
-        const float dchannel_dcolor = alpha * T;
-        float dL_dalpha = 0.0f;
+        for (int q = 0; q < 10; ++q) v[q] = 0.f;
+        if (!skip) {
+          const float4 cd = s_cd[j];
+          const float inv1ma = __frcp_rn(1.f - alpha);
+          T = T * inv1ma;  // reference: T / (1 - alpha); differs by <= 1 ulp
+          const float dchannel_dcolor = alpha * T;
+          float dL_dalpha = 0.0f;
 
-        accum_rec0 = last_alpha * last_c0 + (1.f - last_alpha) * accum_rec0;
-        last_c0 = cd.x;
-        dL_dalpha += (cd.x - accum_rec0) * dLp0;
-        v[6] = dchannel_dcolor * dLp0;
+          accum_rec0 = last_alpha * last_c0 + (1.f - last_alpha) * accum_rec0;
+          last_c0 = cd.x;
+          dL_dalpha += (cd.x - accum_rec0) * dLp0;
+          v[6] = dchannel_dcolor * dLp0;
 
-        accum_rec1 = last_alpha * last_c1 + (1.f - last_alpha) * accum_rec1;
-        last_c1 = cd.y;
-        dL_dalpha += (cd.y - accum_rec1) * dLp1;
-        v[7] = dchannel_dcolor * dLp1;
+          accum_rec1 = last_alpha * last_c1 + (1.f - last_alpha) * accum_rec1;
+          last_c1 = cd.y;
+          dL_dalpha += (cd.y - accum_rec1) * dLp1;
+          v[7] = dchannel_dcolor * dLp1;
 
-        accum_rec2 = last_alpha * last_c2 + (1.f - last_alpha) * accum_rec2;
-        last_c2 = cd.z;
-        dL_dalpha += (cd.z - accum_rec2) * dLp2;
-        v[8] = dchannel_dcolor * dLp2;
+          accum_rec2 = last_alpha * last_c2 + (1.f - last_alpha) * accum_rec2;
+          last_c2 = cd.z;
+          dL_dalpha += (cd.z - accum_rec2) * dLp2;
+          v[8] = dchannel_dcolor * dLp2;
 
-        accum_recd = last_alpha * last_d + (1.f - last_alpha) * accum_recd;
-        last_d = cd.w;
-        dL_dalpha += (cd.w - accum_recd) * dLpd;
-        v[9] = dchannel_dcolor * dLpd;
+          accum_recd = last_alpha * last_d + (1.f - last_alpha) * accum_recd;
+          last_d = cd.w;
+          dL_dalpha += (cd.w - accum_recd) * dLpd;
+          v[9] = dchannel_dcolor * dLpd;
 
-        dL_dalpha *= T;
-        last_alpha = alpha;
-        dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot_dpixel;
+          dL_dalpha *= T;
+          last_alpha = alpha;
+          dL_dalpha += (-T_final * inv1ma) * bg_dot_dpixel;
 
-        const float dL_dG = co.w * dL_dalpha;
-        const float gdx = G * dx;
-        const float gdy = G * dy;
-        const float dG_ddelx = -gdx * co.x - gdy * co.y;
-        const float dG_ddely = -gdy * co.z - gdx * co.y;
-        v[0] = dL_dG * dG_ddelx * ddelx_dx;
-        v[1] = dL_dG * dG_ddely * ddely_dy;
-        v[2] = -0.5f * gdx * dx * dL_dG;
-        v[3] = -0.5f * gdx * dy * dL_dG;
-        v[4] = -0.5f * gdy * dy * dL_dG;
-        v[5] = G * dL_dalpha;
+          const float dL_dG = co.w * dL_dalpha;
+          const float gdx = G * dx;
+          const float gdy = G * dy;
+          const float dG_ddelx = -gdx * co.x - gdy * co.y;
+          const float dG_ddely = -gdy * co.z - gdx * co.y;
+          v[0] = dL_dG * dG_ddelx * ddelx_dx;
+          v[1] = dL_dG * dG_ddely * ddely_dy;
+          v[2] = -0.5f * gdx * dx * dL_dG;
+          v[3] = -0.5f * gdx * dy * dL_dG;
+          v[4] = -0.5f * gdy * dy * dL_dG;
+          v[5] = G * dL_dalpha;
+        }
+        warp_fold10_and_red(v, lane, acc + (size_t)s_id[j] * ACC_STRIDE);
       }
-      warp_fold10_and_red(v, lane, acc + (size_t)s_id[j] * ACC_STRIDE);
     }
   }
 }

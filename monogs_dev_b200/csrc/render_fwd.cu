@@ -8,14 +8,18 @@
 //  * the tile's batch of splats is staged in shared memory as packed 16 B
 //    records (conic+opacity, rgb+depth): no per-pair global colour fetch
 //    (CR/forward.cu:365 reads features[] from global for every contributing pair);
-//  * n_touched (CR/forward.cu:369-371) is counted with one ballot per
-//    (warp, splat) into shared memory and flushed with ONE global atomic per
-//    (tile, splat) instead of one per (pixel, splat).
+//  * each warp first culls the staged batch against its own 8x4 block (cull.cuh, one
+//    lane per splat) and only iterates over the survivors' bit mask;
+//  * n_touched (CR/forward.cu:369-371) is kept as per-lane bit flags, counted with
+//    ballots only for splats that were touched, into shared memory, and flushed with
+//    ONE global atomic per (tile, splat) instead of one per (pixel, splat).
 #include "common.cuh"
+#include "cull.cuh"
 
 namespace b2gs {
 
 constexpr int RF_BATCH = 256;
+constexpr unsigned RF_FULL = 0xffffffffu;
 
 __global__ void __launch_bounds__(256)
 render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W,
@@ -34,11 +38,12 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   const int tile = blockIdx.x;
   const int tile_x = tile % gx, tile_y = tile / gx;
   // warp -> 8x4 sub-block (2 across, 4 down); lane -> pixel inside it
-  const int px = tile_x * TILE + (warp & 1) * 8 + (lane & 7);
-  const int py = tile_y * TILE + (warp >> 1) * 4 + (lane >> 3);
+  const int bx = tile_x * TILE + (warp & 1) * 8, by = tile_y * TILE + (warp >> 1) * 4;
+  const int px = bx + (lane & 7), py = by + (lane >> 3);
   const bool inside = px < W && py < H;
   const int pix_id = W * py + px;
   const float pixfx = (float)px, pixfy = (float)py;
+  const float rx0 = (float)bx, ry0 = (float)by, rx1 = (float)(bx + 7), ry1 = (float)(by + 3);
 
   const uint2 range = ranges[tile];
   const int n = (int)(range.y - range.x);
@@ -62,35 +67,51 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     s_cnt[tid] = 0;
     __syncthreads();
 
-    if (!__all_sync(0xffffffffu, done)) {
-      for (int j = 0; j < cnt; ++j) {
-        const float2 p = s_xy[j];
-        const float4 co = s_co[j];
-        const float dx = p.x - pixfx, dy = p.y - pixfy;
-        const float power = -0.5f * (co.x * dx * dx + co.z * dy * dy) - co.y * dx * dy;
-        bool touch = false;
-        if (!done && !(power > 0.0f)) {
-          const float alpha = fminf(0.99f, co.w * expf(power));
-          if (!(alpha < 1.0f / 255.0f)) {
-            const float test_T = T * (1 - alpha);
-            if (test_T < 0.0001f) {
-              done = true;
-            } else {
-              const float4 cd = s_cd[j];
-              C0 += cd.x * alpha * T;
-              C1 += cd.y * alpha * T;
-              C2 += cd.z * alpha * T;
-              D += cd.w * alpha * T;
-              touch = test_T > 0.5f;
-              T = test_T;
-              last_contributor = (uint32_t)(base + j + 1);
+    if (!__all_sync(RF_FULL, done)) {
+      for (int c0 = 0; c0 < cnt; c0 += 32) {
+        // one lane per splat: can it reach this warp's 8x4 block at all?
+        const int jj = c0 + lane;
+        const bool keep = jj < cnt && splat_may_touch_rect(s_xy[jj], s_co[jj], rx0, ry0, rx1, ry1);
+        unsigned mask = __ballot_sync(RF_FULL, keep);
+        unsigned touchbits = 0u;
+        while (mask) {
+          const int k = __ffs(mask) - 1;
+          mask &= mask - 1;
+          const int j = c0 + k;
+          const float2 p = s_xy[j];
+          const float4 co = s_co[j];
+          const float dx = p.x - pixfx, dy = p.y - pixfy;
+          const float power = -0.5f * (co.x * dx * dx + co.z * dy * dy) - co.y * dx * dy;
+          if (!done && !(power > 0.0f)) {
+            const float alpha = fminf(0.99f, co.w * expf(power));
+            if (!(alpha < 1.0f / 255.0f)) {
+              const float test_T = T * (1 - alpha);
+              if (test_T < 0.0001f) {
+                done = true;
+              } else {
+                const float4 cd = s_cd[j];
+                C0 += cd.x * alpha * T;
+                C1 += cd.y * alpha * T;
+                C2 += cd.z * alpha * T;
+                D += cd.w * alpha * T;
+                if (test_T > 0.5f) touchbits |= 1u << k;
+                T = test_T;
+                last_contributor = (uint32_t)(base + j + 1);
+              }
             }
           }
         }
-        const unsigned m = __ballot_sync(0xffffffffu, touch);
-        if (m != 0u && lane == 0) atomicAdd(&s_cnt[j], __popc(m));
-        // warp-level early termination, checked every 8 splats
-        if ((j & 7) == 7 && __all_sync(0xffffffffu, done)) break;
+        // n_touched: per splat, how many lanes saw it with T still above 0.5
+        unsigned any = __reduce_or_sync(RF_FULL, touchbits);
+        int mycnt = 0;
+        while (any) {
+          const int k = __ffs(any) - 1;
+          any &= any - 1;
+          const int cnt_k = __popc(__ballot_sync(RF_FULL, (touchbits >> k) & 1u));
+          if (lane == k) mycnt = cnt_k;
+        }
+        if (mycnt) atomicAdd(&s_cnt[c0 + lane], mycnt);
+        if (__all_sync(RF_FULL, done)) break;  // warp-level early termination
       }
     }
     __syncthreads();

@@ -141,8 +141,9 @@ class MappingWindow:
     the full list (only its shard's images are touched)."""
 
     def __init__(self, gaussians, keyframes, bg, pose_lr=(0.003, 0.001, 0.01, 0.01),
-                 optimize_pose=True, group=None):
+                 optimize_pose=True, group=None, render_fn=None, adam_cls=FusedAdam):
         self.g, self.kfs, self.bg = gaussians, keyframes, bg
+        self.render_fn = render_fn or render
         self.group = group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
@@ -156,7 +157,7 @@ class MappingWindow:
                            dict(params=[cam.cam_trans_delta], lr=pose_lr[1])]
             groups += [dict(params=[cam.exposure_a], lr=pose_lr[2]),
                        dict(params=[cam.exposure_b], lr=pose_lr[3])]
-        self.kf_optimizer = FusedAdam(groups, lr=0.0, eps=1e-8) if groups else None
+        self.kf_optimizer = adam_cls(groups, lr=0.0, eps=1e-8) if groups else None
         self.last = {}
 
     def step(self):
@@ -165,7 +166,7 @@ class MappingWindow:
         stats = {}
         for v in self.local:
             kf = self.kfs[v]
-            pkg = render(kf["cam"], g, None, self.bg)
+            pkg = self.render_fn(kf["cam"], g, None, self.bg)
             loss = loss + get_loss_mapping_rgbd(pkg["render"], pkg["depth"], kf["cam"],
                                                 kf["gt_image"], kf["gt_depth"])
             stats[v] = pkg
@@ -174,8 +175,14 @@ class MappingWindow:
             loss = loss + 10 * torch.abs(scaling - scaling.mean(dim=1).view(-1, 1)).mean()
         if torch.is_tensor(loss):
             loss.backward()
-        if self.world > 1:         # ONE message for all six parameter groups
-            dist.all_reduce(g.flat_grad, op=dist.ReduceOp.SUM, group=self.group)
+        if self.world > 1:
+            if hasattr(g, "flat_grad"):   # ONE message for all six parameter groups
+                dist.all_reduce(g.flat_grad, op=dist.ReduceOp.SUM, group=self.group)
+            else:                         # stock layout: one message per parameter tensor
+                for p in g.parameters():
+                    if p.grad is None:
+                        p.grad = torch.zeros_like(p)
+                    dist.all_reduce(p.grad, op=dist.ReduceOp.SUM, group=self.group)
         g.optimizer.step()
         g.zero_grad()
         if self.kf_optimizer is not None:

@@ -79,6 +79,7 @@ class Camera:
         self.FoVx = 2 * math.atan(W / (2 * fx))
         self.FoVy = 2 * math.atan(H / (2 * fy))
         self.device = device
+        self._cache = None
         w2c = torch.eye(4) if w2c is None else w2c.float()
         self.R, self.T = w2c[:3, :3].clone(), w2c[:3, 3].clone()
         self.projection_matrix = projection_matrix(znear, zfar, cx, cy, fx, fy, W, H).t().contiguous().to(device)
@@ -93,24 +94,39 @@ class Camera:
         m[:3, :3], m[:3, 3] = self.R, self.T
         return m
 
+    def _mats(self):
+        """view / full-projection / centre for the current (R, T).  Computed on the host and
+        uploaded once per pose: the reference recomputes them (two 4x4 inversions, a bmm)
+        on every property access (utils/camera_utils.py:94-107)."""
+        if self._cache is None:
+            view = self.w2c.t().contiguous()
+            proj_cpu = self.projection_matrix.cpu()
+            full = view @ proj_cpu
+            center = torch.linalg.inv(view)[3, :3].contiguous()
+            self._cache = (view.to(self.device), full.contiguous().to(self.device), center.to(self.device))
+        return self._cache
+
     @property
     def world_view_transform(self):
-        return self.w2c.t().contiguous().to(self.device)
+        return self._mats()[0]
 
     @property
     def full_proj_transform(self):
-        v = self.world_view_transform
-        return (v.unsqueeze(0).bmm(self.projection_matrix.unsqueeze(0))).squeeze(0)
+        return self._mats()[1]
 
     @property
     def camera_center(self):
-        return self.world_view_transform.inverse()[3, :3]
+        return self._mats()[2]
+
+    def update_RT(self, R, T):
+        self.R, self.T = R.clone(), T.clone()
+        self._cache = None
 
     def update_pose(self):
         """utils/pose_utils.py:76-93"""
         tau = torch.cat([self.cam_trans_delta, self.cam_rot_delta]).detach().cpu()
         new = se3_exp(tau) @ self.w2c
-        self.R, self.T = new[:3, :3].clone(), new[:3, 3].clone()
+        self.update_RT(new[:3, :3], new[:3, 3])
         self.cam_rot_delta.data.fill_(0)
         self.cam_trans_delta.data.fill_(0)
         return bool(tau.norm() < 1e-4)

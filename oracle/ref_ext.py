@@ -117,3 +117,85 @@ def decode_image(fwd, W, H):
     tiles = ((W + 15) // 16) * ((H + 15) // 16)
     out["ranges"] = c.take(torch.int32, 2 * N, (N, 2))[:tiles]
     return out
+
+
+class RefRasterizeFunction(torch.autograd.Function):
+    """Autograd bridge over the reference extension with the semantics of the reference's
+    _RasterizeGaussians (DGR/diff_gaussian_rasterization/__init__.py:50-171), restated here
+    because /root/reference does not exist on the GPU box.  Used by bench.py --impl reference."""
+
+    @staticmethod
+    def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
+                cov3Ds_precomp, theta, rho, rs):
+        args = (rs.bg, means3D, colors_precomp, opacities, scales, rotations, rs.scale_modifier,
+                cov3Ds_precomp, rs.viewmatrix, rs.projmatrix, rs.projmatrix_raw, rs.tanfovx, rs.tanfovy,
+                rs.image_height, rs.image_width, sh, rs.sh_degree, rs.campos, rs.prefiltered, rs.debug)
+        (R, color, radii, geom, binning, img, depth, opacity, n_touched) = dgr().rasterize_gaussians(*args)
+        ctx.rs, ctx.R = rs, R
+        ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh,
+                              geom, binning, img)
+        return color, radii, depth, opacity, n_touched
+
+    @staticmethod
+    def backward(ctx, g_color, g_radii, g_depth, g_opacity, g_touched):
+        rs = ctx.rs
+        colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geom, binning, img = ctx.saved_tensors
+        args = (rs.bg, means3D, radii, colors_precomp, scales, rotations, rs.scale_modifier,
+                cov3Ds_precomp, rs.viewmatrix, rs.projmatrix, rs.projmatrix_raw, rs.tanfovx, rs.tanfovy,
+                g_color, g_depth, sh, rs.sh_degree, rs.campos, geom, ctx.R, binning, img, rs.debug)
+        (g_means2D, g_colors, g_opac, g_means3D, g_cov3D, g_sh, g_scales, g_rots,
+         g_tau) = dgr().rasterize_gaussians_backward(*args)
+        g_tau = torch.sum(g_tau.view(-1, 6), dim=0)
+        return (g_means3D, g_means2D, g_sh, g_colors, g_opac, g_scales, g_rots, g_cov3D,
+                g_tau[3:].view(1, -1), g_tau[:3].view(1, -1), None)
+
+
+def ref_render(viewpoint_camera, pc, pipe=None, bg_color=None, scaling_modifier=1.0):
+    """render() of the reference (gaussian_splatting/gaussian_renderer/__init__.py:24-153)
+    over RefRasterizeFunction; same return dict."""
+    import math
+    from types import SimpleNamespace
+    cam = viewpoint_camera
+    screenspace_points = torch.zeros_like(pc.get_xyz, requires_grad=True) + 0
+    rs = SimpleNamespace(
+        image_height=int(cam.image_height), image_width=int(cam.image_width),
+        tanfovx=math.tan(cam.FoVx * 0.5), tanfovy=math.tan(cam.FoVy * 0.5), bg=bg_color,
+        scale_modifier=scaling_modifier, viewmatrix=cam.world_view_transform,
+        projmatrix=cam.full_proj_transform, projmatrix_raw=cam.projection_matrix,
+        sh_degree=pc.active_sh_degree, campos=cam.camera_center, prefiltered=False, debug=False)
+    e = torch.Tensor([])
+    color, radii, depth, opacity, n_touched = RefRasterizeFunction.apply(
+        pc.get_xyz, screenspace_points, pc.get_features, e, pc.get_opacity, pc.get_scaling,
+        pc.get_rotation, e, cam.cam_rot_delta, cam.cam_trans_delta, rs)
+    return {"render": color, "viewspace_points": screenspace_points, "visibility_filter": radii > 0,
+            "radii": radii, "depth": depth, "opacity": opacity, "n_touched": n_touched}
+
+
+class RefGaussianModel:
+    """Stock layout of the reference's GaussianModel: six separate nn.Parameters and
+    torch.optim.Adam(l, lr=0.0, eps=1e-15) (gaussian_splatting/scene/gaussian_model.py:245-283)."""
+
+    def __init__(self, xyz, f_dc, f_rest, opacity, scaling, rotation, sh_degree=0, spatial_lr_scale=6.0):
+        P = torch.nn.Parameter
+        self.max_sh_degree = self.active_sh_degree = sh_degree
+        self._xyz, self._features_dc, self._features_rest = P(xyz.clone()), P(f_dc.clone()), P(f_rest.clone())
+        self._opacity, self._scaling, self._rotation = P(opacity.clone()), P(scaling.clone()), P(rotation.clone())
+        l = [dict(params=[self._xyz], lr=0.00016 * spatial_lr_scale, name="xyz"),
+             dict(params=[self._features_dc], lr=0.0025, name="f_dc"),
+             dict(params=[self._features_rest], lr=0.0025 / 20.0, name="f_rest"),
+             dict(params=[self._opacity], lr=0.05, name="opacity"),
+             dict(params=[self._scaling], lr=0.001 * spatial_lr_scale, name="scaling"),
+             dict(params=[self._rotation], lr=0.001, name="rotation")]
+        self.optimizer = torch.optim.Adam(l, lr=0.0, eps=1e-15)
+
+    get_xyz = property(lambda s: s._xyz)
+    get_scaling = property(lambda s: torch.exp(s._scaling))
+    get_rotation = property(lambda s: torch.nn.functional.normalize(s._rotation))
+    get_opacity = property(lambda s: torch.sigmoid(s._opacity))
+    get_features = property(lambda s: torch.cat((s._features_dc, s._features_rest), dim=1))
+
+    def parameters(self):
+        return [self._xyz, self._features_dc, self._features_rest, self._opacity, self._scaling, self._rotation]
+
+    def zero_grad(self):
+        self.optimizer.zero_grad(set_to_none=True)

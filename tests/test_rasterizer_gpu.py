@@ -92,7 +92,7 @@ def test_native_vs_reference_ext(name, mode, kw):
             continue
         noise = float((rbw2[k] - b).abs().max())
         assert_grad_close(a.reshape(b.shape) if k != "dL_dtau" else a, b, tol=1e-4, name=k,
-                          extra_atol=4 * noise)
+                          extra_atol=4 * noise, outlier_frac=2e-5)
 
 
 def test_full_size_properties():

@@ -41,3 +41,12 @@ if ref_ext.available():
         f = ref_ext.forward(rs, **inp)
         ref_ext.backward(rs, f, gc, gd, inp["means3D"], shs=inp["shs"], scales=inp["scales"], rotations=inp["rotations"])
     print("ref fwd ms", timeit(rfwd)); print("ref fwd+bwd ms", timeit(rfb))
+from monogs_dev_b200 import _lib
+_lib.lib.b2gs_profile_enable(1)
+for _ in range(10): fwdbwd()
+torch.cuda.synchronize()
+prof = _lib.profile_read(); _lib.lib.b2gs_profile_enable(0)
+tot = sum(v[1] for v in prof.values())
+print("per-kernel (10 fwd+bwd): total kernel ms/iter", tot / 10)
+for k, (c, ms) in sorted(prof.items(), key=lambda kv: -kv[1][1]):
+    print(f"  {k:22s} launches {c:4d}  avg {ms / c * 1e3:9.1f} us  share {ms / tot:6.1%}")
