@@ -22,6 +22,7 @@ import subprocess
 import sys
 import sysconfig
 import time
+from concurrent.futures import ThreadPoolExecutor
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 OUT = os.path.join(HERE, "_ref")
@@ -84,12 +85,12 @@ def build(force=False):
             (os.path.join(DGR, "rasterize_points.cu"), "dgr_rasterize_points"),
             (os.path.join(DGR, "ext.cpp"), "dgr_ext"),
         ]
-        objs = []
-        for s, n in srcs:
-            extra = list(glm)
-            if s.endswith(".cpp"):
-                extra += ["-x", "cu"]
-            objs.append(_obj(s, n, extra, inc, defs, "dgr_ref_C"))
+        def one(sn):
+            s, n = sn
+            extra = list(glm) + (["-x", "cu"] if s.endswith(".cpp") else [])
+            return _obj(s, n, extra, inc, defs, "dgr_ref_C")
+        with ThreadPoolExecutor(max_workers=len(srcs)) as ex:  # torch headers make each TU minutes long
+            objs = list(ex.map(one, srcs))
         _run([NVCC, "-shared", "-o", target] + objs + ARCH + link)
 
     # --- simple-knn ---
@@ -101,12 +102,12 @@ def build(force=False):
             (os.path.join(KNN, "spatial.cu"), "knn_spatial"),
             (os.path.join(KNN, "ext.cpp"), "knn_ext"),
         ]
-        objs = []
-        for s, n in srcs:
-            extra = list(extra0)
-            if s.endswith(".cpp"):
-                extra += ["-x", "cu"]
-            objs.append(_obj(s, n, extra, inc, defs, "knn_ref_C"))
+        def one_knn(sn):
+            s, n = sn
+            extra = list(extra0) + (["-x", "cu"] if s.endswith(".cpp") else [])
+            return _obj(s, n, extra, inc, defs, "knn_ref_C")
+        with ThreadPoolExecutor(max_workers=len(srcs)) as ex:
+            objs = list(ex.map(one_knn, srcs))
         _run([NVCC, "-shared", "-o", target] + objs + ARCH + link)
     print(f"[build_ref] done in {time.time() - t0:.1f}s -> {OUT}")
     return True
