@@ -7,7 +7,7 @@
  * (paths relative to the reference tree; DGR = submodules/diff-gaussian-rasterization,
  * CR = DGR/cuda_rasterizer, KNN = submodules/simple-knn, GS = gaussian_splatting):
  *
- *   b2gs_forward_plan + b2gs_forward_render
+ *   b2gs_forward_plan + b2gs_forward_render, or b2gs_forward
  *        <- _C.rasterize_gaussians            DGR/rasterize_points.h:17-38, DGR/ext.cpp:16
  *           CudaRasterizer::Rasterizer::forward   CR/rasterizer.h:35-61, CR/rasterizer_impl.cu:198-344
  *   b2gs_backward
@@ -28,8 +28,9 @@
  * apart from a thread-local last-error string.  All work is enqueued on the
  * given stream.  The only host synchronisation is in b2gs_forward_plan (it must
  * return the instance count so the caller can size the binning workspace — the
- * reference has the same sync at CR/rasterizer_impl.cu:284) and after every
- * kernel when args->debug != 0 (CR/auxiliary.h:166-173).
+ * reference has the same sync at CR/rasterizer_impl.cu:284; b2gs_forward is the
+ * sync-free alternative) and after every kernel when args->debug != 0
+ * (CR/auxiliary.h:166-173).
  *
  * Matrix convention (identical to the reference): all 4x4 inputs
  * are the transpose of the math matrix stored row-major, i.e. column-major math
@@ -100,6 +101,9 @@ typedef struct B2gsForwardOut {
   float* opacity;    /* device [1,H,W] */
   int32_t* radii;    /* device [P] */
   int32_t* n_touched;/* device [P]; zero-filled by the library */
+  uint32_t* status;  /* device [2], optional (b2gs_forward only): [0] = number of (Gaussian, tile)
+                      * instances, [1] = 1 if that exceeded the binning capacity (then the image
+                      * is background only and the caller must retry with a larger workspace) */
 } B2gsForwardOut;
 
 typedef struct B2gsBackwardIO {
@@ -137,17 +141,31 @@ B2GS_API size_t b2gs_image_bytes(int32_t W, int32_t H);
 B2GS_API size_t b2gs_binning_bytes(int64_t R, int32_t W, int32_t H);
 B2GS_API size_t b2gs_backward_scratch_bytes(int32_t P);
 
-/* Phase 1: per-Gaussian preprocessing, depth ordering, instance offsets.
+/* Two-call form (exact sizing, like the reference: one small D2H read + sync).
+ * Phase 1: per-Gaussian preprocessing, per-tile instance counts, tile ranges.
  * Writes out->radii, zero-fills out->n_touched, returns the number of
  * (Gaussian,tile) instances in *num_rendered (synchronises the stream). */
 B2GS_API int b2gs_forward_plan(const B2gsScene* scene, const B2gsWorkspace* ws,
                       const B2gsForwardOut* out, void* stream, int64_t* num_rendered);
 
-/* Phase 2: instance emission, tile binning, tile ranges, alpha blending. */
+/* Phase 2: instance scatter, per-tile depth sort, alpha blending.
+ * ws->binning must hold b2gs_binning_bytes(num_rendered, W, H). */
 B2GS_API int b2gs_forward_render(const B2gsScene* scene, const B2gsWorkspace* ws,
                         const B2gsForwardOut* out, int64_t num_rendered, void* stream);
 
-B2GS_API int b2gs_backward(const B2gsScene* scene, const B2gsWorkspace* ws, int64_t num_rendered,
+/* One-call form WITHOUT any host synchronisation (CUDA-graph capturable): the caller
+ * supplies a binning workspace of any size; its capacity in instances is
+ * b2gs_binning_capacity(ws->binning_bytes).  If the scene needs more, out->status[1] is
+ * set, the images are background only, and the caller retries with a larger workspace
+ * (status[0] holds the required count).  Replaces the reference's sync at
+ * CR/rasterizer_impl.cu:284. */
+B2GS_API int64_t b2gs_binning_capacity(size_t binning_bytes);
+B2GS_API int b2gs_forward(const B2gsScene* scene, const B2gsWorkspace* ws,
+                 const B2gsForwardOut* out, void* stream);
+
+/* binning_capacity: num_rendered as given to b2gs_forward_render, or
+ * b2gs_binning_capacity(ws->binning_bytes) after b2gs_forward. */
+B2GS_API int b2gs_backward(const B2gsScene* scene, const B2gsWorkspace* ws, int64_t binning_capacity,
                   const B2gsBackwardIO* io, void* stream);
 
 /* present[i] = 1 if view-space z > 0.2 (CR/auxiliary.h:139-164). */

@@ -35,7 +35,7 @@ class B2gsWorkspace(C.Structure):
 class B2gsForwardOut(C.Structure):
     _fields_ = [
         ("color", C.c_void_p), ("depth", C.c_void_p), ("opacity", C.c_void_p),
-        ("radii", C.c_void_p), ("n_touched", C.c_void_p),
+        ("radii", C.c_void_p), ("n_touched", C.c_void_p), ("status", C.c_void_p),
     ]
 
 
@@ -71,6 +71,9 @@ SYMBOLS = {
                                     C.POINTER(B2gsForwardOut), C.c_void_p, C.POINTER(C.c_int64)]),
     "b2gs_forward_render": (C.c_int, [C.POINTER(B2gsScene), C.POINTER(B2gsWorkspace),
                                       C.POINTER(B2gsForwardOut), C.c_int64, C.c_void_p]),
+    "b2gs_binning_capacity": (C.c_int64, [C.c_size_t]),
+    "b2gs_forward": (C.c_int, [C.POINTER(B2gsScene), C.POINTER(B2gsWorkspace),
+                               C.POINTER(B2gsForwardOut), C.c_void_p]),
     "b2gs_backward": (C.c_int, [C.POINTER(B2gsScene), C.POINTER(B2gsWorkspace), C.c_int64,
                                 C.POINTER(B2gsBackwardIO), C.c_void_p]),
     "b2gs_mark_visible": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,

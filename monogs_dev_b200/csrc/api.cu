@@ -151,6 +151,47 @@ extern "C" size_t b2gs_backward_scratch_bytes(int32_t P) {
   return align_up(((size_t)(P > 0 ? P : 1) * ACC_STRIDE + blocks * 8) * sizeof(float), 256);
 }
 
+// shared front half: preprocess (+ per-tile instance counts) and the tile scan
+static int forward_front(const B2gsScene& s, const B2gsWorkspace* ws, const B2gsForwardOut* out,
+                         int64_t cap, cudaStream_t st, GeomWS* g_out, ImageWS* im_out) {
+  if (!out->radii || !out->n_touched) { set_error("radii/n_touched outputs must be non-NULL"); return B2GS_ERR_INVALID; }
+  if (s.P >= (1 << 30)) { set_error("P too large"); return B2GS_ERR_INVALID; }
+  size_t need = 0;
+  GeomWS g = carve_geom(ws->geom, s.P, &need);
+  if (!ws->geom || ws->geom_bytes < need) {
+    set_error("geometry workspace too small: %zu < %zu", ws->geom_bytes, need);
+    return B2GS_ERR_WORKSPACE;
+  }
+  ImageWS im = carve_image(ws->image, s.W, s.H, &need);
+  if (!ws->image || ws->image_bytes < need) {
+    set_error("image workspace too small: %zu < %zu", ws->image_bytes, need);
+    return B2GS_ERR_WORKSPACE;
+  }
+  const size_t tiles = (size_t)((s.W + TILE - 1) / TILE) * ((s.H + TILE - 1) / TILE);
+  B2GS_CUDA(cudaMemsetAsync(im.cursor, 0, sizeof(uint32_t) * tiles, st));
+  int rc = launch_preprocess_fwd(s, g, im, out->radii, out->n_touched, st);
+  if (rc) return rc;
+  rc = launch_tile_scan(s, im, cap, st);
+  if (rc) return rc;
+  *g_out = g;
+  *im_out = im;
+  return B2GS_OK;
+}
+
+static int forward_empty(const B2gsScene& s, const B2gsWorkspace* ws, cudaStream_t st) {
+  // P == 0: every tile empty; render still writes the background image
+  size_t need = 0;
+  ImageWS im = carve_image(ws->image, s.W, s.H, &need);
+  if (!ws->image || ws->image_bytes < need) {
+    set_error("image workspace too small: %zu < %zu", ws->image_bytes, need);
+    return B2GS_ERR_WORKSPACE;
+  }
+  const size_t tiles = (size_t)((s.W + TILE - 1) / TILE) * ((s.H + TILE - 1) / TILE);
+  B2GS_CUDA(cudaMemsetAsync(im.ranges, 0, sizeof(uint2) * tiles, st));
+  B2GS_CUDA(cudaMemsetAsync(im.status, 0, sizeof(uint32_t) * 8, st));
+  return B2GS_OK;
+}
+
 extern "C" int b2gs_forward_plan(const B2gsScene* scene, const B2gsWorkspace* ws,
                                  const B2gsForwardOut* out, void* stream, int64_t* num_rendered) {
   int rc = check_scene(scene, false);
@@ -158,26 +199,27 @@ extern "C" int b2gs_forward_plan(const B2gsScene* scene, const B2gsWorkspace* ws
   if (!ws || !out || !num_rendered) { set_error("NULL ws/out/num_rendered"); return B2GS_ERR_INVALID; }
   *num_rendered = 0;
   const B2gsScene& s = *scene;
-  if (s.P == 0) return B2GS_OK;
-  if (s.P >= (1 << 30)) { set_error("P too large"); return B2GS_ERR_INVALID; }
-  if (!out->radii || !out->n_touched) { set_error("radii/n_touched outputs must be non-NULL"); return B2GS_ERR_INVALID; }
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  size_t need = 0;
-  GeomWS g = carve_geom(ws->geom, s.P, &need);
-  if (!ws->geom || ws->geom_bytes < need) {
-    set_error("geometry workspace too small: %zu < %zu", ws->geom_bytes, need);
-    return B2GS_ERR_WORKSPACE;
-  }
-  B2GS_CUDA(cudaMemsetAsync(out->n_touched, 0, sizeof(int32_t) * (size_t)s.P, st));
-  rc = launch_preprocess_fwd(s, g, out->radii, st);
+  if (s.P == 0) return B2GS_OK;  // nothing to plan; b2gs_forward_render clears the ranges
+  GeomWS g;
+  ImageWS im;
+  rc = forward_front(s, ws, out, -1, st, &g, &im);
   if (rc) return rc;
-  rc = launch_depth_order(s, g, st);
-  if (rc) return rc;
-  uint32_t R = 0;
-  B2GS_CUDA(cudaMemcpyAsync(&R, g.offsets + (s.P - 1), sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+  uint32_t status[2] = {0, 0};
+  B2GS_CUDA(cudaMemcpyAsync(status, im.status, sizeof(status), cudaMemcpyDeviceToHost, st));
   B2GS_CUDA(cudaStreamSynchronize(st));
-  *num_rendered = (int64_t)R;
+  if (status[1]) { set_error("too many instances (>= 2^31)"); return B2GS_ERR_INVALID; }
+  *num_rendered = (int64_t)status[0];
   return B2GS_OK;
+}
+
+static int forward_back(const B2gsScene& s, const B2gsWorkspace* ws, const B2gsForwardOut* out,
+                        const GeomWS& g, const ImageWS& im, int64_t cap, cudaStream_t st) {
+  if (!out->color || !out->depth || !out->opacity) { set_error("image outputs must be non-NULL"); return B2GS_ERR_INVALID; }
+  BinWS b = carve_bin(ws->binning, cap, nullptr);
+  int rc = launch_binning(s, g, im, b, cap, st);
+  if (rc) return rc;
+  return launch_render_fwd(s, g, im, b, *out, st);
 }
 
 extern "C" int b2gs_forward_render(const B2gsScene* scene, const B2gsWorkspace* ws,
@@ -186,26 +228,60 @@ extern "C" int b2gs_forward_render(const B2gsScene* scene, const B2gsWorkspace* 
   if (rc) return rc;
   if (!ws || !out) { set_error("NULL ws/out"); return B2GS_ERR_INVALID; }
   const B2gsScene& s = *scene;
-  if (!out->color || !out->depth || !out->opacity) { set_error("image outputs must be non-NULL"); return B2GS_ERR_INVALID; }
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  size_t need = 0;
-  ImageWS im = carve_image(ws->image, s.W, s.H, &need);
-  if (!ws->image || ws->image_bytes < need) {
-    set_error("image workspace too small: %zu < %zu", ws->image_bytes, need);
-    return B2GS_ERR_WORKSPACE;
-  }
   if (s.P == 0) R = 0;
-  GeomWS g = carve_geom(ws->geom, s.P, nullptr);
-  BinWS b = carve_bin(ws->binning, R, &need);
+  if (R < 0 || R >= ((int64_t)1 << 31)) { set_error("bad instance count: %lld", (long long)R); return B2GS_ERR_INVALID; }
+  size_t need = 0;
+  carve_bin(nullptr, R, &need);
   if (R > 0 && (!ws->binning || ws->binning_bytes < need)) {
     set_error("binning workspace too small: %zu < %zu", ws->binning_bytes, need);
     return B2GS_ERR_WORKSPACE;
   }
-  if (R >= ((int64_t)1 << 31)) { set_error("too many instances: %lld", (long long)R); return B2GS_ERR_INVALID; }
-  rc = launch_binning(s, g, im, b, R, st);
+  if (s.P == 0) {
+    rc = forward_empty(s, ws, st);
+    if (rc) return rc;
+  }
+  GeomWS g = carve_geom(ws->geom, s.P, nullptr);
+  ImageWS im = carve_image(ws->image, s.W, s.H, nullptr);
+  return forward_back(s, ws, out, g, im, R, st);
+}
+
+extern "C" int64_t b2gs_binning_capacity(size_t binning_bytes) {
+  // inverse of b2gs_binning_bytes: point_list (4 B) + keys (8 B) per instance, 256 B alignment
+  int64_t n = (int64_t)(binning_bytes / 12);
+  while (n > 0) {
+    size_t need = 0;
+    carve_bin(nullptr, n, &need);
+    if (need <= binning_bytes) break;
+    n -= (int64_t)((need - binning_bytes + 11) / 12);
+  }
+  return n > 0 ? n : 0;
+}
+
+extern "C" int b2gs_forward(const B2gsScene* scene, const B2gsWorkspace* ws,
+                            const B2gsForwardOut* out, void* stream) {
+  int rc = check_scene(scene, false);
   if (rc) return rc;
-  B2gsForwardOut o = *out;
-  return launch_render_fwd(s, g, im, b, o, st);
+  if (!ws || !out) { set_error("NULL ws/out"); return B2GS_ERR_INVALID; }
+  const B2gsScene& s = *scene;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const int64_t cap = b2gs_binning_capacity(ws->binning ? ws->binning_bytes : 0);
+  if (cap <= 0) { set_error("b2gs_forward needs a binning workspace (capacity > 0)"); return B2GS_ERR_WORKSPACE; }
+  GeomWS g = carve_geom(ws->geom, s.P, nullptr);
+  ImageWS im;
+  if (s.P == 0) {
+    rc = forward_empty(s, ws, st);
+    if (rc) return rc;
+    im = carve_image(ws->image, s.W, s.H, nullptr);
+  } else {
+    rc = forward_front(s, ws, out, cap, st, &g, &im);
+    if (rc) return rc;
+  }
+  rc = forward_back(s, ws, out, g, im, cap, st);
+  if (rc) return rc;
+  if (out->status)
+    B2GS_CUDA(cudaMemcpyAsync(out->status, im.status, 2 * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
+  return B2GS_OK;
 }
 
 extern "C" int b2gs_backward(const B2gsScene* scene, const B2gsWorkspace* ws, int64_t R,

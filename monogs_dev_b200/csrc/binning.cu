@@ -1,50 +1,26 @@
-// binning.cu — depth ordering, instance offsets, (tile, Gaussian) instance emission,
-// tile binning and tile ranges.
+// binning.cu — tile ranges, (tile, Gaussian) instance scatter and per-tile depth sort.
 //
 // Replaces: cub InclusiveSum + D2H (CR/rasterizer_impl.cu:280-284), duplicateWithKeys
-// (:70-111), the 64-bit SortPairs over [0, 32+bit) (:306-311) and identifyTileRanges
+// (:70-111), the 64-bit cub SortPairs over [0, 32+bit) (:306-311) and identifyTileRanges
 // (:116-138).
 //
-// B200-first restructuring (DESIGN.md "binning"): the reference sorts R 12-byte
-// (tile<<32|depth, id) pairs with 6 radix passes.  The same final order
-// (tile, depth bits, Gaussian id — the id tie-break comes from radix-sort
-// stability and emission in id order) is produced here by
-//   1. a stable 32-bit sort of the P depth keys (id payload)       ~16 B x P x 4 passes
-//   2. emitting instances in that (depth, id) order, warp-cooperatively
-//   3. a stable sort of the R (tile, id) pairs on tile bits only   ~16 B x R x 2 passes
-// Stable sort by tile of a (depth,id)-ordered list is ordered by (tile, depth, id):
-// exactly the reference's sorted list, bit for bit (tests/test_binning_gpu.py).
+// B200-first restructuring (DESIGN.md "Binning without a global sort"): the reference
+// sorts R 12-byte (tile<<32|depth, id) pairs with 6 global radix passes after a host
+// sync.  The same final order — (tile, depth bits, Gaussian id); the id tie-break is
+// what radix-sort stability plus id-order emission gives the reference — is produced
+// here with no global sort, no scan over the Gaussians, no library call and no sync:
+//   1. preprocess_fwd counts instances per tile          (T counters, red.add)
+//   2. tile_scan_kernel: counters -> ranges, cursors, num_rendered, overflow flag
+//   3. scatter_instances_kernel: each instance's 8 B key (depth bits<<32 | id) goes
+//      to its tile's segment through an atomic cursor (arbitrary order inside a segment)
+//   4. tile_sort_kernel: one CTA per tile sorts its segment (bitonic network on the
+//      unique 64-bit keys, shared memory; oversized segments run it in global/L2) and
+//      writes the sorted id list.
+// Everything is L2-resident at the BASELINE sizes (R = 1.3 M -> 10 MB of keys).
 #include "common.cuh"
-#include <cub/cub.cuh>
+#include "expand.cuh"
 
 namespace b2gs {
-
-struct TouchedInSortedOrder {
-  const uint32_t* touched;
-  const uint32_t* id_sorted;
-  __host__ __device__ __forceinline__ uint32_t operator()(const uint32_t& i) const {
-    return touched[id_sorted[i]];
-  }
-};
-using CountIt = cub::CountingInputIterator<uint32_t>;
-using TouchedIt = cub::TransformInputIterator<uint32_t, TouchedInSortedOrder, CountIt>;
-
-static size_t depth_temp_bytes(int32_t P) {
-  size_t a = 0, b = 0;
-  cub::DeviceRadixSort::SortPairs(nullptr, a, (const uint32_t*)nullptr, (uint32_t*)nullptr,
-                                  (const uint32_t*)nullptr, (uint32_t*)nullptr, P);
-  TouchedInSortedOrder op{nullptr, nullptr};
-  TouchedIt it(CountIt(0), op);
-  cub::DeviceScan::InclusiveSum(nullptr, b, it, (uint32_t*)nullptr, P);
-  return a > b ? a : b;
-}
-
-static size_t tile_temp_bytes(int64_t R) {
-  size_t a = 0;
-  cub::DeviceRadixSort::SortPairs(nullptr, a, (const uint32_t*)nullptr, (uint32_t*)nullptr,
-                                  (const uint32_t*)nullptr, (uint32_t*)nullptr, (int)R);
-  return a;
-}
 
 GeomWS carve_geom(void* base, int32_t P, size_t* total) {
   Carver c(base);
@@ -53,17 +29,9 @@ GeomWS carve_geom(void* base, int32_t P, size_t* total) {
   g.xy = c.take<float2>(n);
   g.conic_o = c.take<float4>(n);
   g.rgbd = c.take<float4>(n);
-  g.depth_key = c.take<uint32_t>(n);
   g.rect = c.take<ushort4>(n);
   g.tiles_touched = c.take<uint32_t>(n);
   g.clamped = c.take<uint8_t>(n);
-  g.iota = c.take<uint32_t>(n);
-  g.key_sorted = c.take<uint32_t>(n);
-  g.id_sorted = c.take<uint32_t>(n);
-  g.offsets = c.take<uint32_t>(n);
-  g.misc = c.take<uint32_t>(64);
-  g.temp_bytes = depth_temp_bytes((int32_t)n);
-  g.temp = c.take<char>(g.temp_bytes);
   if (total) *total = c.total();
   return g;
 }
@@ -76,176 +44,219 @@ ImageWS carve_image(void* base, int32_t W, int32_t H, size_t* total) {
   im.final_T = c.take<float>(N);
   im.n_contrib = c.take<uint32_t>(N);
   im.ranges = c.take<uint2>(tiles);
+  im.cursor = c.take<uint32_t>(tiles);
+  im.status = c.take<uint32_t>(8);
   if (total) *total = c.total();
   return im;
 }
 
-BinWS carve_bin(void* base, int64_t R, size_t* total) {
+BinWS carve_bin(void* base, int64_t cap, size_t* total) {
   Carver c(base);
   BinWS b;
-  size_t n = (size_t)(R > 0 ? R : 1);
+  size_t n = (size_t)(cap > 0 ? cap : 1);
   b.point_list = c.take<uint32_t>(n);
-  b.tile_sorted = c.take<uint32_t>(n);
-  b.tile_unsorted = c.take<uint32_t>(n);
-  b.id_unsorted = c.take<uint32_t>(n);
-  b.temp_bytes = tile_temp_bytes((int64_t)n);
-  b.temp = c.take<char>(b.temp_bytes);
+  b.keys = c.take<uint64_t>(n);
   if (total) *total = c.total();
   return b;
 }
 
-// ---- depth order + offsets -------------------------------------------------------
-int launch_depth_order(const B2gsScene& s, const GeomWS& g, cudaStream_t st) {
-  size_t tb = g.temp_bytes;
-  {
-    B2GS_PROF("depth_sort(cub)", st);
-    B2GS_CUDA(cub::DeviceRadixSort::SortPairs(g.temp, tb, (const uint32_t*)g.depth_key, g.key_sorted,
-                                              (const uint32_t*)g.iota, g.id_sorted, s.P, 0, 32, st));
+// ---- counters -> ranges ------------------------------------------------------------
+// One CTA.  Exclusive scan of the T per-tile instance counts.  Writes ranges (the
+// reference leaves empty tiles at (0,0), CR/rasterizer_impl.cu:313-321), turns the
+// counters into scatter cursors, publishes num_rendered and the overflow flag.
+constexpr int SCAN_THREADS = 1024;
+
+__global__ void __launch_bounds__(SCAN_THREADS)
+tile_scan_kernel(uint32_t tiles, long long cap, uint32_t* __restrict__ cursor,
+                 uint2* __restrict__ ranges, uint32_t* __restrict__ status) {
+  __shared__ uint32_t s_total;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t per = (tiles + SCAN_THREADS - 1) / SCAN_THREADS;
+  const uint32_t lo = min(tiles, (uint32_t)tid * per), hi = min(tiles, lo + per);
+  unsigned long long mine = 0;
+  for (uint32_t t = lo; t < hi; ++t) mine += cursor[t];
+  // block-wide exclusive scan of `mine` (64-bit: the total may exceed 2^32)
+  unsigned long long incl = mine;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const unsigned long long n = __shfl_up_sync(0xffffffffu, incl, d);
+    if (lane >= d) incl += n;
   }
-  if (s.debug) B2GS_CUDA(cudaStreamSynchronize(st));
-  TouchedInSortedOrder op{g.tiles_touched, g.id_sorted};
-  TouchedIt it(CountIt(0), op);
-  tb = g.temp_bytes;
-  {
-    B2GS_PROF("offset_scan(cub)", st);
-    B2GS_CUDA(cub::DeviceScan::InclusiveSum(g.temp, tb, it, g.offsets, s.P, st));
+  __shared__ unsigned long long s_w64[32];
+  if (lane == 31) s_w64[warp] = incl;
+  __syncthreads();
+  if (warp == 0) {
+    unsigned long long w = s_w64[lane];
+    unsigned long long wi = w;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const unsigned long long n = __shfl_up_sync(0xffffffffu, wi, d);
+      if (lane >= d) wi += n;
+    }
+    s_w64[lane] = wi - w;  // exclusive prefix of the warp
+    if (lane == 31) {
+      const bool over = wi >= (1ull << 31) || (cap >= 0 && wi > (unsigned long long)cap);
+      status[0] = (uint32_t)min(wi, 0xffffffffull);
+      status[1] = over ? 1u : 0u;
+      s_total = over ? 0xffffffffu : 0u;
+    }
   }
-  if (s.debug) B2GS_CUDA(cudaStreamSynchronize(st));
+  __syncthreads();
+  const bool over = s_total != 0u;
+  uint32_t run = (uint32_t)(s_w64[warp] + incl - mine);
+  for (uint32_t t = lo; t < hi; ++t) {
+    const uint32_t c = cursor[t];
+    // on overflow every tile is rendered empty; the caller sees status[1] and retries
+    ranges[t] = (c && !over) ? make_uint2(run, run + c) : make_uint2(0u, 0u);
+    cursor[t] = run;
+    run += c;
+  }
+}
+
+int launch_tile_scan(const B2gsScene& s, const ImageWS& im, int64_t cap, cudaStream_t st) {
+  const int gx = (s.W + TILE - 1) / TILE, gy = (s.H + TILE - 1) / TILE;
+  B2GS_PROF("tile_scan", st);
+  tile_scan_kernel<<<1, SCAN_THREADS, 0, st>>>((uint32_t)(gx * gy), (long long)cap, im.cursor,
+                                               im.ranges, im.status);
+  B2GS_LAUNCH_CHECK(st, s.debug);
   return B2GS_OK;
 }
 
-// ---- instance emission -------------------------------------------------------------
-// One warp expands 32 consecutive (depth-ordered) Gaussians into their contiguous
-// span of instances; lanes stride over the span so stores are coalesced no matter
-// how unevenly the 32 splats are sized (the reference's per-thread double loop,
-// CR/rasterizer_impl.cu:97-109, serialises big splats on one thread).
+// ---- instance scatter ----------------------------------------------------------------
 __global__ void __launch_bounds__(256)
-emit_instances_kernel(int P, int gx, const uint32_t* __restrict__ id_sorted,
-                      const uint32_t* __restrict__ offsets,
-                      const uint32_t* __restrict__ tiles_touched,
-                      const ushort4* __restrict__ rect, uint32_t* __restrict__ tile_out,
-                      uint32_t* __restrict__ id_out) {
-  __shared__ uint32_t s_pre[8][32];
-  __shared__ uint32_t s_id[8][32];
-  __shared__ uint32_t s_org[8][32];  // x0 | y0 << 16
-  __shared__ uint32_t s_w[8][32];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+scatter_instances_kernel(int P, uint32_t gx, const uint32_t* __restrict__ tiles_touched,
+                         const ushort4* __restrict__ rect, const float4* __restrict__ rgbd,
+                         uint32_t* __restrict__ cursor, const uint32_t* __restrict__ status,
+                         uint64_t* __restrict__ keys) {
+  __shared__ WarpRects s_rects[8];
+  if (status[1]) return;  // overflow: nothing may be written
+  const int lane = threadIdx.x & 31;
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-
-  uint32_t id = 0, touched = 0, incl = 0;
-  ushort4 r = make_ushort4(0, 0, 0, 0);
+  uint32_t touched = 0, org = 0, w = 1, depth_bits = 0;
   if (i < P) {
-    id = id_sorted[i];
-    touched = tiles_touched[id];
-    incl = offsets[i];
-    if (touched) r = rect[id];
-  } else {
-    incl = offsets[P - 1];  // empty tail lanes sit at the end of the span
-  }
-  // span start of this warp in the instance arrays
-  const uint32_t warp_base = __shfl_sync(0xffffffffu, incl - touched, 0);
-  const uint32_t pre = incl - warp_base;  // inclusive prefix inside the warp
-  const uint32_t total = __shfl_sync(0xffffffffu, pre, 31);
-  if (total == 0) return;
-  s_pre[warp][lane] = pre;
-  s_id[warp][lane] = id;
-  s_org[warp][lane] = (uint32_t)r.x | ((uint32_t)r.y << 16);
-  s_w[warp][lane] = (uint32_t)(r.z - r.x);
-  __syncwarp();
-  for (uint32_t k = lane; k < total; k += 32) {
-    // smallest j with pre[j] > k
-    int lo = 0;
-#pragma unroll
-    for (int step = 16; step > 0; step >>= 1) {
-      if (s_pre[warp][lo + step - 1] <= k) lo += step;
+    touched = tiles_touched[i];
+    if (touched) {
+      const ushort4 r = rect[i];
+      org = (uint32_t)r.x | ((uint32_t)r.y << 16);
+      w = (uint32_t)(r.z - r.x);
+      depth_bits = __float_as_uint(rgbd[i].w);
     }
-    const uint32_t pj = s_pre[warp][lo];
-    const uint32_t prev = lo ? s_pre[warp][lo - 1] : 0u;
-    (void)pj;
-    const uint32_t local = k - prev;
-    const uint32_t w = s_w[warp][lo];
-    const uint32_t org = s_org[warp][lo];
-    const uint32_t dy = local / w, dx = local - dy * w;
-    const uint32_t tile = ((org >> 16) + dy) * (uint32_t)gx + (org & 0xffffu) + dx;
-    tile_out[warp_base + k] = tile;
-    id_out[warp_base + k] = s_id[warp][lo];
+  }
+  warp_expand_rects(s_rects[threadIdx.x >> 5], lane, touched, org, w, depth_bits, (uint32_t)i, gx,
+                    [&](uint32_t tile, uint32_t d, uint32_t id) {
+                      const uint32_t slot = atomicAdd(&cursor[tile], 1u);
+                      keys[slot] = ((uint64_t)d << 32) | id;
+                    });
+}
+
+// ---- per-tile sort -------------------------------------------------------------------
+// Bitonic network in its all-ascending form (first step of every merge stage compares
+// mirrored positions, the rest are half-cleaners).  Because every compare-exchange puts
+// the minimum at the lower index, positions >= n behave as +infinity without being
+// stored: a pair whose upper index is >= n is skipped.  So the segment needs no padding
+// and the same code runs on shared memory or directly on the global segment.
+constexpr int SORT_THREADS = 256;
+constexpr int SORT_SMEM_KEYS = 4096;  // 32 KB
+
+__device__ __forceinline__ void bitonic_sort_block(uint64_t* __restrict__ a, uint32_t n) {
+  uint32_t N = 2;
+  while (N < n) N <<= 1;
+  const uint32_t half = N >> 1;
+  for (uint32_t k = 2; k <= N; k <<= 1) {
+    const uint32_t hk = k >> 1;
+    for (uint32_t t = threadIdx.x; t < half; t += SORT_THREADS) {
+      const uint32_t off = t & (hk - 1);  // hk, j are powers of two
+      const uint32_t i = 2 * t - off, l = 2 * (t - off) + k - 1 - off;
+      if (l < n) {
+        const uint64_t x = a[i], y = a[l];
+        if (y < x) { a[i] = y; a[l] = x; }
+      }
+    }
+    __syncthreads();
+    for (uint32_t j = k >> 2; j > 0; j >>= 1) {
+      for (uint32_t t = threadIdx.x; t < half; t += SORT_THREADS) {
+        const uint32_t i = 2 * t - (t & (j - 1)), l = i + j;
+        if (l < n) {
+          const uint64_t x = a[i], y = a[l];
+          if (y < x) { a[i] = y; a[l] = x; }
+        }
+      }
+      __syncthreads();
+    }
   }
 }
 
-__global__ void __launch_bounds__(256)
-tile_ranges_kernel(uint32_t R, const uint32_t* __restrict__ tile_sorted, uint2* __restrict__ ranges) {
-  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= R) return;
-  uint32_t cur = tile_sorted[i];
-  if (i == 0) {
-    ranges[cur].x = 0;
-  } else {
-    uint32_t prev = tile_sorted[i - 1];
-    if (cur != prev) {
-      ranges[prev].y = i;
-      ranges[cur].x = i;
+__global__ void __launch_bounds__(SORT_THREADS)
+tile_sort_kernel(const uint2* __restrict__ ranges, uint64_t* __restrict__ keys,
+                 uint32_t* __restrict__ point_list) {
+  __shared__ uint64_t s_keys[SORT_SMEM_KEYS];
+  const uint2 r = ranges[blockIdx.x];
+  const uint32_t n = r.y - r.x;
+  if (n == 0) return;
+  uint64_t* seg = keys + r.x;
+  if (n <= SORT_SMEM_KEYS) {
+    for (uint32_t i = threadIdx.x; i < n; i += SORT_THREADS) s_keys[i] = seg[i];
+    __syncthreads();
+    if (n > 1) bitonic_sort_block(s_keys, n);
+    for (uint32_t i = threadIdx.x; i < n; i += SORT_THREADS) {
+      const uint64_t k = s_keys[i];
+      seg[i] = k;  // kept sorted for the parity export (keys are L2-resident)
+      point_list[r.x + i] = (uint32_t)k;
     }
+  } else {
+    __syncthreads();
+    bitonic_sort_block(seg, n);
+    for (uint32_t i = threadIdx.x; i < n; i += SORT_THREADS) point_list[r.x + i] = (uint32_t)seg[i];
   }
-  if (i == R - 1) ranges[cur].y = R;
 }
 
 int launch_binning(const B2gsScene& s, const GeomWS& g, const ImageWS& im, const BinWS& b,
-                   int64_t R, cudaStream_t st) {
+                   int64_t cap, cudaStream_t st) {
   const int gx = (s.W + TILE - 1) / TILE, gy = (s.H + TILE - 1) / TILE;
-  const uint32_t tiles = (uint32_t)gx * gy;
-  B2GS_CUDA(cudaMemsetAsync(im.ranges, 0, sizeof(uint2) * tiles, st));
-  if (R <= 0) return B2GS_OK;
+  if (cap <= 0 || s.P == 0) return B2GS_OK;
   {
-    B2GS_PROF("emit_instances", st);
-    emit_instances_kernel<<<(s.P + 255) / 256, 256, 0, st>>>(s.P, gx, g.id_sorted, g.offsets,
-                                                            g.tiles_touched, g.rect,
-                                                            b.tile_unsorted, b.id_unsorted);
+    B2GS_PROF("scatter_instances", st);
+    scatter_instances_kernel<<<(s.P + 255) / 256, 256, 0, st>>>(s.P, (uint32_t)gx, g.tiles_touched,
+                                                               g.rect, g.rgbd, im.cursor, im.status,
+                                                               b.keys);
     B2GS_LAUNCH_CHECK(st, s.debug);
   }
-  size_t tb = b.temp_bytes;
-  {
-    B2GS_PROF("tile_sort(cub)", st);
-    B2GS_CUDA(cub::DeviceRadixSort::SortPairs(b.temp, tb, (const uint32_t*)b.tile_unsorted,
-                                              b.tile_sorted, (const uint32_t*)b.id_unsorted,
-                                              b.point_list, (int)R, 0, tile_bits(tiles), st));
-  }
-  if (s.debug) B2GS_CUDA(cudaStreamSynchronize(st));
-  B2GS_PROF("tile_ranges", st);
-  tile_ranges_kernel<<<(uint32_t)((R + 255) / 256), 256, 0, st>>>((uint32_t)R, b.tile_sorted,
-                                                                 im.ranges);
+  B2GS_PROF("tile_sort", st);
+  tile_sort_kernel<<<gx * gy, SORT_THREADS, 0, st>>>(im.ranges, b.keys, b.point_list);
   B2GS_LAUNCH_CHECK(st, s.debug);
   return B2GS_OK;
 }
 
 // ---- debug export (parity tests) ---------------------------------------------------
-__global__ void export_keys_kernel(uint32_t R, const uint32_t* __restrict__ tile_sorted,
+// Materialises the reference's sorted key list: (tile << 32) | depth bits, and the ids.
+__global__ void export_keys_kernel(const uint2* __restrict__ ranges,
                                    const uint32_t* __restrict__ point_list,
-                                   const uint32_t* __restrict__ depth_key,
-                                   uint64_t* __restrict__ keys, uint32_t* __restrict__ values) {
-  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= R) return;
-  uint32_t id = point_list[i];
-  if (keys) keys[i] = ((uint64_t)tile_sorted[i] << 32) | depth_key[id];
-  if (values) values[i] = id;
+                                   const float4* __restrict__ rgbd, uint64_t* __restrict__ keys,
+                                   uint32_t* __restrict__ values) {
+  const uint2 r = ranges[blockIdx.x];
+  for (uint32_t i = r.x + threadIdx.x; i < r.y; i += blockDim.x) {
+    const uint32_t id = point_list[i];
+    if (keys) keys[i] = ((uint64_t)blockIdx.x << 32) | __float_as_uint(rgbd[id].w);
+    if (values) values[i] = id;
+  }
 }
 
 }  // namespace b2gs
 
 extern "C" int b2gs_debug_export_binning(const B2gsScene* scene, const B2gsWorkspace* ws,
-                                         int64_t R, uint64_t* keys, uint32_t* values,
+                                         int64_t cap, uint64_t* keys, uint32_t* values,
                                          uint32_t* ranges, void* stream) {
   using namespace b2gs;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   GeomWS g = carve_geom(ws->geom, scene->P, nullptr);
   ImageWS im = carve_image(ws->image, scene->W, scene->H, nullptr);
-  BinWS b = carve_bin(ws->binning, R, nullptr);
-  if (R > 0 && (keys || values)) {
-    export_keys_kernel<<<(uint32_t)((R + 255) / 256), 256, 0, st>>>(
-        (uint32_t)R, b.tile_sorted, b.point_list, g.depth_key, keys, values);
+  BinWS b = carve_bin(ws->binning, cap, nullptr);
+  const size_t tiles = (size_t)((scene->W + TILE - 1) / TILE) * ((scene->H + TILE - 1) / TILE);
+  if (cap > 0 && (keys || values)) {
+    export_keys_kernel<<<(uint32_t)tiles, 256, 0, st>>>(im.ranges, b.point_list, g.rgbd, keys, values);
     B2GS_LAUNCH_CHECK(st, 1);
   }
   if (ranges) {
-    const size_t tiles = (size_t)((scene->W + TILE - 1) / TILE) * ((scene->H + TILE - 1) / TILE);
     B2GS_CUDA(cudaMemcpyAsync(ranges, im.ranges, tiles * sizeof(uint2), cudaMemcpyDeviceToDevice, st));
   }
   return B2GS_OK;

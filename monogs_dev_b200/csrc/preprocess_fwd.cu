@@ -8,6 +8,7 @@
 // payload for the depth-ordering sort in the same pass.
 #include "common.cuh"
 #include "gsmath.cuh"
+#include "expand.cuh"
 
 namespace b2gs {
 
@@ -58,19 +59,23 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
                       const float* __restrict__ colors_precomp, const float* __restrict__ viewmatrix,
                       const float* __restrict__ projmatrix, const float* __restrict__ campos_p, int W,
                       int H, float tan_fovx, float tan_fovy, float focal_x, float focal_y, int gx,
-                      int gy, int prefiltered, int32_t* __restrict__ radii, GeomWS g) {
+                      int gy, int prefiltered, int32_t* __restrict__ radii,
+                      int32_t* __restrict__ n_touched, uint32_t* __restrict__ tile_count, GeomWS g) {
   __shared__ float s_view[16], s_proj[16];
+  __shared__ WarpRects s_rects[8];
   if (threadIdx.x < 16) s_view[threadIdx.x] = viewmatrix[threadIdx.x];
   else if (threadIdx.x < 32) s_proj[threadIdx.x - 16] = projmatrix[threadIdx.x - 16];
   __syncthreads();
 
-  int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= P) return;
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  const bool valid = idx < P;
+  float3 p_orig = {0.f, 0.f, 0.f};
+  if (valid) {
+    p_orig = {means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]};
+    n_touched[idx] = 0;  // render_fwd accumulates into it (CR/forward.cu:369-371)
+  }
 
-  g.iota[idx] = (uint32_t)idx;
-  const float3 p_orig = {means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]};
-
-  bool visible = true;
+  bool visible = valid;
   int my_radius_i = 0;
   uint32_t touched = 0;
   float2 point_image = {0.f, 0.f};
@@ -78,7 +83,7 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
   float3 p_view = xform_point_4x3(p_orig, s_view);
   int x0 = 0, y0 = 0, x1 = 0, y1 = 0;
 
-  if (p_view.z <= 0.2f) {  // near cull only (CR/auxiliary.h:153)
+  if (valid && p_view.z <= 0.2f) {  // near cull only (CR/auxiliary.h:153)
     if (prefiltered) {
       printf("Point is filtered although prefiltered is set. This shouldn't happen!");
       __trap();
@@ -127,31 +132,36 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
     }
   }
 
-  if (!visible) {
+  if (valid && !visible) {
     radii[idx] = 0;
     g.tiles_touched[idx] = 0;
-    g.depth_key[idx] = 0xFFFFFFFFu;
-    return;
+    touched = 0;
+  }
+  if (visible) {
+    float3 rgb;
+    uint8_t clamp_bits = 0;
+    if (colors_precomp == nullptr) {
+      const float3 campos = {campos_p[0], campos_p[1], campos_p[2]};
+      rgb = sh_to_rgb(D, shs + (size_t)idx * M * 3, p_orig, campos, clamp_bits);
+    } else {
+      rgb = {colors_precomp[3 * idx], colors_precomp[3 * idx + 1], colors_precomp[3 * idx + 2]};
+    }
+    radii[idx] = my_radius_i;
+    g.tiles_touched[idx] = touched;
+    g.xy[idx] = point_image;
+    g.conic_o[idx] = con_o;
+    g.rgbd[idx] = make_float4(rgb.x, rgb.y, rgb.z, p_view.z);
+    g.rect[idx] = make_ushort4((unsigned short)x0, (unsigned short)y0, (unsigned short)x1,
+                               (unsigned short)y1);
+    g.clamped[idx] = clamp_bits;
   }
 
-  float3 rgb;
-  uint8_t clamp_bits = 0;
-  if (colors_precomp == nullptr) {
-    const float3 campos = {campos_p[0], campos_p[1], campos_p[2]};
-    rgb = sh_to_rgb(D, shs + (size_t)idx * M * 3, p_orig, campos, clamp_bits);
-  } else {
-    rgb = {colors_precomp[3 * idx], colors_precomp[3 * idx + 1], colors_precomp[3 * idx + 2]};
-  }
-
-  radii[idx] = my_radius_i;
-  g.tiles_touched[idx] = touched;
-  g.depth_key[idx] = __float_as_uint(p_view.z);
-  g.xy[idx] = point_image;
-  g.conic_o[idx] = con_o;
-  g.rgbd[idx] = make_float4(rgb.x, rgb.y, rgb.z, p_view.z);
-  g.rect[idx] = make_ushort4((unsigned short)x0, (unsigned short)y0, (unsigned short)x1,
-                             (unsigned short)y1);
-  g.clamped[idx] = clamp_bits;
+  // instances per tile: the T counters become the tile ranges (binning.cu) — replaces the
+  // P-wide InclusiveSum + identifyTileRanges (CR/rasterizer_impl.cu:280,116-138)
+  const int lane = threadIdx.x & 31;
+  warp_expand_rects(s_rects[threadIdx.x >> 5], lane, touched, (uint32_t)x0 | ((uint32_t)y0 << 16),
+                    (uint32_t)(x1 - x0), 0u, 0u, (uint32_t)gx,
+                    [&](uint32_t tile, uint32_t, uint32_t) { atomicAdd(&tile_count[tile], 1u); });
 }
 
 __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D,
@@ -164,7 +174,8 @@ __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D,
   present[idx] = v.z > 0.2f ? 1 : 0;
 }
 
-int launch_preprocess_fwd(const B2gsScene& s, const GeomWS& g, int32_t* radii, cudaStream_t st) {
+int launch_preprocess_fwd(const B2gsScene& s, const GeomWS& g, const ImageWS& im, int32_t* radii,
+                          int32_t* n_touched, cudaStream_t st) {
   // focal lengths exactly as the reference derives them (CR/rasterizer_impl.cu:225-226)
   const float focal_y = s.H / (2.0f * s.tan_fovy);
   const float focal_x = s.W / (2.0f * s.tan_fovx);
@@ -174,7 +185,7 @@ int launch_preprocess_fwd(const B2gsScene& s, const GeomWS& g, int32_t* radii, c
   preprocess_fwd_kernel<<<blocks, 256, 0, st>>>(
       s.P, s.D, s.M, s.means3D, s.scales, s.scale_modifier, s.rotations, s.opacities, s.shs,
       s.cov3D_precomp, s.colors_precomp, s.viewmatrix, s.projmatrix, s.campos, s.W, s.H,
-      s.tan_fovx, s.tan_fovy, focal_x, focal_y, gx, gy, s.prefiltered, radii, g);
+      s.tan_fovx, s.tan_fovy, focal_x, focal_y, gx, gy, s.prefiltered, radii, n_touched, im.cursor, g);
   B2GS_LAUNCH_CHECK(st, s.debug);
   return B2GS_OK;
 }

@@ -75,8 +75,50 @@ def _scene_struct(rs, P, M, means3D, sh, colors, opac, scales, rots, cov3D, keep
 
 class RasterState:
     """What the forward hands to the backward (the reference's three opaque byte
-    buffers + num_rendered, DGR/diff_gaussian_rasterization/__init__.py:102-104)."""
-    __slots__ = ("geom", "image", "binning", "num_rendered")
+    buffers + num_rendered, DGR/diff_gaussian_rasterization/__init__.py:102-104).
+    `num_rendered` is the binning capacity the backward must carve with: the exact
+    instance count in the default two-call mode, the workspace capacity in sync-free mode
+    (then `status` is the device [2] = (instances, overflow flag) the caller must check)."""
+    __slots__ = ("geom", "image", "binning", "num_rendered", "status", "key")
+
+    def __init__(self):
+        self.status = None
+        self.key = None
+
+
+class _SyncFree:
+    """Sync-free forward (b2gs_forward): no D2H read of the instance count, so the whole
+    render -> loss -> backward chain can be enqueued ahead of the GPU or captured in a CUDA
+    graph.  The binning workspace is sized from the last exactly-measured instance count of
+    the same (device, W, H, P) times `headroom`; the caller checks `check_overflow(states)`
+    once per step and re-runs the step if a view overflowed."""
+    enabled = False
+    headroom = 1.5
+    cap = {}
+
+
+def set_sync_free(enabled=True, headroom=1.5):
+    _SyncFree.enabled = bool(enabled)
+    _SyncFree.headroom = float(headroom)
+    if not enabled:
+        _SyncFree.cap.clear()
+
+
+def check_overflow(states):
+    """One host sync for a whole batch of forwards: returns True (and raises the stored
+    capacities) if any sync-free forward ran out of binning capacity — its outputs are
+    background-only and the step must be re-run."""
+    sts = [s for s in states if s is not None and s.status is not None]
+    if not sts:
+        return False
+    vals = torch.stack([s.status for s in sts]).cpu()
+    over = False
+    for s, v in zip(sts, vals.tolist()):
+        need = int(v[0] * _SyncFree.headroom) + 4096
+        if v[1]:
+            over = True
+            _SyncFree.cap[s.key] = max(_SyncFree.cap.get(s.key, 0), need)
+    return over
 
 
 def _forward_native(rs, means3D, sh, colors, opac, scales, rots, cov3D):
@@ -109,7 +151,19 @@ def _forward_native(rs, means3D, sh, colors, opac, scales, rots, cov3D):
         ws = _lib.B2gsWorkspace(st.geom.data_ptr(), st.geom.numel(), st.image.data_ptr(),
                                 st.image.numel(), None, 0)
         out = _lib.B2gsForwardOut(color.data_ptr(), depth.data_ptr(), opacity.data_ptr(),
-                                  radii.data_ptr(), n_touched.data_ptr())
+                                  radii.data_ptr(), n_touched.data_ptr(), None)
+        key = (dev.index, W, H, P)
+        cap = _SyncFree.cap.get(key) if _SyncFree.enabled else None
+        if cap is not None:
+            # sync-free: fixed-capacity binning workspace, status stays on the device
+            st.binning = torch.empty(lib.b2gs_binning_bytes(cap, W, H), dtype=torch.uint8, device=dev)
+            st.status = torch.empty(2, dtype=torch.int32, device=dev)
+            st.key = key
+            ws.binning, ws.binning_bytes = st.binning.data_ptr(), st.binning.numel()
+            out.status = st.status.data_ptr()
+            check(lib.b2gs_forward(C.byref(scene), C.byref(ws), C.byref(out), stream))
+            st.num_rendered = lib.b2gs_binning_capacity(st.binning.numel())
+            return st, color, radii, depth, opacity, n_touched
         R = C.c_int64(0)
         check(lib.b2gs_forward_plan(C.byref(scene), C.byref(ws), C.byref(out), stream, C.byref(R)))
         R = R.value
@@ -118,6 +172,8 @@ def _forward_native(rs, means3D, sh, colors, opac, scales, rots, cov3D):
         ws.binning, ws.binning_bytes = ptr(st.binning), st.binning.numel()
         check(lib.b2gs_forward_render(C.byref(scene), C.byref(ws), C.byref(out), R, stream))
         st.num_rendered = R
+        if _SyncFree.enabled:      # first call for this shape: measured exactly, remembered
+            _SyncFree.cap[key] = int(R * _SyncFree.headroom) + 4096
     return st, color, radii, depth, opacity, n_touched
 
 

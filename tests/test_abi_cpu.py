@@ -39,7 +39,10 @@ def test_sizes_monotone_and_aligned():
         assert b % 256 == 0 and b > prev
         prev = b
     assert lib.b2gs_image_bytes(1200, 680) >= 1200 * 680 * 8 + 3225 * 8
-    assert lib.b2gs_binning_bytes(1_000_000, 1200, 680) >= 16_000_000
+    assert lib.b2gs_binning_bytes(1_000_000, 1200, 680) >= 12_000_000
+    for R in (1, 1000, 1_273_075):            # capacity is the inverse of the size query
+        cap = lib.b2gs_binning_capacity(lib.b2gs_binning_bytes(R, 1200, 680))
+        assert R <= cap and lib.b2gs_binning_bytes(cap, 1200, 680) <= lib.b2gs_binning_bytes(R, 1200, 680) + 512
     assert lib.b2gs_backward_scratch_bytes(500_000) >= 500_000 * 48
     assert lib.b2gs_knn_bytes(2_000_000) > 2_000_000 * 16
 

@@ -160,3 +160,36 @@ def test_mark_visible_and_pose_only():
     torch.autograd.backward([color, depth], [gc, gd])
     tau = torch.cat([rho.grad.reshape(-1), theta.grad.reshape(-1)])
     assert_grad_close(tau, g_full["dL_dtau"], tol=1e-4, name="pose-only tau")
+
+
+def test_sync_free_forward_matches_exact_and_flags_overflow():
+    """b2gs_forward (capacity-based, no host sync) == the exact two-call form; a too-small
+    capacity raises the overflow flag, renders background only, and is healed by a retry."""
+    from monogs_dev_b200 import rasterizer as rz
+    sc, rs, inp, gc, gd = build_case("cfg2_tracking", device=DEV, bg=(0.1, 0.0, 0.2))
+    out0, g0 = run_native(rs, inp, gc, gd)
+    try:
+        rz.set_sync_free(True, headroom=1.25)
+        out1, g1 = run_native(rs, inp, gc, gd)            # first call measures exactly
+        assert out1["state"].status is None
+        out2, g2 = run_native(rs, inp, gc, gd)            # second call is sync-free
+        st = out2["state"]
+        assert st.status is not None and not rz.check_overflow([st])
+        assert int(st.status[0]) == out0["state"].num_rendered
+        for k in ("color", "depth", "opacity", "radii", "n_touched"):
+            assert torch.equal(out2[k], out0[k]), k
+        e0, e2 = export_native(rs, inp, out0["state"]), export_native(rs, inp, st)
+        R = out0["state"].num_rendered
+        assert torch.equal(e0["keys"][:R], e2["keys"][:R]) and torch.equal(e0["point_list"][:R], e2["point_list"][:R])
+        for k in g0:
+            assert_grad_close(g2[k], g0[k], tol=1e-4, name="sync-free " + k)
+        # starve the capacity
+        rz._SyncFree.cap[st.key] = 1000
+        out3, _ = run_native(rs, inp)
+        assert rz.check_overflow([out3["state"]])
+        assert torch.allclose(out3["color"][0], torch.full_like(out3["color"][0], 0.1))
+        assert rz._SyncFree.cap[st.key] > out0["state"].num_rendered
+        out4, _ = run_native(rs, inp)
+        assert not rz.check_overflow([out4["state"]]) and torch.equal(out4["color"], out0["color"])
+    finally:
+        rz.set_sync_free(False)
