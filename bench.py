@@ -245,13 +245,16 @@ def run(args):
         if not ref_ext.available():
             return run_reference_cpu(args, rank, world)
         render_fn, model_cls, adam_cls = ref_ext.ref_render, ref_ext.RefGaussianModel, torch.optim.Adam
+        loss_fn, graph = mapping.get_loss_mapping_rgbd_torch, False     # the reference's own torch-op loss
     else:
         render_fn, model_cls, adam_cls = mapping.render, mapping.GaussianModel, mapping.FusedAdam
+        loss_fn, graph = mapping.get_loss_mapping_rgbd, not args.no_graph
 
     sc = syn.make_scene(WORKLOAD, device=device, n_views=N_VIEWS)
     kfs, host = build_window(device, render_fn, model_cls, None, sc)
     gm = model_cls(sc.xyz, sc.f_dc, sc.f_rest, sc.opacity, sc.scaling, sc.rotation, sh_degree=sc.sh_degree)
-    win = mapping.MappingWindow(gm, kfs, sc.bg, render_fn=render_fn, adam_cls=adam_cls)
+    win = mapping.MappingWindow(gm, kfs, sc.bg, render_fn=render_fn, adam_cls=adam_cls, loss_fn=loss_fn,
+                                cuda_graph=graph)
     local_views = win.local
 
     def step():
@@ -263,12 +266,14 @@ def run(args):
             kfs[v]["gt_depth"].copy_(host[v][1], non_blocking=True)
         return float(win.step().item())            # result read back: device -> host
 
-    for _ in range(W_):
+    for _ in range(W_ + (4 if graph else 0)):      # graph mode: 3 eager sizing steps + the capture
         step()
     sampler = ClockSampler(local) if rank == 0 else None
     l0 = _lib.lib.b2gs_kernel_launches()
     ms = timed_steps(step, K, world)
     launches = _lib.lib.b2gs_kernel_launches() - l0
+    if graph:      # replays do not pass through the host-side counter: launches captured per step x K
+        launches = win.graph_launches * K
     clocks = sampler.stop() if sampler else {}
     ms = max_over_ranks(ms, world, device)
     launches = int(sum_over_ranks(launches, world, device))
@@ -280,8 +285,7 @@ def run(args):
     if world == 1:
         def one_view():
             pkg = render_fn(kfs[0]["cam"], gm, None, sc.bg)
-            mapping.get_loss_mapping_rgbd(pkg["render"], pkg["depth"], kfs[0]["cam"], kfs[0]["gt_image"],
-                                          kfs[0]["gt_depth"]).backward()
+            loss_fn(pkg["render"], pkg["depth"], kfs[0]["cam"], kfs[0]["gt_image"], kfs[0]["gt_depth"]).backward()
             gm.zero_grad()
             for t in (kfs[0]["cam"].cam_rot_delta, kfs[0]["cam"].cam_trans_delta,
                       kfs[0]["cam"].exposure_a, kfs[0]["cam"].exposure_b):
@@ -295,7 +299,7 @@ def run(args):
     if not impl_ref:
         # per-kernel durations: CUDA events on the launching stream, 2 extra (untimed) steps
         _lib.lib.b2gs_profile_enable(1)
-        step(); step()
+        win._eager_step(set_to_none=False); win._eager_step(set_to_none=False)   # eager: events per launch
         torch.cuda.synchronize()
         prof = _lib.profile_read()
         _lib.lib.b2gs_profile_enable(0)
@@ -347,6 +351,7 @@ def run(args):
         "config": {"workload": "cfg3_replica: 1200x680, 500k Gaussians, SH0, 8-keyframe mapping window "
                                "(fwd+bwd per keyframe, fused Adam, pose Adam)",
                    "keyframes": N_VIEWS, "parallelism": "keyframes sharded round-robin over %d rank(s)" % world,
+                   "launch": "cuda graphs (2 per step, one host sync)" if graph else "eager",
                    "l2_policy": "inputs larger than L2: >400 MB touched per step (8 GT frames 104 MB, "
                                 "4 parameter/moment arenas 112 MB, per-view workspaces+gradients) vs 126 MB L2",
                    **work},
@@ -391,6 +396,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="native arm: eager launches instead of CUDA graphs")
     args = ap.parse_args()
     if not torch.cuda.is_available():
         if args.impl == "reference":

@@ -198,9 +198,49 @@ B2GS_API int b2gs_knn3_dist2(const float* points, int32_t P, float* out, void* w
 typedef struct B2gsAdamSegment {
   float* param; const float* grad; float* exp_avg; float* exp_avg_sq;
   int64_t n; float lr;
+  const float* lr_dev; /* optional DEVICE scalar that overrides lr (b2gs_adam_step_dev only):
+                        * lets a captured graph follow a learning-rate schedule */
 } B2gsAdamSegment;
 B2GS_API int b2gs_adam_step(const B2gsAdamSegment* segments, int32_t num_segments, int64_t step,
                    float beta1, float beta2, float eps, void* stream);
+/* Same, CUDA-graph capturable: the step count is a DEVICE int64 that the call increments
+ * (on the stream) before using it, so a captured graph stays correct across replays. */
+B2GS_API int b2gs_adam_step_dev(const B2gsAdamSegment* segments, int32_t num_segments,
+                       int64_t* step_counter, float beta1, float beta2, float eps, void* stream);
+
+/* ---- fused per-pixel losses (utils/slam_utils.py:56-128) ---------------------------------
+ * mode: 0 mapping rgbd (get_loss_mapping_rgbd :113-128), 1 tracking rgbd (:74-88),
+ *       2 mapping rgb / monocular (:101-110), 3 tracking rgb / monocular (:64-72).
+ * image_ab = exp(exposure_a) * image + exposure_b (:57,95); NULL exposure pointers mean the
+ * `initialization` branch (image_ab = image, :92-93).  All pointers are device pointers. */
+typedef struct B2gsLossArgs {
+  int32_t N;                      /* pixels (H*W) */
+  int32_t mode;
+  float alpha;                    /* config Training.alpha, default 0.95 */
+  float rgb_boundary_threshold;   /* config Training.rgb_boundary_threshold */
+  const float* image;             /* [3,N] rendered colour */
+  const float* depth;             /* [N] rendered depth (rgbd modes) */
+  const float* opacity;           /* [N] rendered opacity (tracking modes) */
+  const float* gt_image;          /* [3,N] */
+  const float* gt_depth;          /* [N] (rgbd modes) */
+  const float* exposure_a;        /* [1] or NULL */
+  const float* exposure_b;        /* [1] or NULL */
+  const float* grad_mask;         /* [N] or NULL: viewpoint.grad_mask (tracking modes) */
+} B2gsLossArgs;
+B2GS_API size_t b2gs_loss_scratch_bytes(int32_t N);
+B2GS_API int b2gs_loss_forward(const B2gsLossArgs* args, float* loss, void* scratch,
+                      size_t scratch_bytes, void* stream);
+/* dL_dloss: device scalar or NULL (= 1).  dL_dopacity optional.  dL_dexposure[2] = (a, b). */
+B2GS_API int b2gs_loss_backward(const B2gsLossArgs* args, const float* dL_dloss, float* dL_dimage,
+                       float* dL_ddepth, float* dL_dopacity, float* dL_dexposure, void* scratch,
+                       size_t scratch_bytes, void* stream);
+
+/* update_pose (utils/pose_utils.py:76-93) on the device: T_w2c <- Exp((trans_delta, rot_delta))
+ * T_w2c; refreshes viewmatrix, full projection and camera centre in place, zeroes the deltas.
+ * cam_state: float[64] = R[9] row-major | T[3] | pad[4] | viewmatrix[16] | projmatrix[16] |
+ * campos[3] | pad.  tau_norm (optional, [1]) receives |tau| for the caller's convergence test. */
+B2GS_API int b2gs_pose_update(float* cam_state, const float* projmatrix_raw, float* rot_delta,
+                     float* trans_delta, float* tau_norm, void* stream);
 
 #ifdef __cplusplus
 }

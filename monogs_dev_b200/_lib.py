@@ -49,10 +49,20 @@ class B2gsBackwardIO(C.Structure):
     ]
 
 
+class B2gsLossArgs(C.Structure):
+    _fields_ = [
+        ("N", C.c_int32), ("mode", C.c_int32), ("alpha", C.c_float), ("rgb_boundary_threshold", C.c_float),
+        ("image", C.c_void_p), ("depth", C.c_void_p), ("opacity", C.c_void_p), ("gt_image", C.c_void_p),
+        ("gt_depth", C.c_void_p), ("exposure_a", C.c_void_p), ("exposure_b", C.c_void_p),
+        ("grad_mask", C.c_void_p),
+    ]
+
+
 class B2gsAdamSegment(C.Structure):
     _fields_ = [
         ("param", C.c_void_p), ("grad", C.c_void_p), ("exp_avg", C.c_void_p),
         ("exp_avg_sq", C.c_void_p), ("n", C.c_int64), ("lr", C.c_float),
+        ("lr_dev", C.c_void_p),
     ]
 
 
@@ -87,6 +97,13 @@ SYMBOLS = {
     "b2gs_knn_bytes": (C.c_size_t, [C.c_int32]),
     "b2gs_knn3_dist2": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_size_t,
                                   C.c_void_p]),
+    "b2gs_loss_scratch_bytes": (C.c_size_t, [C.c_int32]),
+    "b2gs_loss_forward": (C.c_int, [C.POINTER(B2gsLossArgs), C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "b2gs_loss_backward": (C.c_int, [C.POINTER(B2gsLossArgs), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                     C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "b2gs_pose_update": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "b2gs_adam_step_dev": (C.c_int, [C.POINTER(B2gsAdamSegment), C.c_int32, C.c_void_p, C.c_float,
+                                     C.c_float, C.c_float, C.c_void_p]),
     "b2gs_adam_step": (C.c_int, [C.POINTER(B2gsAdamSegment), C.c_int32, C.c_int64, C.c_float,
                                  C.c_float, C.c_float, C.c_void_p]),
 }

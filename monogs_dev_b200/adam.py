@@ -18,10 +18,29 @@ from ._lib import lib, check
 
 
 class FusedAdam(torch.optim.Optimizer):
-    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8):
+    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, capturable=False):
+        """capturable=True keeps ONE step counter per optimizer on the device
+        (b2gs_adam_step_dev) so that step() can be captured in a CUDA graph and replayed;
+        learning rates are then baked into the captured launch."""
         if lr < 0.0 or eps < 0.0:
             raise ValueError("invalid lr / eps")
         super().__init__(params, dict(lr=lr, betas=betas, eps=eps))
+        self.capturable = bool(capturable)
+        self._step_dev = None
+        self._lr_dev = None
+        self._lr_host = None
+
+    def sync_lr(self):
+        """capturable mode: push the current param_group learning rates to the device array the
+        captured kernel reads (call after changing param_group["lr"]; no-op if unchanged)."""
+        lrs = tuple(float(g["lr"]) for g in self.param_groups)
+        if not self.capturable or lrs == self._lr_host:
+            return
+        dev = self.param_groups[0]["params"][0].device
+        if self._lr_dev is None or self._lr_dev.numel() != len(lrs):
+            self._lr_dev = torch.zeros(len(lrs), dtype=torch.float32, device=dev)
+        self._lr_dev.copy_(torch.tensor(lrs, dtype=torch.float32), non_blocking=False)
+        self._lr_host = lrs
 
     @torch.no_grad()
     def step(self, closure=None):
@@ -31,7 +50,9 @@ class FusedAdam(torch.optim.Optimizer):
                 loss = closure()
         # group by (device, step, betas, eps): one launch per distinct combination
         buckets = {}
-        for group in self.param_groups:
+        if self.capturable and not torch.cuda.is_current_stream_capturing():
+            self.sync_lr()
+        for gi, group in enumerate(self.param_groups):
             beta1, beta2 = group["betas"]
             for p in group["params"]:
                 if p.grad is None:
@@ -49,20 +70,32 @@ class FusedAdam(torch.optim.Optimizer):
                 step = int(step.item()) if isinstance(step, torch.Tensor) else int(step)
                 step += 1
                 state["step"] = step
+                if self.capturable:
+                    step = -1          # one device-side counter for the whole optimizer
                 g = p.grad if p.grad.is_contiguous() else p.grad.contiguous()
                 key = (p.device, step, float(beta1), float(beta2), float(group["eps"]))
                 buckets.setdefault(key, []).append(
-                    (p, g, state["exp_avg"], state["exp_avg_sq"], float(group["lr"])))
+                    (p, g, state["exp_avg"], state["exp_avg_sq"], float(group["lr"]), gi))
         for (dev, step, beta1, beta2, eps), items in buckets.items():
             items = [it for it in items if it[0].numel() > 0]
             if not items:
                 continue
             segs = (_lib.B2gsAdamSegment * len(items))()
-            for s, (p, g, m, v, lr) in zip(segs, items):
+            for s, (p, g, m, v, lr, gi) in zip(segs, items):
                 s.param, s.grad, s.exp_avg, s.exp_avg_sq = (p.data_ptr(), g.data_ptr(),
                                                             m.data_ptr(), v.data_ptr())
                 s.n, s.lr = p.numel(), lr
+                if self.capturable and self._lr_dev is not None:
+                    s.lr_dev = self._lr_dev.data_ptr() + 4 * gi
             with torch.cuda.device(dev):
-                check(lib.b2gs_adam_step(segs, len(items), step, beta1, beta2, eps,
-                                         torch.cuda.current_stream().cuda_stream))
+                stream = torch.cuda.current_stream().cuda_stream
+                if self.capturable:
+                    if len(buckets) != 1:
+                        raise RuntimeError("capturable FusedAdam needs one (betas, eps) for all groups")
+                    if self._step_dev is None:
+                        self._step_dev = torch.zeros(1, dtype=torch.int64, device=dev)
+                    check(lib.b2gs_adam_step_dev(segs, len(items), self._step_dev.data_ptr(), beta1,
+                                                 beta2, eps, stream))
+                else:
+                    check(lib.b2gs_adam_step(segs, len(items), step, beta1, beta2, eps, stream))
         return loss

@@ -24,6 +24,8 @@ struct AdamTable {
   long long n[ADAM_MAX_SEG];
   long long first_chunk[ADAM_MAX_SEG + 1];
   float neg_step_size[ADAM_MAX_SEG];
+  float lr[ADAM_MAX_SEG];
+  const float* lr_dev[ADAM_MAX_SEG];
   int num;
 };
 
@@ -37,7 +39,7 @@ __device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, 
 
 __global__ void __launch_bounds__(256)
 adam_kernel(const __grid_constant__ AdamTable t, float w1, float beta2, float w2, float bc2_sqrt,
-            float eps) {
+            float eps, float beta1, const long long* __restrict__ step_dev) {
   // which segment does this block's chunk belong to?
   int s = 0;
   const long long chunk = blockIdx.x;
@@ -51,7 +53,16 @@ adam_kernel(const __grid_constant__ AdamTable t, float w1, float beta2, float w2
   const float* __restrict__ g = t.g[s];
   float* __restrict__ m = t.m[s];
   float* __restrict__ v = t.v[s];
-  const float neg_step = t.neg_step_size[s];
+  float neg_step = t.neg_step_size[s];
+  if (step_dev != nullptr) {
+    // CUDA-graph capturable form: the step count lives on the device (incremented by
+    // adam_tick_kernel just before); same double-precision scalar prep as the host path
+    const double step = (double)*step_dev;
+    const double bc1 = 1.0 - pow((double)beta1, step);
+    bc2_sqrt = (float)sqrt(1.0 - pow((double)beta2, step));
+    const float lr = t.lr_dev[s] ? t.lr_dev[s][0] : t.lr[s];
+    neg_step = (float)(-((double)lr / bc1));
+  }
 
   const bool vec = ((((uintptr_t)p | (uintptr_t)g | (uintptr_t)m | (uintptr_t)v) & 15) == 0);
   if (vec) {
@@ -83,18 +94,24 @@ adam_kernel(const __grid_constant__ AdamTable t, float w1, float beta2, float w2
   }
 }
 
+__global__ void adam_tick_kernel(long long* step) { *step += 1; }
+
 }  // namespace b2gs
 
 using namespace b2gs;
 
-extern "C" int b2gs_adam_step(const B2gsAdamSegment* segments, int32_t num_segments, int64_t step,
-                              float beta1, float beta2, float eps, void* stream) {
+static int adam_impl(const B2gsAdamSegment* segments, int32_t num_segments, int64_t step,
+                     long long* step_dev, float beta1, float beta2, float eps, void* stream) {
   if (num_segments < 0 || (num_segments > 0 && !segments)) {
     set_error("b2gs_adam_step: bad segments");
     return B2GS_ERR_INVALID;
   }
   if (step < 1) { set_error("b2gs_adam_step: step must be >= 1"); return B2GS_ERR_INVALID; }
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (step_dev) {
+    adam_tick_kernel<<<1, 1, 0, st>>>(step_dev);
+    B2GS_LAUNCH_CHECK(st, 0);
+  }
   // scalar prep in double, as torch does in Python (torch/optim/adam.py)
   const double bc1 = 1.0 - pow((double)beta1, (double)step);
   const double bc2 = 1.0 - pow((double)beta2, (double)step);
@@ -118,16 +135,31 @@ extern "C" int b2gs_adam_step(const B2gsAdamSegment* segments, int32_t num_segme
       t.first_chunk[k] = chunks;
       chunks += (sgm.n + ADAM_CHUNK - 1) / ADAM_CHUNK;
       t.neg_step_size[k] = (float)(-((double)sgm.lr / bc1));
+      t.lr[k] = sgm.lr;
+      t.lr_dev[k] = step_dev ? sgm.lr_dev : nullptr;
     }
     t.first_chunk[k] = chunks;
     t.num = k;
     if (chunks > 0) {
       if (chunks > 0x7fffffffLL) { set_error("b2gs_adam_step: too many elements"); return B2GS_ERR_INVALID; }
       B2GS_PROF("adam", st);
-      adam_kernel<<<(unsigned)chunks, 256, 0, st>>>(t, w1, beta2, w2, bc2_sqrt, eps);
+      adam_kernel<<<(unsigned)chunks, 256, 0, st>>>(t, w1, beta2, w2, bc2_sqrt, eps, beta1, step_dev);
       B2GS_LAUNCH_CHECK(st, 0);
     }
     done += k;
   }
   return B2GS_OK;
+}
+
+extern "C" int b2gs_adam_step(const B2gsAdamSegment* segments, int32_t num_segments, int64_t step,
+                              float beta1, float beta2, float eps, void* stream) {
+  return adam_impl(segments, num_segments, step, nullptr, beta1, beta2, eps, stream);
+}
+
+extern "C" int b2gs_adam_step_dev(const B2gsAdamSegment* segments, int32_t num_segments,
+                                  int64_t* step_counter, float beta1, float beta2, float eps,
+                                  void* stream) {
+  if (!step_counter) { set_error("b2gs_adam_step_dev: NULL step counter"); return B2GS_ERR_INVALID; }
+  return adam_impl(segments, num_segments, 1, reinterpret_cast<long long*>(step_counter), beta1,
+                   beta2, eps, stream);
 }

@@ -1,0 +1,359 @@
+// loss.cu — the per-pixel side of one mapping / tracking iteration as two HBM-bound
+// kernels, and the SE(3) pose update as one tiny kernel.
+//
+// Replaces the ~15 elementwise / reduction torch kernels per view of
+//   get_loss_mapping(_rgb|_rgbd)    utils/slam_utils.py:91-128
+//   get_loss_tracking(_rgb|_rgbd)   utils/slam_utils.py:56-88
+// (exposure affine exp(a)*image+b, rgb boundary mask, depth mask, opacity weighting,
+// masked L1, two means, alpha blend) and, in backward, autograd's replay of them.
+// Forward reads 32-36 B/pixel and writes one scalar; backward reads the same and writes
+// dL/dimage, dL/ddepth (16 B/pixel) plus the exposure gradients.
+//
+// Also update_pose (utils/pose_utils.py:76-93): T_w2c <- Exp(tau) T_w2c entirely on the
+// device, refreshing the view / full-projection matrices and the camera centre in place,
+// so that a whole optimisation step is CUDA-graph capturable (no .cpu() round trip).
+#include "common.cuh"
+
+namespace b2gs {
+
+constexpr int LOSS_THREADS = 256;
+constexpr int LOSS_MAX_BLOCKS = 148 * 8;
+
+struct PixelTerms {
+  float d[3];   // image_ab*mask - gt*mask per channel (0 where masked)
+  float dd;     // depth*mask - gt_depth*mask
+  float o;      // opacity weight of the rgb term (1 in mapping)
+  float m;      // rgb mask (0/1), incl. grad_mask in tracking
+  float md;     // depth mask (0/1)
+};
+
+__device__ __forceinline__ float sgnf(float x) { return (float)(x > 0.f) - (float)(x < 0.f); }
+
+// mode bit 0: tracking (opacity weighting, opacity>0.95 depth mask, grad_mask); bit 1: monocular
+__device__ __forceinline__ PixelTerms pixel_terms(const B2gsLossArgs& a, float ea, float eb, int i) {
+  PixelTerms t;
+  const size_t N = (size_t)a.N;
+  const float g0 = a.gt_image[i], g1 = a.gt_image[N + i], g2 = a.gt_image[2 * N + i];
+  // gt_image.sum(dim=0) > threshold  (torch sums channel 0 + 1 + 2 in this order)
+  float m = ((g0 + g1) + g2) > a.rgb_boundary_threshold ? 1.f : 0.f;
+  const bool tracking = a.mode & 1;
+  float op = 1.f;
+  if (tracking) {
+    op = a.opacity[i];
+    if (a.grad_mask) m *= a.grad_mask[i];
+  }
+  t.m = m;
+  t.o = op;
+  const float i0 = ea * a.image[i] + eb, i1 = ea * a.image[N + i] + eb, i2 = ea * a.image[2 * N + i] + eb;
+  t.d[0] = i0 * m - g0 * m;
+  t.d[1] = i1 * m - g1 * m;
+  t.d[2] = i2 * m - g2 * m;
+  t.md = 0.f;
+  t.dd = 0.f;
+  if (!(a.mode & 2)) {
+    const float gd = a.gt_depth[i];
+    float md = gd > 0.01f ? 1.f : 0.f;
+    if (tracking) md *= (op > 0.95f ? 1.f : 0.f);
+    t.md = md;
+    t.dd = a.depth[i] * md - gd * md;
+  }
+  return t;
+}
+
+__device__ __forceinline__ float block_sum(float v, float* s_red) {
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  __syncthreads();
+  if (lane == 0) s_red[warp] = v;
+  __syncthreads();
+  float r = 0.f;
+  if (warp == 0) {
+    r = lane < LOSS_THREADS / 32 ? s_red[lane] : 0.f;
+#pragma unroll
+    for (int d = 4; d > 0; d >>= 1) r += __shfl_xor_sync(0xffffffffu, r, d);
+  }
+  return r;  // valid in thread 0
+}
+
+__device__ __forceinline__ void exposure(const B2gsLossArgs& a, float& ea, float& eb) {
+  ea = a.exposure_a ? expf(a.exposure_a[0]) : 1.f;
+  eb = a.exposure_b ? a.exposure_b[0] : 0.f;
+}
+
+// per-block partials: [0] sum |rgb term|, [1] sum |depth term|
+__global__ void __launch_bounds__(LOSS_THREADS)
+loss_fwd_kernel(const __grid_constant__ B2gsLossArgs a, float* __restrict__ partial) {
+  __shared__ float s_red[LOSS_THREADS / 32];
+  float ea, eb;
+  exposure(a, ea, eb);
+  float rgb = 0.f, dep = 0.f;
+  for (int i = blockIdx.x * LOSS_THREADS + threadIdx.x; i < a.N; i += gridDim.x * LOSS_THREADS) {
+    const PixelTerms t = pixel_terms(a, ea, eb, i);
+    rgb += t.o * (fabsf(t.d[0]) + fabsf(t.d[1]) + fabsf(t.d[2]));
+    dep += fabsf(t.dd);
+  }
+  rgb = block_sum(rgb, s_red);
+  dep = block_sum(dep, s_red);
+  if (threadIdx.x == 0) {
+    partial[2 * blockIdx.x] = rgb;
+    partial[2 * blockIdx.x + 1] = dep;
+  }
+}
+
+// one block: fixed-order (deterministic) sum of the per-block partials in double
+__global__ void __launch_bounds__(LOSS_THREADS)
+loss_fwd_finalize_kernel(int blocks, int N, float alpha, int mono, const float* __restrict__ partial,
+                         float* __restrict__ loss) {
+  __shared__ double s_a[LOSS_THREADS], s_b[LOSS_THREADS];
+  double ra = 0.0, rb = 0.0;
+  for (int i = threadIdx.x; i < blocks; i += LOSS_THREADS) {
+    ra += partial[2 * i];
+    rb += partial[2 * i + 1];
+  }
+  s_a[threadIdx.x] = ra;
+  s_b[threadIdx.x] = rb;
+  __syncthreads();
+  for (int d = LOSS_THREADS / 2; d > 0; d >>= 1) {
+    if (threadIdx.x < d) {
+      s_a[threadIdx.x] += s_a[threadIdx.x + d];
+      s_b[threadIdx.x] += s_b[threadIdx.x + d];
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    const double l_rgb = s_a[0] / (3.0 * (double)N), l_dep = s_b[0] / (double)N;
+    // monocular: l1.mean() alone (utils/slam_utils.py:72,109); rgbd: alpha blend (:88,128)
+    loss[0] = mono ? (float)l_rgb : (float)((double)alpha * l_rgb + (1.0 - (double)alpha) * l_dep);
+  }
+}
+
+// per-block partials: [0] dL/d exposure_a, [1] dL/d exposure_b
+__global__ void __launch_bounds__(LOSS_THREADS)
+loss_bwd_kernel(const __grid_constant__ B2gsLossArgs a, const float* __restrict__ upstream,
+                float* __restrict__ dL_dimage, float* __restrict__ dL_ddepth,
+                float* __restrict__ dL_dopacity, float* __restrict__ partial) {
+  __shared__ float s_red[LOSS_THREADS / 32];
+  float ea, eb;
+  exposure(a, ea, eb);
+  const float up = upstream ? upstream[0] : 1.f;
+  const bool mono = a.mode & 2;
+  const float w_rgb = up * (mono ? 1.f : a.alpha) / (3.0f * (float)a.N);
+  const float w_dep = mono ? 0.f : up * (1.f - a.alpha) / (float)a.N;
+  const size_t N = (size_t)a.N;
+  float ga = 0.f, gb = 0.f;
+  for (int i = blockIdx.x * LOSS_THREADS + threadIdx.x; i < a.N; i += gridDim.x * LOSS_THREADS) {
+    const PixelTerms t = pixel_terms(a, ea, eb, i);
+    float absum = 0.f;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      // d|x|/dx * d(image_ab*m)/d(image_ab) = sign * m ; image_ab = ea*image + eb
+      const float g_ab = w_rgb * t.o * sgnf(t.d[c]) * t.m;
+      const float img = a.image[c * N + i];
+      dL_dimage[c * N + i] = g_ab * ea;
+      ga += g_ab * img;
+      gb += g_ab;
+      absum += fabsf(t.d[c]);
+    }
+    dL_ddepth[i] = w_dep * sgnf(t.dd) * t.md;
+    if (dL_dopacity) dL_dopacity[i] = (a.mode & 1) ? w_rgb * absum : 0.f;
+  }
+  ga = block_sum(ga, s_red);
+  gb = block_sum(gb, s_red);
+  if (threadIdx.x == 0) {
+    partial[2 * blockIdx.x] = ga * ea;  // d exp(a)/da = exp(a)
+    partial[2 * blockIdx.x + 1] = gb;
+  }
+}
+
+__global__ void __launch_bounds__(LOSS_THREADS)
+loss_bwd_finalize_kernel(int blocks, const float* __restrict__ partial, float* __restrict__ dL_dexp) {
+  __shared__ double s_a[LOSS_THREADS], s_b[LOSS_THREADS];
+  double ra = 0.0, rb = 0.0;
+  for (int i = threadIdx.x; i < blocks; i += LOSS_THREADS) {
+    ra += partial[2 * i];
+    rb += partial[2 * i + 1];
+  }
+  s_a[threadIdx.x] = ra;
+  s_b[threadIdx.x] = rb;
+  __syncthreads();
+  for (int d = LOSS_THREADS / 2; d > 0; d >>= 1) {
+    if (threadIdx.x < d) {
+      s_a[threadIdx.x] += s_a[threadIdx.x + d];
+      s_b[threadIdx.x] += s_b[threadIdx.x + d];
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    dL_dexp[0] = (float)s_a[0];
+    dL_dexp[1] = (float)s_b[0];
+  }
+}
+
+static inline int loss_blocks(int N) {
+  int b = (N + LOSS_THREADS - 1) / LOSS_THREADS;
+  return b < 1 ? 1 : (b > LOSS_MAX_BLOCKS ? LOSS_MAX_BLOCKS : b);
+}
+
+static int check_loss(const B2gsLossArgs* a) {
+  if (!a) { set_error("loss: NULL args"); return B2GS_ERR_INVALID; }
+  if (a->N <= 0) { set_error("loss: N must be > 0"); return B2GS_ERR_INVALID; }
+  if (a->mode < 0 || a->mode > 3) { set_error("loss: bad mode %d", a->mode); return B2GS_ERR_INVALID; }
+  if (!a->image || !a->gt_image) { set_error("loss: image / gt_image are NULL"); return B2GS_ERR_INVALID; }
+  if (!(a->mode & 2) && (!a->depth || !a->gt_depth)) { set_error("loss: depth / gt_depth are NULL"); return B2GS_ERR_INVALID; }
+  if ((a->mode & 1) && !a->opacity) { set_error("loss: tracking needs opacity"); return B2GS_ERR_INVALID; }
+  return B2GS_OK;
+}
+
+}  // namespace b2gs
+
+using namespace b2gs;
+
+extern "C" size_t b2gs_loss_scratch_bytes(int32_t N) {
+  (void)N;
+  return align_up((size_t)LOSS_MAX_BLOCKS * 2 * sizeof(float), 256);
+}
+
+extern "C" int b2gs_loss_forward(const B2gsLossArgs* args, float* loss, void* scratch,
+                                 size_t scratch_bytes, void* stream) {
+  int rc = check_loss(args);
+  if (rc) return rc;
+  if (!loss || !scratch || scratch_bytes < b2gs_loss_scratch_bytes(args->N)) {
+    set_error("loss: NULL output or scratch too small");
+    return B2GS_ERR_WORKSPACE;
+  }
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const int blocks = loss_blocks(args->N);
+  float* partial = reinterpret_cast<float*>(scratch);
+  {
+    B2GS_PROF("loss_fwd", st);
+    loss_fwd_kernel<<<blocks, LOSS_THREADS, 0, st>>>(*args, partial);
+    B2GS_LAUNCH_CHECK(st, 0);
+  }
+  loss_fwd_finalize_kernel<<<1, LOSS_THREADS, 0, st>>>(blocks, args->N, args->alpha,
+                                                       (args->mode & 2) ? 1 : 0, partial, loss);
+  B2GS_LAUNCH_CHECK(st, 0);
+  return B2GS_OK;
+}
+
+extern "C" int b2gs_loss_backward(const B2gsLossArgs* args, const float* dL_dloss, float* dL_dimage,
+                                  float* dL_ddepth, float* dL_dopacity, float* dL_dexposure,
+                                  void* scratch, size_t scratch_bytes, void* stream) {
+  int rc = check_loss(args);
+  if (rc) return rc;
+  if (!dL_dimage || !dL_ddepth || !dL_dexposure || !scratch ||
+      scratch_bytes < b2gs_loss_scratch_bytes(args->N)) {
+    set_error("loss backward: NULL output or scratch too small");
+    return B2GS_ERR_WORKSPACE;
+  }
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const int blocks = loss_blocks(args->N);
+  float* partial = reinterpret_cast<float*>(scratch);
+  {
+    B2GS_PROF("loss_bwd", st);
+    loss_bwd_kernel<<<blocks, LOSS_THREADS, 0, st>>>(*args, dL_dloss, dL_dimage, dL_ddepth,
+                                                     dL_dopacity, partial);
+    B2GS_LAUNCH_CHECK(st, 0);
+  }
+  loss_bwd_finalize_kernel<<<1, LOSS_THREADS, 0, st>>>(blocks, partial, dL_dexposure);
+  B2GS_LAUNCH_CHECK(st, 0);
+  return B2GS_OK;
+}
+
+// ---- pose update ---------------------------------------------------------------------
+namespace b2gs {
+
+// state: [0:9] R row-major, [9:12] T, [16:32] viewmatrix, [32:48] full projection,
+// [48:51] camera centre.  One thread: the arithmetic is ~200 flops.
+__global__ void pose_update_kernel(float* __restrict__ state, const float* __restrict__ proj,
+                                   float* __restrict__ rot_delta, float* __restrict__ trans_delta,
+                                   float* __restrict__ tau_norm) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  const float th[3] = {rot_delta[0], rot_delta[1], rot_delta[2]};
+  const float rho[3] = {trans_delta[0], trans_delta[1], trans_delta[2]};
+  // skew(theta), its square (utils/pose_utils.py:12-22)
+  const float Wm[3][3] = {{0.f, -th[2], th[1]}, {th[2], 0.f, -th[0]}, {-th[1], th[0], 0.f}};
+  float W2[3][3];
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) {
+      float s = 0.f;
+      for (int k = 0; k < 3; ++k) s += Wm[i][k] * Wm[k][j];
+      W2[i][j] = s;
+    }
+  const float angle = sqrtf(th[0] * th[0] + th[1] * th[1] + th[2] * th[2]);
+  float ra, rb, va, vb;  // R = I + ra W + rb W2 ; V = I + va W + vb W2  (:25-58)
+  if (angle < 1e-5f) {
+    ra = 1.f; rb = 0.5f; va = 0.5f; vb = 1.0f / 6.0f;
+  } else {
+    const float s = sinf(angle), c = cosf(angle);
+    ra = s / angle;
+    rb = (1.f - c) / (angle * angle);
+    va = (1.0f - c) / (angle * angle);
+    vb = (angle - s) / (angle * angle * angle);
+  }
+  float dR[3][3], V[3][3];
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) {
+      const float I = i == j ? 1.f : 0.f;
+      dR[i][j] = I + ra * Wm[i][j] + rb * W2[i][j];
+      V[i][j] = I + va * Wm[i][j] + vb * W2[i][j];
+    }
+  float t[3];
+  for (int i = 0; i < 3; ++i) t[i] = V[i][0] * rho[0] + V[i][1] * rho[1] + V[i][2] * rho[2];
+  // new_w2c = Exp(tau) @ T_w2c  (:76-93)
+  float R[3][3], T[3], nR[3][3], nT[3];
+  for (int i = 0; i < 3; ++i) {
+    for (int j = 0; j < 3; ++j) R[i][j] = state[3 * i + j];
+    T[i] = state[9 + i];
+  }
+  for (int i = 0; i < 3; ++i) {
+    for (int j = 0; j < 3; ++j) nR[i][j] = dR[i][0] * R[0][j] + dR[i][1] * R[1][j] + dR[i][2] * R[2][j];
+    nT[i] = dR[i][0] * T[0] + dR[i][1] * T[1] + dR[i][2] * T[2] + t[i];
+  }
+  for (int i = 0; i < 3; ++i) {
+    for (int j = 0; j < 3; ++j) state[3 * i + j] = nR[i][j];
+    state[9 + i] = nT[i];
+  }
+  // viewmatrix = w2c^T stored row-major: view[4*c + r] = w2c[r][c] (utils/camera_utils.py:94-96)
+  float view[16];
+  for (int r = 0; r < 3; ++r) {
+    for (int c = 0; c < 3; ++c) view[4 * c + r] = nR[r][c];
+    view[12 + r] = nT[r];
+  }
+  view[3] = view[7] = view[11] = 0.f;
+  view[15] = 1.f;
+  for (int i = 0; i < 16; ++i) state[16 + i] = view[i];
+  // full_proj = view @ proj as stored (utils/camera_utils.py:98-104)
+  for (int i = 0; i < 4; ++i)
+    for (int j = 0; j < 4; ++j) {
+      float s = 0.f;
+      for (int k = 0; k < 4; ++k) s += view[4 * i + k] * proj[4 * k + j];
+      state[32 + 4 * i + j] = s;
+    }
+  // camera centre = inverse(view)[3,:3] = -R^T T (utils/camera_utils.py:106-107)
+  for (int j = 0; j < 3; ++j)
+    state[48 + j] = -(nR[0][j] * nT[0] + nR[1][j] * nT[1] + nR[2][j] * nT[2]);
+  if (tau_norm) {
+    float n2 = 0.f;
+    for (int i = 0; i < 3; ++i) n2 += th[i] * th[i] + rho[i] * rho[i];
+    tau_norm[0] = sqrtf(n2);  // converged = tau.norm() < threshold, evaluated by the caller
+  }
+  for (int i = 0; i < 3; ++i) {
+    rot_delta[i] = 0.f;
+    trans_delta[i] = 0.f;
+  }
+}
+
+}  // namespace b2gs
+
+extern "C" int b2gs_pose_update(float* cam_state, const float* projmatrix_raw, float* rot_delta,
+                                float* trans_delta, float* tau_norm, void* stream) {
+  if (!cam_state || !projmatrix_raw || !rot_delta || !trans_delta) {
+    set_error("b2gs_pose_update: NULL pointer");
+    return B2GS_ERR_INVALID;
+  }
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  pose_update_kernel<<<1, 32, 0, st>>>(cam_state, projmatrix_raw, rot_delta, trans_delta, tau_norm);
+  B2GS_LAUNCH_CHECK(st, 0);
+  return B2GS_OK;
+}

@@ -1,0 +1,118 @@
+"""Fused per-pixel losses of the mapping / tracking loops, backed by libb2gs (csrc/loss.cu).
+
+Same math, names and argument meaning as the reference's utils/slam_utils.py:
+  get_loss_mapping(config, image, depth, viewpoint, opacity, initialization)   :91-99
+  get_loss_mapping_rgb / get_loss_mapping_rgbd                                  :101-128
+  get_loss_tracking(config, image, depth, opacity, viewpoint)                   :56-61
+  get_loss_tracking_rgb / get_loss_tracking_rgbd                                :64-88
+but ONE forward kernel (+ a one-block finalize) instead of ~15 torch kernels, and ONE
+backward kernel producing dL/dimage, dL/ddepth, dL/dopacity and the exposure gradients.
+No CPU path: CPU tensors raise.
+"""
+import ctypes as C
+
+import torch
+
+from . import _lib
+from ._lib import lib, check, ptr
+
+MAPPING_RGBD, TRACKING_RGBD, MAPPING_RGB, TRACKING_RGB = 0, 1, 2, 3
+
+
+def _args(mode, alpha, thr, image, depth, opacity, gt_image, gt_depth, exp_a, exp_b, grad_mask):
+    a = _lib.B2gsLossArgs()
+    a.N = image.shape[-1] * image.shape[-2]
+    a.mode, a.alpha, a.rgb_boundary_threshold = mode, float(alpha), float(thr)
+    a.image, a.depth, a.opacity = ptr(image), ptr(depth), ptr(opacity)
+    a.gt_image, a.gt_depth = ptr(gt_image), ptr(gt_depth)
+    a.exposure_a, a.exposure_b, a.grad_mask = ptr(exp_a), ptr(exp_b), ptr(grad_mask)
+    return a
+
+
+def _c(t, name):
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor: libb2gs has no CPU path")
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t.contiguous()
+
+
+class _FusedLoss(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, image, depth, opacity, exp_a, exp_b, gt_image, gt_depth, grad_mask, mode, alpha, thr):
+        image, depth, opacity = _c(image, "image"), _c(depth, "depth"), _c(opacity, "opacity")
+        gt_image, gt_depth, grad_mask = _c(gt_image, "gt_image"), _c(gt_depth, "gt_depth"), _c(grad_mask, "grad_mask")
+        exp_a, exp_b = _c(exp_a, "exposure_a"), _c(exp_b, "exposure_b")
+        dev = image.device
+        with torch.cuda.device(dev):
+            loss = torch.empty((), dtype=torch.float32, device=dev)
+            n = image.shape[-1] * image.shape[-2]
+            scratch = torch.empty(lib.b2gs_loss_scratch_bytes(n), dtype=torch.uint8, device=dev)
+            a = _args(mode, alpha, thr, image, depth, opacity, gt_image, gt_depth, exp_a, exp_b, grad_mask)
+            check(lib.b2gs_loss_forward(C.byref(a), loss.data_ptr(), scratch.data_ptr(), scratch.numel(),
+                                        torch.cuda.current_stream().cuda_stream))
+        e = lambda t: t if t is not None else torch.empty(0, device=dev)
+        ctx.save_for_backward(image, e(depth), e(opacity), e(exp_a), e(exp_b), gt_image, e(gt_depth),
+                              e(grad_mask))
+        ctx.cfg = (mode, alpha, thr)
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        image, depth, opacity, exp_a, exp_b, gt_image, gt_depth, grad_mask = \
+            [t if t.numel() else None for t in ctx.saved_tensors]
+        mode, alpha, thr = ctx.cfg
+        dev = image.device
+        with torch.cuda.device(dev):
+            g = g.contiguous().float()
+            d_image = torch.empty_like(image)
+            n = image.shape[-1] * image.shape[-2]
+            d_depth = torch.empty(depth.shape if depth is not None else (1,) + tuple(image.shape[-2:]),
+                                  dtype=torch.float32, device=dev)
+            want_op = opacity is not None and ctx.needs_input_grad[2]
+            d_op = torch.empty_like(opacity) if want_op else None
+            d_exp = torch.empty(2, dtype=torch.float32, device=dev)
+            scratch = torch.empty(lib.b2gs_loss_scratch_bytes(n), dtype=torch.uint8, device=dev)
+            a = _args(mode, alpha, thr, image, depth, opacity, gt_image, gt_depth, exp_a, exp_b, grad_mask)
+            check(lib.b2gs_loss_backward(C.byref(a), g.data_ptr(), d_image.data_ptr(), d_depth.data_ptr(),
+                                         ptr(d_op), d_exp.data_ptr(), scratch.data_ptr(), scratch.numel(),
+                                         torch.cuda.current_stream().cuda_stream))
+        return (d_image, d_depth if depth is not None else None, d_op,
+                d_exp[0:1] if exp_a is not None else None, d_exp[1:2] if exp_b is not None else None,
+                None, None, None, None, None, None)
+
+
+def fused_loss(mode, image, depth, opacity, exposure_a, exposure_b, gt_image, gt_depth, grad_mask=None,
+               alpha=0.95, rgb_boundary_threshold=0.01):
+    return _FusedLoss.apply(image, depth, opacity, exposure_a, exposure_b, gt_image, gt_depth, grad_mask,
+                            int(mode), float(alpha), float(rgb_boundary_threshold))
+
+
+def get_loss_mapping_rgbd(image, depth, viewpoint, gt_image, gt_depth, alpha=0.95,
+                          rgb_boundary_threshold=0.01, initialization=False):
+    """utils/slam_utils.py:91-99,113-128; `image` is the raw render (the exposure affine is fused)."""
+    ea, eb = (None, None) if initialization else (viewpoint.exposure_a, viewpoint.exposure_b)
+    return fused_loss(MAPPING_RGBD, image, depth, None, ea, eb, gt_image, gt_depth, None, alpha,
+                      rgb_boundary_threshold)
+
+
+def get_loss_mapping_rgb(image, viewpoint, gt_image, rgb_boundary_threshold=0.01, initialization=False):
+    """utils/slam_utils.py:91-110 (monocular)."""
+    ea, eb = (None, None) if initialization else (viewpoint.exposure_a, viewpoint.exposure_b)
+    return fused_loss(MAPPING_RGB, image, None, None, ea, eb, gt_image, None, None, 0.95,
+                      rgb_boundary_threshold)
+
+
+def get_loss_tracking_rgbd(image, depth, opacity, viewpoint, gt_image, gt_depth, alpha=0.95,
+                           rgb_boundary_threshold=0.01, grad_mask=None):
+    """utils/slam_utils.py:56-61,74-88."""
+    return fused_loss(TRACKING_RGBD, image, depth, opacity, viewpoint.exposure_a, viewpoint.exposure_b,
+                      gt_image, gt_depth, grad_mask, alpha, rgb_boundary_threshold)
+
+
+def get_loss_tracking_rgb(image, opacity, viewpoint, gt_image, rgb_boundary_threshold=0.01, grad_mask=None):
+    """utils/slam_utils.py:56-72 (monocular)."""
+    return fused_loss(TRACKING_RGB, image, None, opacity, viewpoint.exposure_a, viewpoint.exposure_b,
+                      gt_image, None, grad_mask, 0.95, rgb_boundary_threshold)

@@ -21,6 +21,7 @@ import torch
 import torch.distributed as dist
 
 from .adam import FusedAdam
+from .losses import get_loss_mapping_rgbd, get_loss_tracking_rgbd  # fused kernels (csrc/loss.cu)
 from .rasterizer import GaussianRasterizationSettings, GaussianRasterizer
 
 _GROUPS = ("xyz", "f_dc", "f_rest", "opacity", "scaling", "rotation")
@@ -107,9 +108,10 @@ def render(viewpoint_camera, pc, pipe=None, bg_color=None, scaling_modifier=1.0,
             "n_touched": n_touched}
 
 
-def get_loss_mapping_rgbd(image, depth, viewpoint, gt_image, gt_depth, alpha=0.95,
-                          rgb_boundary_threshold=0.01):
-    """utils/slam_utils.py:91-96,113-128 (exposure affine + masked L1 rgb + masked L1 depth)."""
+def get_loss_mapping_rgbd_torch(image, depth, viewpoint, gt_image, gt_depth, alpha=0.95,
+                                rgb_boundary_threshold=0.01):
+    """utils/slam_utils.py:91-96,113-128 restated op for op in torch (what the reference arm of
+    bench.py runs; the product path uses the fused kernels of losses.py)."""
     image_ab = torch.exp(viewpoint.exposure_a) * image + viewpoint.exposure_b
     rgb_pixel_mask = (gt_image.sum(dim=0) > rgb_boundary_threshold).view(*depth.shape)
     depth_pixel_mask = (gt_depth > 0.01).view(*depth.shape)
@@ -118,9 +120,9 @@ def get_loss_mapping_rgbd(image, depth, viewpoint, gt_image, gt_depth, alpha=0.9
     return alpha * l1_rgb.mean() + (1 - alpha) * l1_depth.mean()
 
 
-def get_loss_tracking_rgbd(image, depth, opacity, viewpoint, gt_image, gt_depth, alpha=0.95,
-                           rgb_boundary_threshold=0.01):
-    """utils/slam_utils.py:56-88 (grad_mask taken as all-ones)."""
+def get_loss_tracking_rgbd_torch(image, depth, opacity, viewpoint, gt_image, gt_depth, alpha=0.95,
+                                 rgb_boundary_threshold=0.01):
+    """utils/slam_utils.py:56-88 in torch ops (grad_mask taken as all-ones)."""
     image_ab = torch.exp(viewpoint.exposure_a) * image + viewpoint.exposure_b
     rgb_pixel_mask = (gt_image.sum(dim=0) > rgb_boundary_threshold).view(1, *gt_image.shape[1:])
     l1_rgb = (opacity * torch.abs(image_ab * rgb_pixel_mask - gt_image * rgb_pixel_mask)).mean()
@@ -135,20 +137,31 @@ def shard_views(num_views, rank, world):
 
 
 class MappingWindow:
-    """One BackEnd.map() iteration over a keyframe window, optionally data-parallel.
+    """One BackEnd.map() iteration over a keyframe window (utils/slam_backend.py:156-317),
+    optionally data-parallel over keyframes and optionally replayed as CUDA graphs.
 
     keyframes: list of dicts {cam, gt_image[3,H,W], gt_depth[1,H,W]} — every rank holds
-    the full list (only its shard's images are touched)."""
+    the full list (only its shard's images are touched).
+
+    cuda_graph=True: the step is captured once as two graphs —
+        G1: every local view's render -> fused loss, the regulariser, one backward;
+        G2: [gradient all-reduce] -> fused Adam -> pose/exposure Adam -> pose updates -> zero grads
+    — and replayed with ONE host sync per step (the binning-overflow check between the two:
+    the sync-free forward renders background-only when its instance capacity is exceeded, in
+    which case G1 is re-captured with a larger capacity before any parameter is touched)."""
 
     def __init__(self, gaussians, keyframes, bg, pose_lr=(0.003, 0.001, 0.01, 0.01),
-                 optimize_pose=True, group=None, render_fn=None, adam_cls=FusedAdam):
+                 optimize_pose=True, group=None, render_fn=None, adam_cls=FusedAdam,
+                 loss_fn=None, cuda_graph=False):
         self.g, self.kfs, self.bg = gaussians, keyframes, bg
         self.render_fn = render_fn or render
+        self.loss_fn = loss_fn or get_loss_mapping_rgbd
         self.group = group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self.local = shard_views(len(keyframes), self.rank, self.world)
         self.optimize_pose = optimize_pose
+        self.cuda_graph = bool(cuda_graph)
         groups = []
         for v in self.local:       # utils/slam_backend.py:434-471 (one Adam over the kf params)
             cam = keyframes[v]["cam"]
@@ -157,24 +170,41 @@ class MappingWindow:
                            dict(params=[cam.cam_trans_delta], lr=pose_lr[1])]
             groups += [dict(params=[cam.exposure_a], lr=pose_lr[2]),
                        dict(params=[cam.exposure_b], lr=pose_lr[3])]
-        self.kf_optimizer = adam_cls(groups, lr=0.0, eps=1e-8) if groups else None
+        kw = dict(capturable=True) if (self.cuda_graph and adam_cls is FusedAdam) else {}
+        self.kf_optimizer = adam_cls(groups, lr=0.0, eps=1e-8, **kw) if groups else None
+        if self.cuda_graph:
+            if not isinstance(gaussians.optimizer, FusedAdam):
+                raise RuntimeError("cuda_graph=True needs the FusedAdam optimizer")
+            gaussians.optimizer.capturable = True
         self.last = {}
+        self._g1 = self._g2 = None
+        self.graph_launches = 0
+        self._loss = None
+        self._steps = 0
 
-    def step(self):
+    # -- the two halves of a step ------------------------------------------------------
+    def _forward_backward(self):
         g = self.g
         loss = 0
         stats = {}
         for v in self.local:
             kf = self.kfs[v]
             pkg = self.render_fn(kf["cam"], g, None, self.bg)
-            loss = loss + get_loss_mapping_rgbd(pkg["render"], pkg["depth"], kf["cam"],
-                                                kf["gt_image"], kf["gt_depth"])
+            loss = loss + self.loss_fn(pkg["render"], pkg["depth"], kf["cam"], kf["gt_image"],
+                                       kf["gt_depth"])
             stats[v] = pkg
         if self.rank == 0:         # view-independent regulariser counted once (slam_backend.py:229-231)
             scaling = g.get_scaling
             loss = loss + 10 * torch.abs(scaling - scaling.mean(dim=1).view(-1, 1)).mean()
         if torch.is_tensor(loss):
             loss.backward()
+            loss = loss.detach()
+        else:
+            loss = torch.zeros((), device=g.flat.device)
+        return loss, stats
+
+    def _update(self, set_to_none):
+        g = self.g
         if self.world > 1:
             if hasattr(g, "flat_grad"):   # ONE message for all six parameter groups
                 dist.all_reduce(g.flat_grad, op=dist.ReduceOp.SUM, group=self.group)
@@ -187,10 +217,89 @@ class MappingWindow:
         g.zero_grad()
         if self.kf_optimizer is not None:
             self.kf_optimizer.step()
-            self.kf_optimizer.zero_grad(set_to_none=True)
+            self.kf_optimizer.zero_grad(set_to_none=set_to_none)
             if self.optimize_pose:
                 for v in self.local:
                     if v > 0:
-                        self.kfs[v]["cam"].update_pose()
+                        cam = self.kfs[v]["cam"]
+                        try:
+                            cam.update_pose(check_converged=False)
+                        except TypeError:
+                            cam.update_pose()
+
+    def _states(self, stats):
+        out = []
+        for pkg in stats.values():
+            fn = pkg["render"].grad_fn
+            out.append(getattr(fn, "state", None) if fn is not None else None)
+        return out
+
+    # -- eager -------------------------------------------------------------------------
+    def _eager_step(self, set_to_none=True):
+        from . import rasterizer as rz
+        loss, stats = self._forward_backward()
+        if rz._SyncFree.enabled and rz.check_overflow(self._states(stats)):
+            self.g.zero_grad()              # discard the background-only pass and redo it
+            if self.kf_optimizer is not None:
+                self.kf_optimizer.zero_grad(set_to_none=set_to_none)
+            loss, stats = self._forward_backward()
+            if rz.check_overflow(self._states(stats)):
+                raise RuntimeError("binning capacity overflow persisted after a retry")
+        self._update(set_to_none)
         self.last = stats
-        return loss.detach() if torch.is_tensor(loss) else torch.zeros((), device=g.flat.device)
+        return loss
+
+    # -- CUDA graphs -------------------------------------------------------------------
+    def _capture(self):
+        from . import rasterizer as rz
+        rz.set_sync_free(True, rz._SyncFree.headroom)
+        from ._lib import lib
+        torch.cuda.synchronize()
+        l0 = lib.b2gs_kernel_launches()
+        self._g1 = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self._g1):
+            self._loss, self._stats = self._forward_backward()
+        self._gstates = self._states(self._stats)
+        l1 = lib.b2gs_kernel_launches()
+        if self._g2 is None:
+            self._g2 = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self._g2):
+                self._update(set_to_none=False)
+            self._l2 = lib.b2gs_kernel_launches() - l1
+        self.graph_launches = (l1 - l0) + self._l2      # libb2gs kernels per replayed step
+
+    def _graph_step(self):
+        from . import rasterizer as rz
+        if self._steps < 3:                 # warm-up: exact sizing, optimizer state, .grad buffers
+            rz.set_sync_free(True, rz._SyncFree.headroom)
+            s = torch.cuda.Stream()
+            s.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(s):
+                loss = self._eager_step(set_to_none=False)
+            torch.cuda.current_stream().wait_stream(s)
+            return loss
+        if self._g1 is None:
+            self._capture()
+        for opt in (self.g.optimizer, self.kf_optimizer):
+            if opt is not None:
+                opt.sync_lr()
+        self._g1.replay()
+        if rz.check_overflow(self._gstates):    # the one host sync of the step
+            self.g.zero_grad()
+            if self.kf_optimizer is not None:
+                self.kf_optimizer.zero_grad(set_to_none=False)
+            g2 = self._g2
+            self._g1 = None
+            self._capture()                       # larger capacities are now in rz._SyncFree.cap
+            self._g2 = g2
+            self._g1.replay()
+            if rz.check_overflow(self._gstates):
+                raise RuntimeError("binning capacity overflow persisted after re-capture")
+        self._g2.replay()
+        self.last = self._stats
+        return self._loss
+
+    def step(self):
+        loss = self._graph_step() if self.cuda_graph else self._eager_step()
+        self._steps += 1
+        return loss

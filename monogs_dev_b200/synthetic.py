@@ -71,22 +71,37 @@ def se3_exp(tau):
 
 
 class Camera:
-    """The part of utils/camera_utils.py:Camera that the rasterizer path reads."""
+    """The part of utils/camera_utils.py:Camera that the rasterizer path reads.
+
+    Pose-derived tensors live in ONE 64-float device block (layout of b2gs_pose_update,
+    include/b2gs.h): R | T | viewmatrix | full projection | camera centre.  The properties
+    below are stable views into it, so a CUDA graph that captured them stays valid when
+    the pose changes; on CUDA `update_pose()` runs on the device (no .cpu() round trip)."""
 
     def __init__(self, W, H, fx, fy, cx, cy, w2c=None, device="cpu", znear=0.01, zfar=100.0):
         self.image_width, self.image_height = W, H
         self.fx, self.fy, self.cx, self.cy = fx, fy, cx, cy
         self.FoVx = 2 * math.atan(W / (2 * fx))
         self.FoVy = 2 * math.atan(H / (2 * fy))
-        self.device = device
-        self._cache = None
+        self.device = torch.device(device)
         w2c = torch.eye(4) if w2c is None else w2c.float()
-        self.R, self.T = w2c[:3, :3].clone(), w2c[:3, 3].clone()
         self.projection_matrix = projection_matrix(znear, zfar, cx, cy, fx, fy, W, H).t().contiguous().to(device)
+        self.state = torch.zeros(64, device=device)
+        self._host_RT = None
+        self.update_RT(w2c[:3, :3], w2c[:3, 3])
         self.cam_rot_delta = torch.zeros(3, device=device, requires_grad=True)
         self.cam_trans_delta = torch.zeros(3, device=device, requires_grad=True)
         self.exposure_a = torch.zeros(1, device=device, requires_grad=True)
         self.exposure_b = torch.zeros(1, device=device, requires_grad=True)
+
+    def _host(self):
+        if self._host_RT is None:       # pose was last changed on the device: read it back
+            h = self.state[:12].detach().cpu()
+            self._host_RT = (h[:9].view(3, 3).clone(), h[9:12].clone())
+        return self._host_RT
+
+    R = property(lambda self: self._host()[0])
+    T = property(lambda self: self._host()[1])
 
     @property
     def w2c(self):
@@ -94,42 +109,45 @@ class Camera:
         m[:3, :3], m[:3, 3] = self.R, self.T
         return m
 
-    def _mats(self):
-        """view / full-projection / centre for the current (R, T).  Computed on the host and
-        uploaded once per pose: the reference recomputes them (two 4x4 inversions, a bmm)
-        on every property access (utils/camera_utils.py:94-107)."""
-        if self._cache is None:
-            view = self.w2c.t().contiguous()
-            proj_cpu = self.projection_matrix.cpu()
-            full = view @ proj_cpu
-            center = torch.linalg.inv(view)[3, :3].contiguous()
-            self._cache = (view.to(self.device), full.contiguous().to(self.device), center.to(self.device))
-        return self._cache
-
-    @property
-    def world_view_transform(self):
-        return self._mats()[0]
-
-    @property
-    def full_proj_transform(self):
-        return self._mats()[1]
-
-    @property
-    def camera_center(self):
-        return self._mats()[2]
-
     def update_RT(self, R, T):
-        self.R, self.T = R.clone(), T.clone()
-        self._cache = None
+        """view / full-projection / centre for (R, T), computed on the host and uploaded in one
+        copy: the reference recomputes them (two 4x4 inversions, a bmm) on every property
+        access (utils/camera_utils.py:94-107)."""
+        R, T = R.detach().float().cpu().clone(), T.detach().float().cpu().clone()
+        self._host_RT = (R, T)
+        w2c = torch.eye(4)
+        w2c[:3, :3], w2c[:3, 3] = R, T
+        view = w2c.t().contiguous()
+        full = view @ self.projection_matrix.cpu()
+        center = torch.linalg.inv(view)[3, :3]
+        h = torch.zeros(64)
+        h[:9], h[9:12] = R.reshape(-1), T
+        h[16:32], h[32:48], h[48:51] = view.reshape(-1), full.reshape(-1), center
+        self.state.copy_(h)
 
-    def update_pose(self):
-        """utils/pose_utils.py:76-93"""
+    world_view_transform = property(lambda self: self.state[16:32].view(4, 4))
+    full_proj_transform = property(lambda self: self.state[32:48].view(4, 4))
+    camera_center = property(lambda self: self.state[48:51])
+
+    def update_pose(self, converged_threshold=1e-4, check_converged=True):
+        """utils/pose_utils.py:76-93.  On CUDA the update is one kernel on the current stream;
+        `check_converged=False` skips the only host sync (the convergence read-back)."""
+        if self.state.is_cuda:
+            from ._lib import lib, check
+            norm = torch.empty(1, device=self.state.device) if check_converged else None
+            with torch.cuda.device(self.state.device):
+                check(lib.b2gs_pose_update(self.state.data_ptr(), self.projection_matrix.data_ptr(),
+                                           self.cam_rot_delta.data_ptr(), self.cam_trans_delta.data_ptr(),
+                                           norm.data_ptr() if norm is not None else None,
+                                           torch.cuda.current_stream().cuda_stream))
+            self._host_RT = None
+            return bool(norm.item() < converged_threshold) if check_converged else False
         tau = torch.cat([self.cam_trans_delta, self.cam_rot_delta]).detach().cpu()
         new = se3_exp(tau) @ self.w2c
         self.update_RT(new[:3, :3], new[:3, 3])
         self.cam_rot_delta.data.fill_(0)
         self.cam_trans_delta.data.fill_(0)
-        return bool(tau.norm() < 1e-4)
+        return bool(tau.norm() < converged_threshold)
 
     def settings(self, bg, sh_degree=0, scale_modifier=1.0, debug=False):
         return GaussianRasterizationSettings(
