@@ -85,6 +85,14 @@ typedef struct B2gsScene {
   const float* scales;         /* device [P,3] or NULL */
   const float* rotations;      /* device [P,4] (r,x,y,z) or NULL */
   const float* cov3D_precomp;  /* device [P,6] or NULL */
+  /* Fused parameter activations (GS/scene/gaussian_model.py:76-101,
+   * GS/gaussian_renderer/__init__.py:76-93): when raw_params != 0 the per-Gaussian inputs are the
+   * RAW optimiser parameters and the kernels apply the activations themselves —
+   *   scales = exp(scales), rotations = rotations / max(|rotations|, 1e-12),
+   *   opacities = sigmoid(opacities), SH = cat(shs [P,1,3], shs_rest [P,M-1,3]) —
+   * and the backward returns gradients with respect to the raw parameters. */
+  int32_t raw_params;
+  const float* shs_rest;       /* device [P,M-1,3]; only with raw_params (NULL if M == 1) */
 } B2gsScene;
 
 /* Workspaces.  Layout is private to the library; the same three buffers must be
@@ -113,7 +121,7 @@ typedef struct B2gsBackwardIO {
   /* outputs: every row is written by the library (zeros for culled Gaussians);
    * pointers marked optional may be NULL to skip that output. */
   float* dL_dmeans3D;   /* [P,3] */
-  float* dL_dmeans2D;   /* [P,3] (z always 0; x,y scaled by W/2, H/2 — CR/backward.cu:643-644) */
+  float* dL_dmeans2D;   /* [P,3] optional (z always 0; x,y scaled by W/2, H/2 — CR/backward.cu:643-644) */
   float* dL_dopacity;   /* [P] */
   float* dL_dcolors;    /* [P,3] optional: gradient wrt colors_precomp */
   float* dL_dsh;        /* [P,M,3] optional: gradient wrt shs */
@@ -122,6 +130,17 @@ typedef struct B2gsBackwardIO {
   float* dL_dcov3D;     /* [P,6] optional */
   float* dL_dtau;       /* [6] = (rho(3), theta(3)), already summed over Gaussians */
   void* scratch; size_t scratch_bytes; /* >= b2gs_backward_scratch_bytes(P) */
+  /* accumulate != 0: per-Gaussian gradient outputs are ADDED to (rows of culled Gaussians left
+   * untouched) instead of written — lets every view of a mapping window sum straight into the
+   * optimiser's gradient arena (replaces autograd's AccumulateGrad adds and the zero fills). */
+  int32_t accumulate;
+  float* dL_dsh_rest;          /* [P,M-1,3]; with raw_params: dL_dsh is the [P,1,3] DC part */
+  /* optional densification statistics of this view, fused (GS/scene/gaussian_model.py:691-695,
+   * utils/slam_backend.py:277-284): for radii > 0:  xyz_gradient_accum += |dL_dmeans2D.xy|,
+   * denom += 1, max_radii2D = max(max_radii2D, radii).  Any may be NULL. */
+  float* densify_grad_accum;   /* [P] */
+  float* densify_denom;        /* [P] */
+  float* max_radii2D;          /* [P] */
 } B2gsBackwardIO;
 
 B2GS_API int b2gs_version(void);

@@ -21,6 +21,7 @@ class B2gsScene(C.Structure):
         ("projmatrix_raw", C.c_void_p), ("campos", C.c_void_p), ("means3D", C.c_void_p),
         ("shs", C.c_void_p), ("colors_precomp", C.c_void_p), ("opacities", C.c_void_p),
         ("scales", C.c_void_p), ("rotations", C.c_void_p), ("cov3D_precomp", C.c_void_p),
+        ("raw_params", C.c_int32), ("shs_rest", C.c_void_p),
     ]
 
 
@@ -46,6 +47,8 @@ class B2gsBackwardIO(C.Structure):
         ("dL_dcolors", C.c_void_p), ("dL_dsh", C.c_void_p), ("dL_dscales", C.c_void_p),
         ("dL_drotations", C.c_void_p), ("dL_dcov3D", C.c_void_p), ("dL_dtau", C.c_void_p),
         ("scratch", C.c_void_p), ("scratch_bytes", C.c_size_t),
+        ("accumulate", C.c_int32), ("dL_dsh_rest", C.c_void_p), ("densify_grad_accum", C.c_void_p),
+        ("densify_denom", C.c_void_p), ("max_radii2D", C.c_void_p),
     ]
 
 

@@ -82,6 +82,16 @@ static int check_scene(const B2gsScene* s, bool backward) {
       return B2GS_ERR_INVALID;
     }
   }
+  if (s->raw_params) {
+    if (!s->shs || !s->scales || !s->rotations) {
+      set_error("raw_params needs shs (DC part), scales and rotations");
+      return B2GS_ERR_INVALID;
+    }
+    if (s->M > 1 && !s->shs_rest) {
+      set_error("raw_params with M=%d needs shs_rest", s->M);
+      return B2GS_ERR_INVALID;
+    }
+  }
   if (backward && !s->projmatrix_raw) {
     set_error("projmatrix_raw must be non-NULL in backward");
     return B2GS_ERR_INVALID;
@@ -296,9 +306,12 @@ extern "C" int b2gs_backward(const B2gsScene* scene, const B2gsWorkspace* ws, in
     B2GS_CUDA(cudaMemsetAsync(io->dL_dtau, 0, 6 * sizeof(float), st));
     return B2GS_OK;
   }
-  if (!io->dL_dcolor || !io->dL_ddepth || !io->radii || !io->dL_dmeans3D || !io->dL_dmeans2D ||
-      !io->dL_dopacity) {
+  if (!io->dL_dcolor || !io->dL_ddepth || !io->radii || !io->dL_dmeans3D || !io->dL_dopacity) {
     set_error("backward: required pointer is NULL");
+    return B2GS_ERR_INVALID;
+  }
+  if (s.raw_params && io->dL_dsh && s.M > 1 && !io->dL_dsh_rest) {
+    set_error("backward: raw_params needs dL_dsh_rest when dL_dsh is requested");
     return B2GS_ERR_INVALID;
   }
   const size_t need = b2gs_backward_scratch_bytes(s.P);

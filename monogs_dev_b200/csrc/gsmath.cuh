@@ -135,6 +135,14 @@ __device__ __forceinline__ Mat3 ewa_cov2d(const Ewa& e) {
   return mat3_mul(mat3_mul(mat3_transpose(e.T), mat3_transpose(e.Vrk)), e.T);
 }
 
+// ---- fused parameter activations (GS/scene/gaussian_model.py:76-101) ---------------------
+// scaling_activation = exp, opacity_activation = sigmoid, rotation_activation = F.normalize
+__device__ __forceinline__ float act_sigmoid(float x) { return 1.0f / (1.0f + expf(-x)); }
+__device__ __forceinline__ float4 act_normalize(float4 q, float& norm) {
+  norm = fmaxf(sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w), 1e-12f);
+  return make_float4(q.x / norm, q.y / norm, q.z / norm, q.w / norm);
+}
+
 // SH basis constants (CR/auxiliary.h:22-39)
 #define B2GS_SH_C0 0.28209479177387814f
 #define B2GS_SH_C1 0.4886025119029199f

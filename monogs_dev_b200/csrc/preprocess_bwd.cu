@@ -33,9 +33,13 @@ __device__ __forceinline__ V3 dnormvdv3(V3 v, V3 dv) {
 
 // SH backward for one Gaussian: writes dL_dsh rows [0, M), returns dL/d(mean) through
 // the view direction (CR/backward.cu:21-145).
-__device__ __forceinline__ V3 sh_backward(int deg, int M, const float* __restrict__ sh, V3 pos,
-                                          V3 campos, uint8_t clamp_bits, V3 dL_dRGB,
-                                          float* __restrict__ dL_dsh) {
+// dc / rest: coefficient 0 and coefficients 1..M-1 (packed layout: rest = dc + 3), same split
+// for the outputs; `accumulate` adds instead of writing.
+#define B2GS_SHK(k, c) ((k) == 0 ? dc[(c)] : rest[3 * ((k) - 1) + (c)])
+__device__ __forceinline__ V3 sh_backward(int deg, int M, const float* __restrict__ dc,
+                                          const float* __restrict__ rest, V3 pos, V3 campos,
+                                          uint8_t clamp_bits, V3 dL_dRGB, float* __restrict__ d_dc,
+                                          float* __restrict__ d_rest, bool accumulate) {
   V3 dir_orig = {pos.x - campos.x, pos.y - campos.y, pos.z - campos.z};
   float len = sqrtf(dir_orig.x * dir_orig.x + dir_orig.y * dir_orig.y + dir_orig.z * dir_orig.z);
   const float x = dir_orig.x / len, y = dir_orig.y / len, z = dir_orig.z / len;
@@ -73,28 +77,27 @@ __device__ __forceinline__ V3 sh_backward(int deg, int M, const float* __restric
     }
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
-      const float* s = sh + c;  // s[3*k] = coefficient k, channel c
-      float dx = -B2GS_SH_C1 * s[9];
-      float dy = -B2GS_SH_C1 * s[3];
-      float dz = B2GS_SH_C1 * s[6];
+      float dx = -B2GS_SH_C1 * B2GS_SHK(3, c);
+      float dy = -B2GS_SH_C1 * B2GS_SHK(1, c);
+      float dz = B2GS_SH_C1 * B2GS_SHK(2, c);
       if (deg > 1) {
-        dx += B2GS_SH_C2_0 * y * s[12] + B2GS_SH_C2_2 * 2.f * -x * s[18] + B2GS_SH_C2_3 * z * s[21] +
-              B2GS_SH_C2_4 * 2.f * x * s[24];
-        dy += B2GS_SH_C2_0 * x * s[12] + B2GS_SH_C2_1 * z * s[15] + B2GS_SH_C2_2 * 2.f * -y * s[18] +
-              B2GS_SH_C2_4 * 2.f * -y * s[24];
-        dz += B2GS_SH_C2_1 * y * s[15] + B2GS_SH_C2_2 * 2.f * 2.f * z * s[18] + B2GS_SH_C2_3 * x * s[21];
+        dx += B2GS_SH_C2_0 * y * B2GS_SHK(4, c) + B2GS_SH_C2_2 * 2.f * -x * B2GS_SHK(6, c) + B2GS_SH_C2_3 * z * B2GS_SHK(7, c) +
+              B2GS_SH_C2_4 * 2.f * x * B2GS_SHK(8, c);
+        dy += B2GS_SH_C2_0 * x * B2GS_SHK(4, c) + B2GS_SH_C2_1 * z * B2GS_SHK(5, c) + B2GS_SH_C2_2 * 2.f * -y * B2GS_SHK(6, c) +
+              B2GS_SH_C2_4 * 2.f * -y * B2GS_SHK(8, c);
+        dz += B2GS_SH_C2_1 * y * B2GS_SHK(5, c) + B2GS_SH_C2_2 * 2.f * 2.f * z * B2GS_SHK(6, c) + B2GS_SH_C2_3 * x * B2GS_SHK(7, c);
         if (deg > 2) {
-          dx += (B2GS_SH_C3_0 * s[27] * 3.f * 2.f * xy + B2GS_SH_C3_1 * s[30] * yz +
-                 B2GS_SH_C3_2 * s[33] * -2.f * xy + B2GS_SH_C3_3 * s[36] * -3.f * 2.f * xz +
-                 B2GS_SH_C3_4 * s[39] * (-3.f * xx + 4.f * zz - yy) +
-                 B2GS_SH_C3_5 * s[42] * 2.f * xz + B2GS_SH_C3_6 * s[45] * 3.f * (xx - yy));
-          dy += (B2GS_SH_C3_0 * s[27] * 3.f * (xx - yy) + B2GS_SH_C3_1 * s[30] * xz +
-                 B2GS_SH_C3_2 * s[33] * (-3.f * yy + 4.f * zz - xx) +
-                 B2GS_SH_C3_3 * s[36] * -3.f * 2.f * yz + B2GS_SH_C3_4 * s[39] * -2.f * xy +
-                 B2GS_SH_C3_5 * s[42] * -2.f * yz + B2GS_SH_C3_6 * s[45] * -3.f * 2.f * xy);
-          dz += (B2GS_SH_C3_1 * s[30] * xy + B2GS_SH_C3_2 * s[33] * 4.f * 2.f * yz +
-                 B2GS_SH_C3_3 * s[36] * 3.f * (2.f * zz - xx - yy) +
-                 B2GS_SH_C3_4 * s[39] * 4.f * 2.f * xz + B2GS_SH_C3_5 * s[42] * (xx - yy));
+          dx += (B2GS_SH_C3_0 * B2GS_SHK(9, c) * 3.f * 2.f * xy + B2GS_SH_C3_1 * B2GS_SHK(10, c) * yz +
+                 B2GS_SH_C3_2 * B2GS_SHK(11, c) * -2.f * xy + B2GS_SH_C3_3 * B2GS_SHK(12, c) * -3.f * 2.f * xz +
+                 B2GS_SH_C3_4 * B2GS_SHK(13, c) * (-3.f * xx + 4.f * zz - yy) +
+                 B2GS_SH_C3_5 * B2GS_SHK(14, c) * 2.f * xz + B2GS_SH_C3_6 * B2GS_SHK(15, c) * 3.f * (xx - yy));
+          dy += (B2GS_SH_C3_0 * B2GS_SHK(9, c) * 3.f * (xx - yy) + B2GS_SH_C3_1 * B2GS_SHK(10, c) * xz +
+                 B2GS_SH_C3_2 * B2GS_SHK(11, c) * (-3.f * yy + 4.f * zz - xx) +
+                 B2GS_SH_C3_3 * B2GS_SHK(12, c) * -3.f * 2.f * yz + B2GS_SH_C3_4 * B2GS_SHK(13, c) * -2.f * xy +
+                 B2GS_SH_C3_5 * B2GS_SHK(14, c) * -2.f * yz + B2GS_SH_C3_6 * B2GS_SHK(15, c) * -3.f * 2.f * xy);
+          dz += (B2GS_SH_C3_1 * B2GS_SHK(10, c) * xy + B2GS_SH_C3_2 * B2GS_SHK(11, c) * 4.f * 2.f * yz +
+                 B2GS_SH_C3_3 * B2GS_SHK(12, c) * 3.f * (2.f * zz - xx - yy) +
+                 B2GS_SH_C3_4 * B2GS_SHK(13, c) * 4.f * 2.f * xz + B2GS_SH_C3_5 * B2GS_SHK(14, c) * (xx - yy));
         }
       }
       ddir[0] += dx * g[c];
@@ -103,15 +106,19 @@ __device__ __forceinline__ V3 sh_backward(int deg, int M, const float* __restric
     }
   }
   const int active = (deg + 1) * (deg + 1);
-  for (int k = 0; dL_dsh != nullptr && k < M; ++k) {
+  for (int k = 0; d_dc != nullptr && k < M; ++k) {
     const float bk = (k < active && k < 16) ? basis[k] : 0.f;
-    dL_dsh[3 * k + 0] = bk * g[0];
-    dL_dsh[3 * k + 1] = bk * g[1];
-    dL_dsh[3 * k + 2] = bk * g[2];
+    float* o = k == 0 ? d_dc : d_rest + 3 * (k - 1);
+    if (accumulate) {
+      if (bk != 0.f) { o[0] += bk * g[0]; o[1] += bk * g[1]; o[2] += bk * g[2]; }
+    } else {
+      o[0] = bk * g[0]; o[1] = bk * g[1]; o[2] = bk * g[2];
+    }
   }
   return dnormvdv3(dir_orig, V3{ddir[0], ddir[1], ddir[2]});
 }
 
+template <bool RAW>
 __global__ void __launch_bounds__(256)
 preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
                       const int32_t* __restrict__ radii, const float* __restrict__ shs,
@@ -125,7 +132,11 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
                       float* __restrict__ dL_dopacity, float* __restrict__ dL_dcolors,
                       float* __restrict__ dL_dsh, float* __restrict__ dL_dscales,
                       float* __restrict__ dL_drots, float* __restrict__ dL_dcov3D,
-                      float* __restrict__ tau_partials) {
+                      float* __restrict__ tau_partials,
+                      const float* __restrict__ shs_rest, const float* __restrict__ opacities,
+                      int accumulate, float* __restrict__ dL_dsh_rest,
+                      float* __restrict__ st_grad_accum, float* __restrict__ st_denom,
+                      float* __restrict__ st_max_radii) {
   __shared__ float s_view[16], s_proj[16];
   __shared__ float s_tau[8][6];
   if (threadIdx.x < 16) s_view[threadIdx.x] = viewmatrix[threadIdx.x];
@@ -138,13 +149,17 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
   float tau[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   const bool live = idx < P && radii[idx] > 0;
 
-  if (idx < P && !live) {
+  if (idx < P && !live && !accumulate) {
     // culled: every gradient row is zero (reference: torch::zeros, DGR/rasterize_points.cu:160-170)
     dL_dmeans3D[3 * idx] = 0.f; dL_dmeans3D[3 * idx + 1] = 0.f; dL_dmeans3D[3 * idx + 2] = 0.f;
-    dL_dmeans2D[3 * idx] = 0.f; dL_dmeans2D[3 * idx + 1] = 0.f; dL_dmeans2D[3 * idx + 2] = 0.f;
+    if (dL_dmeans2D) { dL_dmeans2D[3 * idx] = 0.f; dL_dmeans2D[3 * idx + 1] = 0.f; dL_dmeans2D[3 * idx + 2] = 0.f; }
     dL_dopacity[idx] = 0.f;
     if (dL_dcolors) { dL_dcolors[3 * idx] = 0.f; dL_dcolors[3 * idx + 1] = 0.f; dL_dcolors[3 * idx + 2] = 0.f; }
-    if (dL_dsh) for (int k = 0; k < 3 * M; ++k) dL_dsh[(size_t)idx * M * 3 + k] = 0.f;
+    if (dL_dsh && !RAW) for (int k = 0; k < 3 * M; ++k) dL_dsh[(size_t)idx * M * 3 + k] = 0.f;
+    if (dL_dsh && RAW) {
+      for (int k = 0; k < 3; ++k) dL_dsh[(size_t)idx * 3 + k] = 0.f;
+      for (int k = 0; k < 3 * (M - 1); ++k) dL_dsh_rest[(size_t)idx * (M - 1) * 3 + k] = 0.f;
+    }
     if (dL_dscales) { dL_dscales[3 * idx] = 0.f; dL_dscales[3 * idx + 1] = 0.f; dL_dscales[3 * idx + 2] = 0.f; }
     if (dL_drots) reinterpret_cast<float4*>(dL_drots)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
     if (dL_dcov3D) for (int k = 0; k < 6; ++k) dL_dcov3D[6 * idx + k] = 0.f;
@@ -162,13 +177,17 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
     const float3 mean = {means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]};
     float cov6[6];
     float4 q = make_float4(1.f, 0.f, 0.f, 0.f);
-    float sx = 0.f, sy = 0.f, sz = 0.f;
+    float sx = 0.f, sy = 0.f, sz = 0.f, q_norm = 1.f;
     if (cov3D_precomp != nullptr) {
 #pragma unroll
       for (int i = 0; i < 6; ++i) cov6[i] = cov3D_precomp[6 * idx + i];
     } else {
       q = reinterpret_cast<const float4*>(rotations)[idx];
       sx = scales[3 * idx]; sy = scales[3 * idx + 1]; sz = scales[3 * idx + 2];
+      if (RAW) {  // same activations as the forward (gsmath.cuh)
+        q = act_normalize(q, q_norm);
+        sx = expf(sx); sy = expf(sy); sz = expf(sz);
+      }
       cov3d_from_scale_rot(sx, sy, sz, scale_modifier, q, cov6);
     }
 
@@ -316,9 +335,16 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
     // ---------------- colour ----------------
     if (shs != nullptr) {
       const V3 campos = {campos_p[0], campos_p[1], campos_p[2]};
-      const V3 dm = sh_backward(D, M, shs + (size_t)idx * M * 3, V3{mean.x, mean.y, mean.z}, campos,
-                                clamped[idx], dL_dcol,
-                                dL_dsh ? dL_dsh + (size_t)idx * M * 3 : nullptr);
+      const float* dc = RAW ? shs + (size_t)idx * 3 : shs + (size_t)idx * M * 3;
+      const float* rest = RAW ? shs_rest + (size_t)idx * (M - 1) * 3 : dc + 3;
+      float* d_dc = nullptr;
+      float* d_rest = nullptr;
+      if (dL_dsh) {
+        d_dc = RAW ? dL_dsh + (size_t)idx * 3 : dL_dsh + (size_t)idx * M * 3;
+        d_rest = RAW ? dL_dsh_rest + (size_t)idx * (M - 1) * 3 : d_dc + 3;
+      }
+      const V3 dm = sh_backward(D, M, dc, rest, V3{mean.x, mean.y, mean.z}, campos, clamped[idx],
+                                dL_dcol, d_dc, d_rest, accumulate != 0);
       dmean.x += dm.x; dmean.y += dm.y; dmean.z += dm.z;
       tau[0] += -dm.x; tau[1] += -dm.y; tau[2] += -dm.z;
       if (dL_dcolors) { dL_dcolors[3 * idx] = dL_dcol.x; dL_dcolors[3 * idx + 1] = dL_dcol.y; dL_dcolors[3 * idx + 2] = dL_dcol.z; }
@@ -346,9 +372,15 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
       const Mat3 Rt = mat3_transpose(R);
       Mat3 dL_dMt = mat3_transpose(dL_dM);
       if (dL_dscales) {
-        dL_dscales[3 * idx + 0] = Rt.m[0][0] * dL_dMt.m[0][0] + Rt.m[0][1] * dL_dMt.m[0][1] + Rt.m[0][2] * dL_dMt.m[0][2];
-        dL_dscales[3 * idx + 1] = Rt.m[1][0] * dL_dMt.m[1][0] + Rt.m[1][1] * dL_dMt.m[1][1] + Rt.m[1][2] * dL_dMt.m[1][2];
-        dL_dscales[3 * idx + 2] = Rt.m[2][0] * dL_dMt.m[2][0] + Rt.m[2][1] * dL_dMt.m[2][1] + Rt.m[2][2] * dL_dMt.m[2][2];
+        float ds0 = Rt.m[0][0] * dL_dMt.m[0][0] + Rt.m[0][1] * dL_dMt.m[0][1] + Rt.m[0][2] * dL_dMt.m[0][2];
+        float ds1 = Rt.m[1][0] * dL_dMt.m[1][0] + Rt.m[1][1] * dL_dMt.m[1][1] + Rt.m[1][2] * dL_dMt.m[1][2];
+        float ds2 = Rt.m[2][0] * dL_dMt.m[2][0] + Rt.m[2][1] * dL_dMt.m[2][1] + Rt.m[2][2] * dL_dMt.m[2][2];
+        if (RAW) { ds0 *= sx; ds1 *= sy; ds2 *= sz; }  // d exp(x) = exp(x) dx
+        if (accumulate) {
+          dL_dscales[3 * idx + 0] += ds0; dL_dscales[3 * idx + 1] += ds1; dL_dscales[3 * idx + 2] += ds2;
+        } else {
+          dL_dscales[3 * idx + 0] = ds0; dL_dscales[3 * idx + 1] = ds1; dL_dscales[3 * idx + 2] = ds2;
+        }
       }
 #pragma unroll
       for (int rr = 0; rr < 3; ++rr) {
@@ -362,9 +394,23 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
         dq.y = 2 * y * (dL_dMt.m[1][0] + dL_dMt.m[0][1]) + 2 * z * (dL_dMt.m[2][0] + dL_dMt.m[0][2]) + 2 * r * (dL_dMt.m[1][2] - dL_dMt.m[2][1]) - 4 * x * (dL_dMt.m[2][2] + dL_dMt.m[1][1]);
         dq.z = 2 * x * (dL_dMt.m[1][0] + dL_dMt.m[0][1]) + 2 * r * (dL_dMt.m[2][0] - dL_dMt.m[0][2]) + 2 * z * (dL_dMt.m[1][2] + dL_dMt.m[2][1]) - 4 * y * (dL_dMt.m[2][2] + dL_dMt.m[0][0]);
         dq.w = 2 * r * (dL_dMt.m[0][1] - dL_dMt.m[1][0]) + 2 * x * (dL_dMt.m[2][0] + dL_dMt.m[0][2]) + 2 * y * (dL_dMt.m[1][2] + dL_dMt.m[2][1]) - 4 * z * (dL_dMt.m[1][1] + dL_dMt.m[0][0]);
-        reinterpret_cast<float4*>(dL_drots)[idx] = dq;  // raw-quaternion gradient (quirk q3)
+        // dq is the gradient wrt the quaternion the kernel used (quirk q3: the rasterizer never
+        // back-propagates its own normalisation); with RAW the F.normalize backward
+        // that autograd would run (GS/scene/gaussian_model.py:80-82) is applied here
+        if (RAW) {
+          const float dot = q.x * dq.x + q.y * dq.y + q.z * dq.z + q.w * dq.w;
+          const float inv = 1.0f / q_norm;
+          dq.x = (dq.x - q.x * dot) * inv; dq.y = (dq.y - q.y * dot) * inv;
+          dq.z = (dq.z - q.z * dot) * inv; dq.w = (dq.w - q.w * dot) * inv;
+        }
+        float4* out = reinterpret_cast<float4*>(dL_drots) + idx;
+        if (accumulate) {
+          const float4 o = *out;
+          dq.x += o.x; dq.y += o.y; dq.z += o.z; dq.w += o.w;
+        }
+        *out = dq;
       }
-    } else {
+    } else if (!accumulate) {
       if (dL_dscales) { dL_dscales[3 * idx] = 0.f; dL_dscales[3 * idx + 1] = 0.f; dL_dscales[3 * idx + 2] = 0.f; }
       if (dL_drots) reinterpret_cast<float4*>(dL_drots)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
@@ -373,13 +419,32 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
 #pragma unroll
       for (int k = 0; k < 6; ++k) dL_dcov3D[6 * idx + k] = dcov[k];
     }
-    dL_dmeans3D[3 * idx] = dmean.x;
-    dL_dmeans3D[3 * idx + 1] = dmean.y;
-    dL_dmeans3D[3 * idx + 2] = dmean.z;
-    dL_dmeans2D[3 * idx] = dmean2D_x;
-    dL_dmeans2D[3 * idx + 1] = dmean2D_y;
-    dL_dmeans2D[3 * idx + 2] = 0.f;
-    dL_dopacity[idx] = dL_dop;
+    float d_op = dL_dop;
+    if (RAW) {  // d sigmoid(x) = o (1 - o) dx
+      const float o = act_sigmoid(opacities[idx]);
+      d_op *= o * (1.f - o);
+    }
+    if (accumulate) {
+      dL_dmeans3D[3 * idx] += dmean.x;
+      dL_dmeans3D[3 * idx + 1] += dmean.y;
+      dL_dmeans3D[3 * idx + 2] += dmean.z;
+      dL_dopacity[idx] += d_op;
+    } else {
+      dL_dmeans3D[3 * idx] = dmean.x;
+      dL_dmeans3D[3 * idx + 1] = dmean.y;
+      dL_dmeans3D[3 * idx + 2] = dmean.z;
+      dL_dopacity[idx] = d_op;
+    }
+    if (dL_dmeans2D) {
+      dL_dmeans2D[3 * idx] = dmean2D_x;
+      dL_dmeans2D[3 * idx + 1] = dmean2D_y;
+      dL_dmeans2D[3 * idx + 2] = 0.f;
+    }
+    // densification statistics of this view (GS/scene/gaussian_model.py:691-695,
+    // utils/slam_backend.py:277-284), visibility_filter = radii > 0
+    if (st_grad_accum) st_grad_accum[idx] += sqrtf(dmean2D_x * dmean2D_x + dmean2D_y * dmean2D_y);
+    if (st_denom) st_denom[idx] += 1.f;
+    if (st_max_radii) st_max_radii[idx] = fmaxf(st_max_radii[idx], (float)radii[idx]);
   }
 
   // ---- dL_dtau: warp -> block -> one partial row per block ----
@@ -433,11 +498,14 @@ int launch_preprocess_bwd(const B2gsScene& s, const GeomWS& g, const B2gsBackwar
   const int blocks = (s.P + 255) / 256;
   float* partials = const_cast<float*>(acc) + (size_t)s.P * ACC_STRIDE;  // scratch tail
   B2GS_PROF("preprocess_bwd", st);
-  preprocess_bwd_kernel<<<blocks, 256, 0, st>>>(
+  auto kern = s.raw_params ? preprocess_bwd_kernel<true> : preprocess_bwd_kernel<false>;
+  kern<<<blocks, 256, 0, st>>>(
       s.P, s.D, s.M, s.means3D, io.radii, s.shs, g.clamped, s.scales, s.rotations, s.scale_modifier,
       s.cov3D_precomp, s.viewmatrix, s.projmatrix, s.projmatrix_raw, s.campos, focal_x, focal_y,
       s.tan_fovx, s.tan_fovy, acc, io.dL_dmeans3D, io.dL_dmeans2D, io.dL_dopacity, io.dL_dcolors,
-      s.shs ? io.dL_dsh : nullptr, io.dL_dscales, io.dL_drotations, io.dL_dcov3D, partials);
+      s.shs ? io.dL_dsh : nullptr, io.dL_dscales, io.dL_drotations, io.dL_dcov3D, partials,
+      s.shs_rest, s.opacities, io.accumulate, io.dL_dsh_rest, io.densify_grad_accum,
+      io.densify_denom, io.max_radii2D);
   B2GS_LAUNCH_CHECK(st, s.debug);
   tau_finalize_kernel<<<1, 256, 0, st>>>(blocks, partials, io.dL_dtau);
   B2GS_LAUNCH_CHECK(st, s.debug);

@@ -12,7 +12,10 @@
 
 namespace b2gs {
 
-__device__ __forceinline__ float3 sh_to_rgb(int deg, const float* __restrict__ sh, float3 pos,
+// coefficient k, channel c: DC from `dc`, the rest from `rest` (packed layout: rest = dc + 3)
+#define B2GS_SHK(k, c) ((k) == 0 ? dc[(c)] : rest[3 * ((k) - 1) + (c)])
+__device__ __forceinline__ float3 sh_to_rgb(int deg, const float* __restrict__ dc,
+                                            const float* __restrict__ rest, float3 pos,
                                             float3 campos, uint8_t& clamp_bits) {
   // CR/forward.cu:22-73
   float3 dir = {pos.x - campos.x, pos.y - campos.y, pos.z - campos.z};
@@ -23,24 +26,24 @@ __device__ __forceinline__ float3 sh_to_rgb(int deg, const float* __restrict__ s
   float res[3];
 #pragma unroll
   for (int c = 0; c < 3; ++c) {
-    float r = B2GS_SH_C0 * sh[c];
+    float r = B2GS_SH_C0 * B2GS_SHK(0, c);
     if (deg > 0) {
       float x = dir.x, y = dir.y, z = dir.z;
-      r = r - B2GS_SH_C1 * y * sh[3 + c] + B2GS_SH_C1 * z * sh[6 + c] - B2GS_SH_C1 * x * sh[9 + c];
+      r = r - B2GS_SH_C1 * y * B2GS_SHK(1, c) + B2GS_SH_C1 * z * B2GS_SHK(2, c) - B2GS_SH_C1 * x * B2GS_SHK(3, c);
       if (deg > 1) {
         float xx = x * x, yy = y * y, zz = z * z;
         float xy = x * y, yz = y * z, xz = x * z;
-        r = r + B2GS_SH_C2_0 * xy * sh[12 + c] + B2GS_SH_C2_1 * yz * sh[15 + c] +
-            B2GS_SH_C2_2 * (2.0f * zz - xx - yy) * sh[18 + c] + B2GS_SH_C2_3 * xz * sh[21 + c] +
-            B2GS_SH_C2_4 * (xx - yy) * sh[24 + c];
+        r = r + B2GS_SH_C2_0 * xy * B2GS_SHK(4, c) + B2GS_SH_C2_1 * yz * B2GS_SHK(5, c) +
+            B2GS_SH_C2_2 * (2.0f * zz - xx - yy) * B2GS_SHK(6, c) + B2GS_SH_C2_3 * xz * B2GS_SHK(7, c) +
+            B2GS_SH_C2_4 * (xx - yy) * B2GS_SHK(8, c);
         if (deg > 2) {
-          r = r + B2GS_SH_C3_0 * y * (3.0f * xx - yy) * sh[27 + c] +
-              B2GS_SH_C3_1 * xy * z * sh[30 + c] +
-              B2GS_SH_C3_2 * y * (4.0f * zz - xx - yy) * sh[33 + c] +
-              B2GS_SH_C3_3 * z * (2.0f * zz - 3.0f * xx - 3.0f * yy) * sh[36 + c] +
-              B2GS_SH_C3_4 * x * (4.0f * zz - xx - yy) * sh[39 + c] +
-              B2GS_SH_C3_5 * z * (xx - yy) * sh[42 + c] +
-              B2GS_SH_C3_6 * x * (xx - 3.0f * yy) * sh[45 + c];
+          r = r + B2GS_SH_C3_0 * y * (3.0f * xx - yy) * B2GS_SHK(9, c) +
+              B2GS_SH_C3_1 * xy * z * B2GS_SHK(10, c) +
+              B2GS_SH_C3_2 * y * (4.0f * zz - xx - yy) * B2GS_SHK(11, c) +
+              B2GS_SH_C3_3 * z * (2.0f * zz - 3.0f * xx - 3.0f * yy) * B2GS_SHK(12, c) +
+              B2GS_SH_C3_4 * x * (4.0f * zz - xx - yy) * B2GS_SHK(13, c) +
+              B2GS_SH_C3_5 * z * (xx - yy) * B2GS_SHK(14, c) +
+              B2GS_SH_C3_6 * x * (xx - 3.0f * yy) * B2GS_SHK(15, c);
         }
       }
     }
@@ -51,6 +54,9 @@ __device__ __forceinline__ float3 sh_to_rgb(int deg, const float* __restrict__ s
   return make_float3(res[0], res[1], res[2]);
 }
 
+// RAW is a template parameter so that the RAW=false instantiation is, instruction for
+// instruction, the kernel whose roundings are bit-identical to the reference's.
+template <bool RAW>
 __global__ void __launch_bounds__(256)
 preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
                       const float* __restrict__ scales, float scale_modifier,
@@ -59,7 +65,8 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
                       const float* __restrict__ colors_precomp, const float* __restrict__ viewmatrix,
                       const float* __restrict__ projmatrix, const float* __restrict__ campos_p, int W,
                       int H, float tan_fovx, float tan_fovy, float focal_x, float focal_y, int gx,
-                      int gy, int prefiltered, int32_t* __restrict__ radii,
+                      int gy, int prefiltered,
+                      const float* __restrict__ shs_rest, int32_t* __restrict__ radii,
                       int32_t* __restrict__ n_touched, uint32_t* __restrict__ tile_count, GeomWS g) {
   __shared__ float s_view[16], s_proj[16];
   __shared__ WarpRects s_rects[8];
@@ -102,8 +109,13 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
       for (int i = 0; i < 6; ++i) cov6[i] = cov3D_precomp[6 * idx + i];
     } else {
       float4 q = reinterpret_cast<const float4*>(rotations)[idx];
-      cov3d_from_scale_rot(scales[3 * idx], scales[3 * idx + 1], scales[3 * idx + 2],
-                           scale_modifier, q, cov6);
+      float sx = scales[3 * idx], sy = scales[3 * idx + 1], sz = scales[3 * idx + 2];
+      if (RAW) {  // fused activations: exp / normalize
+        float qn;
+        q = act_normalize(q, qn);
+        sx = expf(sx); sy = expf(sy); sz = expf(sz);
+      }
+      cov3d_from_scale_rot(sx, sy, sz, scale_modifier, q, cov6);
     }
 
     Ewa e;
@@ -128,7 +140,7 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
       tile_rect(point_image, my_radius_i, gx, gy, x0, y0, x1, y1);
       touched = (uint32_t)((x1 - x0) * (y1 - y0));
       if (touched == 0) visible = false;
-      con_o = {conic.x, conic.y, conic.z, opacities[idx]};
+      con_o = {conic.x, conic.y, conic.z, RAW ? act_sigmoid(opacities[idx]) : opacities[idx]};
     }
   }
 
@@ -142,7 +154,9 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
     uint8_t clamp_bits = 0;
     if (colors_precomp == nullptr) {
       const float3 campos = {campos_p[0], campos_p[1], campos_p[2]};
-      rgb = sh_to_rgb(D, shs + (size_t)idx * M * 3, p_orig, campos, clamp_bits);
+      const float* dc = RAW ? shs + (size_t)idx * 3 : shs + (size_t)idx * M * 3;
+      const float* rest = RAW ? shs_rest + (size_t)idx * (M - 1) * 3 : dc + 3;
+      rgb = sh_to_rgb(D, dc, rest, p_orig, campos, clamp_bits);
     } else {
       rgb = {colors_precomp[3 * idx], colors_precomp[3 * idx + 1], colors_precomp[3 * idx + 2]};
     }
@@ -182,10 +196,12 @@ int launch_preprocess_fwd(const B2gsScene& s, const GeomWS& g, const ImageWS& im
   const int gx = (s.W + TILE - 1) / TILE, gy = (s.H + TILE - 1) / TILE;
   const int blocks = (s.P + 255) / 256;
   B2GS_PROF("preprocess_fwd", st);
-  preprocess_fwd_kernel<<<blocks, 256, 0, st>>>(
+  auto kern = s.raw_params ? preprocess_fwd_kernel<true> : preprocess_fwd_kernel<false>;
+  kern<<<blocks, 256, 0, st>>>(
       s.P, s.D, s.M, s.means3D, s.scales, s.scale_modifier, s.rotations, s.opacities, s.shs,
       s.cov3D_precomp, s.colors_precomp, s.viewmatrix, s.projmatrix, s.campos, s.W, s.H,
-      s.tan_fovx, s.tan_fovy, focal_x, focal_y, gx, gy, s.prefiltered, radii, n_touched, im.cursor, g);
+      s.tan_fovx, s.tan_fovy, focal_x, focal_y, gx, gy, s.prefiltered, s.shs_rest, radii,
+      n_touched, im.cursor, g);
   B2GS_LAUNCH_CHECK(st, s.debug);
   return B2GS_OK;
 }

@@ -22,7 +22,8 @@ import torch.distributed as dist
 
 from .adam import FusedAdam
 from .losses import get_loss_mapping_rgbd, get_loss_tracking_rgbd  # fused kernels (csrc/loss.cu)
-from .rasterizer import GaussianRasterizationSettings, GaussianRasterizer
+from .rasterizer import (GaussianRasterizationSettings, GaussianRasterizer, GradSinks,
+                         rasterize_gaussians_raw)
 
 _GROUPS = ("xyz", "f_dc", "f_rest", "opacity", "scaling", "rotation")
 
@@ -81,6 +82,26 @@ class GaussianModel:
     def zero_grad(self):
         self.flat_grad.zero_()
 
+    # densification statistics (GS/scene/gaussian_model.py:233-235,691-695)
+    def _stats(self):
+        if not hasattr(self, "xyz_gradient_accum"):
+            P, dev = self._xyz.shape[0], self.flat.device
+            self.xyz_gradient_accum = torch.zeros(P, 1, device=dev)
+            self.denom = torch.zeros(P, 1, device=dev)
+            self.max_radii2D = torch.zeros(P, device=dev)
+        return self.xyz_gradient_accum, self.denom, self.max_radii2D
+
+    def add_densification_stats(self, viewspace_point_tensor, update_filter):
+        acc, den, _ = self._stats()
+        acc[update_filter] += torch.norm(viewspace_point_tensor.grad[update_filter, :2], dim=-1, keepdim=True)
+        den[update_filter] += 1
+
+    def grad_sinks(self, with_stats=True):
+        """gradient arena views + statistics buffers for the fused-activation rasterizer."""
+        st = self._stats() if with_stats else (None, None, None)
+        g = {k: self._params[k].grad for k in _GROUPS}
+        return GradSinks(g["xyz"], g["f_dc"], g["f_rest"], g["opacity"], g["scaling"], g["rotation"], *st)
+
 
 def render(viewpoint_camera, pc, pipe=None, bg_color=None, scaling_modifier=1.0, override_color=None):
     """Same contract as the reference's render(): returns the dict with keys render,
@@ -106,6 +127,27 @@ def render(viewpoint_camera, pc, pipe=None, bg_color=None, scaling_modifier=1.0,
     return {"render": rendered_image, "viewspace_points": screenspace_points,
             "visibility_filter": radii > 0, "radii": radii, "depth": depth, "opacity": opacity,
             "n_touched": n_touched}
+
+
+def render_fused(viewpoint_camera, pc, pipe=None, bg_color=None, scaling_modifier=1.0, with_stats=True):
+    """render() with the parameter activations, the gradient accumulation into the optimiser's
+    arena and the per-view densification statistics fused into the rasterizer kernels
+    (SURVEY.md §8f row 1).  Same return dict; `viewspace_points` is None (its only consumer,
+    add_densification_stats, is fused: pc.xyz_gradient_accum / denom / max_radii2D are updated
+    by the backward)."""
+    cam = viewpoint_camera
+    rs = GaussianRasterizationSettings(
+        image_height=int(cam.image_height), image_width=int(cam.image_width),
+        tanfovx=math.tan(cam.FoVx * 0.5), tanfovy=math.tan(cam.FoVy * 0.5), bg=bg_color,
+        scale_modifier=scaling_modifier, viewmatrix=cam.world_view_transform,
+        projmatrix=cam.full_proj_transform, projmatrix_raw=cam.projection_matrix,
+        sh_degree=pc.active_sh_degree, campos=cam.camera_center, prefiltered=False, debug=False)
+    rendered_image, radii, depth, opacity, n_touched = rasterize_gaussians_raw(
+        pc._xyz, pc._features_dc, pc._features_rest, pc._opacity, pc._scaling, pc._rotation, rs,
+        theta=cam.cam_rot_delta, rho=cam.cam_trans_delta, sinks=pc.grad_sinks(with_stats))
+    return {"render": rendered_image, "viewspace_points": None, "visibility_filter": radii > 0,
+            "radii": radii, "depth": depth, "opacity": opacity, "n_touched": n_touched,
+            "stats_fused": with_stats}
 
 
 def get_loss_mapping_rgbd_torch(image, depth, viewpoint, gt_image, gt_depth, alpha=0.95,
@@ -152,9 +194,9 @@ class MappingWindow:
 
     def __init__(self, gaussians, keyframes, bg, pose_lr=(0.003, 0.001, 0.01, 0.01),
                  optimize_pose=True, group=None, render_fn=None, adam_cls=FusedAdam,
-                 loss_fn=None, cuda_graph=False):
+                 loss_fn=None, cuda_graph=False, densify_stats=True):
         self.g, self.kfs, self.bg = gaussians, keyframes, bg
-        self.render_fn = render_fn or render
+        self.render_fn = render_fn or (render_fused if isinstance(gaussians, GaussianModel) else render)
         self.loss_fn = loss_fn or get_loss_mapping_rgbd
         self.group = group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
@@ -162,6 +204,9 @@ class MappingWindow:
         self.local = shard_views(len(keyframes), self.rank, self.world)
         self.optimize_pose = optimize_pose
         self.cuda_graph = bool(cuda_graph)
+        self.densify_stats = bool(densify_stats)
+        if self.densify_stats and hasattr(gaussians, "_stats"):
+            gaussians._stats()
         groups = []
         for v in self.local:       # utils/slam_backend.py:434-471 (one Adam over the kf params)
             cam = keyframes[v]["cam"]
@@ -200,7 +245,17 @@ class MappingWindow:
             loss.backward()
             loss = loss.detach()
         else:
-            loss = torch.zeros((), device=g.flat.device)
+            loss = torch.zeros((), device=self.bg.device)
+        # densification statistics of every view (utils/slam_backend.py:277-284); the fused
+        # renderer has already accumulated them inside its backward kernel
+        if self.densify_stats and hasattr(g, "add_densification_stats"):
+            with torch.no_grad():
+                for pkg in stats.values():
+                    if pkg.get("stats_fused"):
+                        continue
+                    vis = pkg["visibility_filter"]
+                    g.max_radii2D[vis] = torch.max(g.max_radii2D[vis], pkg["radii"][vis])
+                    g.add_densification_stats(pkg["viewspace_points"], vis)
         return loss, stats
 
     def _update(self, set_to_none):

@@ -48,7 +48,8 @@ def _f32c(t, name):
     return t.contiguous()
 
 
-def _scene_struct(rs, P, M, means3D, sh, colors, opac, scales, rots, cov3D, keep):
+def _scene_struct(rs, P, M, means3D, sh, colors, opac, scales, rots, cov3D, keep, sh_rest=None,
+                  raw=False):
     dev = means3D.device
     def mat(t, name):
         t = _f32c(t, name)
@@ -70,6 +71,7 @@ def _scene_struct(rs, P, M, means3D, sh, colors, opac, scales, rots, cov3D, keep
     s.means3D = ptr(means3D)
     s.shs, s.colors_precomp, s.opacities = ptr(sh), ptr(colors), ptr(opac)
     s.scales, s.rotations, s.cov3D_precomp = ptr(scales), ptr(rots), ptr(cov3D)
+    s.raw_params, s.shs_rest = int(bool(raw)), ptr(sh_rest)
     return s
 
 
@@ -121,7 +123,7 @@ def check_overflow(states):
     return over
 
 
-def _forward_native(rs, means3D, sh, colors, opac, scales, rots, cov3D):
+def _forward_native(rs, means3D, sh, colors, opac, scales, rots, cov3D, sh_rest=None, raw=False):
     if means3D.dim() != 2 or means3D.size(1) != 3:
         # message of DGR/rasterize_points.cu:58-60
         raise RuntimeError("means3D must have dimensions (num_points, 3)")
@@ -129,6 +131,8 @@ def _forward_native(rs, means3D, sh, colors, opac, scales, rots, cov3D):
     H, W = int(rs.image_height), int(rs.image_width)
     dev = means3D.device
     M = sh.size(1) if sh is not None else 0
+    if raw:
+        M = 1 + (sh_rest.size(1) if sh_rest is not None else 0)
     st = RasterState()
     if P == 0:
         z = lambda *s: torch.zeros(*s, dtype=torch.float32, device=dev)
@@ -147,7 +151,8 @@ def _forward_native(rs, means3D, sh, colors, opac, scales, rots, cov3D):
         st.geom = torch.empty(lib.b2gs_geom_bytes(P), dtype=torch.uint8, device=dev)
         st.image = torch.empty(lib.b2gs_image_bytes(W, H), dtype=torch.uint8, device=dev)
         keep = []
-        scene = _scene_struct(rs, P, M, means3D, sh, colors, opac, scales, rots, cov3D, keep)
+        scene = _scene_struct(rs, P, M, means3D, sh, colors, opac, scales, rots, cov3D, keep,
+                              sh_rest=sh_rest, raw=raw)
         ws = _lib.B2gsWorkspace(st.geom.data_ptr(), st.geom.numel(), st.image.data_ptr(),
                                 st.image.numel(), None, 0)
         out = _lib.B2gsForwardOut(color.data_ptr(), depth.data_ptr(), opacity.data_ptr(),
@@ -281,6 +286,93 @@ class _RasterizeGaussians(torch.autograd.Function):
         grad_theta = g_tau[3:].view(1, -1)
         return (g_means3D, g_means2D, g_sh, g_colors, g_opac, g_scales, g_rots, g_cov3D,
                 grad_theta if need[8] else None, grad_rho if need[9] else None, None)
+
+
+class GradSinks:
+    """Where the fused-activation rasterizer puts its per-Gaussian results in backward: the
+    optimiser's gradient buffers (accumulated in place, one `+=` per live Gaussian per view —
+    replaces autograd's AccumulateGrad adds) and, optionally, the densification statistics of
+    GaussianModel.add_densification_stats / max_radii2D (GS/scene/gaussian_model.py:691-695,
+    utils/slam_backend.py:277-284)."""
+
+    def __init__(self, xyz, f_dc, f_rest, opacity, scaling, rotation, xyz_gradient_accum=None,
+                 denom=None, max_radii2D=None):
+        self.xyz, self.f_dc, self.f_rest = xyz, f_dc, f_rest
+        self.opacity, self.scaling, self.rotation = opacity, scaling, rotation
+        self.xyz_gradient_accum, self.denom, self.max_radii2D = xyz_gradient_accum, denom, max_radii2D
+
+
+class _RasterizeRaw(torch.autograd.Function):
+    """Rasterizer over the RAW optimiser parameters with the activations fused into the
+    preprocess kernels: exp(_scaling), normalize(_rotation),
+    sigmoid(_opacity), cat(_features_dc, _features_rest) and their backward never exist as
+    separate kernels.  With `sinks`, gradients are accumulated straight into the given
+    buffers and autograd receives None for the six parameter inputs."""
+
+    @staticmethod
+    def forward(ctx, xyz, f_dc, f_rest, opacity, scaling, rotation, means2D, theta, rho, rs, sinks):
+        ins = (_f32c(xyz, "xyz"), _f32c(f_dc, "features_dc"), _f32c(f_rest, "features_rest"),
+               _f32c(opacity, "opacity"), _f32c(scaling, "scaling"), _f32c(rotation, "rotation"))
+        m3, dc, rest, op, sc, rot = ins
+        if m3 is None:
+            raise RuntimeError("xyz must be a non-empty CUDA tensor")
+        st, color, radii, depth, opac_img, n_touched = _forward_native(
+            rs, m3, dc, None, op, sc, rot, None, sh_rest=rest, raw=True)
+        ctx.raster_settings, ctx.state, ctx.sinks = rs, st, sinks
+        ctx.save_for_backward(*[t if t is not None else torch.empty(0) for t in ins], radii)
+        ctx.mark_non_differentiable(radii, n_touched)
+        return color, radii, depth, opac_img, n_touched
+
+    @staticmethod
+    def backward(ctx, g_color, g_radii, g_depth, g_opacity, g_nt):
+        rs, st, sinks = ctx.raster_settings, ctx.state, ctx.sinks
+        m3, dc, rest, op, sc, rot, radii = ctx.saved_tensors
+        rest = rest if rest.numel() else None
+        P, dev = m3.size(0), m3.device
+        H, W = int(rs.image_height), int(rs.image_width)
+        M = 1 + (rest.size(1) if rest is not None else 0)
+        f32 = dict(dtype=torch.float32, device=dev)
+        g_color = (g_color if g_color is not None else torch.zeros(3, H, W, **f32)).contiguous()
+        g_depth = (g_depth if g_depth is not None else torch.zeros(1, H, W, **f32)).contiguous()
+        need = ctx.needs_input_grad
+        with torch.cuda.device(dev):
+            stream = torch.cuda.current_stream().cuda_stream
+            g_tau = torch.empty(6, **f32)
+            scratch = torch.empty(lib.b2gs_backward_scratch_bytes(P), dtype=torch.uint8, device=dev)
+            g_m2d = torch.empty(P, 3, **f32) if need[6] else None
+            if sinks is not None:
+                outs = (sinks.xyz, sinks.f_dc, sinks.f_rest, sinks.opacity, sinks.scaling, sinks.rotation)
+                acc = 1
+            else:
+                outs = (torch.empty(P, 3, **f32), torch.empty(P, 1, 3, **f32),
+                        torch.empty(P, M - 1, 3, **f32) if M > 1 else None, torch.empty(P, 1, **f32),
+                        torch.empty(P, 3, **f32), torch.empty(P, 4, **f32))
+                acc = 0
+            o_xyz, o_dc, o_rest, o_op, o_sc, o_rot = outs
+            keep = []
+            scene = _scene_struct(rs, P, M, m3, dc, None, op, sc, rot, None, keep, sh_rest=rest, raw=True)
+            ws = _lib.B2gsWorkspace(ptr(st.geom), st.geom.numel(), ptr(st.image), st.image.numel(),
+                                    ptr(st.binning), st.binning.numel())
+            io = _lib.B2gsBackwardIO(
+                g_color.data_ptr(), g_depth.data_ptr(), radii.data_ptr(), o_xyz.data_ptr(), ptr(g_m2d),
+                o_op.data_ptr(), None, o_dc.data_ptr(), o_sc.data_ptr(), o_rot.data_ptr(), None,
+                g_tau.data_ptr(), scratch.data_ptr(), scratch.numel(), acc, ptr(o_rest),
+                ptr(sinks.xyz_gradient_accum) if sinks is not None else None,
+                ptr(sinks.denom) if sinks is not None else None,
+                ptr(sinks.max_radii2D) if sinks is not None else None)
+            check(lib.b2gs_backward(C.byref(scene), C.byref(ws), st.num_rendered, C.byref(io), stream))
+        grads = (None,) * 6 if sinks is not None else (o_xyz, o_dc, o_rest, o_op, o_sc, o_rot)
+        return grads + (g_m2d, g_tau[3:].view(1, -1) if need[7] else None,
+                        g_tau[:3].view(1, -1) if need[8] else None, None, None)
+
+
+def rasterize_gaussians_raw(xyz, features_dc, features_rest, opacity, scaling, rotation, raster_settings,
+                            means2D=None, theta=None, rho=None, sinks=None):
+    """5-tuple (color, radii, depth, opacity, n_touched) like GaussianRasterizer.forward, from the raw
+    parameters of GaussianModel (_xyz, _features_dc, _features_rest, _opacity, _scaling, _rotation)."""
+    e = lambda t: torch.Tensor([]) if t is None else t
+    return _RasterizeRaw.apply(xyz, features_dc, e(features_rest), opacity, scaling, rotation,
+                               e(means2D), e(theta), e(rho), raster_settings, sinks)
 
 
 def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,

@@ -157,6 +157,10 @@ def ref_render(viewpoint_camera, pc, pipe=None, bg_color=None, scaling_modifier=
     from types import SimpleNamespace
     cam = viewpoint_camera
     screenspace_points = torch.zeros_like(pc.get_xyz, requires_grad=True) + 0
+    try:
+        screenspace_points.retain_grad()  # gaussian_renderer/__init__.py:50-52
+    except Exception:
+        pass
     rs = SimpleNamespace(
         image_height=int(cam.image_height), image_width=int(cam.image_width),
         tanfovx=math.tan(cam.FoVx * 0.5), tanfovy=math.tan(cam.FoVy * 0.5), bg=bg_color,
@@ -187,6 +191,20 @@ class RefGaussianModel:
              dict(params=[self._scaling], lr=0.001 * spatial_lr_scale, name="scaling"),
              dict(params=[self._rotation], lr=0.001, name="rotation")]
         self.optimizer = torch.optim.Adam(l, lr=0.0, eps=1e-15)
+        # gaussian_splatting/scene/gaussian_model.py:233-235
+        n = xyz.shape[0]
+        self.xyz_gradient_accum = torch.zeros((n, 1), device=xyz.device)
+        self.denom = torch.zeros((n, 1), device=xyz.device)
+        self.max_radii2D = torch.zeros((n), device=xyz.device)
+
+    def _stats(self):
+        return self.xyz_gradient_accum, self.denom, self.max_radii2D
+
+    def add_densification_stats(self, viewspace_point_tensor, update_filter):
+        """gaussian_splatting/scene/gaussian_model.py:691-695, verbatim semantics."""
+        self.xyz_gradient_accum[update_filter] += torch.norm(
+            viewspace_point_tensor.grad[update_filter, :2], dim=-1, keepdim=True)
+        self.denom[update_filter] += 1
 
     get_xyz = property(lambda s: s._xyz)
     get_scaling = property(lambda s: torch.exp(s._scaling))

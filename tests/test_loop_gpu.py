@@ -165,3 +165,41 @@ def test_graph_mapping_step_matches_eager():
         assert abs(l0b - l1b) <= 5e-4 * abs(l0b)
     finally:
         rz.set_sync_free(False)
+
+
+@pytest.mark.parametrize("name", ["cfg1_plumbing", "tiny_sh3"])
+def test_fused_activation_render_matches_unfused(name):
+    """render_fused (raw parameters, activations + grad accumulation + densify stats inside the
+    kernels) == render (torch activations, autograd accumulation, torch statistics)."""
+    sc = syn.make_scene(name, device=DEV, n_views=2)
+    mk = lambda: mapping.GaussianModel(sc.xyz, sc.f_dc, sc.f_rest, sc.opacity, sc.scaling, sc.rotation,
+                                       sh_degree=sc.sh_degree)
+    ga, gb = mk(), mk()
+    gc, gd = syn.upstream_grads(sc, device=DEV)
+    outs = []
+    for g, fn in ((ga, mapping.render), (gb, mapping.render_fused)):
+        g._stats()
+        for cam in sc.cameras:                      # two views: exercises the accumulation
+            cam.cam_rot_delta.grad = cam.cam_trans_delta.grad = None
+            pkg = fn(cam, g, None, sc.bg)
+            torch.autograd.backward([pkg["render"], pkg["depth"]], [gc, gd])
+            if not pkg.get("stats_fused"):
+                vis = pkg["visibility_filter"]
+                g.max_radii2D[vis] = torch.max(g.max_radii2D[vis], pkg["radii"][vis])
+                g.add_densification_stats(pkg["viewspace_points"], vis)
+        outs.append((pkg, cam.cam_rot_delta.grad.clone(), cam.cam_trans_delta.grad.clone()))
+    (pa, ra, ta), (pb, rb, tb) = outs
+    # activations differ from torch's by <= 1 ulp, so a rare radius / tile flip is possible
+    assert float((pa["radii"] != pb["radii"]).float().mean()) < 1e-3
+    for k in ("render", "depth", "opacity"):
+        assert float(((pa[k] - pb[k]).abs() > 1e-5 + 1e-4 * pa[k].abs()).float().mean()) < 1e-3, k
+    scale = float(ga.flat_grad.abs().max())
+    bad = (ga.flat_grad - gb.flat_grad).abs() > 2e-4 * ga.flat_grad.abs() + 2e-5 * scale
+    assert float(bad.float().mean()) < 1e-3, "parameter gradients"
+    assert torch.allclose(ra, rb, rtol=1e-3, atol=1e-4 * float(ra.abs().max()))
+    assert torch.allclose(ta, tb, rtol=1e-3, atol=1e-4 * float(ta.abs().max()))
+    assert float((ga.denom != gb.denom).float().mean()) < 1e-3
+    assert float((ga.max_radii2D != gb.max_radii2D).float().mean()) < 1e-3
+    acc_scale = float(ga.xyz_gradient_accum.abs().max())
+    bad = (ga.xyz_gradient_accum - gb.xyz_gradient_accum).abs() > 1e-3 * ga.xyz_gradient_accum.abs() + 1e-4 * acc_scale
+    assert float(bad.float().mean()) < 1e-3

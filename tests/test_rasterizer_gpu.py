@@ -182,7 +182,7 @@ def test_sync_free_forward_matches_exact_and_flags_overflow():
         R = out0["state"].num_rendered
         assert torch.equal(e0["keys"][:R], e2["keys"][:R]) and torch.equal(e0["point_list"][:R], e2["point_list"][:R])
         for k in g0:
-            assert_grad_close(g2[k], g0[k], tol=1e-4, name="sync-free " + k)
+            assert_grad_close(g2[k], g0[k], tol=1e-4, name="sync-free " + k, outlier_frac=2e-5)
         # starve the capacity
         rz._SyncFree.cap[st.key] = 1000
         out3, _ = run_native(rs, inp)
