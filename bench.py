@@ -362,12 +362,8 @@ def run(args):
     if rank == 0 and world == 1 and not args.no_cpu_baseline and not impl_ref:
         cpu = cpu_oracle_sample()
 
-    if world > 1:
-        import torch.distributed as dist
-        dist.barrier()
-        dist.destroy_process_group()
     if rank != 0:
-        return
+        return finish(world, win)
     views_per_s = N_VIEWS * K / (ms / 1e3)
     h2d = sum(host[v][0].numel() * 4 + host[v][1].numel() * 4 for v in range(N_VIEWS))
     line = {
@@ -399,6 +395,23 @@ def run(args):
         line["rooflines_all"] = rooftab
         line["cpu_baseline"] = cpu
     print(json.dumps(line), flush=True)
+    finish(world, win)
+
+
+def finish(world, win):
+    """multi-rank teardown.  Captured CUDA graphs that contain NCCL kernels keep communicator
+    resources alive and destroy_process_group() then blocks, so the graphs are released first and
+    the process leaves through os._exit once every rank has reached the final barrier."""
+    if world == 1:
+        return
+    import torch.distributed as dist
+    torch.cuda.synchronize()
+    dist.barrier()
+    torch.cuda.synchronize()
+    win._g1 = win._g2 = None
+    sys.stdout.flush()
+    sys.stderr.flush()
+    os._exit(0)
 
 
 def run_reference_cpu(args, rank, world):
@@ -416,6 +429,9 @@ def run_reference_cpu(args, rank, world):
 
 
 def main():
+    if os.environ.get("B2GS_BENCH_WATCHDOG"):   # dev aid: dump every thread's stack and exit if stuck
+        import faulthandler
+        faulthandler.dump_traceback_later(int(os.environ["B2GS_BENCH_WATCHDOG"]), exit=True)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
