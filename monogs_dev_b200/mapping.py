@@ -35,9 +35,25 @@ class GaussianModel:
 
     def __init__(self, xyz, f_dc, f_rest, opacity, scaling, rotation, sh_degree=0,
                  spatial_lr_scale=6.0, lrs=None):
-        dev = xyz.device
         self.max_sh_degree = self.active_sh_degree = sh_degree
-        src = dict(xyz=xyz, f_dc=f_dc, f_rest=f_rest, opacity=opacity, scaling=scaling, rotation=rotation)
+        self.spatial_lr_scale = spatial_lr_scale
+        self.percent_dense = 0.01          # opt_params.percent_dense (GS/arguments/__init__.py)
+        lr = dict(xyz=0.00016 * spatial_lr_scale, f_dc=0.0025, f_rest=0.0025 / 20.0, opacity=0.05,
+                  scaling=0.001 * spatial_lr_scale, rotation=0.001)
+        lr.update(lrs or {})
+        self._lr = lr
+        self.optimizer = None
+        self._allocate(dict(xyz=xyz, f_dc=f_dc, f_rest=f_rest, opacity=opacity, scaling=scaling,
+                            rotation=rotation))
+
+    def _allocate(self, src, moments=None, steps=None):
+        """(re)build the four packed arenas (parameters, gradients, Adam m / v) from per-group
+        tensors; used at construction and after densify / prune (the reference re-wraps six
+        nn.Parameters and twelve moment tensors, GS/scene/gaussian_model.py:468-555)."""
+        dev = src["xyz"].device
+        capturable = bool(getattr(self.optimizer, "capturable", False))
+        if self.optimizer is not None:
+            self._lr = {g["name"]: g["lr"] for g in self.optimizer.param_groups}
         sizes = [src[k].numel() for k in _GROUPS]
         offs, total = [], 0
         for n in sizes:
@@ -54,16 +70,27 @@ class GaussianModel:
             p = torch.nn.Parameter(view)
             p.grad = self.flat_grad[o:o + n].view(src[k].shape)
             self._params[k] = p
-        lr = dict(xyz=0.00016 * spatial_lr_scale, f_dc=0.0025, f_rest=0.0025 / 20.0, opacity=0.05,
-                  scaling=0.001 * spatial_lr_scale, rotation=0.001)
-        lr.update(lrs or {})
-        self.optimizer = FusedAdam([dict(params=[self._params[k]], lr=lr[k], name=k) for k in _GROUPS],
-                                   lr=0.0, eps=1e-15)
+        self.optimizer = FusedAdam([dict(params=[self._params[k]], lr=self._lr[k], name=k) for k in _GROUPS],
+                                   lr=0.0, eps=1e-15, capturable=capturable)
         for k, o, n in zip(_GROUPS, offs, sizes):   # Adam moments are views of the arenas too
             st = self.optimizer.state[self._params[k]]
-            st["step"] = 0
+            st["step"] = (steps or {}).get(k, 0)
             st["exp_avg"] = self.flat_m[o:o + n].view(src[k].shape)
             st["exp_avg_sq"] = self.flat_v[o:o + n].view(src[k].shape)
+            if moments is not None:
+                st["exp_avg"].copy_(moments[k][0])
+                st["exp_avg_sq"].copy_(moments[k][1])
+        for a in ("xyz_gradient_accum", "denom", "max_radii2D"):
+            if hasattr(self, a):
+                delattr(self, a)
+
+    def densify_and_prune(self, max_grad, min_opacity, extent, max_screen_size, **kw):
+        from .densify import densify_and_prune
+        return densify_and_prune(self, max_grad, min_opacity, extent, max_screen_size, **kw)
+
+    def prune_points(self, mask):
+        from .densify import prune_points
+        return prune_points(self, mask)
 
     _xyz = property(lambda s: s._params["xyz"])
     _features_dc = property(lambda s: s._params["f_dc"])
@@ -358,3 +385,135 @@ class MappingWindow:
         loss = self._graph_step() if self.cuda_graph else self._eager_step()
         self._steps += 1
         return loss
+
+
+def render_pose_only(viewpoint_camera, pc, pipe=None, bg_color=None, scaling_modifier=1.0):
+    """render() for tracking (BASELINE config 2): the map is frozen, only the camera deltas
+    (theta / rho -> dL_dtau) receive gradients, so the backward skips every per-Gaussian
+    gradient output it can (SURVEY.md §7.2 'pose-only mode')."""
+    cam = viewpoint_camera
+    rs = GaussianRasterizationSettings(
+        image_height=int(cam.image_height), image_width=int(cam.image_width),
+        tanfovx=math.tan(cam.FoVx * 0.5), tanfovy=math.tan(cam.FoVy * 0.5), bg=bg_color,
+        scale_modifier=scaling_modifier, viewmatrix=cam.world_view_transform,
+        projmatrix=cam.full_proj_transform, projmatrix_raw=cam.projection_matrix,
+        sh_degree=pc.active_sh_degree, campos=cam.camera_center, prefiltered=False, debug=False)
+    d = lambda t: t.detach()
+    image, radii, depth, opacity, n_touched = rasterize_gaussians_raw(
+        d(pc._xyz), d(pc._features_dc), d(pc._features_rest), d(pc._opacity), d(pc._scaling),
+        d(pc._rotation), rs, theta=cam.cam_rot_delta, rho=cam.cam_trans_delta, sinks=None)
+    return {"render": image, "viewspace_points": None, "visibility_filter": radii > 0, "radii": radii,
+            "depth": depth, "opacity": opacity, "n_touched": n_touched}
+
+
+class TrackingLoop:
+    """FrontEnd.tracking() (utils/slam_frontend.py:128-196): `iters` iterations of
+    render -> tracking loss -> backward -> Adam over (cam_rot_delta, cam_trans_delta, exposure_a,
+    exposure_b) -> update_pose, on one GPU (tracking does not shard).
+
+    The loop owns ONE persistent camera and ground-truth buffers; `track()` loads a frame into
+    them.  With cuda_graph=True one iteration is captured once and replayed `iters` times per
+    frame with no host synchronisation inside the loop (the reference syncs every iteration for
+    its convergence test); binning overflow is checked once per frame and the frame re-run."""
+
+    def __init__(self, gaussians, camera, bg, lr_rot=0.003, lr_trans=0.001, lr_exposure=0.01, iters=100,
+                 cuda_graph=False, render_fn=None, loss_fn=None, adam_cls=FusedAdam):
+        self.g, self.cam, self.bg, self.iters = gaussians, camera, bg, iters
+        self.render_fn = render_fn or render_pose_only
+        self.loss_fn = loss_fn or get_loss_tracking_rgbd
+        self.cuda_graph = bool(cuda_graph)
+        dev, H, W = bg.device, camera.image_height, camera.image_width
+        self.gt_image = torch.zeros(3, H, W, device=dev)
+        self.gt_depth = torch.zeros(1, H, W, device=dev)
+        groups = [dict(params=[camera.cam_rot_delta], lr=lr_rot), dict(params=[camera.cam_trans_delta], lr=lr_trans),
+                  dict(params=[camera.exposure_a], lr=lr_exposure), dict(params=[camera.exposure_b], lr=lr_exposure)]
+        kw = dict(capturable=True) if (self.cuda_graph and adam_cls is FusedAdam) else {}
+        self.opt = adam_cls(groups, lr=0.0, eps=1e-8, **kw)
+        self._graph = None
+        self.graph_launches = 0
+        self.pkg = None
+        self._ever, self._key = None, None
+
+    def _iteration(self, check_converged=False):
+        cam = self.cam
+        pkg = self.render_fn(cam, self.g, None, self.bg)
+        st = getattr(pkg["render"].grad_fn, "state", None)
+        if st is not None and st.status is not None:   # sticky (max instances, overflow flag) of the frame
+            if self._ever is None:
+                self._ever = torch.zeros_like(st.status)
+            self._ever.copy_(torch.maximum(self._ever, st.status))
+            self._key = st.key
+        loss = self.loss_fn(pkg["render"], pkg["depth"], pkg["opacity"], cam, self.gt_image, self.gt_depth)
+        loss.backward()
+        self.opt.step()
+        self.opt.zero_grad(set_to_none=False)
+        try:
+            conv = cam.update_pose(check_converged=check_converged)
+        except TypeError:
+            conv = cam.update_pose()
+        return pkg, loss.detach(), conv
+
+    def _reset_optimizer(self):
+        for st in self.opt.state.values():
+            if "exp_avg" in st:
+                st["exp_avg"].zero_()
+                st["exp_avg_sq"].zero_()
+                st["step"] = st["step"].zero_() if torch.is_tensor(st["step"]) else 0
+        if getattr(self.opt, "_step_dev", None) is not None:
+            self.opt._step_dev.zero_()
+
+    def load_frame(self, R, T, gt_image, gt_depth, exposure=(0.0, 0.0)):
+        """viewpoint.update_RT(prev.R, prev.T) + a fresh pose optimizer (slam_frontend.py:129-161)."""
+        self.cam.update_RT(R, T)
+        self.gt_image.copy_(gt_image, non_blocking=True)
+        self.gt_depth.copy_(gt_depth, non_blocking=True)
+        with torch.no_grad():
+            self.cam.cam_rot_delta.zero_(); self.cam.cam_trans_delta.zero_()
+            self.cam.exposure_a.fill_(exposure[0]); self.cam.exposure_b.fill_(exposure[1])
+        self._reset_optimizer()
+
+    def track(self, iters=None, check_converged=False):
+        """runs the loop on the loaded frame; returns the last render package."""
+        from . import rasterizer as rz
+        from ._lib import lib
+        iters = self.iters if iters is None else iters
+        if not self.cuda_graph:
+            for _ in range(iters):
+                self.pkg, self.loss, conv = self._iteration(check_converged)
+                if check_converged and conv:
+                    break
+            return self.pkg
+        rz.set_sync_free(True, rz._SyncFree.headroom)
+        done = 0
+        if self._graph is None:
+            s = torch.cuda.Stream()
+            s.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(s):
+                for _ in range(min(3, iters)):      # exact sizing, optimizer state, .grad buffers
+                    self.pkg, self.loss, _ = self._iteration()
+                    done += 1
+            torch.cuda.current_stream().wait_stream(s)
+            torch.cuda.synchronize()
+            l0 = lib.b2gs_kernel_launches()
+            self._graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self._graph):
+                self.pkg, self.loss, _ = self._iteration()
+            self.graph_launches = lib.b2gs_kernel_launches() - l0
+        snap = self.cam.state.clone(), [p.detach().clone() for g in self.opt.param_groups for p in g["params"]]
+        for _ in range(iters - done):
+            self._graph.replay()
+        from types import SimpleNamespace
+        worst = SimpleNamespace(status=self._ever, key=self._key) if self._ever is not None else None
+        over = rz.check_overflow([worst])           # one host sync per frame
+        if self._ever is not None:
+            self._ever.zero_()
+        if over:
+            # capacity was exceeded somewhere in the loop: restore the frame, re-capture, re-run
+            self.cam.state.copy_(snap[0]); self.cam._host_RT = None
+            with torch.no_grad():
+                for p, q in zip([p for g in self.opt.param_groups for p in g["params"]], snap[1]):
+                    p.copy_(q)
+            self._reset_optimizer()
+            self._graph = None
+            return self.track(iters - done, check_converged)
+        return self.pkg

@@ -344,9 +344,12 @@ class _RasterizeRaw(torch.autograd.Function):
                 outs = (sinks.xyz, sinks.f_dc, sinks.f_rest, sinks.opacity, sinks.scaling, sinks.rotation)
                 acc = 1
             else:
-                outs = (torch.empty(P, 3, **f32), torch.empty(P, 1, 3, **f32),
-                        torch.empty(P, M - 1, 3, **f32) if M > 1 else None, torch.empty(P, 1, **f32),
-                        torch.empty(P, 3, **f32), torch.empty(P, 4, **f32))
+                # pose-only (tracking shape): parameter inputs that need no gradient get no output
+                w_sh, w_sr = need[1] or need[2], need[4] or need[5]
+                outs = (torch.empty(P, 3, **f32), torch.empty(P, 1, 3, **f32) if w_sh else None,
+                        torch.empty(P, M - 1, 3, **f32) if (M > 1 and w_sh) else None,
+                        torch.empty(P, 1, **f32), torch.empty(P, 3, **f32) if w_sr else None,
+                        torch.empty(P, 4, **f32) if w_sr else None)
                 acc = 0
             o_xyz, o_dc, o_rest, o_op, o_sc, o_rot = outs
             keep = []
@@ -355,13 +358,14 @@ class _RasterizeRaw(torch.autograd.Function):
                                     ptr(st.binning), st.binning.numel())
             io = _lib.B2gsBackwardIO(
                 g_color.data_ptr(), g_depth.data_ptr(), radii.data_ptr(), o_xyz.data_ptr(), ptr(g_m2d),
-                o_op.data_ptr(), None, o_dc.data_ptr(), o_sc.data_ptr(), o_rot.data_ptr(), None,
+                o_op.data_ptr(), None, ptr(o_dc), ptr(o_sc), ptr(o_rot), None,
                 g_tau.data_ptr(), scratch.data_ptr(), scratch.numel(), acc, ptr(o_rest),
                 ptr(sinks.xyz_gradient_accum) if sinks is not None else None,
                 ptr(sinks.denom) if sinks is not None else None,
                 ptr(sinks.max_radii2D) if sinks is not None else None)
             check(lib.b2gs_backward(C.byref(scene), C.byref(ws), st.num_rendered, C.byref(io), stream))
-        grads = (None,) * 6 if sinks is not None else (o_xyz, o_dc, o_rest, o_op, o_sc, o_rot)
+        grads = (None,) * 6 if sinks is not None else tuple(
+            o if n else None for o, n in zip((o_xyz, o_dc, o_rest, o_op, o_sc, o_rot), need[:6]))
         return grads + (g_m2d, g_tau[3:].view(1, -1) if need[7] else None,
                         g_tau[:3].view(1, -1) if need[8] else None, None, None)
 

@@ -203,3 +203,65 @@ def test_fused_activation_render_matches_unfused(name):
     acc_scale = float(ga.xyz_gradient_accum.abs().max())
     bad = (ga.xyz_gradient_accum - gb.xyz_gradient_accum).abs() > 1e-3 * ga.xyz_gradient_accum.abs() + 1e-4 * acc_scale
     assert float(bad.float().mean()) < 1e-3
+
+
+def test_tracking_loop_recovers_pose_and_graph_matches_eager():
+    """BASELINE config 2 shape at reduced size: pose-only tracking converges towards the true
+    pose, and the CUDA-graph loop gives the eager loop's result."""
+    try:
+        sc = syn.make_scene("cfg1_plumbing", device=DEV, n_views=1)
+        gm = mapping.GaussianModel(sc.xyz, sc.f_dc, sc.f_rest, sc.opacity, sc.scaling, sc.rotation,
+                                   sh_degree=sc.sh_degree)
+        true_w2c = syn.se3_exp(torch.tensor([0.02, -0.015, 0.01, 0.004, -0.006, 0.003]))
+        cam_true = syn.Camera(sc.W, sc.H, 300.0, 300.0, 159.5, 119.5, w2c=true_w2c, device=DEV)
+        with torch.no_grad():
+            gt = mapping.render_pose_only(cam_true, gm, None, sc.bg)
+        res = []
+        for graph in (False, True):
+            cam = syn.Camera(sc.W, sc.H, 300.0, 300.0, 159.5, 119.5, device=DEV)
+            loop = mapping.TrackingLoop(gm, cam, sc.bg, iters=60, cuda_graph=graph)
+            loop.load_frame(torch.eye(3), torch.zeros(3), gt["render"], gt["depth"])
+            loop.track()
+            res.append((cam.R.clone(), cam.T.clone(), float(loop.loss)))
+            if graph:
+                assert loop._graph is not None and loop.graph_launches > 0
+        e0 = float((torch.zeros(3) - true_w2c[:3, 3]).norm())
+        for R, T, _ in res:
+            assert float((T - true_w2c[:3, 3]).norm()) < 0.5 * e0, "tracking did not approach the true pose"
+        assert torch.allclose(res[0][1], res[1][1], atol=2e-3) and torch.allclose(res[0][0], res[1][0], atol=2e-3)
+        # no gradient leaks into the frozen map
+        assert float(gm.flat_grad.abs().max()) == 0.0
+    finally:
+        rz.set_sync_free(False)
+
+
+def test_densify_prune_config4_size_on_gpu():
+    """BASELINE config 4: one densify_and_prune(max_grad=2e-4, min_opacity=0.7, extent=6.0,
+    max_screen_size=20) on a 2M-Gaussian model with synthetic statistics, on the device."""
+    P = 2_000_000
+    g = torch.Generator().manual_seed(1238)
+    r = lambda *s: torch.randn(*s, generator=g).to(DEV)
+    gm = mapping.GaussianModel(r(P, 3), r(P, 1, 3), torch.zeros(P, 0, 3, device=DEV), 1.5 * r(P, 1),
+                               torch.log(0.06 * torch.exp(0.9 * r(P, 3))), r(P, 4))
+    acc, den, _ = gm._stats()
+    acc.copy_(4e-4 * torch.rand(P, 1, generator=g).to(DEV))
+    den.fill_(1.0)
+    gm.flat_m.fill_(0.5)
+    before = gm._xyz.detach().clone()
+    op_before = torch.sigmoid(gm._opacity.detach()).reshape(-1)
+    nc, ns, npr = gm.densify_and_prune(2e-4, 0.7, 6.0, 20)
+    n = gm._xyz.shape[0]
+    assert n == P + nc + ns - npr and nc > 0 and ns > 0 and npr > 0
+    assert bool((torch.sigmoid(gm._opacity) >= 0.7).all()), "pruned by opacity"
+    assert bool((torch.exp(gm._scaling).max(1).values <= 0.6).all()), "pruned by world size"
+    assert gm.flat.is_cuda and gm.flat_grad.numel() == gm.flat.numel()
+    # surviving originals come first, in order, with their moments; new rows have zero moments
+    m_xyz = gm.optimizer.state[gm._xyz]["exp_avg"]
+    n_old = int((m_xyz[:, 0] != 0).sum())
+    assert bool((m_xyz[:n_old] == 0.5).all()) and bool((m_xyz[n_old:] == 0).all())
+    surv = torch.nonzero(op_before >= 0.7).squeeze(1)
+    assert n_old <= surv.numel()
+    # an optimizer step works on the rebuilt arena
+    gm.flat_grad.fill_(1e-3)
+    gm.optimizer.step()
+    assert bool(torch.isfinite(gm.flat).all())
