@@ -254,6 +254,13 @@ B2GS_API int b2gs_loss_backward(const B2gsLossArgs* args, const float* dL_dloss,
                        float* dL_ddepth, float* dL_dopacity, float* dL_dexposure, void* scratch,
                        size_t scratch_bytes, void* stream);
 
+/* Isotropic-scale regulariser of the mapping loss (utils/slam_backend.py:229-231):
+ * loss[0] = weight * mean(|exp(raw) - mean_row(exp(raw))|) over the [P,3] log-scales, and its
+ * gradient wrt the RAW log-scales ADDED to dL_draw_scaling (may be NULL: value only). */
+B2GS_API int b2gs_scale_regulariser(int32_t P, const float* raw_scaling, float weight,
+                           float* dL_draw_scaling, float* loss, void* scratch, size_t scratch_bytes,
+                           void* stream);
+
 /* update_pose (utils/pose_utils.py:76-93) on the device: T_w2c <- Exp((trans_delta, rot_delta))
  * T_w2c; refreshes viewmatrix, full projection and camera centre in place, zeroes the deltas.
  * cam_state: float[64] = R[9] row-major | T[3] | pad[4] | viewmatrix[16] | projmatrix[16] |

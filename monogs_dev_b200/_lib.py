@@ -104,6 +104,8 @@ SYMBOLS = {
     "b2gs_loss_forward": (C.c_int, [C.POINTER(B2gsLossArgs), C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     "b2gs_loss_backward": (C.c_int, [C.POINTER(B2gsLossArgs), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                      C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "b2gs_scale_regulariser": (C.c_int, [C.c_int32, C.c_void_p, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p,
+                                         C.c_size_t, C.c_void_p]),
     "b2gs_pose_update": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "b2gs_adam_step_dev": (C.c_int, [C.POINTER(B2gsAdamSegment), C.c_int32, C.c_void_p, C.c_float,
                                      C.c_float, C.c_float, C.c_void_p]),

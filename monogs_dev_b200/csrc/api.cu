@@ -157,7 +157,7 @@ extern "C" size_t b2gs_binning_bytes(int64_t R, int32_t W, int32_t H) {
   return t;
 }
 extern "C" size_t b2gs_backward_scratch_bytes(int32_t P) {
-  const size_t blocks = ((size_t)(P > 0 ? P : 1) + 255) / 256;
+  const size_t blocks = ((size_t)(P > 0 ? P : 1) + 127) / 128;
   return align_up(((size_t)(P > 0 ? P : 1) * ACC_STRIDE + blocks * 8) * sizeof(float), 256);
 }
 
@@ -178,7 +178,7 @@ static int forward_front(const B2gsScene& s, const B2gsWorkspace* ws, const B2gs
     return B2GS_ERR_WORKSPACE;
   }
   const size_t tiles = (size_t)((s.W + TILE - 1) / TILE) * ((s.H + TILE - 1) / TILE);
-  B2GS_CUDA(cudaMemsetAsync(im.cursor, 0, sizeof(uint32_t) * tiles, st));
+  B2GS_CUDA(cudaMemsetAsync(im.cursor, 0, sizeof(uint32_t) * tiles * CURSOR_STRIDE, st));
   int rc = launch_preprocess_fwd(s, g, im, out->radii, out->n_touched, st);
   if (rc) return rc;
   rc = launch_tile_scan(s, im, cap, st);

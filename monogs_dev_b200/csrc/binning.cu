@@ -44,7 +44,7 @@ ImageWS carve_image(void* base, int32_t W, int32_t H, size_t* total) {
   im.final_T = c.take<float>(N);
   im.n_contrib = c.take<uint32_t>(N);
   im.ranges = c.take<uint2>(tiles);
-  im.cursor = c.take<uint32_t>(tiles);
+  im.cursor = c.take<uint32_t>(tiles * CURSOR_STRIDE);
   im.status = c.take<uint32_t>(8);
   if (total) *total = c.total();
   return im;
@@ -74,7 +74,7 @@ tile_scan_kernel(uint32_t tiles, long long cap, uint32_t* __restrict__ cursor,
   const uint32_t per = (tiles + SCAN_THREADS - 1) / SCAN_THREADS;
   const uint32_t lo = min(tiles, (uint32_t)tid * per), hi = min(tiles, lo + per);
   unsigned long long mine = 0;
-  for (uint32_t t = lo; t < hi; ++t) mine += cursor[t];
+  for (uint32_t t = lo; t < hi; ++t) mine += cursor[t * CURSOR_STRIDE];
   // block-wide exclusive scan of `mine` (64-bit: the total may exceed 2^32)
   unsigned long long incl = mine;
 #pragma unroll
@@ -105,10 +105,10 @@ tile_scan_kernel(uint32_t tiles, long long cap, uint32_t* __restrict__ cursor,
   const bool over = s_total != 0u;
   uint32_t run = (uint32_t)(s_w64[warp] + incl - mine);
   for (uint32_t t = lo; t < hi; ++t) {
-    const uint32_t c = cursor[t];
+    const uint32_t c = cursor[t * CURSOR_STRIDE];
     // on overflow every tile is rendered empty; the caller sees status[1] and retries
     ranges[t] = (c && !over) ? make_uint2(run, run + c) : make_uint2(0u, 0u);
-    cursor[t] = run;
+    cursor[t * CURSOR_STRIDE] = run;
     run += c;
   }
 }
@@ -142,11 +142,10 @@ scatter_instances_kernel(int P, uint32_t gx, const uint32_t* __restrict__ tiles_
       depth_bits = __float_as_uint(rgbd[i].w);
     }
   }
-  warp_expand_rects(s_rects[threadIdx.x >> 5], lane, touched, org, w, depth_bits, (uint32_t)i, gx,
-                    [&](uint32_t tile, uint32_t d, uint32_t id) {
-                      const uint32_t slot = atomicAdd(&cursor[tile], 1u);
-                      keys[slot] = ((uint64_t)d << 32) | id;
-                    });
+  warp_expand_rects<8>(
+      s_rects[threadIdx.x >> 5], lane, touched, org, w, depth_bits, (uint32_t)i, gx,
+      [&](uint32_t tile) { return atomicAdd(&cursor[tile * CURSOR_STRIDE], 1u); },
+      [&](uint32_t slot, uint32_t d, uint32_t id) { keys[slot] = ((uint64_t)d << 32) | id; });
 }
 
 // ---- per-tile sort -------------------------------------------------------------------

@@ -20,11 +20,14 @@ struct WarpRects {
   uint32_t b[32];    // payload (Gaussian id)
 };
 
-// f(tile, a, b) is called once per (Gaussian, tile) instance.  All 32 lanes must call.
-template <class F>
+// For every (Gaussian, tile) instance:  token = issue(tile);  ...;  commit(token, a, b).
+// Instances are handled U per lane per trip with all `issue` calls ahead of the `commit`s, so
+// that U atomics (with return) are in flight per lane instead of one: a huge splat spread over
+// the warp is a chain of total/32 dependent L2 round trips otherwise.  All 32 lanes must call.
+template <int U, class Issue, class Commit>
 __device__ __forceinline__ void warp_expand_rects(WarpRects& s, int lane, uint32_t touched,
                                                   uint32_t org, uint32_t w, uint32_t a, uint32_t b,
-                                                  uint32_t gx, F f) {
+                                                  uint32_t gx, Issue issue, Commit commit) {
   uint32_t pre = touched;
 #pragma unroll
   for (int d = 1; d < 32; d <<= 1) {
@@ -39,17 +42,31 @@ __device__ __forceinline__ void warp_expand_rects(WarpRects& s, int lane, uint32
   s.a[lane] = a;
   s.b[lane] = b;
   __syncwarp();
-  for (uint32_t k = lane; k < total; k += 32) {
-    int lo = 0;  // smallest j with pre[j] > k
+  for (uint32_t k0 = lane; k0 < total; k0 += 32 * U) {
+    int lo[U];
+    uint32_t token[U];
 #pragma unroll
-    for (int step = 16; step > 0; step >>= 1) {
-      if (s.pre[lo + step - 1] <= k) lo += step;
+    for (int u = 0; u < U; ++u) {
+      const uint32_t k = k0 + 32 * u;
+      lo[u] = -1;
+      if (k < total) {
+        int l = 0;  // smallest j with pre[j] > k
+#pragma unroll
+        for (int step = 16; step > 0; step >>= 1) {
+          if (s.pre[l + step - 1] <= k) l += step;
+        }
+        const uint32_t local = k - (l ? s.pre[l - 1] : 0u);
+        const uint32_t ww = s.w[l];
+        const uint32_t o = s.org[l];
+        const uint32_t dy = local / ww, dx = local - dy * ww;
+        lo[u] = l;
+        token[u] = issue(((o >> 16) + dy) * gx + (o & 0xffffu) + dx);
+      }
     }
-    const uint32_t local = k - (lo ? s.pre[lo - 1] : 0u);
-    const uint32_t ww = s.w[lo];
-    const uint32_t o = s.org[lo];
-    const uint32_t dy = local / ww, dx = local - dy * ww;
-    f(((o >> 16) + dy) * gx + (o & 0xffffu) + dx, s.a[lo], s.b[lo]);
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if (lo[u] >= 0) commit(token[u], s.a[lo[u]], s.b[lo[u]]);
+    }
   }
   __syncwarp();
 }

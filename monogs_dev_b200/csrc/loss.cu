@@ -357,3 +357,65 @@ extern "C" int b2gs_pose_update(float* cam_state, const float* projmatrix_raw, f
   B2GS_LAUNCH_CHECK(st, 0);
   return B2GS_OK;
 }
+
+// ---- isotropic-scale regulariser -------------------------------------------------------
+// utils/slam_backend.py:229-231:  scaling = exp(_scaling);
+//   loss += 10 * |scaling - scaling.mean(dim=1, keepdim)|.mean()
+// Forward value and the gradient wrt the RAW log-scales in one pass, accumulated into the
+// optimiser's gradient buffer (replaces ~8 torch kernels fwd + their autograd replay).
+namespace b2gs {
+__global__ void __launch_bounds__(LOSS_THREADS)
+iso_reg_kernel(int P, const float* __restrict__ raw_scaling, float weight,
+               float* __restrict__ dL_draw, float* __restrict__ partial) {
+  __shared__ float s_red[LOSS_THREADS / 32];
+  const float w = weight / (3.0f * (float)P);
+  float acc = 0.f;
+  for (int i = blockIdx.x * LOSS_THREADS + threadIdx.x; i < P; i += gridDim.x * LOSS_THREADS) {
+    const float s0 = expf(raw_scaling[3 * i]), s1 = expf(raw_scaling[3 * i + 1]), s2 = expf(raw_scaling[3 * i + 2]);
+    const float m = (s0 + s1 + s2) / 3.0f;
+    const float d0 = s0 - m, d1 = s1 - m, d2 = s2 - m;
+    acc += fabsf(d0) + fabsf(d1) + fabsf(d2);
+    if (dL_draw) {
+      const float g0 = sgnf(d0), g1 = sgnf(d1), g2 = sgnf(d2);
+      const float gm = (g0 + g1 + g2) / 3.0f;          // through the mean
+      dL_draw[3 * i] += w * (g0 - gm) * s0;             // d exp(x) = exp(x) dx
+      dL_draw[3 * i + 1] += w * (g1 - gm) * s1;
+      dL_draw[3 * i + 2] += w * (g2 - gm) * s2;
+    }
+  }
+  acc = block_sum(acc, s_red);
+  if (threadIdx.x == 0) partial[blockIdx.x] = acc;
+}
+
+__global__ void __launch_bounds__(LOSS_THREADS)
+iso_reg_finalize_kernel(int blocks, float scale, const float* __restrict__ partial, float* __restrict__ loss) {
+  __shared__ double s_a[LOSS_THREADS];
+  double ra = 0.0;
+  for (int i = threadIdx.x; i < blocks; i += LOSS_THREADS) ra += partial[i];
+  s_a[threadIdx.x] = ra;
+  __syncthreads();
+  for (int d = LOSS_THREADS / 2; d > 0; d >>= 1) {
+    if (threadIdx.x < d) s_a[threadIdx.x] += s_a[threadIdx.x + d];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) loss[0] = (float)(s_a[0] * (double)scale);
+}
+}  // namespace b2gs
+
+extern "C" int b2gs_scale_regulariser(int32_t P, const float* raw_scaling, float weight,
+                                      float* dL_draw_scaling, float* loss, void* scratch,
+                                      size_t scratch_bytes, void* stream) {
+  if (P <= 0 || !raw_scaling || !loss || !scratch || scratch_bytes < b2gs_loss_scratch_bytes(P)) {
+    set_error("b2gs_scale_regulariser: bad arguments");
+    return B2GS_ERR_INVALID;
+  }
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const int blocks = loss_blocks(P);
+  float* partial = reinterpret_cast<float*>(scratch);
+  B2GS_PROF("iso_reg", st);
+  iso_reg_kernel<<<blocks, LOSS_THREADS, 0, st>>>(P, raw_scaling, weight, dL_draw_scaling, partial);
+  B2GS_LAUNCH_CHECK(st, 0);
+  iso_reg_finalize_kernel<<<1, LOSS_THREADS, 0, st>>>(blocks, weight / (3.0f * (float)P), partial, loss);
+  B2GS_LAUNCH_CHECK(st, 0);
+  return B2GS_OK;
+}

@@ -119,7 +119,7 @@ __device__ __forceinline__ V3 sh_backward(int deg, int M, const float* __restric
 }
 
 template <bool RAW>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(128, 6)
 preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
                       const int32_t* __restrict__ radii, const float* __restrict__ shs,
                       const uint8_t* __restrict__ clamped, const float* __restrict__ scales,
@@ -138,7 +138,7 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
                       float* __restrict__ st_grad_accum, float* __restrict__ st_denom,
                       float* __restrict__ st_max_radii) {
   __shared__ float s_view[16], s_proj[16];
-  __shared__ float s_tau[8][6];
+  __shared__ float s_tau[4][6];
   if (threadIdx.x < 16) s_view[threadIdx.x] = viewmatrix[threadIdx.x];
   else if (threadIdx.x < 32) s_proj[threadIdx.x - 16] = projmatrix[threadIdx.x - 16];
   __syncthreads();
@@ -460,7 +460,7 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
   if (threadIdx.x < 6) {
     float v = 0.f;
 #pragma unroll
-    for (int w = 0; w < 8; ++w) v += s_tau[w][threadIdx.x];
+    for (int w = 0; w < 4; ++w) v += s_tau[w][threadIdx.x];
     tau_partials[(size_t)blockIdx.x * 8 + threadIdx.x] = v;
   }
 }
@@ -495,11 +495,11 @@ int launch_preprocess_bwd(const B2gsScene& s, const GeomWS& g, const B2gsBackwar
                           const float* acc, cudaStream_t st) {
   const float focal_y = s.H / (2.0f * s.tan_fovy);
   const float focal_x = s.W / (2.0f * s.tan_fovx);
-  const int blocks = (s.P + 255) / 256;
+  const int blocks = (s.P + 127) / 128;
   float* partials = const_cast<float*>(acc) + (size_t)s.P * ACC_STRIDE;  // scratch tail
   B2GS_PROF("preprocess_bwd", st);
   auto kern = s.raw_params ? preprocess_bwd_kernel<true> : preprocess_bwd_kernel<false>;
-  kern<<<blocks, 256, 0, st>>>(
+  kern<<<blocks, 128, 0, st>>>(
       s.P, s.D, s.M, s.means3D, io.radii, s.shs, g.clamped, s.scales, s.rotations, s.scale_modifier,
       s.cov3D_precomp, s.viewmatrix, s.projmatrix, s.projmatrix_raw, s.campos, focal_x, focal_y,
       s.tan_fovx, s.tan_fovy, acc, io.dL_dmeans3D, io.dL_dmeans2D, io.dL_dopacity, io.dL_dcolors,

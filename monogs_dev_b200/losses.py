@@ -116,3 +116,21 @@ def get_loss_tracking_rgb(image, opacity, viewpoint, gt_image, rgb_boundary_thre
     """utils/slam_utils.py:56-72 (monocular)."""
     return fused_loss(TRACKING_RGB, image, None, opacity, viewpoint.exposure_a, viewpoint.exposure_b,
                       gt_image, None, grad_mask, 0.95, rgb_boundary_threshold)
+
+
+def scale_regulariser(raw_scaling, grad_sink=None, weight=10.0):
+    """10 * |exp(s) - mean_row(exp(s))|.mean() (utils/slam_backend.py:229-231) as one kernel; the
+    gradient wrt the raw log-scales is ADDED to `grad_sink` (the optimiser's gradient buffer) — not
+    an autograd op: the caller adds the returned value to the reported loss."""
+    if not raw_scaling.is_cuda:
+        raise RuntimeError("scale_regulariser needs CUDA tensors: libb2gs has no CPU path")
+    s = raw_scaling.detach()
+    s = s if s.is_contiguous() else s.contiguous()
+    dev = s.device
+    with torch.cuda.device(dev):
+        out = torch.empty((), dtype=torch.float32, device=dev)
+        scratch = torch.empty(lib.b2gs_loss_scratch_bytes(s.shape[0]), dtype=torch.uint8, device=dev)
+        check(lib.b2gs_scale_regulariser(s.shape[0], s.data_ptr(), float(weight), ptr(grad_sink),
+                                         out.data_ptr(), scratch.data_ptr(), scratch.numel(),
+                                         torch.cuda.current_stream().cuda_stream))
+    return out

@@ -21,7 +21,7 @@ import torch
 import torch.distributed as dist
 
 from .adam import FusedAdam
-from .losses import get_loss_mapping_rgbd, get_loss_tracking_rgbd  # fused kernels (csrc/loss.cu)
+from .losses import get_loss_mapping_rgbd, get_loss_tracking_rgbd, scale_regulariser  # csrc/loss.cu
 from .rasterizer import (GaussianRasterizationSettings, GaussianRasterizer, GradSinks,
                          rasterize_gaussians_raw)
 
@@ -232,6 +232,7 @@ class MappingWindow:
         self.optimize_pose = optimize_pose
         self.cuda_graph = bool(cuda_graph)
         self.densify_stats = bool(densify_stats)
+        self.fused_reg = isinstance(gaussians, GaussianModel) and gaussians.flat.is_cuda
         if self.densify_stats and hasattr(gaussians, "_stats"):
             gaussians._stats()
         groups = []
@@ -265,14 +266,20 @@ class MappingWindow:
             loss = loss + self.loss_fn(pkg["render"], pkg["depth"], kf["cam"], kf["gt_image"],
                                        kf["gt_depth"])
             stats[v] = pkg
+        reg = None
         if self.rank == 0:         # view-independent regulariser counted once (slam_backend.py:229-231)
-            scaling = g.get_scaling
-            loss = loss + 10 * torch.abs(scaling - scaling.mean(dim=1).view(-1, 1)).mean()
+            if self.fused_reg:     # one kernel: value + gradient added to the scaling grad arena
+                reg = scale_regulariser(g._scaling, g._scaling.grad)
+            else:
+                scaling = g.get_scaling
+                loss = loss + 10 * torch.abs(scaling - scaling.mean(dim=1).view(-1, 1)).mean()
         if torch.is_tensor(loss):
             loss.backward()
             loss = loss.detach()
         else:
             loss = torch.zeros((), device=self.bg.device)
+        if reg is not None:
+            loss = loss + reg
         # densification statistics of every view (utils/slam_backend.py:277-284); the fused
         # renderer has already accumulated them inside its backward kernel
         if self.densify_stats and hasattr(g, "add_densification_stats"):

@@ -265,3 +265,15 @@ def test_densify_prune_config4_size_on_gpu():
     gm.flat_grad.fill_(1e-3)
     gm.optimizer.step()
     assert bool(torch.isfinite(gm.flat).all())
+
+
+def test_scale_regulariser_matches_torch():
+    g = torch.Generator().manual_seed(2)
+    raw = (0.7 * torch.randn(5001, 3, generator=g) - 3).to(DEV).requires_grad_(True)
+    s = torch.exp(raw)
+    ref = 10 * torch.abs(s - s.mean(dim=1).view(-1, 1)).mean()
+    ref.backward()
+    sink = torch.full_like(raw, 0.25)
+    val = losses.scale_regulariser(raw, sink)
+    assert abs(float(val) - float(ref)) <= 1e-6 * abs(float(ref))
+    assert torch.allclose(sink - 0.25, raw.grad, rtol=1e-4, atol=2e-8)   # sink holds 0.25 + g: fp32 ulp of 0.25
