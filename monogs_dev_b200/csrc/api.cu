@@ -165,7 +165,8 @@ extern "C" size_t b2gs_backward_scratch_bytes(int32_t P) {
 static int forward_front(const B2gsScene& s, const B2gsWorkspace* ws, const B2gsForwardOut* out,
                          int64_t cap, cudaStream_t st, GeomWS* g_out, ImageWS* im_out) {
   if (!out->radii || !out->n_touched) { set_error("radii/n_touched outputs must be non-NULL"); return B2GS_ERR_INVALID; }
-  if (s.P >= (1 << 30)) { set_error("P too large"); return B2GS_ERR_INVALID; }
+  // Gaussian ids travel in 24 bits of the per-tile sort key (the low 8 carry the block mask)
+  if (s.P >= (1 << 24)) { set_error("P too large: at most 16,777,215 Gaussians"); return B2GS_ERR_INVALID; }
   size_t need = 0;
   GeomWS g = carve_geom(ws->geom, s.P, &need);
   if (!ws->geom || ws->geom_bytes < need) {
@@ -257,7 +258,7 @@ extern "C" int b2gs_forward_render(const B2gsScene* scene, const B2gsWorkspace* 
 }
 
 extern "C" int64_t b2gs_binning_capacity(size_t binning_bytes) {
-  // inverse of b2gs_binning_bytes: point_list (4 B) + keys (8 B) per instance, 256 B alignment
+  // inverse of b2gs_binning_bytes: point_list (4 B) + keys (8 B) per instance
   int64_t n = (int64_t)(binning_bytes / 12);
   while (n > 0) {
     size_t need = 0;

@@ -11,7 +11,7 @@
 // here with no global sort, no scan over the Gaussians, no library call and no sync:
 //   1. preprocess_fwd counts instances per tile          (T counters, red.add)
 //   2. tile_scan_kernel: counters -> ranges, cursors, num_rendered, overflow flag
-//   3. scatter_instances_kernel: each instance's 8 B key (depth bits<<32 | id) goes
+//   3. scatter_instances_kernel: each instance's 8 B key (depth bits<<32 | id<<8 | block mask) goes
 //      to its tile's segment through an atomic cursor (arbitrary order inside a segment)
 //   4. tile_sort_kernel: one CTA per tile sorts its segment (bitonic network on the
 //      unique 64-bit keys, shared memory; oversized segments run it in global/L2) and
@@ -19,6 +19,7 @@
 // Everything is L2-resident at the BASELINE sizes (R = 1.3 M -> 10 MB of keys).
 #include "common.cuh"
 #include "expand.cuh"
+#include "cull.cuh"
 
 namespace b2gs {
 
@@ -123,29 +124,43 @@ int launch_tile_scan(const B2gsScene& s, const ImageWS& im, int64_t cap, cudaStr
 }
 
 // ---- instance scatter ----------------------------------------------------------------
+// key = depth bits << 32 | Gaussian id << 8 | block mask.  The low byte says which of the
+// tile's eight 8x4 warp blocks the splat can touch (cull.cuh); it is computed here, where the
+// splat's conic is already in the owner lane's hands and the atomic's latency hides the
+// arithmetic, rides through the per-tile sort for free (ids are unique, so the order is still
+// (depth, id)), and reaches both render kernels inside the sorted list word.
 __global__ void __launch_bounds__(256)
 scatter_instances_kernel(int P, uint32_t gx, const uint32_t* __restrict__ tiles_touched,
-                         const ushort4* __restrict__ rect, const float4* __restrict__ rgbd,
+                         const ushort4* __restrict__ rect, const float2* __restrict__ xy,
+                         const float4* __restrict__ conic_o, const float4* __restrict__ rgbd,
                          uint32_t* __restrict__ cursor, const uint32_t* __restrict__ status,
                          uint64_t* __restrict__ keys) {
   __shared__ WarpRects s_rects[8];
+  __shared__ SplatCullBox s_cull[8][32];
+  __shared__ uint32_t s_depth[8][32];
   if (status[1]) return;  // overflow: nothing may be written
-  const int lane = threadIdx.x & 31;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  uint32_t touched = 0, org = 0, w = 1, depth_bits = 0;
+  uint32_t touched = 0, org = 0, w = 1;
   if (i < P) {
     touched = tiles_touched[i];
     if (touched) {
       const ushort4 r = rect[i];
       org = (uint32_t)r.x | ((uint32_t)r.y << 16);
       w = (uint32_t)(r.z - r.x);
-      depth_bits = __float_as_uint(rgbd[i].w);
+      s_depth[warp][lane] = __float_as_uint(rgbd[i].w);
+      s_cull[warp][lane] = splat_cull_setup(xy[i], conic_o[i]);
     }
   }
-  warp_expand_rects<8>(
-      s_rects[threadIdx.x >> 5], lane, touched, org, w, depth_bits, (uint32_t)i, gx,
+  const uint32_t id0 = (uint32_t)(blockIdx.x * blockDim.x + warp * 32);   // id of lane 0's Gaussian
+  warp_expand_rects<4>(
+      s_rects[warp], lane, touched, org, w, gx,
       [&](uint32_t tile) { return atomicAdd(&cursor[tile * CURSOR_STRIDE], 1u); },
-      [&](uint32_t slot, uint32_t d, uint32_t id) { keys[slot] = ((uint64_t)d << 32) | id; });
+      [&](uint32_t slot, uint32_t tile, int owner) {
+        const uint32_t ty = tile / gx, tx = tile - ty * gx;
+        const uint32_t bm = splat_block_mask(s_cull[warp][owner], (float)(tx * TILE), (float)(ty * TILE));
+        keys[slot] = ((uint64_t)s_depth[warp][owner] << 32) | ((id0 + (uint32_t)owner) << 8) | bm;
+      });
 }
 
 // ---- per-tile sort -------------------------------------------------------------------
@@ -216,7 +231,8 @@ int launch_binning(const B2gsScene& s, const GeomWS& g, const ImageWS& im, const
   {
     B2GS_PROF("scatter_instances", st);
     scatter_instances_kernel<<<(s.P + 255) / 256, 256, 0, st>>>(s.P, (uint32_t)gx, g.tiles_touched,
-                                                               g.rect, g.rgbd, im.cursor, im.status,
+                                                               g.rect, g.xy, g.conic_o, g.rgbd, im.cursor,
+                                                               im.status,
                                                                b.keys);
     B2GS_LAUNCH_CHECK(st, s.debug);
   }
@@ -234,7 +250,7 @@ __global__ void export_keys_kernel(const uint2* __restrict__ ranges,
                                    uint32_t* __restrict__ values) {
   const uint2 r = ranges[blockIdx.x];
   for (uint32_t i = r.x + threadIdx.x; i < r.y; i += blockDim.x) {
-    const uint32_t id = point_list[i];
+    const uint32_t id = point_list[i] >> 8;   // low byte: block mask
     if (keys) keys[i] = ((uint64_t)blockIdx.x << 32) | __float_as_uint(rgbd[id].w);
     if (values) values[i] = id;
   }

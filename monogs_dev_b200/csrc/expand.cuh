@@ -16,18 +16,17 @@ struct WarpRects {
   uint32_t pre[32];  // inclusive prefix of `touched` inside the warp
   uint32_t org[32];  // x0 | y0 << 16
   uint32_t w[32];    // rect width in tiles
-  uint32_t a[32];    // payload (depth bits)
-  uint32_t b[32];    // payload (Gaussian id)
 };
 
-// For every (Gaussian, tile) instance:  token = issue(tile);  ...;  commit(token, a, b).
+// For every (Gaussian, tile) instance:  token = issue(tile);  ...;  commit(token, tile, owner)
+// where `owner` is the lane (0..31) whose Gaussian the instance belongs to.
 // Instances are handled U per lane per trip with all `issue` calls ahead of the `commit`s, so
 // that U atomics (with return) are in flight per lane instead of one: a huge splat spread over
 // the warp is a chain of total/32 dependent L2 round trips otherwise.  All 32 lanes must call.
 template <int U, class Issue, class Commit>
 __device__ __forceinline__ void warp_expand_rects(WarpRects& s, int lane, uint32_t touched,
-                                                  uint32_t org, uint32_t w, uint32_t a, uint32_t b,
-                                                  uint32_t gx, Issue issue, Commit commit) {
+                                                  uint32_t org, uint32_t w, uint32_t gx, Issue issue,
+                                                  Commit commit) {
   uint32_t pre = touched;
 #pragma unroll
   for (int d = 1; d < 32; d <<= 1) {
@@ -39,12 +38,10 @@ __device__ __forceinline__ void warp_expand_rects(WarpRects& s, int lane, uint32
   s.pre[lane] = pre;
   s.org[lane] = org;
   s.w[lane] = w;
-  s.a[lane] = a;
-  s.b[lane] = b;
   __syncwarp();
   for (uint32_t k0 = lane; k0 < total; k0 += 32 * U) {
     int lo[U];
-    uint32_t token[U];
+    uint32_t token[U], tile[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const uint32_t k = k0 + 32 * u;
@@ -60,12 +57,13 @@ __device__ __forceinline__ void warp_expand_rects(WarpRects& s, int lane, uint32
         const uint32_t o = s.org[l];
         const uint32_t dy = local / ww, dx = local - dy * ww;
         lo[u] = l;
-        token[u] = issue(((o >> 16) + dy) * gx + (o & 0xffffu) + dx);
+        tile[u] = ((o >> 16) + dy) * gx + (o & 0xffffu) + dx;
+        token[u] = issue(tile[u]);
       }
     }
 #pragma unroll
     for (int u = 0; u < U; ++u) {
-      if (lo[u] >= 0) commit(token[u], s.a[lo[u]], s.b[lo[u]]);
+      if (lo[u] >= 0) commit(token[u], tile[u], lo[u]);
     }
   }
   __syncwarp();

@@ -110,7 +110,7 @@ __device__ __forceinline__ V3 sh_backward(int deg, int M, const float* __restric
     const float bk = (k < active && k < 16) ? basis[k] : 0.f;
     float* o = k == 0 ? d_dc : d_rest + 3 * (k - 1);
     if (accumulate) {
-      if (bk != 0.f) { o[0] += bk * g[0]; o[1] += bk * g[1]; o[2] += bk * g[2]; }
+      if (bk != 0.f) { atomicAdd(o, bk * g[0]); atomicAdd(o + 1, bk * g[1]); atomicAdd(o + 2, bk * g[2]); }
     } else {
       o[0] = bk * g[0]; o[1] = bk * g[1]; o[2] = bk * g[2];
     }
@@ -377,7 +377,10 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
         float ds2 = Rt.m[2][0] * dL_dMt.m[2][0] + Rt.m[2][1] * dL_dMt.m[2][1] + Rt.m[2][2] * dL_dMt.m[2][2];
         if (RAW) { ds0 *= sx; ds1 *= sy; ds2 *= sz; }  // d exp(x) = exp(x) dx
         if (accumulate) {
-          dL_dscales[3 * idx + 0] += ds0; dL_dscales[3 * idx + 1] += ds1; dL_dscales[3 * idx + 2] += ds2;
+          // red.global.add: fire-and-forget, no load latency at the tail of the kernel (rows are
+          // private to this thread, so there is no contention)
+          atomicAdd(&dL_dscales[3 * idx + 0], ds0); atomicAdd(&dL_dscales[3 * idx + 1], ds1);
+          atomicAdd(&dL_dscales[3 * idx + 2], ds2);
         } else {
           dL_dscales[3 * idx + 0] = ds0; dL_dscales[3 * idx + 1] = ds1; dL_dscales[3 * idx + 2] = ds2;
         }
@@ -403,12 +406,12 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
           dq.x = (dq.x - q.x * dot) * inv; dq.y = (dq.y - q.y * dot) * inv;
           dq.z = (dq.z - q.z * dot) * inv; dq.w = (dq.w - q.w * dot) * inv;
         }
-        float4* out = reinterpret_cast<float4*>(dL_drots) + idx;
         if (accumulate) {
-          const float4 o = *out;
-          dq.x += o.x; dq.y += o.y; dq.z += o.z; dq.w += o.w;
+          float* out = dL_drots + 4 * (size_t)idx;
+          atomicAdd(out, dq.x); atomicAdd(out + 1, dq.y); atomicAdd(out + 2, dq.z); atomicAdd(out + 3, dq.w);
+        } else {
+          reinterpret_cast<float4*>(dL_drots)[idx] = dq;
         }
-        *out = dq;
       }
     } else if (!accumulate) {
       if (dL_dscales) { dL_dscales[3 * idx] = 0.f; dL_dscales[3 * idx + 1] = 0.f; dL_dscales[3 * idx + 2] = 0.f; }
@@ -425,10 +428,10 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
       d_op *= o * (1.f - o);
     }
     if (accumulate) {
-      dL_dmeans3D[3 * idx] += dmean.x;
-      dL_dmeans3D[3 * idx + 1] += dmean.y;
-      dL_dmeans3D[3 * idx + 2] += dmean.z;
-      dL_dopacity[idx] += d_op;
+      atomicAdd(&dL_dmeans3D[3 * idx], dmean.x);
+      atomicAdd(&dL_dmeans3D[3 * idx + 1], dmean.y);
+      atomicAdd(&dL_dmeans3D[3 * idx + 2], dmean.z);
+      atomicAdd(&dL_dopacity[idx], d_op);
     } else {
       dL_dmeans3D[3 * idx] = dmean.x;
       dL_dmeans3D[3 * idx + 1] = dmean.y;
@@ -442,8 +445,8 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
     }
     // densification statistics of this view (GS/scene/gaussian_model.py:691-695,
     // utils/slam_backend.py:277-284), visibility_filter = radii > 0
-    if (st_grad_accum) st_grad_accum[idx] += sqrtf(dmean2D_x * dmean2D_x + dmean2D_y * dmean2D_y);
-    if (st_denom) st_denom[idx] += 1.f;
+    if (st_grad_accum) atomicAdd(&st_grad_accum[idx], sqrtf(dmean2D_x * dmean2D_x + dmean2D_y * dmean2D_y));
+    if (st_denom) atomicAdd(&st_denom[idx], 1.f);
     if (st_max_radii) st_max_radii[idx] = fmaxf(st_max_radii[idx], (float)radii[idx]);
   }
 

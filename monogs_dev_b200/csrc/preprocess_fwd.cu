@@ -175,9 +175,9 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
   const int lane = threadIdx.x & 31;
   warp_expand_rects<4>(
       s_rects[threadIdx.x >> 5], lane, touched, (uint32_t)x0 | ((uint32_t)y0 << 16),
-      (uint32_t)(x1 - x0), 0u, 0u, (uint32_t)gx,
+      (uint32_t)(x1 - x0), (uint32_t)gx,
       [&](uint32_t tile) { atomicAdd(&tile_count[tile * CURSOR_STRIDE], 1u); return 0u; },
-      [](uint32_t, uint32_t, uint32_t) {});
+      [](uint32_t, uint32_t, int) {});
 }
 
 __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D,

@@ -29,6 +29,14 @@ constexpr unsigned FULL = 0xffffffffu;
 // 0 dmean2D.x  1 dmean2D.y  2 dconic.x  3 dconic.y  4 dconic.w
 // 5 dopacity   6 dcolor.r   7 dcolor.g  8 dcolor.b  9 ddepth   10,11 pad
 
+// 1/x for x in [0.01, 1] (x = 1 - alpha, alpha <= 0.99): MUFU.RCP + one Newton step, <= 1 ulp,
+// without the range / denormal handling of a full-range reciprocal.
+__device__ __forceinline__ float rcp_unit_range(float x) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return fmaf(r, fmaf(-x, r, 1.0f), r);
+}
+
 __device__ __forceinline__ float xchg_add(bool upper, float lo_val, float hi_val, int offset) {
   // lanes with the bit clear keep lo_val and hand hi_val to their partner (and vice versa)
   const float send = upper ? lo_val : hi_val;
@@ -68,6 +76,7 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   __shared__ float4 s_co[RB_BATCH];
   __shared__ float4 s_cd[RB_BATCH];
   __shared__ int s_id[RB_BATCH];
+  __shared__ uint8_t s_bm[RB_BATCH];
   __shared__ int s_max;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -78,7 +87,6 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   const bool inside = px < W && py < H;
   const int pix_id = W * py + px;
   const float pixfx = (float)px, pixfy = (float)py;
-  const float rx0 = (float)bx, ry0 = (float)by, rx1 = (float)(bx + 7), ry1 = (float)(by + 3);
 
   const uint2 range = ranges[tile];
 
@@ -117,7 +125,9 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     if (base) __syncthreads();
     if (tid < cnt) {
       const int pos = tile_max - 1 - (base + tid);
-      const int id = (int)point_list[range.x + pos];
+      const uint32_t v = point_list[range.x + pos];   // id << 8 | block mask
+      const int id = (int)(v >> 8);
+      s_bm[tid] = (uint8_t)v;
       s_id[tid] = id;
       s_xy[tid] = xy[id];
       s_co[tid] = conic_o[id];
@@ -131,8 +141,7 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     for (int c0 = j0 & ~31; c0 < cnt; c0 += 32) {
       // one lane per splat: can it reach this warp's 8x4 block at all? (cull.cuh)
       const int jj = c0 + lane;
-      const bool keep = jj >= j0 && jj < cnt &&
-                        splat_may_touch_rect(s_xy[jj], s_co[jj], rx0, ry0, rx1, ry1);
+      const bool keep = jj >= j0 && jj < cnt && ((s_bm[jj] >> warp) & 1);
       unsigned mask = __ballot_sync(FULL, keep);
       while (mask) {
         const int k = __ffs(mask) - 1;
@@ -155,7 +164,7 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
         for (int q = 0; q < 10; ++q) v[q] = 0.f;
         if (!skip) {
           const float4 cd = s_cd[j];
-          const float inv1ma = __frcp_rn(1.f - alpha);
+          const float inv1ma = rcp_unit_range(1.f - alpha);
           T = T * inv1ma;  // reference: T / (1 - alpha); differs by <= 1 ulp
           const float dchannel_dcolor = alpha * T;
           float dL_dalpha = 0.0f;

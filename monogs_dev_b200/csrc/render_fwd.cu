@@ -33,6 +33,7 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   __shared__ float4 s_cd[RF_BATCH];
   __shared__ int s_id[RF_BATCH];
   __shared__ int s_cnt[RF_BATCH];
+  __shared__ uint8_t s_bm[RF_BATCH];
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int tile = blockIdx.x;
@@ -43,7 +44,6 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   const bool inside = px < W && py < H;
   const int pix_id = W * py + px;
   const float pixfx = (float)px, pixfy = (float)py;
-  const float rx0 = (float)bx, ry0 = (float)by, rx1 = (float)(bx + 7), ry1 = (float)(by + 3);
 
   const uint2 range = ranges[tile];
   const int n = (int)(range.y - range.x);
@@ -58,7 +58,9 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     if (__syncthreads_count(done) == TILE_PIX) break;
     const int cnt = min(RF_BATCH, n - base);
     if (tid < cnt) {
-      const int id = (int)point_list[range.x + base + tid];
+      const uint32_t v = point_list[range.x + base + tid];   // id << 8 | block mask
+      const int id = (int)(v >> 8);
+      s_bm[tid] = (uint8_t)v;
       s_id[tid] = id;
       s_xy[tid] = xy[id];
       s_co[tid] = conic_o[id];
@@ -69,9 +71,10 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
 
     if (!__all_sync(RF_FULL, done)) {
       for (int c0 = 0; c0 < cnt; c0 += 32) {
-        // one lane per splat: can it reach this warp's 8x4 block at all?
+        // can the splat reach this warp's 8x4 block at all?  (bit computed once by the binning
+        // stage, cull.cuh: splat_block_mask)
         const int jj = c0 + lane;
-        const bool keep = jj < cnt && splat_may_touch_rect(s_xy[jj], s_co[jj], rx0, ry0, rx1, ry1);
+        const bool keep = jj < cnt && ((s_bm[jj] >> warp) & 1);
         unsigned mask = __ballot_sync(RF_FULL, keep);
         unsigned touchbits = 0u;
         while (mask) {
