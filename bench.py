@@ -216,6 +216,29 @@ def rooflines(prof, units, pk):
     return table
 
 
+def ncu_traffic(kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel`, from the newest
+    `ncu --set full` summary committed under profiles/ (tools/ncu_summary.py); None if absent."""
+    import glob
+    import re
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "*_ncu_render_full.txt")))
+    if not files:
+        return None
+    vals, cur = [], None
+    for line in open(files[-1]):
+        if line.startswith("----"):
+            cur = {} if kernel + "_kernel" in line else None
+            if cur is not None:
+                vals.append(cur)
+        elif cur is not None:
+            m = re.match(r"\s+dram__bytes_(read|write)\.sum\s+([0-9.]+)\s+(\w+)", line)
+            if m:
+                mult = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(m.group(3), 1.0)
+                cur[m.group(1)] = float(m.group(2)) * mult
+    tot = [v.get("read", 0.0) + v.get("write", 0.0) for v in vals if v]
+    return round(sum(tot) / len(tot)) if tot else None
+
+
 def cpu_oracle_sample():
     """bounded CPU sample: ONE fwd+bwd of a 1/10-scale config 3 (50k Gaussians, 380x216,
     focal / sqrt(10)) through the PyTorch oracle; scaled to full-size iters/s by 1/10."""
@@ -336,15 +359,19 @@ def run(args):
         pairs = sum_n_contrib(st, sc.W, sc.H, device) if st is not None else 0
         R = st.num_rendered if st is not None else 0
         n_par = gm.flat.numel()
-        units = {   # algorithmic work per launch (SURVEY.md §8d, DESIGN.md §kernels)
+        N = sc.W * sc.H
+        tiles = ((sc.W + 15) // 16) * ((sc.H + 15) // 16)
+        units = {   # algorithmic work per launch (SURVEY.md §8d, DESIGN.md §4)
             "preprocess_fwd": ("hbm", 131.0 * pvis + 20.0 * (P - pvis)),
-            "emit_instances": ("hbm", 20.0 * P + 8.0 * R),
-            "tile_sort(cub)": ("hbm", 16.0 * R),
-            "depth_sort(cub)": ("hbm", 16.0 * P),
-            "tile_ranges": ("hbm", 4.0 * R),
+            "tile_scan": ("hbm", 16.0 * tiles),
+            "scatter_instances": ("hbm", 12.0 * P + 40.0 * pvis + 8.0 * R),
+            "tile_sort": ("hbm", 24.0 * R),                       # the sort's lower bound: one read + one write of a 12 B pair
             "render_fwd": ("fp32", 26.0 * pairs),
             "render_bwd": ("fp32", 80.0 * pairs),
             "preprocess_bwd": ("hbm", 319.0 * pvis + 60.0 * (P - pvis)),
+            "loss_fwd": ("hbm", 32.0 * N),
+            "loss_bwd": ("hbm", 48.0 * N),
+            "iso_reg": ("hbm", 36.0 * P),
             "adam": ("hbm", 28.0 * n_par),
         }
         rooftab = rooflines(prof, units, peaks())
@@ -352,6 +379,7 @@ def run(args):
         if own:
             top = max(own, key=lambda k: own[k][1])
             roof = dict(kernel=top, **rooftab[top])
+            roof["traffic"] = ncu_traffic(top)
             tot = sum(v[1] for v in prof.values())
             roof["share_of_gpu_kernel_time"] = round(prof[top][1] / tot, 3) if tot else None
         work = dict(P=P, P_visible=pvis, instances=R, effective_pairs=pairs)
