@@ -200,6 +200,58 @@ __device__ __forceinline__ void bitonic_sort_block(uint64_t* __restrict__ a, uin
   }
 }
 
+// 32 keys, one per lane, ascending: bitonic network on shuffles (no shared memory, no barrier)
+__device__ __forceinline__ uint64_t warp_sort32(uint64_t key, int lane) {
+#pragma unroll
+  for (int k = 2; k <= 32; k <<= 1) {
+#pragma unroll
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      const uint64_t other = __shfl_xor_sync(0xffffffffu, key, j);
+      const bool take_min = ((lane & j) == 0) == ((lane & k) == 0);
+      key = ((key < other) == take_min) ? key : other;   // equal keys (padding): either one
+    }
+  }
+  return key;
+}
+
+// Segments up to MERGE_KEYS: every warp sorts 32-key chunks in registers, then log2(n/32) merge
+// levels in which each key finds its output slot by a binary search of the sibling run (keys are
+// unique, so rank = own position + number of smaller sibling keys): 5 barriers for a 512-key
+// tile instead of the 45 of a full bitonic network.  Keys of a right run count sibling keys <=
+// themselves, written as v < key + 1; the padding is 2^64 - 2 so that this cannot wrap.  A warp's
+// 32 keys share run and sibling, so the full-sibling fast path (fixed trip count, no bounds
+// test) is warp-uniform; only the last run pair of a level takes the bounded search.
+// Larger segments: the bitonic network in shared memory (<= SORT_SMEM_KEYS) or in global / L2.
+constexpr uint32_t MERGE_KEYS = SORT_SMEM_KEYS / 2;
+constexpr uint64_t SORT_PAD = ~0ull - 1;
+
+template <uint32_t L>
+__device__ __forceinline__ void merge_level(const uint64_t* __restrict__ in, uint64_t* __restrict__ out,
+                                            uint32_t nn) {
+  for (uint32_t i = threadIdx.x; i < nn; i += SORT_THREADS) {
+    const uint64_t key = in[i];
+    const uint32_t pos = i & (L - 1), run = i - pos;   // run start
+    const uint32_t sib = run ^ L;                       // sibling run start
+    const uint64_t kk = key + ((run & L) ? 1ull : 0ull);
+    const uint64_t* sp = in + sib;
+    uint32_t lo = 0;                                    // number of sibling keys < kk
+    if (sib + L <= nn) {
+      // count is in [lo, lo + 2 st] before each probe; lo <= L - 1 throughout, so no bounds test
+#pragma unroll
+      for (uint32_t st = L >> 1; st > 0; st >>= 1)
+        if (sp[lo + st - 1] < kk) lo += st;
+      if (sp[lo] < kk) lo += 1;
+    } else if (sib < nn) {
+      const uint32_t len = nn - sib;
+      for (uint32_t st = L; st > 0; st >>= 1) {
+        const uint32_t m = lo + st;
+        if (m <= len && sp[m - 1] < kk) lo = m;
+      }
+    }
+    out[(run & ~L) + pos + lo] = key;
+  }
+}
+
 __global__ void __launch_bounds__(SORT_THREADS)
 tile_sort_kernel(const uint2* __restrict__ ranges, uint64_t* __restrict__ keys,
                  uint32_t* __restrict__ point_list) {
@@ -208,15 +260,30 @@ tile_sort_kernel(const uint2* __restrict__ ranges, uint64_t* __restrict__ keys,
   const uint32_t n = r.y - r.x;
   if (n == 0) return;
   uint64_t* seg = keys + r.x;
-  if (n <= SORT_SMEM_KEYS) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (n <= MERGE_KEYS) {
+    const uint32_t nn = (n + 31u) & ~31u;               // padded to whole warps
+    for (uint32_t c = warp * 32; c < nn; c += SORT_THREADS) {
+      const uint32_t i = c + lane;
+      s_keys[i] = warp_sort32(i < n ? seg[i] : SORT_PAD, lane);
+    }
+    __syncthreads();
+    uint64_t* a = s_keys;
+    uint64_t* b = s_keys + MERGE_KEYS;
+#define B2GS_MERGE(LV)                                                        \
+    if (LV < nn) {                                                            \
+      merge_level<LV>(a, b, nn);                                              \
+      __syncthreads();                                                        \
+      uint64_t* t = a; a = b; b = t;                                          \
+    }
+    B2GS_MERGE(32u) B2GS_MERGE(64u) B2GS_MERGE(128u) B2GS_MERGE(256u) B2GS_MERGE(512u) B2GS_MERGE(1024u)
+#undef B2GS_MERGE
+    for (uint32_t i = threadIdx.x; i < n; i += SORT_THREADS) point_list[r.x + i] = (uint32_t)a[i];
+  } else if (n <= SORT_SMEM_KEYS) {
     for (uint32_t i = threadIdx.x; i < n; i += SORT_THREADS) s_keys[i] = seg[i];
     __syncthreads();
-    if (n > 1) bitonic_sort_block(s_keys, n);
-    for (uint32_t i = threadIdx.x; i < n; i += SORT_THREADS) {
-      const uint64_t k = s_keys[i];
-      seg[i] = k;  // kept sorted for the parity export (keys are L2-resident)
-      point_list[r.x + i] = (uint32_t)k;
-    }
+    bitonic_sort_block(s_keys, n);
+    for (uint32_t i = threadIdx.x; i < n; i += SORT_THREADS) point_list[r.x + i] = (uint32_t)s_keys[i];
   } else {
     __syncthreads();
     bitonic_sort_block(seg, n);

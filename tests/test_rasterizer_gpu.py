@@ -50,7 +50,9 @@ needs_ref = pytest.mark.skipif(not ref_ext.available(), reason="oracle/_ref not 
 @pytest.mark.parametrize("name,mode,kw", [
     ("cfg1_plumbing", "sh", {}), ("tiny_sh3", "sh", {}), ("tiny", "precomp", {}),
     ("cfg2_tracking", "sh", {}), ("cfg3_replica", "sh", {}),
-    ("cfg5_large", "sh", dict(P=400_000))])
+    ("cfg5_large", "sh", dict(P=400_000)),
+    # few tiles, very long lists: the > 2048-key (smem bitonic) and > 4096-key (global) sort paths
+    ("tiny", "sh", dict(P=30_000, W=48, H=32)), ("tiny", "sh", dict(P=9_000, W=64, H=48))])
 def test_native_vs_reference_ext(name, mode, kw):
     bg = (0.0, 0.0, 0.0) if name.startswith("cfg") else (0.2, 0.4, 0.1)
     sc, rs, inp, gc, gd = build_case(name, device=DEV, mode=mode, bg=bg, **kw)
