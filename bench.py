@@ -277,7 +277,7 @@ def run(args):
     kfs, host = build_window(device, render_fn, model_cls, None, sc)
     gm = model_cls(sc.xyz, sc.f_dc, sc.f_rest, sc.opacity, sc.scaling, sc.rotation, sh_degree=sc.sh_degree)
     win = mapping.MappingWindow(gm, kfs, sc.bg, render_fn=render_fn, adam_cls=adam_cls, loss_fn=loss_fn,
-                                cuda_graph=graph)
+                                cuda_graph=graph, view_streams=1 if impl_ref else args.view_streams)
     local_views = win.local
 
     def step():
@@ -347,8 +347,12 @@ def run(args):
     roof, rooftab = None, {}
     if not impl_ref:
         # per-kernel durations: CUDA events on the launching stream, 2 extra (untimed) steps
+        # (views serialised on one stream for this pass: a kernel timed while another view's
+        # kernels share the SMs would not be that kernel's duration)
         _lib.lib.b2gs_profile_enable(1)
+        vs, win.view_streams = win.view_streams, 1
         win._eager_step(set_to_none=False); win._eager_step(set_to_none=False)   # eager: events per launch
+        win.view_streams = vs
         torch.cuda.synchronize()
         prof = _lib.profile_read()
         _lib.lib.b2gs_profile_enable(0)
@@ -401,7 +405,9 @@ def run(args):
         "config": {"workload": "cfg3_replica: 1200x680, 500k Gaussians, SH0, 8-keyframe mapping window "
                                "(fwd+bwd per keyframe, fused Adam, pose Adam)",
                    "keyframes": N_VIEWS, "parallelism": "keyframes sharded round-robin over %d rank(s)" % world,
-                   "launch": "cuda graphs (2 per step, one host sync)" if graph else "eager",
+                   "launch": ("cuda graphs (2 per step, one host sync)" if graph else "eager") +
+                             ("" if impl_ref or args.view_streams < 2 else
+                              ", views issued on %d forked streams" % args.view_streams),
                    "l2_policy": "inputs larger than L2: >400 MB touched per step (8 GT frames 104 MB, "
                                 "4 parameter/moment arenas 112 MB, per-view workspaces+gradients) vs 126 MB L2",
                    **work},
@@ -467,6 +473,8 @@ def main():
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="native arm: eager launches instead of CUDA graphs")
+    ap.add_argument("--view-streams", type=int, default=4,
+                    help="native arm: side streams the window's views are issued on (1 = serial)")
     args = ap.parse_args()
     if not torch.cuda.is_available():
         if args.impl == "reference":

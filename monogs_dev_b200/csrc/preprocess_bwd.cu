@@ -447,7 +447,9 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
     // utils/slam_backend.py:277-284), visibility_filter = radii > 0
     if (st_grad_accum) atomicAdd(&st_grad_accum[idx], sqrtf(dmean2D_x * dmean2D_x + dmean2D_y * dmean2D_y));
     if (st_denom) atomicAdd(&st_denom[idx], 1.f);
-    if (st_max_radii) st_max_radii[idx] = fmaxf(st_max_radii[idx], (float)radii[idx]);
+    // radii >= 0: the int order of the bit patterns is the float order; atomic so that views
+    // running on concurrent streams can share the statistics arrays
+    if (st_max_radii) atomicMax(reinterpret_cast<int*>(st_max_radii) + idx, __float_as_int((float)radii[idx]));
   }
 
   // ---- dL_dtau: warp -> block -> one partial row per block ----

@@ -15,6 +15,7 @@ gradients / Adam moments in three more), so that
 The loss is a plain sum over views (utils/slam_backend.py:160-231), so keyframe sharding
 with a SUM all-reduce is exact up to fp32 summation order.
 """
+import contextlib
 import math
 
 import torch
@@ -221,7 +222,7 @@ class MappingWindow:
 
     def __init__(self, gaussians, keyframes, bg, pose_lr=(0.003, 0.001, 0.01, 0.01),
                  optimize_pose=True, group=None, render_fn=None, adam_cls=FusedAdam,
-                 loss_fn=None, cuda_graph=False, densify_stats=True):
+                 loss_fn=None, cuda_graph=False, densify_stats=True, view_streams=1):
         self.g, self.kfs, self.bg = gaussians, keyframes, bg
         self.render_fn = render_fn or (render_fused if isinstance(gaussians, GaussianModel) else render)
         self.loss_fn = loss_fn or get_loss_mapping_rgbd
@@ -249,6 +250,12 @@ class MappingWindow:
             if not isinstance(gaussians.optimizer, FusedAdam):
                 raise RuntimeError("cuda_graph=True needs the FusedAdam optimizer")
             gaussians.optimizer.capturable = True
+        # view_streams > 1: the local views are issued round-robin on that many side streams
+        # (forked from / joined into the calling stream, also inside the captured graph), so one
+        # view's single-CTA tile scan, kernel tails and loss reductions overlap another view's
+        # render kernels.  Gradients meet in the arena through atomics either way.
+        self.view_streams = max(1, int(view_streams))
+        self._side = None
         self.last = {}
         self._g1 = self._g2 = None
         self.graph_launches = 0
@@ -260,12 +267,26 @@ class MappingWindow:
         g = self.g
         loss = 0
         stats = {}
-        for v in self.local:
+        side = []
+        if self.view_streams > 1 and len(self.local) > 1 and self.bg.is_cuda:
+            if self._side is None:
+                self._side = [torch.cuda.Stream(self.bg.device) for _ in range(self.view_streams)]
+            side = self._side
+            main = torch.cuda.current_stream()
+            for s in side:
+                s.wait_stream(main)
+        terms = []
+        for i, v in enumerate(self.local):
             kf = self.kfs[v]
-            pkg = self.render_fn(kf["cam"], g, None, self.bg)
-            loss = loss + self.loss_fn(pkg["render"], pkg["depth"], kf["cam"], kf["gt_image"],
-                                       kf["gt_depth"])
+            with (torch.cuda.stream(side[i % len(side)]) if side else contextlib.nullcontext()):
+                pkg = self.render_fn(kf["cam"], g, None, self.bg)
+                terms.append(self.loss_fn(pkg["render"], pkg["depth"], kf["cam"], kf["gt_image"],
+                                          kf["gt_depth"]))
             stats[v] = pkg
+        for s in side:
+            main.wait_stream(s)
+        for t in terms:
+            loss = loss + t
         reg = None
         if self.rank == 0:         # view-independent regulariser counted once (slam_backend.py:229-231)
             if self.fused_reg:     # one kernel: value + gradient added to the scaling grad arena
@@ -274,7 +295,9 @@ class MappingWindow:
                 scaling = g.get_scaling
                 loss = loss + 10 * torch.abs(scaling - scaling.mean(dim=1).view(-1, 1)).mean()
         if torch.is_tensor(loss):
-            loss.backward()
+            loss.backward()      # every node runs on the stream of its forward
+            for s in side:
+                main.wait_stream(s)
             loss = loss.detach()
         else:
             loss = torch.zeros((), device=self.bg.device)

@@ -123,7 +123,7 @@ def test_capturable_adam_in_graph_matches_torch():
         assert float((x - y).abs().max()) <= 2e-6 * float(y.abs().max()) + 1e-7
 
 
-def _window(cuda_graph, n_views=3):
+def _window(cuda_graph, view_streams=1, n_views=3):
     sc = syn.make_scene("cfg1_plumbing", device=DEV, n_views=n_views)
     gt = dict(xyz=sc.xyz + 0.01, scaling=sc.scaling, rotation=sc.rotation, opacity=sc.opacity + 0.1,
               f_dc=sc.f_dc + 0.05, f_rest=sc.f_rest)
@@ -136,13 +136,14 @@ def _window(cuda_graph, n_views=3):
             kfs.append(dict(cam=cam, gt_image=pkg["render"].clone(), gt_depth=pkg["depth"].clone()))
     gm = mapping.GaussianModel(sc.xyz, sc.f_dc, sc.f_rest, sc.opacity, sc.scaling, sc.rotation,
                                sh_degree=sc.sh_degree)
-    return mapping.MappingWindow(gm, kfs, sc.bg, cuda_graph=cuda_graph), gm, kfs
+    return mapping.MappingWindow(gm, kfs, sc.bg, cuda_graph=cuda_graph, view_streams=view_streams), gm, kfs
 
 
-def test_graph_mapping_step_matches_eager():
+@pytest.mark.parametrize("view_streams", [1, 2])
+def test_graph_mapping_step_matches_eager(view_streams):
     try:
         w0, g0, k0 = _window(False)
-        w1, g1, k1 = _window(True)
+        w1, g1, k1 = _window(True, view_streams)
         l0 = [float(w0.step()) for _ in range(8)]
         l1 = [float(w1.step()) for _ in range(8)]
         assert w1._g1 is not None and w1.graph_launches > 0, "graph path not taken"

@@ -9,7 +9,9 @@ dev = torch.device("cuda", 0)
 sc = syn.make_scene(bench.WORKLOAD, device=dev, n_views=bench.N_VIEWS)
 kfs, host = bench.build_window(dev, mapping.render_fused, mapping.GaussianModel, None, sc)
 gm = mapping.GaussianModel(sc.xyz, sc.f_dc, sc.f_rest, sc.opacity, sc.scaling, sc.rotation)
-win = mapping.MappingWindow(gm, kfs, sc.bg)
+import sys as _s
+VS = int(_s.argv[1]) if len(_s.argv) > 1 else 1
+win = mapping.MappingWindow(gm, kfs, sc.bg, view_streams=VS)
 for _ in range(3): win.step()
 torch.cuda.synchronize()
 _lib.lib.b2gs_profile_enable(1)
