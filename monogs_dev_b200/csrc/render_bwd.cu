@@ -44,8 +44,21 @@ __device__ __forceinline__ float xchg_add(bool upper, float lo_val, float hi_val
   return keep + __shfl_xor_sync(FULL, send, offset);
 }
 
+// owner lanes of the fold below and the accumulator column each one ends up holding: lane
+// constants, formed once per thread (and kept opaque so that they are not re-derived per splat)
+__device__ __forceinline__ int fold10_slot(int lane) {
+  const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4, b1 = lane & 2;
+  const int local = (b3 ? 3 : 0) + (b2 ? 2 : 0) + (b1 ? 1 : 0);
+  // bit0 clear, and (b3,b2,b1) not a padding slot
+  const bool owner = !(lane & 1) && !(b2 && (b3 || b1));
+  int slot = owner ? (b4 ? 5 : 0) + local : -1;
+  asm volatile("" : "+r"(slot));
+  return slot;
+}
+
+// slot_row = acc + slot (owners) / nullptr; row_off = splat id * ACC_STRIDE
 __device__ __forceinline__ void warp_fold10_and_red(const float v[10], int lane,
-                                                    float* __restrict__ row) {
+                                                    float* __restrict__ slot_row, size_t row_off) {
   const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4, b1 = lane & 2;
   float w0 = xchg_add(b4, v[0], v[5], 16);
   float w1 = xchg_add(b4, v[1], v[6], 16);
@@ -59,11 +72,17 @@ __device__ __forceinline__ void warp_fold10_and_red(const float v[10], int lane,
   float t1 = xchg_add(b2, u1, 0.f, 4);
   float s = xchg_add(b1, t0, t1, 2);
   s += __shfl_xor_sync(FULL, s, 1);
-  // owner lanes: bit0 clear, and (b3,b2,b1) not a padding slot
-  const int local = (b3 ? 3 : 0) + (b2 ? 2 : 0) + (b1 ? 1 : 0);
-  const bool owner = !(lane & 1) && !(b2 && (b3 || b1));
-  if (owner) atomicAdd(row + (b4 ? 5 : 0) + local, s);
+  if (slot_row) atomicAdd(slot_row + row_off, s);
 }
+
+// one staged splat: everything a visit reads sits behind ONE shared-memory address
+struct __align__(16) SplatRec {
+  float4 co;    // conic a, b, c, opacity
+  float4 cd;    // rgb, depth
+  float2 xy;    // pixel-space mean
+  int id;
+  uint32_t bm;  // block mask (cull.cuh)
+};              // 48 B: a quarter-warp's 16 B stores at this stride cover all 32 banks once
 
 __global__ void __launch_bounds__(256)
 render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W,
@@ -72,11 +91,7 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
                   const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib,
                   const float* __restrict__ dL_dpixels, const float* __restrict__ dL_dpixels_depth,
                   float* __restrict__ acc) {
-  __shared__ float2 s_xy[RB_BATCH];
-  __shared__ float4 s_co[RB_BATCH];
-  __shared__ float4 s_cd[RB_BATCH];
-  __shared__ int s_id[RB_BATCH];
-  __shared__ uint8_t s_bm[RB_BATCH];
+  __shared__ SplatRec s_rec[RB_BATCH];
   __shared__ int s_max;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -94,7 +109,12 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   float T = T_final;
   const int last_contributor = inside ? (int)n_contrib[pix_id] : 0;
 
+  // accum_rec_c: blended colour behind the current splat; diff_c: (colour - accum_rec) of the last
+  // contributor.  The reference's replay  accum = last_alpha * last_colour + (1 - last_alpha) * accum
+  // (CR/backward.cu:716-727) is written as  accum += last_alpha * (last_colour - accum): the
+  // difference is the one the previous contributor already formed for its dL_dalpha.
   float accum_rec0 = 0.f, accum_rec1 = 0.f, accum_rec2 = 0.f, accum_recd = 0.f;
+  float diff0 = 0.f, diff1 = 0.f, diff2 = 0.f, diffd = 0.f;
   float dLp0 = 0.f, dLp1 = 0.f, dLp2 = 0.f, dLpd = 0.f;
   if (inside) {
     const size_t plane = (size_t)H * W;
@@ -103,14 +123,17 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     dLp2 = dL_dpixels[2 * plane + pix_id];
     dLpd = dL_dpixels_depth[pix_id];
   }
-  float last_alpha = 0.f, last_c0 = 0.f, last_c1 = 0.f, last_c2 = 0.f, last_d = 0.f;
+  float last_alpha = 0.f;
   float bg_dot_dpixel = 0.f;
   bg_dot_dpixel += bg[0] * dLp0;
   bg_dot_dpixel += bg[1] * dLp1;
   bg_dot_dpixel += bg[2] * dLp2;
+  const float neg_Tf_bg = -T_final * bg_dot_dpixel;   // dL_dalpha += (-T_final / (1 - alpha)) * bg . dL_dpixel
 
   const float ddelx_dx = 0.5f * W;
   const float ddely_dy = 0.5f * H;
+  const int slot = fold10_slot(lane);
+  float* const slot_row = slot >= 0 ? acc + slot : nullptr;
 
   // deepest contributor over the warp / the tile
   const int warp_max = __reduce_max_sync(FULL, last_contributor);
@@ -127,11 +150,12 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
       const int pos = tile_max - 1 - (base + tid);
       const uint32_t v = point_list[range.x + pos];   // id << 8 | block mask
       const int id = (int)(v >> 8);
-      s_bm[tid] = (uint8_t)v;
-      s_id[tid] = id;
-      s_xy[tid] = xy[id];
-      s_co[tid] = conic_o[id];
-      s_cd[tid] = rgbd[id];
+      SplatRec& r = s_rec[tid];
+      r.co = conic_o[id];
+      r.cd = rgbd[id];
+      r.xy = xy[id];
+      r.id = id;
+      r.bm = v & 0xffu;
     }
     __syncthreads();
 
@@ -141,15 +165,16 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     for (int c0 = j0 & ~31; c0 < cnt; c0 += 32) {
       // one lane per splat: can it reach this warp's 8x4 block at all? (cull.cuh)
       const int jj = c0 + lane;
-      const bool keep = jj >= j0 && jj < cnt && ((s_bm[jj] >> warp) & 1);
+      const bool keep = jj >= j0 && jj < cnt && ((s_rec[jj].bm >> warp) & 1);
       unsigned mask = __ballot_sync(FULL, keep);
       while (mask) {
         const int k = __ffs(mask) - 1;
         mask &= mask - 1;
         const int j = c0 + k;
         const int pos = tile_max - 1 - (base + j);
-        const float2 p = s_xy[j];
-        const float4 co = s_co[j];
+        const SplatRec& r = s_rec[j];
+        const float2 p = r.xy;
+        const float4 co = r.co;
         const float dx = p.x - pixfx, dy = p.y - pixfy;
         const float power = -0.5f * (co.x * dx * dx + co.z * dy * dy) - co.y * dx * dy;
         bool skip = !(pos < last_contributor);  // also false-inside lanes: last_contributor == 0
@@ -159,53 +184,48 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
         skip |= alpha < 1.0f / 255.0f;
         if (__all_sync(FULL, skip)) continue;
 
-        float v[10];
-#pragma unroll
-        for (int q = 0; q < 10; ++q) v[q] = 0.f;
+        // skipping lanes contribute exact zeros: every partial is a product with one of these three
+        float dL_dalpha = 0.f, dchannel_dcolor = 0.f;
+        const float Gs = skip ? 0.f : G;
         if (!skip) {
-          const float4 cd = s_cd[j];
+          const float4 cd = r.cd;
           const float inv1ma = rcp_unit_range(1.f - alpha);
           T = T * inv1ma;  // reference: T / (1 - alpha); differs by <= 1 ulp
-          const float dchannel_dcolor = alpha * T;
-          float dL_dalpha = 0.0f;
+          dchannel_dcolor = alpha * T;
 
-          accum_rec0 = last_alpha * last_c0 + (1.f - last_alpha) * accum_rec0;
-          last_c0 = cd.x;
-          dL_dalpha += (cd.x - accum_rec0) * dLp0;
-          v[6] = dchannel_dcolor * dLp0;
-
-          accum_rec1 = last_alpha * last_c1 + (1.f - last_alpha) * accum_rec1;
-          last_c1 = cd.y;
-          dL_dalpha += (cd.y - accum_rec1) * dLp1;
-          v[7] = dchannel_dcolor * dLp1;
-
-          accum_rec2 = last_alpha * last_c2 + (1.f - last_alpha) * accum_rec2;
-          last_c2 = cd.z;
-          dL_dalpha += (cd.z - accum_rec2) * dLp2;
-          v[8] = dchannel_dcolor * dLp2;
-
-          accum_recd = last_alpha * last_d + (1.f - last_alpha) * accum_recd;
-          last_d = cd.w;
-          dL_dalpha += (cd.w - accum_recd) * dLpd;
-          v[9] = dchannel_dcolor * dLpd;
-
-          dL_dalpha *= T;
+          accum_rec0 = fmaf(last_alpha, diff0, accum_rec0);
+          accum_rec1 = fmaf(last_alpha, diff1, accum_rec1);
+          accum_rec2 = fmaf(last_alpha, diff2, accum_rec2);
+          accum_recd = fmaf(last_alpha, diffd, accum_recd);
+          diff0 = cd.x - accum_rec0;
+          diff1 = cd.y - accum_rec1;
+          diff2 = cd.z - accum_rec2;
+          diffd = cd.w - accum_recd;
+          float d = diff0 * dLp0;
+          d = fmaf(diff1, dLp1, d);
+          d = fmaf(diff2, dLp2, d);
+          d = fmaf(diffd, dLpd, d);
           last_alpha = alpha;
-          dL_dalpha += (-T_final * inv1ma) * bg_dot_dpixel;
-
-          const float dL_dG = co.w * dL_dalpha;
-          const float gdx = G * dx;
-          const float gdy = G * dy;
-          const float dG_ddelx = -gdx * co.x - gdy * co.y;
-          const float dG_ddely = -gdy * co.z - gdx * co.y;
-          v[0] = dL_dG * dG_ddelx * ddelx_dx;
-          v[1] = dL_dG * dG_ddely * ddely_dy;
-          v[2] = -0.5f * gdx * dx * dL_dG;
-          v[3] = -0.5f * gdx * dy * dL_dG;
-          v[4] = -0.5f * gdy * dy * dL_dG;
-          v[5] = G * dL_dalpha;
+          dL_dalpha = fmaf(inv1ma, neg_Tf_bg, d * T);
         }
-        warp_fold10_and_red(v, lane, acc + (size_t)s_id[j] * ACC_STRIDE);
+        const float dL_dG = co.w * dL_dalpha;
+        const float gdx = Gs * dx;
+        const float gdy = Gs * dy;
+        const float dG_ddelx = -gdx * co.x - gdy * co.y;
+        const float dG_ddely = -gdy * co.z - gdx * co.y;
+        const float hg = -0.5f * dL_dG;
+        float v[10];
+        v[0] = dL_dG * dG_ddelx * ddelx_dx;
+        v[1] = dL_dG * dG_ddely * ddely_dy;
+        v[2] = hg * gdx * dx;
+        v[3] = hg * gdx * dy;
+        v[4] = hg * gdy * dy;
+        v[5] = Gs * dL_dalpha;
+        v[6] = dchannel_dcolor * dLp0;
+        v[7] = dchannel_dcolor * dLp1;
+        v[8] = dchannel_dcolor * dLp2;
+        v[9] = dchannel_dcolor * dLpd;
+        warp_fold10_and_red(v, lane, slot_row, (size_t)r.id * ACC_STRIDE);
       }
     }
   }
