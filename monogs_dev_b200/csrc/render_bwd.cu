@@ -75,15 +75,6 @@ __device__ __forceinline__ void warp_fold10_and_red(const float v[10], int lane,
   if (slot_row) atomicAdd(slot_row + row_off, s);
 }
 
-// one staged splat: everything a visit reads sits behind ONE shared-memory address
-struct __align__(16) SplatRec {
-  float4 co;    // conic a, b, c, opacity
-  float4 cd;    // rgb, depth
-  float2 xy;    // pixel-space mean
-  int id;
-  uint32_t bm;  // block mask (cull.cuh)
-};              // 48 B: a quarter-warp's 16 B stores at this stride cover all 32 banks once
-
 __global__ void __launch_bounds__(256)
 render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W,
                   int H, int gx, const float* __restrict__ bg, const float2* __restrict__ xy,

@@ -28,12 +28,8 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
                   float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
                   float* __restrict__ out_color, float* __restrict__ out_depth,
                   float* __restrict__ out_opacity, int* __restrict__ n_touched) {
-  __shared__ float2 s_xy[RF_BATCH];
-  __shared__ float4 s_co[RF_BATCH];
-  __shared__ float4 s_cd[RF_BATCH];
-  __shared__ int s_id[RF_BATCH];
+  __shared__ SplatRec s_rec[RF_BATCH];
   __shared__ int s_cnt[RF_BATCH];
-  __shared__ uint8_t s_bm[RF_BATCH];
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int tile = blockIdx.x;
@@ -48,7 +44,8 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   const uint2 range = ranges[tile];
   const int n = (int)(range.y - range.x);
 
-  bool done = !inside;
+  const uint32_t cnt_base = (uint32_t)__cvta_generic_to_shared(s_cnt);
+  int done = !inside;
   float T = 1.0f;
   float C0 = 0.f, C1 = 0.f, C2 = 0.f, D = 0.f;
   uint32_t last_contributor = 0;
@@ -60,11 +57,12 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     if (tid < cnt) {
       const uint32_t v = point_list[range.x + base + tid];   // id << 8 | block mask
       const int id = (int)(v >> 8);
-      s_bm[tid] = (uint8_t)v;
-      s_id[tid] = id;
-      s_xy[tid] = xy[id];
-      s_co[tid] = conic_o[id];
-      s_cd[tid] = rgbd[id];
+      SplatRec& r = s_rec[tid];
+      r.co = conic_o[id];
+      r.cd = rgbd[id];
+      r.xy = xy[id];
+      r.id = id;
+      r.bm = v & 0xffu;
     }
     s_cnt[tid] = 0;
     __syncthreads();
@@ -74,53 +72,50 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
         // can the splat reach this warp's 8x4 block at all?  (bit computed once by the binning
         // stage, cull.cuh: splat_block_mask)
         const int jj = c0 + lane;
-        const bool keep = jj < cnt && ((s_bm[jj] >> warp) & 1);
+        const bool keep = jj < cnt && ((s_rec[jj].bm >> warp) & 1);
         unsigned mask = __ballot_sync(RF_FULL, keep);
-        unsigned touchbits = 0u;
         while (mask) {
           const int k = __ffs(mask) - 1;
           mask &= mask - 1;
           const int j = c0 + k;
-          const float2 p = s_xy[j];
-          const float4 co = s_co[j];
+          const SplatRec& r = s_rec[j];
+          const float2 p = r.xy;
+          const float4 co = r.co;
           const float dx = p.x - pixfx, dy = p.y - pixfy;
           const float power = -0.5f * (co.x * dx * dx + co.z * dy * dy) - co.y * dx * dy;
+          bool touch = false;
           if (!done && !(power > 0.0f)) {
             const float alpha = fminf(0.99f, co.w * expf(power));
             if (!(alpha < 1.0f / 255.0f)) {
               const float test_T = T * (1 - alpha);
               if (test_T < 0.0001f) {
-                done = true;
+                done = 1;
               } else {
-                const float4 cd = s_cd[j];
-                C0 += cd.x * alpha * T;
-                C1 += cd.y * alpha * T;
-                C2 += cd.z * alpha * T;
-                D += cd.w * alpha * T;
-                if (test_T > 0.5f) touchbits |= 1u << k;
+                const float4 cd = r.cd;
+                const float w = alpha * T;
+                C0 += cd.x * w;
+                C1 += cd.y * w;
+                C2 += cd.z * w;
+                D += cd.w * w;
+                touch = test_T > 0.5f;
                 T = test_T;
                 last_contributor = (uint32_t)(base + j + 1);
               }
             }
           }
+          // n_touched: how many pixels saw this splat with T still above 0.5
+          const unsigned tb = __ballot_sync(RF_FULL, touch);
+          if (tb != 0u && lane == 0) {   // plain red.shared: one lane, nothing to aggregate
+            asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(cnt_base + 4u * (uint32_t)j), "r"(__popc(tb)) : "memory");
+          }
         }
-        // n_touched: per splat, how many lanes saw it with T still above 0.5
-        unsigned any = __reduce_or_sync(RF_FULL, touchbits);
-        int mycnt = 0;
-        while (any) {
-          const int k = __ffs(any) - 1;
-          any &= any - 1;
-          const int cnt_k = __popc(__ballot_sync(RF_FULL, (touchbits >> k) & 1u));
-          if (lane == k) mycnt = cnt_k;
-        }
-        if (mycnt) atomicAdd(&s_cnt[c0 + lane], mycnt);
         if (__all_sync(RF_FULL, done)) break;  // warp-level early termination
       }
     }
     __syncthreads();
     if (tid < cnt) {
       const int c = s_cnt[tid];
-      if (c) atomicAdd(&n_touched[s_id[tid]], c);
+      if (c) atomicAdd(&n_touched[s_rec[tid].id], c);
     }
   }
 
