@@ -75,7 +75,19 @@ __device__ __forceinline__ void warp_fold10_and_red(const float v[10], int lane,
   if (slot_row) atomicAdd(slot_row + row_off, s);
 }
 
-__global__ void __launch_bounds__(256)
+// ---- packed fp32x2 helpers: .x = the lane's upper pixel, .y = its lower pixel (4 rows down) ----
+// FFMA2 / FMUL2 / FADD2 (sm_100) issue one instruction for both pixels; each half is the IEEE
+// single-rounding operation of the scalar instruction.
+using f2 = float2;
+__device__ __forceinline__ f2 bc(float s) { return make_float2(s, s); }
+__device__ __forceinline__ f2 mul2(f2 a, f2 b) { return __fmul2_rn(a, b); }
+__device__ __forceinline__ f2 add2(f2 a, f2 b) { return __fadd2_rn(a, b); }
+__device__ __forceinline__ f2 fma2(f2 a, f2 b, f2 c) { return __ffma2_rn(a, b, c); }
+__device__ __forceinline__ float hsum(f2 a) { return a.x + a.y; }
+
+constexpr int RB_THREADS = 128;   // 4 warps x (8x8 pixels, two per lane) = one 16x16 tile
+
+__global__ void __launch_bounds__(RB_THREADS)
 render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W,
                   int H, int gx, const float* __restrict__ bg, const float2* __restrict__ xy,
                   const float4* __restrict__ conic_o, const float4* __restrict__ rgbd,
@@ -88,38 +100,54 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int tile = blockIdx.x;
   const int tile_x = tile % gx, tile_y = tile / gx;
-  const int bx = tile_x * TILE + (warp & 1) * 8, by = tile_y * TILE + (warp >> 1) * 4;
-  const int px = bx + (lane & 7), py = by + (lane >> 3);
-  const bool inside = px < W && py < H;
-  const int pix_id = W * py + px;
-  const float pixfx = (float)px, pixfy = (float)py;
+  // warp -> 8x8 quadrant of the tile; lane -> column lane & 7, rows lane >> 3 and (lane >> 3) + 4:
+  // the upper pixel lies in the 8x4 cull block 4 * (warp >> 1) + (warp & 1), the lower one in the
+  // block two bits up (cull.cuh numbers the blocks 2 across, 4 down)
+  const int bx = tile_x * TILE + (warp & 1) * 8, by = tile_y * TILE + (warp >> 1) * 8;
+  const int px = bx + (lane & 7), pyA = by + (lane >> 3), pyB = pyA + 4;
+  const bool insideA = px < W && pyA < H, insideB = px < W && pyB < H;
+  const int pixA = W * pyA + px, pixB = W * pyB + px;
+  const float pixfx = (float)px;
+  const f2 npixfy = make_float2(-(float)pyA, -(float)pyB);
+  const uint32_t wmask = 0x5u << (4 * (warp >> 1) + (warp & 1));
 
   const uint2 range = ranges[tile];
 
-  const float T_final = inside ? final_Ts[pix_id] : 0.f;
-  float T = T_final;
-  const int last_contributor = inside ? (int)n_contrib[pix_id] : 0;
+  const f2 T_final = make_float2(insideA ? final_Ts[pixA] : 0.f, insideB ? final_Ts[pixB] : 0.f);
+  f2 T = T_final;
+  const int lastA = insideA ? (int)n_contrib[pixA] : 0, lastB = insideB ? (int)n_contrib[pixB] : 0;
 
-  // accum_rec_c: blended colour behind the current splat; diff_c: (colour - accum_rec) of the last
-  // contributor.  The reference's replay  accum = last_alpha * last_colour + (1 - last_alpha) * accum
+  // accum_c: blended colour behind the current splat; diff_c: (colour - accum) of the previous list
+  // entry.  The reference's replay  accum = last_alpha * last_colour + (1 - last_alpha) * accum
   // (CR/backward.cu:716-727) is written as  accum += last_alpha * (last_colour - accum): the
-  // difference is the one the previous contributor already formed for its dL_dalpha.
-  float accum_rec0 = 0.f, accum_rec1 = 0.f, accum_rec2 = 0.f, accum_recd = 0.f;
-  float diff0 = 0.f, diff1 = 0.f, diff2 = 0.f, diffd = 0.f;
-  float dLp0 = 0.f, dLp1 = 0.f, dLp2 = 0.f, dLpd = 0.f;
-  if (inside) {
+  // difference is the one the previous contributor already formed for its dL_dalpha.  A pixel that
+  // skips a splat runs the same recurrences with alpha = 0 — a transparent contributor: it applies
+  // the pending update, leaves T alone (T * 1/(1 - 0), exact) and parks last_alpha at 0 — so the
+  // two pixels of a lane need no divergent state updates.
+  f2 accum0 = bc(0.f), accum1 = bc(0.f), accum2 = bc(0.f), accumd = bc(0.f);
+  f2 diff0 = bc(0.f), diff1 = bc(0.f), diff2 = bc(0.f), diffd = bc(0.f);
+  f2 dLp0 = bc(0.f), dLp1 = bc(0.f), dLp2 = bc(0.f), dLpd = bc(0.f);
+  {
     const size_t plane = (size_t)H * W;
-    dLp0 = dL_dpixels[0 * plane + pix_id];
-    dLp1 = dL_dpixels[1 * plane + pix_id];
-    dLp2 = dL_dpixels[2 * plane + pix_id];
-    dLpd = dL_dpixels_depth[pix_id];
+    if (insideA) {
+      dLp0.x = dL_dpixels[0 * plane + pixA];
+      dLp1.x = dL_dpixels[1 * plane + pixA];
+      dLp2.x = dL_dpixels[2 * plane + pixA];
+      dLpd.x = dL_dpixels_depth[pixA];
+    }
+    if (insideB) {
+      dLp0.y = dL_dpixels[0 * plane + pixB];
+      dLp1.y = dL_dpixels[1 * plane + pixB];
+      dLp2.y = dL_dpixels[2 * plane + pixB];
+      dLpd.y = dL_dpixels_depth[pixB];
+    }
   }
-  float last_alpha = 0.f;
-  float bg_dot_dpixel = 0.f;
-  bg_dot_dpixel += bg[0] * dLp0;
-  bg_dot_dpixel += bg[1] * dLp1;
-  bg_dot_dpixel += bg[2] * dLp2;
-  const float neg_Tf_bg = -T_final * bg_dot_dpixel;   // dL_dalpha += (-T_final / (1 - alpha)) * bg . dL_dpixel
+  f2 last_alpha = bc(0.f);
+  f2 bg_dot = mul2(bc(bg[0]), dLp0);
+  bg_dot = fma2(bc(bg[1]), dLp1, bg_dot);
+  bg_dot = fma2(bc(bg[2]), dLp2, bg_dot);
+  // dL_dalpha += (-T_final / (1 - alpha)) * bg . dL_dpixel
+  const f2 neg_Tf_bg = mul2(make_float2(-T_final.x, -T_final.y), bg_dot);
 
   const float ddelx_dx = 0.5f * W;
   const float ddely_dy = 0.5f * H;
@@ -127,7 +155,7 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   float* const slot_row = slot >= 0 ? acc + slot : nullptr;
 
   // deepest contributor over the warp / the tile
-  const int warp_max = __reduce_max_sync(FULL, last_contributor);
+  const int warp_max = __reduce_max_sync(FULL, max(lastA, lastB));
   if (tid == 0) s_max = 0;
   __syncthreads();
   if (lane == 0 && warp_max > 0) atomicMax(&s_max, warp_max);
@@ -137,11 +165,11 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   for (int base = 0; base < tile_max; base += RB_BATCH) {
     const int cnt = min(RB_BATCH, tile_max - base);
     if (base) __syncthreads();
-    if (tid < cnt) {
-      const int pos = tile_max - 1 - (base + tid);
+    for (int t = tid; t < cnt; t += RB_THREADS) {
+      const int pos = tile_max - 1 - (base + t);
       const uint32_t v = point_list[range.x + pos];   // id << 8 | block mask
       const int id = (int)(v >> 8);
-      SplatRec& r = s_rec[tid];
+      SplatRec& r = s_rec[t];
       r.co = conic_o[id];
       r.cd = rgbd[id];
       r.xy = xy[id];
@@ -154,9 +182,9 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     int j0 = tile_max - base - warp_max;
     if (j0 < 0) j0 = 0;
     for (int c0 = j0 & ~31; c0 < cnt; c0 += 32) {
-      // one lane per splat: can it reach this warp's 8x4 block at all? (cull.cuh)
+      // one lane per splat: can it reach this warp's 8x8 quadrant at all? (cull.cuh)
       const int jj = c0 + lane;
-      const bool keep = jj >= j0 && jj < cnt && ((s_rec[jj].bm >> warp) & 1);
+      const bool keep = jj >= j0 && jj < cnt && (s_rec[jj].bm & wmask);
       unsigned mask = __ballot_sync(FULL, keep);
       while (mask) {
         const int k = __ffs(mask) - 1;
@@ -166,56 +194,64 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
         const SplatRec& r = s_rec[j];
         const float2 p = r.xy;
         const float4 co = r.co;
-        const float dx = p.x - pixfx, dy = p.y - pixfy;
-        const float power = -0.5f * (co.x * dx * dx + co.z * dy * dy) - co.y * dx * dy;
-        bool skip = !(pos < last_contributor);  // also false-inside lanes: last_contributor == 0
-        skip |= power > 0.0f;
-        const float G = expf(power);
-        const float alpha = fminf(0.99f, co.w * G);
-        skip |= alpha < 1.0f / 255.0f;
-        if (__all_sync(FULL, skip)) continue;
+        // power: the forward's operation tree, operation for operation (render_fwd.cu), so that
+        // both passes take the same skip decisions
+        const float dx = p.x - pixfx;
+        const f2 dy = add2(bc(p.y), npixfy);
+        const float adx = co.x * dx, nbdx = -(co.y * dx);
+        const f2 cdy2 = mul2(dy, mul2(bc(co.z), dy));
+        const f2 quad = fma2(bc(dx), bc(adx), cdy2);
+        const f2 power = fma2(quad, bc(-0.5f), mul2(dy, bc(nbdx)));
+        const f2 G = make_float2(expf(power.x), expf(power.y));
+        const f2 og = mul2(bc(co.w), G);
+        const float alphaA = fminf(0.99f, og.x), alphaB = fminf(0.99f, og.y);
+        const bool skipA = !(pos < lastA) || power.x > 0.0f || alphaA < 1.0f / 255.0f;
+        const bool skipB = !(pos < lastB) || power.y > 0.0f || alphaB < 1.0f / 255.0f;
+        if (__all_sync(FULL, skipA && skipB)) continue;
 
-        // skipping lanes contribute exact zeros: every partial is a product with one of these three
-        float dL_dalpha = 0.f, dchannel_dcolor = 0.f;
-        const float Gs = skip ? 0.f : G;
-        if (!skip) {
-          const float4 cd = r.cd;
-          const float inv1ma = rcp_unit_range(1.f - alpha);
-          T = T * inv1ma;  // reference: T / (1 - alpha); differs by <= 1 ulp
-          dchannel_dcolor = alpha * T;
+        const f2 alpha = make_float2(skipA ? 0.f : alphaA, skipB ? 0.f : alphaB);
+        const f2 Gs = make_float2(skipA ? 0.f : G.x, skipB ? 0.f : G.y);
+        const float4 cd = r.cd;
+        const f2 oma = add2(bc(1.f), make_float2(-alpha.x, -alpha.y));
+        const f2 inv1ma = make_float2(rcp_unit_range(oma.x), rcp_unit_range(oma.y));
+        T = mul2(T, inv1ma);  // reference: T / (1 - alpha); differs by <= 1 ulp
+        const f2 dchannel_dcolor = mul2(alpha, T);
 
-          accum_rec0 = fmaf(last_alpha, diff0, accum_rec0);
-          accum_rec1 = fmaf(last_alpha, diff1, accum_rec1);
-          accum_rec2 = fmaf(last_alpha, diff2, accum_rec2);
-          accum_recd = fmaf(last_alpha, diffd, accum_recd);
-          diff0 = cd.x - accum_rec0;
-          diff1 = cd.y - accum_rec1;
-          diff2 = cd.z - accum_rec2;
-          diffd = cd.w - accum_recd;
-          float d = diff0 * dLp0;
-          d = fmaf(diff1, dLp1, d);
-          d = fmaf(diff2, dLp2, d);
-          d = fmaf(diffd, dLpd, d);
-          last_alpha = alpha;
-          dL_dalpha = fmaf(inv1ma, neg_Tf_bg, d * T);
-        }
-        const float dL_dG = co.w * dL_dalpha;
-        const float gdx = Gs * dx;
-        const float gdy = Gs * dy;
-        const float dG_ddelx = -gdx * co.x - gdy * co.y;
-        const float dG_ddely = -gdy * co.z - gdx * co.y;
-        const float hg = -0.5f * dL_dG;
+        accum0 = fma2(last_alpha, diff0, accum0);
+        accum1 = fma2(last_alpha, diff1, accum1);
+        accum2 = fma2(last_alpha, diff2, accum2);
+        accumd = fma2(last_alpha, diffd, accumd);
+        diff0 = fma2(accum0, bc(-1.f), bc(cd.x));
+        diff1 = fma2(accum1, bc(-1.f), bc(cd.y));
+        diff2 = fma2(accum2, bc(-1.f), bc(cd.z));
+        diffd = fma2(accumd, bc(-1.f), bc(cd.w));
+        f2 d = mul2(diff0, dLp0);
+        d = fma2(diff1, dLp1, d);
+        d = fma2(diff2, dLp2, d);
+        d = fma2(diffd, dLpd, d);
+        last_alpha = alpha;
+        const f2 dL_dalpha = fma2(inv1ma, neg_Tf_bg, mul2(d, T));
+
+        // per-pixel partials -> the lane's two pixels are summed before the warp fold; a skipping
+        // pixel contributes exact zeros (every partial is a product with Gs or alpha = 0)
+        const f2 dL_dG = mul2(bc(co.w), dL_dalpha);
+        const f2 gdx = mul2(Gs, bc(dx));
+        const f2 gdy = mul2(Gs, dy);
+        const f2 dG_ddelx = fma2(gdx, bc(-co.x), mul2(gdy, bc(-co.y)));
+        const f2 dG_ddely = fma2(gdy, bc(-co.z), mul2(gdx, bc(-co.y)));
+        const f2 hg = mul2(dL_dG, bc(-0.5f));
+        const f2 hgdx = mul2(hg, gdx);
         float v[10];
-        v[0] = dL_dG * dG_ddelx * ddelx_dx;
-        v[1] = dL_dG * dG_ddely * ddely_dy;
-        v[2] = hg * gdx * dx;
-        v[3] = hg * gdx * dy;
-        v[4] = hg * gdy * dy;
-        v[5] = Gs * dL_dalpha;
-        v[6] = dchannel_dcolor * dLp0;
-        v[7] = dchannel_dcolor * dLp1;
-        v[8] = dchannel_dcolor * dLp2;
-        v[9] = dchannel_dcolor * dLpd;
+        v[0] = hsum(mul2(dL_dG, dG_ddelx)) * ddelx_dx;
+        v[1] = hsum(mul2(dL_dG, dG_ddely)) * ddely_dy;
+        v[2] = hsum(hgdx) * dx;
+        v[3] = hsum(mul2(hgdx, dy));
+        v[4] = hsum(mul2(mul2(hg, gdy), dy));
+        v[5] = hsum(mul2(Gs, dL_dalpha));
+        v[6] = hsum(mul2(dchannel_dcolor, dLp0));
+        v[7] = hsum(mul2(dchannel_dcolor, dLp1));
+        v[8] = hsum(mul2(dchannel_dcolor, dLp2));
+        v[9] = hsum(mul2(dchannel_dcolor, dLpd));
         warp_fold10_and_red(v, lane, slot_row, (size_t)r.id * ACC_STRIDE);
       }
     }
@@ -226,9 +262,9 @@ int launch_render_bwd(const B2gsScene& s, const GeomWS& g, const ImageWS& im, co
                       const B2gsBackwardIO& io, float* acc, cudaStream_t st) {
   const int gx = (s.W + TILE - 1) / TILE, gy = (s.H + TILE - 1) / TILE;
   B2GS_PROF("render_bwd", st);
-  render_bwd_kernel<<<gx * gy, 256, 0, st>>>(im.ranges, b.point_list, s.W, s.H, gx, s.bg, g.xy,
-                                             g.conic_o, g.rgbd, im.final_T, im.n_contrib,
-                                             io.dL_dcolor, io.dL_ddepth, acc);
+  render_bwd_kernel<<<gx * gy, RB_THREADS, 0, st>>>(im.ranges, b.point_list, s.W, s.H, gx, s.bg, g.xy,
+                                                    g.conic_o, g.rgbd, im.final_T, im.n_contrib,
+                                                    io.dL_dcolor, io.dL_ddepth, acc);
   B2GS_LAUNCH_CHECK(st, s.debug);
   return B2GS_OK;
 }

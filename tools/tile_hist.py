@@ -28,6 +28,10 @@ for i, cam in enumerate([k["cam"] for k in kfs[:3]]):
     q = torch.quantile(n, torch.tensor([0.1, 0.5, 0.9, 0.99], device=dev))
     print(f"view {i}: R={st.num_rendered} tiles={n.numel()} mean={n.mean():.0f} max={n.max():.0f} "
           f"q10/50/90/99={[int(v) for v in q]} >2048:{int((n > 2048).sum())} >4096:{int((n > 4096).sum())}")
-    m = ex["point_list"] & 0xff
-    bits = sum(((m >> k) & 1).float().mean() for k in range(8)) / 8
-    print(f"   mean block-mask density {float(bits):.3f}")
+    R = st.num_rendered
+    m = st.binning.view(torch.int32)[:R] & 0xff          # raw list words: id << 8 | block mask
+    v84 = sum(((m >> k) & 1).sum() for k in range(8))
+    # 8x8 blocks: (col, R) = 8x4 blocks w = 2*(2R)+col and 2*(2R+1)+col
+    v88 = sum((((m >> (4 * Rr + c)) | (m >> (4 * Rr + 2 + c))) & 1).sum() for Rr in range(2) for c in range(2))
+    v168 = sum((((m >> (2 * r)) | (m >> (2 * r + 1))) & 1).sum() for r in range(4))   # 16x4 rows
+    print(f"   visits 8x4: {int(v84)} ({int(v84)/R:.2f}/instance)  8x8: {int(v88)} ({int(v88)/int(v84):.3f} of 8x4)  16x4: {int(v168)} ({int(v168)/int(v84):.3f})  any: {int((m != 0).sum())}")
