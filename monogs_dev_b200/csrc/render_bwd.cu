@@ -170,11 +170,13 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
       const uint32_t v = point_list[range.x + pos];   // id << 8 | block mask
       const int id = (int)(v >> 8);
       SplatRec& r = s_rec[t];
-      r.co = conic_o[id];
-      r.cd = rgbd[id];
-      r.xy = xy[id];
       r.id = id;
       r.bm = v & 0xffu;
+      if (v & 0xffu) {        // a splat that reaches no block of the tile is never visited
+        r.co = conic_o[id];
+        r.cd = rgbd[id];
+        r.xy = xy[id];
+      }
     }
     __syncthreads();
 

@@ -19,9 +19,18 @@
 namespace b2gs {
 
 constexpr int RF_BATCH = 256;
+constexpr int RF_THREADS = 128;   // 4 warps x (8x8 pixels, two per lane) = one 16x16 tile
 constexpr unsigned RF_FULL = 0xffffffffu;
 
-__global__ void __launch_bounds__(256)
+// packed fp32x2: .x = the lane's upper pixel, .y = its lower pixel (4 rows down); each half is the
+// IEEE single-rounding operation of the scalar instruction (FFMA2 / FMUL2 / FADD2, sm_100)
+using f2 = float2;
+__device__ __forceinline__ f2 bc(float s) { return make_float2(s, s); }
+__device__ __forceinline__ f2 mul2(f2 a, f2 b) { return __fmul2_rn(a, b); }
+__device__ __forceinline__ f2 add2(f2 a, f2 b) { return __fadd2_rn(a, b); }
+__device__ __forceinline__ f2 fma2(f2 a, f2 b, f2 c) { return __ffma2_rn(a, b, c); }
+
+__global__ void __launch_bounds__(RF_THREADS)
 render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W,
                   int H, int gx, const float2* __restrict__ xy, const float4* __restrict__ conic_o,
                   const float4* __restrict__ rgbd, const float* __restrict__ bg,
@@ -34,45 +43,53 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int tile = blockIdx.x;
   const int tile_x = tile % gx, tile_y = tile / gx;
-  // warp -> 8x4 sub-block (2 across, 4 down); lane -> pixel inside it
-  const int bx = tile_x * TILE + (warp & 1) * 8, by = tile_y * TILE + (warp >> 1) * 4;
-  const int px = bx + (lane & 7), py = by + (lane >> 3);
-  const bool inside = px < W && py < H;
-  const int pix_id = W * py + px;
-  const float pixfx = (float)px, pixfy = (float)py;
+  // warp -> 8x8 quadrant of the tile; lane -> column lane & 7, rows lane >> 3 and (lane >> 3) + 4:
+  // the upper pixel lies in the 8x4 cull block 4 * (warp >> 1) + (warp & 1), the lower one in the
+  // block two bits up (cull.cuh numbers the blocks 2 across, 4 down)
+  const int bx = tile_x * TILE + (warp & 1) * 8, by = tile_y * TILE + (warp >> 1) * 8;
+  const int px = bx + (lane & 7), pyA = by + (lane >> 3), pyB = pyA + 4;
+  const bool insideA = px < W && pyA < H, insideB = px < W && pyB < H;
+  const int pixA = W * pyA + px, pixB = W * pyB + px;
+  const float pixfx = (float)px;
+  const f2 npixfy = make_float2(-(float)pyA, -(float)pyB);
+  const uint32_t wmask = 0x5u << (4 * (warp >> 1) + (warp & 1));
 
   const uint2 range = ranges[tile];
   const int n = (int)(range.y - range.x);
 
   const uint32_t cnt_base = (uint32_t)__cvta_generic_to_shared(s_cnt);
-  int done = !inside;
-  float T = 1.0f;
-  float C0 = 0.f, C1 = 0.f, C2 = 0.f, D = 0.f;
-  uint32_t last_contributor = 0;
+  bool doneA = !insideA, doneB = !insideB;
+  f2 T = bc(1.0f);
+  f2 C0 = bc(0.f), C1 = bc(0.f), C2 = bc(0.f), D = bc(0.f);
+  uint32_t lastA = 0, lastB = 0;
 
   for (int base = 0; base < n; base += RF_BATCH) {
     // whole tile finished?  (also the barrier that protects the staging buffers)
-    if (__syncthreads_count(done) == TILE_PIX) break;
+    if (__syncthreads_count(doneA && doneB) == RF_THREADS) break;
     const int cnt = min(RF_BATCH, n - base);
-    if (tid < cnt) {
-      const uint32_t v = point_list[range.x + base + tid];   // id << 8 | block mask
-      const int id = (int)(v >> 8);
-      SplatRec& r = s_rec[tid];
-      r.co = conic_o[id];
-      r.cd = rgbd[id];
-      r.xy = xy[id];
-      r.id = id;
-      r.bm = v & 0xffu;
+    for (int t = tid; t < RF_BATCH; t += RF_THREADS) {
+      if (t < cnt) {
+        const uint32_t v = point_list[range.x + base + t];   // id << 8 | block mask
+        const int id = (int)(v >> 8);
+        SplatRec& r = s_rec[t];
+        r.bm = v & 0xffu;
+        r.id = id;
+        if (v & 0xffu) {      // a splat that reaches no block of the tile is never visited
+          r.co = conic_o[id];
+          r.cd = rgbd[id];
+          r.xy = xy[id];
+        }
+      }
+      s_cnt[t] = 0;
     }
-    s_cnt[tid] = 0;
     __syncthreads();
 
-    if (!__all_sync(RF_FULL, done)) {
+    if (!__all_sync(RF_FULL, doneA && doneB)) {
       for (int c0 = 0; c0 < cnt; c0 += 32) {
-        // can the splat reach this warp's 8x4 block at all?  (bit computed once by the binning
+        // can the splat reach this warp's quadrant at all?  (bits computed once by the binning
         // stage, cull.cuh: splat_block_mask)
         const int jj = c0 + lane;
-        const bool keep = jj < cnt && ((s_rec[jj].bm >> warp) & 1);
+        const bool keep = jj < cnt && (s_rec[jj].bm & wmask);
         unsigned mask = __ballot_sync(RF_FULL, keep);
         while (mask) {
           const int k = __ffs(mask) - 1;
@@ -81,53 +98,71 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
           const SplatRec& r = s_rec[j];
           const float2 p = r.xy;
           const float4 co = r.co;
-          const float dx = p.x - pixfx, dy = p.y - pixfy;
-          const float power = -0.5f * (co.x * dx * dx + co.z * dy * dy) - co.y * dx * dy;
-          bool touch = false;
-          if (!done && !(power > 0.0f)) {
-            const float alpha = fminf(0.99f, co.w * expf(power));
-            if (!(alpha < 1.0f / 255.0f)) {
-              const float test_T = T * (1 - alpha);
-              if (test_T < 0.0001f) {
-                done = 1;
-              } else {
-                const float4 cd = r.cd;
-                const float w = alpha * T;
-                C0 += cd.x * w;
-                C1 += cd.y * w;
-                C2 += cd.z * w;
-                D += cd.w * w;
-                touch = test_T > 0.5f;
-                T = test_T;
-                last_contributor = (uint32_t)(base + j + 1);
-              }
-            }
-          }
+          // power = -0.5f * (a dx dx + c dy dy) - b dx dy in the operation tree the reference's
+          // expression compiles to (CR/forward.cu:346): (c*dy)*dy, fma(dx, a*dx, .), (b*dx)*dy,
+          // fma(., -0.5, -.)  — render_bwd.cu evaluates the same tree
+          const float dx = p.x - pixfx;
+          const f2 dy = add2(bc(p.y), npixfy);
+          const float adx = co.x * dx, nbdx = -(co.y * dx);
+          const f2 cdy2 = mul2(dy, mul2(bc(co.z), dy));
+          const f2 quad = fma2(bc(dx), bc(adx), cdy2);
+          const f2 power = fma2(quad, bc(-0.5f), mul2(dy, bc(nbdx)));
+          bool actA = !doneA && !(power.x > 0.0f), actB = !doneB && !(power.y > 0.0f);
+          if (!__any_sync(RF_FULL, actA || actB)) continue;
+          const f2 og = mul2(bc(co.w), make_float2(expf(power.x), expf(power.y)));
+          const float alphaA = fminf(0.99f, og.x), alphaB = fminf(0.99f, og.y);
+          actA = actA && !(alphaA < 1.0f / 255.0f);
+          actB = actB && !(alphaB < 1.0f / 255.0f);
+          const f2 test_T = mul2(T, add2(bc(1.f), make_float2(-alphaA, -alphaB)));
+          if (actA && test_T.x < 0.0001f) { doneA = true; actA = false; }
+          if (actB && test_T.y < 0.0001f) { doneB = true; actB = false; }
+          // a pixel that does not take the splat blends it with alpha = 0: exact no-ops
+          const f2 w = mul2(make_float2(actA ? alphaA : 0.f, actB ? alphaB : 0.f), T);
+          const float4 cd = r.cd;
+          C0 = fma2(bc(cd.x), w, C0);
+          C1 = fma2(bc(cd.y), w, C1);
+          C2 = fma2(bc(cd.z), w, C2);
+          D = fma2(bc(cd.w), w, D);
+          T = make_float2(actA ? test_T.x : T.x, actB ? test_T.y : T.y);
+          const uint32_t here = (uint32_t)(base + j + 1);
+          lastA = actA ? here : lastA;
+          lastB = actB ? here : lastB;
           // n_touched: how many pixels saw this splat with T still above 0.5
-          const unsigned tb = __ballot_sync(RF_FULL, touch);
-          if (tb != 0u && lane == 0) {   // plain red.shared: one lane, nothing to aggregate
-            asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(cnt_base + 4u * (uint32_t)j), "r"(__popc(tb)) : "memory");
+          const unsigned ta = __ballot_sync(RF_FULL, actA && test_T.x > 0.5f);
+          const unsigned tb = __ballot_sync(RF_FULL, actB && test_T.y > 0.5f);
+          if ((ta | tb) != 0u && lane == 0) {   // plain red.shared: one lane, nothing to aggregate
+            asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(cnt_base + 4u * (uint32_t)j),
+                         "r"(__popc(ta) + __popc(tb)) : "memory");
           }
         }
-        if (__all_sync(RF_FULL, done)) break;  // warp-level early termination
+        if (__all_sync(RF_FULL, doneA && doneB)) break;  // warp-level early termination
       }
     }
     __syncthreads();
-    if (tid < cnt) {
-      const int c = s_cnt[tid];
-      if (c) atomicAdd(&n_touched[s_rec[tid].id], c);
+    for (int t = tid; t < cnt; t += RF_THREADS) {
+      const int c = s_cnt[t];
+      if (c) atomicAdd(&n_touched[s_rec[t].id], c);
     }
   }
 
-  if (inside) {
-    final_T[pix_id] = T;
-    n_contrib[pix_id] = last_contributor;
-    const size_t plane = (size_t)H * W;
-    out_color[0 * plane + pix_id] = C0 + T * bg[0];
-    out_color[1 * plane + pix_id] = C1 + T * bg[1];
-    out_color[2 * plane + pix_id] = C2 + T * bg[2];
-    out_depth[pix_id] = D;
-    out_opacity[pix_id] = 1 - T;
+  const size_t plane = (size_t)H * W;
+  if (insideA) {
+    final_T[pixA] = T.x;
+    n_contrib[pixA] = lastA;
+    out_color[0 * plane + pixA] = C0.x + T.x * bg[0];
+    out_color[1 * plane + pixA] = C1.x + T.x * bg[1];
+    out_color[2 * plane + pixA] = C2.x + T.x * bg[2];
+    out_depth[pixA] = D.x;
+    out_opacity[pixA] = 1 - T.x;
+  }
+  if (insideB) {
+    final_T[pixB] = T.y;
+    n_contrib[pixB] = lastB;
+    out_color[0 * plane + pixB] = C0.y + T.y * bg[0];
+    out_color[1 * plane + pixB] = C1.y + T.y * bg[1];
+    out_color[2 * plane + pixB] = C2.y + T.y * bg[2];
+    out_depth[pixB] = D.y;
+    out_opacity[pixB] = 1 - T.y;
   }
 }
 
@@ -135,7 +170,7 @@ int launch_render_fwd(const B2gsScene& s, const GeomWS& g, const ImageWS& im, co
                       const B2gsForwardOut& out, cudaStream_t st) {
   const int gx = (s.W + TILE - 1) / TILE, gy = (s.H + TILE - 1) / TILE;
   B2GS_PROF("render_fwd", st);
-  render_fwd_kernel<<<gx * gy, 256, 0, st>>>(im.ranges, b.point_list, s.W, s.H, gx, g.xy, g.conic_o,
+  render_fwd_kernel<<<gx * gy, RF_THREADS, 0, st>>>(im.ranges, b.point_list, s.W, s.H, gx, g.xy, g.conic_o,
                                              g.rgbd, s.bg, im.final_T, im.n_contrib, out.color,
                                              out.depth, out.opacity, out.n_touched);
   B2GS_LAUNCH_CHECK(st, s.debug);
