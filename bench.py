@@ -5,8 +5,9 @@
 
 A STEP is one iteration of the keyframe mapping window (utils/slam_backend.py:156-317 of
 the reference) at BASELINE config 3 (Replica shape): 1200x680, 500k Gaussians, SH degree 0,
-8 keyframes: 8 x (render -> RGB-D mapping loss) -> one backward -> [N>1: ONE NCCL all-reduce
-of the packed per-Gaussian gradients] -> fused Adam over the packed parameter arena ->
+8 keyframes: 8 x (render -> RGB-D mapping loss) -> one backward -> [N>1: the packed per-Gaussian gradients
+are summed over ranks — by the sharded peer-memory optimiser kernel, or with --no-peer-adam by ONE
+NCCL all-reduce] -> fused Adam over the packed parameter arena ->
 per-keyframe pose/exposure Adam + pose update.  Keyframes are sharded over ranks, so the
 total work is fixed ("strong" scaling).
 
@@ -277,7 +278,8 @@ def run(args):
     kfs, host = build_window(device, render_fn, model_cls, None, sc)
     gm = model_cls(sc.xyz, sc.f_dc, sc.f_rest, sc.opacity, sc.scaling, sc.rotation, sh_degree=sc.sh_degree)
     win = mapping.MappingWindow(gm, kfs, sc.bg, render_fn=render_fn, adam_cls=adam_cls, loss_fn=loss_fn,
-                                cuda_graph=graph, view_streams=1 if impl_ref else args.view_streams)
+                                cuda_graph=graph, view_streams=1 if impl_ref else args.view_streams,
+                                peer_adam=(not impl_ref) and world > 1 and not args.no_peer_adam)
     local_views = win.local
 
     def step():
@@ -404,7 +406,9 @@ def run(args):
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": "cfg3_replica: 1200x680, 500k Gaussians, SH0, 8-keyframe mapping window "
                                "(fwd+bwd per keyframe, fused Adam, pose Adam)",
-                   "keyframes": N_VIEWS, "parallelism": "keyframes sharded round-robin over %d rank(s)" % world,
+                   "keyframes": N_VIEWS, "parallelism": "keyframes sharded round-robin over %d rank(s)" % world + (
+                       "; gradient exchange + Adam + zero_grad as one kernel over NVLink peer memory"
+                       if getattr(win, "peer", None) is not None else ""),
                    "launch": ("cuda graphs (2 per step, one host sync)" if graph else "eager") +
                              ("" if impl_ref or args.view_streams < 2 else
                               ", views issued on %d forked streams" % args.view_streams),
@@ -473,6 +477,8 @@ def main():
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="native arm: eager launches instead of CUDA graphs")
+    ap.add_argument("--no-peer-adam", action="store_true",
+                    help="native arm, N>1: NCCL all-reduce + replicated Adam instead of the peer-memory step")
     ap.add_argument("--view-streams", type=int, default=4,
                     help="native arm: side streams the window's views are issued on (1 = serial)")
     args = ap.parse_args()

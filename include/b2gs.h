@@ -227,6 +227,25 @@ B2GS_API int b2gs_adam_step(const B2gsAdamSegment* segments, int32_t num_segment
 B2GS_API int b2gs_adam_step_dev(const B2gsAdamSegment* segments, int32_t num_segments,
                        int64_t* step_counter, float beta1, float beta2, float eps, void* stream);
 
+/* Sharded optimiser step over NVLink peer memory — replaces, for data-parallel ranks that hold
+ * replicas of the parameter arena,  dist.all_reduce(grad) + Adam.step() + zero_grad()
+ * (the reference has no multi-GPU path).  Every rank calls it with the same
+ * segments (pointers into ITS arenas).  Chunks of 1024 floats are owned round-robin by rank; the
+ * owner sums that chunk of every rank's gradients in rank order, clears them, updates its own
+ * Adam moments (moments of chunks a rank does not own stay untouched) and writes the new
+ * parameters into every replica.  Two inter-rank flag barriers bracket the kernel on the stream.
+ * All arrays are HOST arrays of DEVICE pointers valid in this process (peer mappings). */
+typedef struct B2gsPeerArena {
+  int32_t world, rank;
+  float* const* param_base;   /* [world] base of every rank's parameter arena */
+  float* const* grad_base;    /* [world] base of every rank's gradient arena */
+  uint32_t* const* signal;    /* [world] every rank's signal pad: >= 16 zero-initialised uint32 */
+  uint32_t* fail_flag;        /* local device word, set to 1 if a barrier timed out (about 4 s) */
+} B2gsPeerArena;
+B2GS_API int b2gs_adam_step_peer(const B2gsAdamSegment* segments, int32_t num_segments,
+                        int64_t* step_counter, float beta1, float beta2, float eps,
+                        const B2gsPeerArena* peers, void* stream);
+
 /* ---- fused per-pixel losses (utils/slam_utils.py:56-128) ---------------------------------
  * mode: 0 mapping rgbd (get_loss_mapping_rgbd :113-128), 1 tracking rgbd (:74-88),
  *       2 mapping rgb / monocular (:101-110), 3 tracking rgb / monocular (:64-72).

@@ -69,6 +69,14 @@ class B2gsAdamSegment(C.Structure):
     ]
 
 
+class B2gsPeerArena(C.Structure):
+    _fields_ = [
+        ("world", C.c_int32), ("rank", C.c_int32),
+        ("param_base", C.POINTER(C.c_void_p)), ("grad_base", C.POINTER(C.c_void_p)),
+        ("signal", C.POINTER(C.c_void_p)), ("fail_flag", C.c_void_p),
+    ]
+
+
 # every symbol include/b2gs.h declares: name -> (restype, argtypes)
 SYMBOLS = {
     "b2gs_version": (C.c_int, []),
@@ -111,6 +119,8 @@ SYMBOLS = {
                                      C.c_float, C.c_float, C.c_void_p]),
     "b2gs_adam_step": (C.c_int, [C.POINTER(B2gsAdamSegment), C.c_int32, C.c_int64, C.c_float,
                                  C.c_float, C.c_float, C.c_void_p]),
+    "b2gs_adam_step_peer": (C.c_int, [C.POINTER(B2gsAdamSegment), C.c_int32, C.c_void_p, C.c_float,
+                                      C.c_float, C.c_float, C.POINTER(B2gsPeerArena), C.c_void_p]),
 }
 
 

@@ -26,6 +26,7 @@ class FusedAdam(torch.optim.Optimizer):
             raise ValueError("invalid lr / eps")
         super().__init__(params, dict(lr=lr, betas=betas, eps=eps))
         self.capturable = bool(capturable)
+        self.peer = None        # peer.PeerArena: step() = all-reduce + Adam + zero_grad over NVLink peers
         self._step_dev = None
         self._lr_dev = None
         self._lr_host = None
@@ -71,6 +72,7 @@ class FusedAdam(torch.optim.Optimizer):
                 step += 1
                 state["step"] = step
                 if self.capturable:
+                    self._host_step = step
                     step = -1          # one device-side counter for the whole optimizer
                 g = p.grad if p.grad.is_contiguous() else p.grad.contiguous()
                 key = (p.device, step, float(beta1), float(beta2), float(group["eps"]))
@@ -93,9 +95,17 @@ class FusedAdam(torch.optim.Optimizer):
                     if len(buckets) != 1:
                         raise RuntimeError("capturable FusedAdam needs one (betas, eps) for all groups")
                     if self._step_dev is None:
-                        self._step_dev = torch.zeros(1, dtype=torch.int64, device=dev)
-                    check(lib.b2gs_adam_step_dev(segs, len(items), self._step_dev.data_ptr(), beta1,
-                                                 beta2, eps, stream))
+                        # continues from the host-side count (state restored after densify / resume)
+                        self._step_dev = torch.full((1,), int(getattr(self, "_host_step", 1)) - 1,
+                                                    dtype=torch.int64, device=dev)
+                    if self.peer is not None:
+                        check(lib.b2gs_adam_step_peer(segs, len(items), self._step_dev.data_ptr(), beta1,
+                                                      beta2, eps, self.peer.struct(), stream))
+                    else:
+                        check(lib.b2gs_adam_step_dev(segs, len(items), self._step_dev.data_ptr(), beta1,
+                                                     beta2, eps, stream))
+                elif self.peer is not None:
+                    raise RuntimeError("the peer-memory step needs FusedAdam(capturable=True)")
                 else:
                     check(lib.b2gs_adam_step(segs, len(items), step, beta1, beta2, eps, stream))
         return loss

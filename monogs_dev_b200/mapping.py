@@ -53,6 +53,7 @@ class GaussianModel:
         nn.Parameters and twelve moment tensors, GS/scene/gaussian_model.py:468-555)."""
         dev = src["xyz"].device
         capturable = bool(getattr(self.optimizer, "capturable", False))
+        step_dev = getattr(self.optimizer, "_step_dev", None)     # device step count survives re-allocation
         if self.optimizer is not None:
             self._lr = {g["name"]: g["lr"] for g in self.optimizer.param_groups}
         sizes = [src[k].numel() for k in _GROUPS]
@@ -60,8 +61,12 @@ class GaussianModel:
         for n in sizes:
             offs.append(total)
             total += (n + 3) // 4 * 4          # keep every segment 16 B aligned for float4 access
-        self.flat = torch.zeros(total, device=dev)
-        self.flat_grad = torch.zeros(total, device=dev)
+        peer = getattr(self, "peer", None)
+        if peer is not None:                   # arenas every rank of the node can address (peer.py)
+            self.flat, self.flat_grad = peer.alloc(total)
+        else:
+            self.flat = torch.zeros(total, device=dev)
+            self.flat_grad = torch.zeros(total, device=dev)
         self.flat_m = torch.zeros(total, device=dev)
         self.flat_v = torch.zeros(total, device=dev)
         self._params = {}
@@ -81,9 +86,46 @@ class GaussianModel:
             if moments is not None:
                 st["exp_avg"].copy_(moments[k][0])
                 st["exp_avg_sq"].copy_(moments[k][1])
+        self.optimizer.peer = peer
+        self.optimizer._step_dev = step_dev
         for a in ("xyz_gradient_accum", "denom", "max_radii2D"):
             if hasattr(self, a):
                 delattr(self, a)
+
+    def enable_peer_arena(self, peer):
+        """move the arenas into peer-mapped memory and make optimizer.step() the sharded
+        all-reduce + Adam + zero_grad kernel (csrc/adam.cu: adam_peer_kernel).  Collective: every
+        rank calls it with identical parameters.  The Adam moments of a chunk then live on the
+        rank that owns it; `gather_moments()` rebuilds full copies (needed before densify)."""
+        src = {k: self._params[k].detach().clone() for k in _GROUPS}
+        mom = {k: (self.optimizer.state[self._params[k]]["exp_avg"].clone(),
+                   self.optimizer.state[self._params[k]]["exp_avg_sq"].clone()) for k in _GROUPS}
+        steps = {k: self.optimizer.state[self._params[k]]["step"] for k in _GROUPS}
+        self.peer = peer
+        self.optimizer.capturable = True
+        self._allocate(src, mom, steps)
+
+    def gather_moments(self):
+        """peer mode: moments are only maintained by each chunk's owner (the other ranks' copies
+        keep their value from before enable_peer_arena); sum the owners' copies back together."""
+        peer = getattr(self, "peer", None)
+        if peer is None:
+            return
+        chunk = 1024                            # csrc/adam.cu: PEER_CHUNK
+        idx = torch.arange(self.flat_m.numel(), device=self.flat_m.device)
+        # chunk ownership is per segment (chunks restart at every segment start)
+        own = torch.zeros_like(idx, dtype=torch.bool)
+        c0 = 0
+        for k in _GROUPS:
+            p = self._params[k]
+            o = (p.data_ptr() - self.flat.data_ptr()) // 4
+            n = p.numel()
+            ch = c0 + torch.arange(n, device=idx.device) // chunk
+            own[o:o + n] = (ch % peer.world) == peer.rank
+            c0 += (n + chunk - 1) // chunk
+        for t in (self.flat_m, self.flat_v):
+            t.mul_(own)
+            dist.all_reduce(t, op=dist.ReduceOp.SUM, group=peer.group)
 
     def densify_and_prune(self, max_grad, min_opacity, extent, max_screen_size, **kw):
         from .densify import densify_and_prune
@@ -222,7 +264,7 @@ class MappingWindow:
 
     def __init__(self, gaussians, keyframes, bg, pose_lr=(0.003, 0.001, 0.01, 0.01),
                  optimize_pose=True, group=None, render_fn=None, adam_cls=FusedAdam,
-                 loss_fn=None, cuda_graph=False, densify_stats=True, view_streams=1):
+                 loss_fn=None, cuda_graph=False, densify_stats=True, view_streams=1, peer_adam=False):
         self.g, self.kfs, self.bg = gaussians, keyframes, bg
         self.render_fn = render_fn or (render_fused if isinstance(gaussians, GaussianModel) else render)
         self.loss_fn = loss_fn or get_loss_mapping_rgbd
@@ -256,6 +298,13 @@ class MappingWindow:
         # render kernels.  Gradients meet in the arena through atomics either way.
         self.view_streams = max(1, int(view_streams))
         self._side = None
+        # peer_adam: gradient exchange + optimiser step as one kernel over NVLink peer memory
+        # (GaussianModel.enable_peer_arena) instead of NCCL all-reduce + replicated Adam
+        self.peer = None
+        if peer_adam and self.world > 1 and self.fused_reg:
+            from .peer import PeerArena
+            self.peer = PeerArena(gaussians.flat.device, group)
+            gaussians.enable_peer_arena(self.peer)
         self.last = {}
         self._g1 = self._g2 = None
         self.graph_launches = 0
@@ -317,7 +366,9 @@ class MappingWindow:
 
     def _update(self, set_to_none):
         g = self.g
-        if self.world > 1:
+        if self.peer is not None:
+            g.optimizer.step()            # all-reduce + Adam + zero_grad: one kernel over peer memory
+        elif self.world > 1:
             if hasattr(g, "flat_grad"):   # ONE message for all six parameter groups
                 dist.all_reduce(g.flat_grad, op=dist.ReduceOp.SUM, group=self.group)
             else:                         # stock layout: one message per parameter tensor
@@ -325,8 +376,9 @@ class MappingWindow:
                     if p.grad is None:
                         p.grad = torch.zeros_like(p)
                     dist.all_reduce(p.grad, op=dist.ReduceOp.SUM, group=self.group)
-        g.optimizer.step()
-        g.zero_grad()
+        if self.peer is None:
+            g.optimizer.step()
+            g.zero_grad()
         if self.kf_optimizer is not None:
             self.kf_optimizer.step()
             self.kf_optimizer.zero_grad(set_to_none=set_to_none)
