@@ -288,6 +288,16 @@ class MappingWindow:
                        dict(params=[cam.exposure_b], lr=pose_lr[3])]
         kw = dict(capturable=True) if (self.cuda_graph and adam_cls is FusedAdam) else {}
         self.kf_optimizer = adam_cls(groups, lr=0.0, eps=1e-8, **kw) if groups else None
+        # the window's camera / exposure gradients live in ONE buffer: zeroing them is one fill
+        # instead of four per keyframe
+        self._kf_grad = None
+        kf_params = [p for gr in groups for p in gr["params"]]
+        if kf_params and all(p.is_cuda for p in kf_params):
+            self._kf_grad = torch.zeros(sum(p.numel() for p in kf_params), device=kf_params[0].device)
+            o = 0
+            for p in kf_params:
+                p.grad = self._kf_grad[o:o + p.numel()].view_as(p)
+                o += p.numel()
         if self.cuda_graph:
             if not isinstance(gaussians.optimizer, FusedAdam):
                 raise RuntimeError("cuda_graph=True needs the FusedAdam optimizer")
@@ -310,6 +320,12 @@ class MappingWindow:
         self.graph_launches = 0
         self._loss = None
         self._steps = 0
+
+    def _zero_kf_grads(self, set_to_none):
+        if self._kf_grad is not None:
+            self._kf_grad.zero_()
+        elif self.kf_optimizer is not None:
+            self.kf_optimizer.zero_grad(set_to_none=set_to_none)
 
     # -- the two halves of a step ------------------------------------------------------
     def _forward_backward(self):
@@ -381,7 +397,7 @@ class MappingWindow:
             g.zero_grad()
         if self.kf_optimizer is not None:
             self.kf_optimizer.step()
-            self.kf_optimizer.zero_grad(set_to_none=set_to_none)
+            self._zero_kf_grads(set_to_none)
             if self.optimize_pose:
                 for v in self.local:
                     if v > 0:
@@ -404,8 +420,7 @@ class MappingWindow:
         loss, stats = self._forward_backward()
         if rz._SyncFree.enabled and rz.check_overflow(self._states(stats)):
             self.g.zero_grad()              # discard the background-only pass and redo it
-            if self.kf_optimizer is not None:
-                self.kf_optimizer.zero_grad(set_to_none=set_to_none)
+            self._zero_kf_grads(set_to_none)
             loss, stats = self._forward_backward()
             if rz.check_overflow(self._states(stats)):
                 raise RuntimeError("binning capacity overflow persisted after a retry")
@@ -450,8 +465,7 @@ class MappingWindow:
         self._g1.replay()
         if rz.check_overflow(self._gstates):    # the one host sync of the step
             self.g.zero_grad()
-            if self.kf_optimizer is not None:
-                self.kf_optimizer.zero_grad(set_to_none=False)
+            self._zero_kf_grads(False)
             g2 = self._g2
             self._g1 = None
             self._capture()                       # larger capacities are now in rz._SyncFree.cap

@@ -278,3 +278,84 @@ def test_scale_regulariser_matches_torch():
     val = losses.scale_regulariser(raw, sink)
     assert abs(float(val) - float(ref)) <= 1e-6 * abs(float(ref))
     assert torch.allclose(sink - 0.25, raw.grad, rtol=1e-4, atol=2e-8)   # sink holds 0.25 + g: fp32 ulp of 0.25
+
+
+def test_peer_adam_two_ranks_on_one_gpu_matches_allreduce_plus_adam():
+    """b2gs_adam_step_peer through the C ABI with two 'ranks' that live on ONE device (two arenas,
+    two streams — the flag barriers make the streams wait for each other): equals gradient sum +
+    b2gs_adam_step_dev bit for bit, clears every gradient arena, leaves both replicas identical,
+    and only touches the moments of the chunks a rank owns."""
+    import ctypes as C
+    from monogs_dev_b200 import _lib
+    lib = _lib.lib
+    torch.manual_seed(3)
+    sizes, lrs = [5000, 1234, 4099], [1e-2, 3e-3, 5e-4]        # 4099: a ragged, non-float4 tail
+    offs, total = [], 0
+    for n in sizes:
+        offs.append(total)
+        total += (n + 3) // 4 * 4
+    W = 2
+    p0 = torch.randn(total, device=DEV)
+    params = [p0.clone() for _ in range(W)]
+    grads = [torch.randn(total, device=DEV) for _ in range(W)]
+    ms = [torch.zeros(total, device=DEV) for _ in range(W)]
+    vs = [torch.zeros(total, device=DEV) for _ in range(W)]
+    sig = [torch.zeros(64, dtype=torch.int32, device=DEV) for _ in range(W)]
+    fail = [torch.zeros(1, dtype=torch.int32, device=DEV) for _ in range(W)]
+    steps = [torch.zeros(1, dtype=torch.int64, device=DEV) for _ in range(W)]
+    # expected: sum in rank order, then the single-rank kernel
+    pe, me, ve, se = p0.clone(), torch.zeros(total, device=DEV), torch.zeros(total, device=DEV), \
+        torch.zeros(1, dtype=torch.int64, device=DEV)
+    streams = [torch.cuda.Stream() for _ in range(W)]
+
+    def segs(p, g, m, v):
+        a = (_lib.B2gsAdamSegment * len(sizes))()
+        for s, o, n, lr in zip(a, offs, sizes, lrs):
+            s.param, s.grad, s.exp_avg, s.exp_avg_sq = (p.data_ptr() + 4 * o, g.data_ptr() + 4 * o,
+                                                        m.data_ptr() + 4 * o, v.data_ptr() + 4 * o)
+            s.n, s.lr = n, lr
+        return a
+
+    # world = 1 call first: CUDA loads a kernel lazily at its first launch and that load waits for
+    # running kernels — here the other "rank"'s spinning barrier (separate processes do not share
+    # this: each loads its own copy while only its own barrier is in flight)
+    wp, wg, wm, wv = (torch.zeros(total, device=DEV) for _ in range(4))
+    wsig, wst = torch.zeros(64, dtype=torch.int32, device=DEV), torch.zeros(1, dtype=torch.int64, device=DEV)
+    one = (C.c_void_p * 1)
+    pa1 = _lib.B2gsPeerArena(1, 0, one(wp.data_ptr()), one(wg.data_ptr()), one(wsig.data_ptr()), fail[0].data_ptr())
+    _lib.check(lib.b2gs_adam_step_peer(segs(wp, wg, wm, wv), len(sizes), wst.data_ptr(), 0.9, 0.999, 1e-15,
+                                       C.byref(pa1), torch.cuda.current_stream().cuda_stream))
+    torch.cuda.synchronize()
+
+    for it in range(3):
+        for g in grads:
+            g.normal_()
+        gsum = (torch.zeros_like(grads[0]) + grads[0]) + grads[1]
+        _lib.check(lib.b2gs_adam_step_dev(segs(pe, gsum, me, ve), len(sizes), se.data_ptr(), 0.9, 0.999, 1e-15,
+                                          torch.cuda.current_stream().cuda_stream))
+        torch.cuda.synchronize()
+        keep = []
+        for r in range(W):
+            pb = (C.c_void_p * W)(*[t.data_ptr() for t in params])
+            gb = (C.c_void_p * W)(*[t.data_ptr() for t in grads])
+            sb = (C.c_void_p * W)(*[t.data_ptr() for t in sig])
+            pa = _lib.B2gsPeerArena(W, r, pb, gb, sb, fail[r].data_ptr())
+            keep.append((pb, gb, sb, pa))
+            _lib.check(lib.b2gs_adam_step_peer(segs(params[r], grads[r], ms[r], vs[r]), len(sizes),
+                                               steps[r].data_ptr(), 0.9, 0.999, 1e-15, C.byref(pa),
+                                               streams[r].cuda_stream))
+        torch.cuda.synchronize()
+        assert int(fail[0]) == 0 and int(fail[1]) == 0, "peer barrier timed out"
+        assert torch.equal(params[0], params[1]), "replicas differ"
+        assert torch.equal(params[0], pe), "peer step != sum + Adam"
+        for o, n in zip(offs, sizes):       # every rank's gradients are cleared by the chunk owners
+            assert float(grads[0][o:o + n].abs().max()) == 0.0 and float(grads[1][o:o + n].abs().max()) == 0.0
+        # padding between segments is never touched
+        for o, n in zip(offs, sizes):
+            pad = slice(o + n, o + (n + 3) // 4 * 4)
+            assert torch.equal(params[0][pad], p0[pad])
+    # moments: each element maintained by exactly one rank, the other rank's copy still zero
+    own0, own1 = vs[0] != 0, vs[1] != 0
+    assert not bool((own0 & own1).any())
+    assert bool(own0.any()) and bool(own1.any())
+    assert torch.equal(ms[0] + ms[1], me) and torch.equal(vs[0] + vs[1], ve)

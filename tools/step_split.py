@@ -13,7 +13,7 @@ dev = torch.device("cuda", local)
 sc = syn.make_scene(bench.WORKLOAD, device=dev, n_views=bench.N_VIEWS)
 kfs, host = bench.build_window(dev, mapping.render_fused, mapping.GaussianModel, None, sc)
 gm = mapping.GaussianModel(sc.xyz, sc.f_dc, sc.f_rest, sc.opacity, sc.scaling, sc.rotation, sh_degree=sc.sh_degree)
-win = mapping.MappingWindow(gm, kfs, sc.bg, cuda_graph=True, view_streams=4)
+win = mapping.MappingWindow(gm, kfs, sc.bg, cuda_graph=True, view_streams=4, peer_adam=True)
 for _ in range(6):
     win.step()
 bench.barrier_sync(world)
