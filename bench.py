@@ -217,6 +217,30 @@ def rooflines(prof, units, pk):
     return table
 
 
+def ncu_metrics(kernel):
+    """issue-slot and FMA-pipe utilisation of `kernel` from the newest committed `ncu --set full`
+    summary under profiles/ (what the FP32 'frac' does not say: see DESIGN.md §7)."""
+    import glob
+    import re
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "*_ncu_render_full.txt")))
+    if not files:
+        return None
+    want = {"smsp__issue_active.avg.pct_of_peak_sustained_active": "issue_slot_pct",
+            "sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active": "fma_pipe_pct",
+            "gpu__time_duration.sum": "ncu_us"}
+    out, on = {}, False
+    for line in open(files[-1]):
+        if line.startswith("----"):
+            on = kernel + "_kernel" in line
+        elif on:
+            m = re.match(r"\s+(\S+)\s+([0-9.]+)", line)
+            if m and m.group(1) in want:
+                out[want[m.group(1)]] = round(float(m.group(2)), 1)
+    if out:
+        out["source"] = os.path.basename(files[-1])
+    return out or None
+
+
 def ncu_traffic(kernel):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel`, from the newest
     `ncu --set full` summary committed under profiles/ (tools/ncu_summary.py); None if absent."""
@@ -386,6 +410,7 @@ def run(args):
             top = max(own, key=lambda k: own[k][1])
             roof = dict(kernel=top, **rooftab[top])
             roof["traffic"] = ncu_traffic(top)
+            roof["ncu"] = ncu_metrics(top)
             tot = sum(v[1] for v in prof.values())
             roof["share_of_gpu_kernel_time"] = round(prof[top][1] / tot, 3) if tot else None
         work = dict(P=P, P_visible=pvis, instances=R, effective_pairs=pairs)
