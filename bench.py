@@ -149,12 +149,16 @@ def sum_over_ranks(x, world, device):
     return float(t.item())
 
 
-def timed_steps(step_fn, K, world):
+def timed_steps(step_fn, K, world, settle=None):
+    """`settle`: called inside the timed region after the K steps — the mapping window's flush(),
+    which confirms that no step was discarded by a binning overflow (and re-runs any that were)."""
     barrier_sync(world)
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     a.record()
     for _ in range(K):
         step_fn()
+    if settle is not None:
+        settle()
     b.record()
     barrier_sync(world)
     return a.elapsed_time(b)
@@ -343,7 +347,7 @@ def run(args):
         step()
     sampler = ClockSampler(local) if rank == 0 else None
     l0 = _lib.lib.b2gs_kernel_launches()
-    ms = timed_steps(step, K, world)
+    ms = timed_steps(step, K, world, settle=win.flush)
     launches = _lib.lib.b2gs_kernel_launches() - l0
     if graph:      # replays do not pass through the host-side counter: launches captured per step x K
         launches = win.graph_launches * K
@@ -353,7 +357,7 @@ def run(args):
     step_e2e()
     torch.cuda.synchronize()
     pending[0] = False                             # the timed region issues its own first copy
-    ms_e2e = max_over_ranks(timed_steps(step_e2e, K, world), world, device)
+    ms_e2e = max_over_ranks(timed_steps(step_e2e, K, world, settle=win.flush), world, device)
 
     # headline companion: single-view fwd+bwd only (no optimizer), rank-local, N=1 only
     single = None
@@ -434,7 +438,8 @@ def run(args):
                    "keyframes": N_VIEWS, "parallelism": "keyframes sharded round-robin over %d rank(s)" % world + (
                        "; gradient exchange + Adam + zero_grad as one kernel over NVLink peer memory"
                        if getattr(win, "peer", None) is not None else ""),
-                   "launch": ("cuda graphs (2 per step, one host sync)" if graph else "eager") +
+                   "launch": ("cuda graphs (2 per step, no host sync inside a step: overflow flags are read back "
+                              "asynchronously, flush() inside the timed region)" if graph else "eager") +
                              ("" if impl_ref or args.view_streams < 2 else
                               ", views issued on %d forked streams" % args.view_streams),
                    "l2_policy": "inputs larger than L2: >400 MB touched per step (8 GT frames 104 MB, "

@@ -239,12 +239,20 @@ typedef struct B2gsPeerArena {
   int32_t world, rank;
   float* const* param_base;   /* [world] base of every rank's parameter arena */
   float* const* grad_base;    /* [world] base of every rank's gradient arena */
-  uint32_t* const* signal;    /* [world] every rank's signal pad: >= 16 zero-initialised uint32 */
+  uint32_t* const* signal;    /* [world] every rank's signal pad: >= 32 zero-initialised uint32 */
   uint32_t* fail_flag;        /* local device word, set to 1 if a barrier timed out (about 4 s) */
 } B2gsPeerArena;
 B2GS_API int b2gs_adam_step_peer(const B2gsAdamSegment* segments, int32_t num_segments,
                         int64_t* step_counter, float beta1, float beta2, float eps,
                         const B2gsPeerArena* peers, void* stream);
+
+/* Update guard: while `device_flag` (a device int32, or NULL to clear) is set for the calling host
+ * thread, the state-updating launches enqueued by b2gs_adam_step_dev / b2gs_adam_step_peer /
+ * b2gs_pose_update read it ON THE DEVICE and do nothing when it is non-zero.  A CUDA-graph step
+ * can thus discard its own update after a sync-free forward overflowed (b2gs_forward status) with
+ * no host round trip inside the step.  b2gs_adam_step_peer additionally ORs the flag over all
+ * ranks (the result is left in the flag), so data-parallel replicas agree. */
+B2GS_API void b2gs_set_update_guard(const int32_t* device_flag);
 
 /* ---- fused per-pixel losses (utils/slam_utils.py:56-128) ---------------------------------
  * mode: 0 mapping rgbd (get_loss_mapping_rgbd :113-128), 1 tracking rgbd (:74-88),

@@ -39,7 +39,9 @@ __device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, 
 
 __global__ void __launch_bounds__(256)
 adam_kernel(const __grid_constant__ AdamTable t, float w1, float beta2, float w2, float bc2_sqrt,
-            float eps, float beta1, const long long* __restrict__ step_dev) {
+            float eps, float beta1, const long long* __restrict__ step_dev,
+            const int32_t* __restrict__ guard) {
+  if (guard && *guard) return;   // the step is being discarded (b2gs_set_update_guard)
   // which segment does this block's chunk belong to?
   int s = 0;
   const long long chunk = blockIdx.x;
@@ -94,7 +96,10 @@ adam_kernel(const __grid_constant__ AdamTable t, float w1, float beta2, float w2
   }
 }
 
-__global__ void adam_tick_kernel(long long* step) { *step += 1; }
+__global__ void adam_tick_kernel(long long* step, const int32_t* __restrict__ guard) {
+  if (guard && *guard) return;
+  *step += 1;
+}
 
 // ---- sharded step over NVLink peer memory --------------------------------------------------
 // Data-parallel ranks hold replicas of the parameter arena and their own gradient arena, both
@@ -117,26 +122,45 @@ struct PeerTable {
 // All-to-all flag barrier between the ranks' streams (one thread per peer).  Slot [src] on the
 // destination's pad: 0 -> 1 by the arriving rank, 1 -> 0 by the owner; CAS on both sides makes
 // back-to-back barriers safe.  Bounded spin (about 4 s): a dead peer must not hang the GPU.
-__global__ void peer_barrier_kernel(const __grid_constant__ PeerTable pt, uint32_t* __restrict__ fail) {
+// With a guard word: every rank also posts its guard value on all pads (slots 16 + src) before
+// arriving, and leaves the OR over all ranks in its own guard word — the ranks then agree on
+// whether this step's update is discarded.
+__global__ void peer_barrier_kernel(const __grid_constant__ PeerTable pt, uint32_t* __restrict__ fail,
+                                    int32_t* __restrict__ guard) {
   const int t = threadIdx.x;
-  if (t >= pt.world || t == pt.rank) return;
-  __threadfence_system();
-  const long long t0 = clock64();
-  const long long limit = 8000000000LL;
-  uint32_t* dst = pt.signal[t] + pt.rank;
-  while (atomicCAS_system(dst, 0u, 1u) != 0u)
-    if (clock64() - t0 > limit) { *fail = 1u; return; }
-  uint32_t* src = pt.signal[pt.rank] + t;
-  while (atomicCAS_system(src, 1u, 0u) != 1u)
-    if (clock64() - t0 > limit) { *fail = 1u; return; }
-  __threadfence_system();
+  const bool peer = t < pt.world && t != pt.rank;
+  if (guard && t < pt.world) {
+    volatile uint32_t* slot = pt.signal[t] + PEER_MAX + pt.rank;
+    *slot = (uint32_t)(*guard != 0);
+  }
+  if (peer) {
+    __threadfence_system();
+    const long long t0 = clock64();
+    const long long limit = 8000000000LL;
+    uint32_t* dst = pt.signal[t] + pt.rank;
+    bool ok = true;
+    while (ok && atomicCAS_system(dst, 0u, 1u) != 0u)
+      if (clock64() - t0 > limit) { *fail = 1u; ok = false; }
+    uint32_t* src = pt.signal[pt.rank] + t;
+    while (ok && atomicCAS_system(src, 1u, 0u) != 1u)
+      if (clock64() - t0 > limit) { *fail = 1u; ok = false; }
+    __threadfence_system();
+  }
+  __syncthreads();
+  if (guard && t == 0) {
+    uint32_t any = 0;
+    for (int r = 0; r < pt.world; ++r) any |= *(volatile uint32_t*)(pt.signal[pt.rank] + PEER_MAX + r);
+    *guard = (int32_t)any;
+  }
 }
 
 constexpr int PEER_CHUNK = 1024;   // floats per ownership chunk = one float4 per thread of a block
 
 __global__ void __launch_bounds__(256)
 adam_peer_kernel(const __grid_constant__ AdamTable t, const __grid_constant__ PeerTable pt, float w1,
-                 float beta2, float w2, float eps, float beta1, const long long* __restrict__ step_dev) {
+                 float beta2, float w2, float eps, float beta1, const long long* __restrict__ step_dev,
+                 const int32_t* __restrict__ guard) {
+  if (guard && *guard) return;   // some rank overflowed: every rank discards this step
   const long long chunk = (long long)blockIdx.x * pt.world + pt.rank;   // chunks this rank owns
   if (chunk >= t.first_chunk[t.num]) return;
   int s = 0;
@@ -212,7 +236,7 @@ static int adam_impl(const B2gsAdamSegment* segments, int32_t num_segments, int6
   if (step < 1) { set_error("b2gs_adam_step: step must be >= 1"); return B2GS_ERR_INVALID; }
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   if (step_dev) {
-    adam_tick_kernel<<<1, 1, 0, st>>>(step_dev);
+    adam_tick_kernel<<<1, 1, 0, st>>>(step_dev, update_guard());
     B2GS_LAUNCH_CHECK(st, 0);
   }
   // scalar prep in double, as torch does in Python (torch/optim/adam.py)
@@ -246,7 +270,8 @@ static int adam_impl(const B2gsAdamSegment* segments, int32_t num_segments, int6
     if (chunks > 0) {
       if (chunks > 0x7fffffffLL) { set_error("b2gs_adam_step: too many elements"); return B2GS_ERR_INVALID; }
       B2GS_PROF("adam", st);
-      adam_kernel<<<(unsigned)chunks, 256, 0, st>>>(t, w1, beta2, w2, bc2_sqrt, eps, beta1, step_dev);
+      adam_kernel<<<(unsigned)chunks, 256, 0, st>>>(t, w1, beta2, w2, bc2_sqrt, eps, beta1, step_dev,
+                                                        update_guard());
       B2GS_LAUNCH_CHECK(st, 0);
     }
     done += k;
@@ -282,6 +307,7 @@ extern "C" int b2gs_adam_step_peer(const B2gsAdamSegment* segments, int32_t num_
     return B2GS_ERR_INVALID;
   }
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  int32_t* guard = const_cast<int32_t*>(update_guard());
   PeerTable pt;
   memset(&pt, 0, sizeof(pt));
   pt.world = peers->world; pt.rank = peers->rank;
@@ -307,10 +333,10 @@ extern "C" int b2gs_adam_step_peer(const B2gsAdamSegment* segments, int32_t num_
   }
   t.first_chunk[num_segments] = chunks;
   t.num = num_segments;
-  adam_tick_kernel<<<1, 1, 0, st>>>(reinterpret_cast<long long*>(step_counter));
+  adam_tick_kernel<<<1, 1, 0, st>>>(reinterpret_cast<long long*>(step_counter), guard);
   B2GS_LAUNCH_CHECK(st, 0);
   // every rank's gradients are final ...
-  peer_barrier_kernel<<<1, 32, 0, st>>>(pt, peers->fail_flag);
+  peer_barrier_kernel<<<1, 32, 0, st>>>(pt, peers->fail_flag, guard);
   B2GS_LAUNCH_CHECK(st, 0);
   if (chunks > 0) {
     const long long blocks = (chunks + pt.world - 1) / pt.world;
@@ -318,11 +344,11 @@ extern "C" int b2gs_adam_step_peer(const B2gsAdamSegment* segments, int32_t num_
     B2GS_PROF("adam_peer", st);
     adam_peer_kernel<<<(unsigned)blocks, 256, 0, st>>>(t, pt, (float)(1.0 - (double)beta1), beta2,
                                                       (float)(1.0 - (double)beta2), eps, beta1,
-                                                      reinterpret_cast<const long long*>(step_counter));
+                                                      reinterpret_cast<const long long*>(step_counter), guard);
     B2GS_LAUNCH_CHECK(st, 0);
   }
   // ... and every replica / gradient arena has been written by all of its chunk owners
-  peer_barrier_kernel<<<1, 32, 0, st>>>(pt, peers->fail_flag);
+  peer_barrier_kernel<<<1, 32, 0, st>>>(pt, peers->fail_flag, nullptr);
   B2GS_LAUNCH_CHECK(st, 0);
   return B2GS_OK;
 }

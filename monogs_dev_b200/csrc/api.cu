@@ -16,6 +16,9 @@ namespace b2gs {
 static thread_local char g_err[512] = "";
 static std::atomic<unsigned long long> g_launches{0};
 
+static thread_local const int32_t* g_guard = nullptr;
+const int32_t* update_guard() { return g_guard; }
+
 void note_launches(int n) { g_launches.fetch_add((unsigned long long)n, std::memory_order_relaxed); }
 
 // ---- per-kernel event timing ------------------------------------------------------
@@ -105,6 +108,8 @@ using namespace b2gs;
 
 extern "C" int b2gs_version(void) { return 100; }
 extern "C" const char* b2gs_last_error(void) { return g_err; }
+extern "C" void b2gs_set_update_guard(const int32_t* device_flag) { b2gs::g_guard = device_flag; }
+
 extern "C" uint64_t b2gs_kernel_launches(void) { return g_launches.load(std::memory_order_relaxed); }
 
 extern "C" void b2gs_profile_enable(int on) {

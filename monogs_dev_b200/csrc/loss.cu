@@ -267,8 +267,9 @@ namespace b2gs {
 // [48:51] camera centre.  One thread: the arithmetic is ~200 flops.
 __global__ void pose_update_kernel(float* __restrict__ state, const float* __restrict__ proj,
                                    float* __restrict__ rot_delta, float* __restrict__ trans_delta,
-                                   float* __restrict__ tau_norm) {
+                                   float* __restrict__ tau_norm, const int32_t* __restrict__ guard) {
   if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  if (guard && *guard) return;   // the step is being discarded (b2gs_set_update_guard)
   const float th[3] = {rot_delta[0], rot_delta[1], rot_delta[2]};
   const float rho[3] = {trans_delta[0], trans_delta[1], trans_delta[2]};
   // skew(theta), its square (utils/pose_utils.py:12-22)
@@ -353,7 +354,8 @@ extern "C" int b2gs_pose_update(float* cam_state, const float* projmatrix_raw, f
     return B2GS_ERR_INVALID;
   }
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  pose_update_kernel<<<1, 32, 0, st>>>(cam_state, projmatrix_raw, rot_delta, trans_delta, tau_norm);
+  pose_update_kernel<<<1, 32, 0, st>>>(cam_state, projmatrix_raw, rot_delta, trans_delta, tau_norm,
+                                       update_guard());
   B2GS_LAUNCH_CHECK(st, 0);
   return B2GS_OK;
 }

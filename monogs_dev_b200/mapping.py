@@ -256,11 +256,15 @@ class MappingWindow:
     the full list (only its shard's images are touched).
 
     cuda_graph=True: the step is captured once as two graphs —
-        G1: every local view's render -> fused loss, the regulariser, one backward;
-        G2: [gradient all-reduce] -> fused Adam -> pose/exposure Adam -> pose updates -> zero grads
-    — and replayed with ONE host sync per step (the binning-overflow check between the two:
-    the sync-free forward renders background-only when its instance capacity is exceeded, in
-    which case G1 is re-captured with a larger capacity before any parameter is touched)."""
+        G1: every local view's render -> fused loss, the regulariser, one backward, and the OR of
+            the views' binning-overflow flags into one device word;
+        G2: [gradient exchange] -> fused Adam -> pose/exposure Adam -> pose updates -> zero grads,
+            every state-changing kernel guarded by that word (b2gs_set_update_guard)
+    — and replayed back to back with NO host sync inside or between steps.  The sync-free forward
+    renders background-only when its instance capacity is exceeded; such a step discards its own
+    update on the device.  The host reads the flags asynchronously and looks at them two step()
+    calls later (or at flush()): G1 is then re-captured with a larger capacity and the discarded
+    steps are run again, so after flush() every step() has been applied exactly once."""
 
     def __init__(self, gaussians, keyframes, bg, pose_lr=(0.003, 0.001, 0.01, 0.01),
                  optimize_pose=True, group=None, render_fn=None, adam_cls=FusedAdam,
@@ -317,6 +321,8 @@ class MappingWindow:
             gaussians.enable_peer_arena(self.peer)
         self.last = {}
         self._g1 = self._g2 = None
+        self._ovf = self._status_all = None
+        self._pending, self._launched = [], 0
         self.graph_launches = 0
         self._loss = None
         self._steps = 0
@@ -434,18 +440,89 @@ class MappingWindow:
         rz.set_sync_free(True, rz._SyncFree.headroom)
         from ._lib import lib
         torch.cuda.synchronize()
+        dev = self.bg.device
+        if self._ovf is None:
+            self._ovf = torch.zeros(1, dtype=torch.int32, device=dev)
         l0 = lib.b2gs_kernel_launches()
         self._g1 = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self._g1):
             self._loss, self._stats = self._forward_backward()
-        self._gstates = self._states(self._stats)
+            # did any local view run out of binning capacity?  -> the device word that guards G2
+            sts = [s for s in self._states(self._stats) if s is not None and s.status is not None]
+            if sts:
+                self._status_all = torch.stack([s.status for s in sts])
+                self._ovf.copy_(self._status_all[:, 1].max().reshape(1))
+            else:
+                self._status_all = None
+        self._gstates = sts
         l1 = lib.b2gs_kernel_launches()
         if self._g2 is None:
             self._g2 = torch.cuda.CUDAGraph()
             with torch.cuda.graph(self._g2):
-                self._update(set_to_none=False)
+                if self.world > 1 and self.peer is None:     # the ranks must agree (peer mode: the
+                    dist.all_reduce(self._ovf, op=dist.ReduceOp.MAX, group=self.group)   # barrier ORs)
+                lib.b2gs_set_update_guard(self._ovf.data_ptr())
+                try:
+                    self._update(set_to_none=False)
+                finally:
+                    lib.b2gs_set_update_guard(None)
             self._l2 = lib.b2gs_kernel_launches() - l1
         self.graph_launches = (l1 - l0) + self._l2      # libb2gs kernels per replayed step
+        if self._status_all is not None:
+            self._flag_host = [(torch.empty(self._status_all.shape, dtype=torch.int32).pin_memory(),
+                                torch.empty(1, dtype=torch.int32).pin_memory()) for _ in range(3)]
+
+    def _launch(self):
+        """one replay of the captured step + an asynchronous read-back of its overflow flags"""
+        for opt in (self.g.optimizer, self.kf_optimizer):
+            if opt is not None:
+                opt.sync_lr()
+        self._g1.replay()
+        self._g2.replay()
+        if self._status_all is not None:
+            st, ov = self._flag_host[self._launched % 3]
+            st.copy_(self._status_all, non_blocking=True)      # this rank's views: sizes the retry
+            ov.copy_(self._ovf, non_blocking=True)             # after G2: the OR over all ranks
+            ev = torch.cuda.Event()
+            ev.record()
+            self._pending.append((ev, st, ov))
+        self._launched += 1
+
+    def _settle(self, keep):
+        """look at the flags of all but the `keep` newest launches; on overflow: drain, enlarge the
+        capacities, re-capture G1 and run the discarded steps again (their updates were no-ops: the
+        guard word made every Adam / pose kernel return, on every rank — the word is the OR over
+        all ranks, so all ranks take this path together)."""
+        from . import rasterizer as rz
+        over = False
+        while len(self._pending) > keep:
+            ev, st, ov = self._pending.pop(0)
+            ev.synchronize()
+            rz.note_overflow(self._gstates, st.tolist())
+            over = over or bool(int(ov[0]))
+        if not over:
+            return
+        torch.cuda.synchronize()
+        lost = 1 + len(self._pending)           # every launch since the overflowing one was discarded
+        for ev, st, ov in self._pending:
+            rz.note_overflow(self._gstates, st.tolist())
+        self._pending.clear()
+        for _ in range(lost):
+            self.g.zero_grad()
+            self._zero_kf_grads(False)
+            self._g1 = None
+            self._capture()                     # larger capacities are now in rz._SyncFree.cap
+            self._launch()
+            torch.cuda.synchronize()
+            ev, st, ov = self._pending.pop(0)
+            rz.note_overflow(self._gstates, st.tolist())
+            if int(ov[0]):
+                raise RuntimeError("binning capacity overflow persisted after re-capture")
+
+    def flush(self):
+        """settle every launched step (one host sync): afterwards all of them have been applied."""
+        if self.cuda_graph and self._g1 is not None:
+            self._settle(0)
 
     def _graph_step(self):
         from . import rasterizer as rz
@@ -459,21 +536,10 @@ class MappingWindow:
             return loss
         if self._g1 is None:
             self._capture()
-        for opt in (self.g.optimizer, self.kf_optimizer):
-            if opt is not None:
-                opt.sync_lr()
-        self._g1.replay()
-        if rz.check_overflow(self._gstates):    # the one host sync of the step
-            self.g.zero_grad()
-            self._zero_kf_grads(False)
-            g2 = self._g2
-            self._g1 = None
-            self._capture()                       # larger capacities are now in rz._SyncFree.cap
-            self._g2 = g2
-            self._g1.replay()
-            if rz.check_overflow(self._gstates):
-                raise RuntimeError("binning capacity overflow persisted after re-capture")
-        self._g2.replay()
+        # no host sync inside the step: the flags of the step launched two calls ago are looked at
+        # now (its event completed long ago, the GPU is busy with the previous step meanwhile)
+        self._settle(1)
+        self._launch()
         self.last = self._stats
         return self._loss
 

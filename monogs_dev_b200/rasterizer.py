@@ -113,9 +113,14 @@ def check_overflow(states):
     sts = [s for s in states if s is not None and s.status is not None]
     if not sts:
         return False
-    vals = torch.stack([s.status for s in sts]).cpu()
+    return note_overflow(sts, torch.stack([s.status for s in sts]).cpu().tolist())
+
+
+def note_overflow(sts, vals):
+    """host half of check_overflow: `vals` = the (instances, overflow flag) pairs of `sts` already
+    on the host (MappingWindow reads them back asynchronously, two steps late)."""
     over = False
-    for s, v in zip(sts, vals.tolist()):
+    for s, v in zip(sts, vals):
         need = int(v[0] * _SyncFree.headroom) + 4096
         if v[1]:
             over = True

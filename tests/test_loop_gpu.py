@@ -157,13 +157,25 @@ def test_graph_mapping_step_matches_eager(view_streams):
         for a, b in zip(k0[1:], k1[1:]):
             assert torch.allclose(a["cam"].T, b["cam"].T, atol=2e-3)
             assert torch.allclose(a["cam"].exposure_a, b["cam"].exposure_a, atol=2e-3)
-        # overflow path: starve the capacity -> re-capture, same loss as eager
+        # overflow path: starve the capacity -> the step discards its own update on the device, the
+        # host notices two calls later (or at flush), re-captures and runs the discarded steps again
+        w1.flush()
+        before = g1.flat.clone()
         for key in list(rz._SyncFree.cap):
             rz._SyncFree.cap[key] = 64
         w1._g1 = None
-        l1b = float(w1.step())
+        w1.step()
+        torch.cuda.synchronize()
+        assert torch.equal(g1.flat, before), "an overflowed step must not touch the parameters"
+        w1.flush()
+        assert not torch.equal(g1.flat, before), "flush() must re-run the discarded step"
+        l1b = float(w1._loss)
         l0b = float(w0.step())
         assert abs(l0b - l1b) <= 5e-4 * abs(l0b)
+        w1.step(); w1.step(); w1.step(); w1.flush()        # and the deferred path stays clean
+        w0.step(); w0.step(); w0.step()
+        diff = (g0.flat - g1.flat).abs()
+        assert float((diff > 1e-3 * (1 + g0.flat.abs())).float().mean()) < 2e-3
     finally:
         rz.set_sync_free(False)
 
