@@ -380,9 +380,11 @@ iso_reg_kernel(int P, const float* __restrict__ raw_scaling, float weight,
     if (dL_draw) {
       const float g0 = sgnf(d0), g1 = sgnf(d1), g2 = sgnf(d2);
       const float gm = (g0 + g1 + g2) / 3.0f;          // through the mean
-      dL_draw[3 * i] += w * (g0 - gm) * s0;             // d exp(x) = exp(x) dx
-      dL_draw[3 * i + 1] += w * (g1 - gm) * s1;
-      dL_draw[3 * i + 2] += w * (g2 - gm) * s2;
+      // d exp(x) = exp(x) dx; red.global.add: the views' backward kernels may be adding to the same
+      // arena on other streams
+      atomicAdd(&dL_draw[3 * i], w * (g0 - gm) * s0);
+      atomicAdd(&dL_draw[3 * i + 1], w * (g1 - gm) * s1);
+      atomicAdd(&dL_draw[3 * i + 2], w * (g2 - gm) * s2);
     }
   }
   acc = block_sum(acc, s_red);

@@ -129,10 +129,12 @@ class GaussianModel:
 
     def densify_and_prune(self, max_grad, min_opacity, extent, max_screen_size, **kw):
         from .densify import densify_and_prune
+        self.gather_moments()              # peer mode: full Adam moments before they are re-packed
         return densify_and_prune(self, max_grad, min_opacity, extent, max_screen_size, **kw)
 
     def prune_points(self, mask):
         from .densify import prune_points
+        self.gather_moments()
         return prune_points(self, mask)
 
     _xyz = property(lambda s: s._params["xyz"])
@@ -311,7 +313,7 @@ class MappingWindow:
         # view's single-CTA tile scan, kernel tails and loss reductions overlap another view's
         # render kernels.  Gradients meet in the arena through atomics either way.
         self.view_streams = max(1, int(view_streams))
-        self._side = None
+        self._side = self._reg_stream = None
         # peer_adam: gradient exchange + optimiser step as one kernel over NVLink peer memory
         # (GaussianModel.enable_peer_arena) instead of NCCL all-reduce + replicated Adam
         self.peer = None
@@ -339,13 +341,26 @@ class MappingWindow:
         loss = 0
         stats = {}
         side = []
-        if self.view_streams > 1 and len(self.local) > 1 and self.bg.is_cuda:
+        cuda = self.bg.is_cuda
+        main = torch.cuda.current_stream() if cuda else None
+        if self.view_streams > 1 and len(self.local) > 1 and cuda:
             if self._side is None:
                 self._side = [torch.cuda.Stream(self.bg.device) for _ in range(self.view_streams)]
             side = self._side
-            main = torch.cuda.current_stream()
             for s in side:
                 s.wait_stream(main)
+        reg = None
+        reg_stream = None
+        if self.rank == 0 and self.fused_reg:
+            # view-independent regulariser, counted once (slam_backend.py:229-231): one kernel,
+            # value + gradient added (atomically) to the scaling grad arena — on its own stream, next
+            # to the views instead of after them
+            if self._reg_stream is None:
+                self._reg_stream = torch.cuda.Stream(self.bg.device)
+            reg_stream = self._reg_stream
+            reg_stream.wait_stream(main)
+            with torch.cuda.stream(reg_stream):
+                reg = scale_regulariser(g._scaling, g._scaling.grad)
         terms = []
         for i, v in enumerate(self.local):
             kf = self.kfs[v]
@@ -358,13 +373,9 @@ class MappingWindow:
             main.wait_stream(s)
         for t in terms:
             loss = loss + t
-        reg = None
-        if self.rank == 0:         # view-independent regulariser counted once (slam_backend.py:229-231)
-            if self.fused_reg:     # one kernel: value + gradient added to the scaling grad arena
-                reg = scale_regulariser(g._scaling, g._scaling.grad)
-            else:
-                scaling = g.get_scaling
-                loss = loss + 10 * torch.abs(scaling - scaling.mean(dim=1).view(-1, 1)).mean()
+        if self.rank == 0 and not self.fused_reg:
+            scaling = g.get_scaling
+            loss = loss + 10 * torch.abs(scaling - scaling.mean(dim=1).view(-1, 1)).mean()
         if torch.is_tensor(loss):
             loss.backward()      # every node runs on the stream of its forward
             for s in side:
@@ -373,6 +384,7 @@ class MappingWindow:
         else:
             loss = torch.zeros((), device=self.bg.device)
         if reg is not None:
+            main.wait_stream(reg_stream)
             loss = loss + reg
         # densification statistics of every view (utils/slam_backend.py:277-284); the fused
         # renderer has already accumulated them inside its backward kernel
