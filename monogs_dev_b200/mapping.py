@@ -127,8 +127,19 @@ class GaussianModel:
             t.mul_(own)
             dist.all_reduce(t, op=dist.ReduceOp.SUM, group=peer.group)
 
+    def sync_densification_stats(self):
+        """data-parallel window: every rank has accumulated the statistics of ITS views only; the
+        densification decision must be the same on all replicas -> sum / max them over ranks."""
+        grp = getattr(self, "_dist_group", None)
+        if grp is None or not hasattr(self, "xyz_gradient_accum"):
+            return
+        dist.all_reduce(self.xyz_gradient_accum, op=dist.ReduceOp.SUM, group=grp)
+        dist.all_reduce(self.denom, op=dist.ReduceOp.SUM, group=grp)
+        dist.all_reduce(self.max_radii2D, op=dist.ReduceOp.MAX, group=grp)
+
     def densify_and_prune(self, max_grad, min_opacity, extent, max_screen_size, **kw):
         from .densify import densify_and_prune
+        self.sync_densification_stats()
         self.gather_moments()              # peer mode: full Adam moments before they are re-packed
         return densify_and_prune(self, max_grad, min_opacity, extent, max_screen_size, **kw)
 
@@ -316,6 +327,8 @@ class MappingWindow:
         self._side = self._reg_stream = None
         # peer_adam: gradient exchange + optimiser step as one kernel over NVLink peer memory
         # (GaussianModel.enable_peer_arena) instead of NCCL all-reduce + replicated Adam
+        if self.world > 1 and hasattr(gaussians, "sync_densification_stats"):
+            gaussians._dist_group = group if group is not None else dist.group.WORLD
         self.peer = None
         if peer_adam and self.world > 1 and self.fused_reg:
             from .peer import PeerArena

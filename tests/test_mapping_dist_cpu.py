@@ -68,6 +68,12 @@ def _worker(rank, world, port, out_dir):
         assert win.world == world and win.rank == rank
         assert win.local == [v for v in range(VIEWS) if v % world == rank]
         poses = {v: (kfs[v]["cam"].T.clone(), kfs[v]["cam"].exposure_a.detach().clone()) for v in win.local}
+        # densification statistics are per-rank (own views) until densify sums / maxes them
+        acc, den, rad = gm._stats()
+        acc.fill_(rank + 1.0); den.fill_(float(len(win.local))); rad.fill_(10.0 * (rank + 1))
+        gm.sync_densification_stats()
+        assert float(acc[0]) == sum(r + 1.0 for r in range(world)) and float(den[0]) == VIEWS
+        assert float(rad[0]) == 10.0 * world
         torch.save(dict(flat=gm.flat.detach().clone(), losses=losses, local=win.local, poses=poses),
                    os.path.join(out_dir, f"rank{rank}.pt"))
     finally:
