@@ -246,6 +246,20 @@ B2GS_API int b2gs_adam_step_peer(const B2gsAdamSegment* segments, int32_t num_se
                         int64_t* step_counter, float beta1, float beta2, float eps,
                         const B2gsPeerArena* peers, void* stream);
 
+/* RGB-D keyframe back-projection (the seed point cloud of new Gaussians; feeds b2gs_knn3_dist2).
+ * Replaces GaussianModel.create_pcd_from_image_and_depth's host round trip through open3d 0.17
+ * (GS/scene/gaussian_model.py:107-156: RGBDImage.create_from_color_and_depth(depth_scale=1,
+ * depth_trunc, convert_rgb_to_intensity=False) + PointCloud.create_from_rgbd_image(intrinsic,
+ * extrinsic, project_valid_depth_only=True)).
+ *   image [3,H,W] float32 (cam.original_image), exposure_a/b device scalars or NULL,
+ *   depth [H,W] float32, cam2world: HOST, 12 doubles = first three rows of inverse(extrinsic).
+ * Dense outputs in pixel (row-major) order: xyz [H*W,3], rgb [H*W,3] (uint8-quantised / 255),
+ * valid [H*W] (depth > 0 after truncation); rows of invalid pixels hold zeros. */
+B2GS_API int b2gs_backproject_rgbd(int32_t W, int32_t H, const float* image, const float* exposure_a,
+                          const float* exposure_b, const float* depth, double fx, double fy,
+                          double cx, double cy, const double* cam2world, float depth_trunc,
+                          float* xyz, float* rgb, uint8_t* valid, void* stream);
+
 /* Update guard: while `device_flag` (a device int32, or NULL to clear) is set for the calling host
  * thread, the state-updating launches enqueued by b2gs_adam_step_dev / b2gs_adam_step_peer /
  * b2gs_pose_update read it ON THE DEVICE and do nothing when it is non-zero.  A CUDA-graph step

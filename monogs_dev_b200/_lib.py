@@ -120,6 +120,10 @@ SYMBOLS = {
     "b2gs_adam_step": (C.c_int, [C.POINTER(B2gsAdamSegment), C.c_int32, C.c_int64, C.c_float,
                                  C.c_float, C.c_float, C.c_void_p]),
     "b2gs_set_update_guard": (None, [C.c_void_p]),
+    "b2gs_backproject_rgbd": (C.c_int, [C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                        C.c_double, C.c_double, C.c_double, C.c_double,
+                                        C.POINTER(C.c_double), C.c_float, C.c_void_p, C.c_void_p,
+                                        C.c_void_p, C.c_void_p]),
     "b2gs_adam_step_peer": (C.c_int, [C.POINTER(B2gsAdamSegment), C.c_int32, C.c_void_p, C.c_float,
                                       C.c_float, C.c_float, C.POINTER(B2gsPeerArena), C.c_void_p]),
 }

@@ -143,6 +143,19 @@ class GaussianModel:
         self.gather_moments()              # peer mode: full Adam moments before they are re-packed
         return densify_and_prune(self, max_grad, min_opacity, extent, max_screen_size, **kw)
 
+    # keyframe seeding (gaussian_model.py:107-227): back-projection, down-sample, distCUDA2 scales
+    def create_pcd_from_image(self, cam_info, init=False, scale=2.0, depthmap=None, generator=None):
+        from .seeding import create_pcd_from_image
+        return create_pcd_from_image(self, cam_info, init, scale, depthmap, generator)
+
+    def extend_from_pcd(self, fused_point_cloud, features, scales, rots, opacities, kf_id):
+        from .seeding import extend_from_pcd
+        return extend_from_pcd(self, fused_point_cloud, features, scales, rots, opacities, kf_id)
+
+    def extend_from_pcd_seq(self, cam_info, kf_id=-1, init=False, scale=2.0, depthmap=None, generator=None):
+        from .seeding import extend_from_pcd_seq
+        return extend_from_pcd_seq(self, cam_info, kf_id, init, scale, depthmap, generator)
+
     def prune_points(self, mask):
         from .densify import prune_points
         self.gather_moments()
