@@ -156,11 +156,39 @@ def init_densify():
     print("cfg4_init_densify", json.dumps(row), flush=True)
 
 
+def seeding_step():
+    """keyframe insertion at the Replica shape: back-projection + down-sample + distCUDA2 scales +
+    append to a 500k-Gaussian arena (the reference goes through the host and open3d: not timed here)."""
+    sc = syn.make_scene("cfg3_replica", device=DEV, n_views=1)
+    gm = mapping.GaussianModel(sc.xyz, sc.f_dc, sc.f_rest, sc.opacity, sc.scaling, sc.rotation, sh_degree=0)
+    cam = sc.cameras[0]
+    g = torch.Generator().manual_seed(3)
+    cam.original_image = torch.rand(3, sc.H, sc.W, generator=g).to(DEV)
+    cam.depth = (torch.rand(sc.H, sc.W, generator=g) * 5 + 0.5).numpy()
+    from monogs_dev_b200 import seeding
+    depth_dev = torch.as_tensor(cam.depth).to(DEV)
+    row = dict(W=sc.W, H=sc.H,
+               backproject_kernel_ms=timeit(lambda: seeding.backproject_rgbd(cam.original_image, depth_dev, cam.fx, cam.fy,
+                                                                             cam.cx, cam.cy, seeding._w2c(cam)), 20, 3))
+    ts = []
+    for rep in range(4):
+        torch.cuda.synchronize(); t0 = time.perf_counter()
+        pcd = gm.create_pcd_from_image(cam, init=False)
+        torch.cuda.synchronize(); t1 = time.perf_counter()
+        n = gm.extend_from_pcd(*pcd, kf_id=rep)
+        torch.cuda.synchronize(); t2 = time.perf_counter()
+        ts.append(((t1 - t0) * 1e3, (t2 - t1) * 1e3, n))
+    row["create_pcd_from_image_ms"], row["extend_from_pcd_ms"], row["seeded"] = min(t[0] for t in ts[1:]), min(t[1] for t in ts[1:]), ts[-1][2]
+    OUT["cfg3_keyframe_seeding"] = row
+    print("cfg3_keyframe_seeding", json.dumps(row), flush=True)
+
+
 if __name__ == "__main__":
-    out = sys.argv[1] if len(sys.argv) > 1 else os.path.join(ROOT, "gpurun_out", "secondary_configs.json")
-    for step in (lambda: single_view("cfg1_plumbing", 50), lambda: single_view("cfg2_tracking", 50),
+    out = sys.argv[1] if len(sys.argv) > 1 and not sys.argv[1].startswith("--") else os.path.join(ROOT, "gpurun_out", "secondary_configs.json")
+    steps = (seeding_step,) if "--seeding-only" in sys.argv else None
+    for step in steps or (lambda: single_view("cfg1_plumbing", 50), lambda: single_view("cfg2_tracking", 50),
                  lambda: single_view("cfg3_replica", 20), tracking, init_densify,
-                 lambda: single_view("cfg5_large", 5)):
+                 lambda: single_view("cfg5_large", 5), seeding_step):
         try:
             step()
         except Exception as e:
