@@ -320,6 +320,9 @@ def run(args):
     stage = {v: (torch.empty_like(kfs[v]["gt_image"]), torch.empty_like(kfs[v]["gt_depth"])) for v in local_views}
     ev_ready, ev_free = torch.cuda.Event(), torch.cuda.Event()
     pending = [False]
+    loss_host = [torch.empty(1, dtype=torch.float32).pin_memory() for _ in range(2)]
+    loss_ev = [torch.cuda.Event(), torch.cuda.Event()]
+    n_e2e, losses_read = [0], []
 
     def prefetch():
         copy_stream.wait_event(ev_free)
@@ -341,7 +344,23 @@ def run(args):
             kfs[v]["gt_depth"].copy_(stage[v][1], non_blocking=True)
         ev_free.record(cur)
         prefetch()                                 # next step's inputs, overlapped with this step
-        return float(win.step().item())            # result read back: device -> host
+        loss = win.step()
+        # result read back, device -> host, every step: an async copy into pinned memory that the
+        # host reads after it has enqueued the NEXT step (settle_e2e reads the last one)
+        i = n_e2e[0] % 2
+        loss_host[i].copy_(loss.detach().reshape(1), non_blocking=True)
+        loss_ev[i].record(cur)
+        if n_e2e[0] > 0:
+            loss_ev[1 - i].synchronize()
+            losses_read.append(float(loss_host[1 - i][0]))
+        n_e2e[0] += 1
+
+    def settle_e2e():
+        win.flush()
+        if n_e2e[0] > 0:
+            i = (n_e2e[0] - 1) % 2
+            loss_ev[i].synchronize()
+            losses_read.append(float(loss_host[i][0]))
 
     for _ in range(W_ + (4 if graph else 0)):      # graph mode: 3 eager sizing steps + the capture
         step()
@@ -355,9 +374,13 @@ def run(args):
     ms = max_over_ranks(ms, world, device)
     launches = int(sum_over_ranks(launches, world, device))
     step_e2e()
+    settle_e2e()
     torch.cuda.synchronize()
     pending[0] = False                             # the timed region issues its own first copy
-    ms_e2e = max_over_ranks(timed_steps(step_e2e, K, world, settle=win.flush), world, device)
+    n_e2e[0] = 0
+    del losses_read[:]
+    ms_e2e = max_over_ranks(timed_steps(step_e2e, K, world, settle=settle_e2e), world, device)
+    assert len(losses_read) == K, "every step's loss must have been read back inside the timed region"
 
     # headline companion: single-view fwd+bwd only (no optimizer), rank-local, N=1 only
     single = None
@@ -447,7 +470,9 @@ def run(args):
                    **work},
         "clocks": clocks,
         "e2e": {"value": round(N_VIEWS * K / (ms_e2e / 1e3), 3), "unit": "iters/s",
-                "ms_per_step": round(ms_e2e / K, 4), "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4 * world},
+                "ms_per_step": round(ms_e2e / K, 4), "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4 * world,
+                "readback": "every step's loss copied to pinned host memory and read by the host one step "
+                            "later (after the next step is enqueued); the last one before the region ends"},
         "gpu_launches": launches,
         "single_view_fwd_bwd_iters_s": round(single, 2) if single else None,
     }
