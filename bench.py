@@ -534,7 +534,7 @@ def main():
     ap.add_argument("--no-graph", action="store_true", help="native arm: eager launches instead of CUDA graphs")
     ap.add_argument("--no-peer-adam", action="store_true",
                     help="native arm, N>1: NCCL all-reduce + replicated Adam instead of the peer-memory step")
-    ap.add_argument("--view-streams", type=int, default=4,
+    ap.add_argument("--view-streams", type=int, default=8,
                     help="native arm: side streams the window's views are issued on (1 = serial)")
     args = ap.parse_args()
     if not torch.cuda.is_available():
