@@ -43,6 +43,10 @@ class GaussianModel:
                   scaling=0.001 * spatial_lr_scale, rotation=0.001)
         lr.update(lrs or {})
         self._lr = lr
+        # xyz schedule of update_learning_rate (configs/rgbd/replica/base_config.yaml:66-69);
+        # training_setup() overrides it from an opt_params object
+        self.lr_init, self.lr_final = lr["xyz"], 0.0000016 * spatial_lr_scale
+        self.lr_delay_mult, self.max_steps = 0.01, 30000
         self.optimizer = None
         self._allocate(dict(xyz=xyz, f_dc=f_dc, f_rest=f_rest, opacity=opacity, scaling=scaling,
                             rotation=rotation))
@@ -160,6 +164,51 @@ class GaussianModel:
         from .densify import prune_points
         self.gather_moments()
         return prune_points(self, mask)
+
+    # schedule, opacity resets, SH degree, PLY (gaussian_model.py:103-105,205-206,245-465): model_io.py
+    def init_lr(self, spatial_lr_scale):
+        self.spatial_lr_scale = spatial_lr_scale
+
+    def training_setup(self, training_args):
+        from .model_io import training_setup
+        return training_setup(self, training_args)
+
+    def update_learning_rate(self, iteration):
+        from .model_io import update_learning_rate
+        return update_learning_rate(self, iteration)
+
+    def oneupSHdegree(self):
+        from .model_io import oneupSHdegree
+        return oneupSHdegree(self)
+
+    def reset_opacity(self):
+        from .model_io import reset_opacity
+        return reset_opacity(self)
+
+    def reset_opacity_nonvisible(self, visibility_filters):
+        from .model_io import reset_opacity_nonvisible
+        return reset_opacity_nonvisible(self, visibility_filters)
+
+    def construct_list_of_attributes(self):
+        from .model_io import construct_list_of_attributes
+        return construct_list_of_attributes(self)
+
+    def save_ply(self, path):
+        from .model_io import save_ply
+        return save_ply(self, path)
+
+    def load_ply(self, path):
+        """replaces the whole map by the file's Gaussians: fresh arenas, zero Adam moments,
+        active_sh_degree = max_sh_degree, statistics and keyframe ids reset (:377-466)."""
+        from .model_io import load_ply_tensors
+        src = load_ply_tensors(path, self.max_sh_degree, self.flat.device)
+        self._allocate(src)
+        self.optimizer._step_dev = None         # a new map: the device step count restarts too
+        self.active_sh_degree = self.max_sh_degree
+        P = src["xyz"].shape[0]
+        self.unique_kfIDs = torch.zeros(P, dtype=torch.int32, device=self.flat.device)
+        self.n_obs = torch.zeros(P, dtype=torch.int32, device=self.flat.device)
+        self._stats()
 
     _xyz = property(lambda s: s._params["xyz"])
     _features_dc = property(lambda s: s._params["f_dc"])
