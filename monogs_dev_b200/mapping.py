@@ -80,11 +80,16 @@ class GaussianModel:
             p = torch.nn.Parameter(view)
             p.grad = self.flat_grad[o:o + n].view(src[k].shape)
             self._params[k] = p
-        self.optimizer = FusedAdam([dict(params=[self._params[k]], lr=self._lr[k], name=k) for k in _GROUPS],
-                                   lr=0.0, eps=1e-15, capturable=capturable)
+        # optimizer_cls: the CPU host-logic tests run the same arena under torch.optim.Adam (the fused
+        # optimizer has no CPU path); torch's Adam keeps its step count as a tensor
+        cls = getattr(self, "optimizer_cls", FusedAdam)
+        fused = cls is FusedAdam
+        self.optimizer = cls([dict(params=[self._params[k]], lr=self._lr[k], name=k) for k in _GROUPS],
+                             lr=0.0, eps=1e-15, **(dict(capturable=capturable) if fused else {}))
         for k, o, n in zip(_GROUPS, offs, sizes):   # Adam moments are views of the arenas too
             st = self.optimizer.state[self._params[k]]
-            st["step"] = (steps or {}).get(k, 0)
+            step = (steps or {}).get(k, 0)
+            st["step"] = step if fused else torch.tensor(float(step))
             st["exp_avg"] = self.flat_m[o:o + n].view(src[k].shape)
             st["exp_avg_sq"] = self.flat_v[o:o + n].view(src[k].shape)
             if moments is not None:
@@ -296,10 +301,10 @@ def render_fused(viewpoint_camera, pc, pipe=None, bg_color=None, scaling_modifie
 
 
 def get_loss_mapping_rgbd_torch(image, depth, viewpoint, gt_image, gt_depth, alpha=0.95,
-                                rgb_boundary_threshold=0.01):
+                                rgb_boundary_threshold=0.01, initialization=False):
     """utils/slam_utils.py:91-96,113-128 restated op for op in torch (what the reference arm of
     bench.py runs; the product path uses the fused kernels of losses.py)."""
-    image_ab = torch.exp(viewpoint.exposure_a) * image + viewpoint.exposure_b
+    image_ab = image if initialization else torch.exp(viewpoint.exposure_a) * image + viewpoint.exposure_b
     rgb_pixel_mask = (gt_image.sum(dim=0) > rgb_boundary_threshold).view(*depth.shape)
     depth_pixel_mask = (gt_depth > 0.01).view(*depth.shape)
     l1_rgb = torch.abs(image_ab * rgb_pixel_mask - gt_image * rgb_pixel_mask)
@@ -343,8 +348,16 @@ class MappingWindow:
 
     def __init__(self, gaussians, keyframes, bg, pose_lr=(0.003, 0.001, 0.01, 0.01),
                  optimize_pose=True, group=None, render_fn=None, adam_cls=FusedAdam,
-                 loss_fn=None, cuda_graph=False, densify_stats=True, view_streams=1, peer_adam=False):
+                 loss_fn=None, cuda_graph=False, densify_stats=True, view_streams=1, peer_adam=False,
+                 kf_optimizer=None, regulariser=True):
+        """keyframe dict flags (optional): `optimize_pose` (default: every view but the first, as
+        viewpoint.uid == 0 is never moved, utils/slam_backend.py:315-316,434-436) and
+        `optimize_exposure` (default True; the reference gives keyframe 0 and the two random
+        views of an iteration no optimised parameter at all, :196-227,434-471).
+        kf_optimizer: an existing optimizer over the camera parameters (BackEnd.keyframe_optimizers
+        outlives a map() call); by default one is built for the local views."""
         self.g, self.kfs, self.bg = gaussians, keyframes, bg
+        self.regulariser = bool(regulariser)     # BackEnd.initialize_map has no isotropic term (:86-139)
         self.render_fn = render_fn or (render_fused if isinstance(gaussians, GaussianModel) else render)
         self.loss_fn = loss_fn or get_loss_mapping_rgbd
         self.group = group
@@ -360,13 +373,17 @@ class MappingWindow:
         groups = []
         for v in self.local:       # utils/slam_backend.py:434-471 (one Adam over the kf params)
             cam = keyframes[v]["cam"]
-            if optimize_pose and v > 0:
+            if self._moves(v):
                 groups += [dict(params=[cam.cam_rot_delta], lr=pose_lr[0]),
                            dict(params=[cam.cam_trans_delta], lr=pose_lr[1])]
-            groups += [dict(params=[cam.exposure_a], lr=pose_lr[2]),
-                       dict(params=[cam.exposure_b], lr=pose_lr[3])]
+            if keyframes[v].get("optimize_exposure", True):
+                groups += [dict(params=[cam.exposure_a], lr=pose_lr[2]),
+                           dict(params=[cam.exposure_b], lr=pose_lr[3])]
         kw = dict(capturable=True) if (self.cuda_graph and adam_cls is FusedAdam) else {}
-        self.kf_optimizer = adam_cls(groups, lr=0.0, eps=1e-8, **kw) if groups else None
+        if kf_optimizer is not None:
+            self.kf_optimizer, groups = kf_optimizer, []
+        else:
+            self.kf_optimizer = adam_cls(groups, lr=0.0, eps=1e-8, **kw) if groups else None
         # the window's camera / exposure gradients live in ONE buffer: zeroing them is one fill
         # instead of four per keyframe
         self._kf_grad = None
@@ -404,6 +421,9 @@ class MappingWindow:
         self._loss = None
         self._steps = 0
 
+    def _moves(self, v):
+        return bool(self.optimize_pose and self.kfs[v].get("optimize_pose", v > 0))
+
     def _zero_kf_grads(self, set_to_none):
         if self._kf_grad is not None:
             self._kf_grad.zero_()
@@ -426,7 +446,7 @@ class MappingWindow:
                 s.wait_stream(main)
         reg = None
         reg_stream = None
-        if self.rank == 0 and self.fused_reg:
+        if self.rank == 0 and self.fused_reg and self.regulariser:
             # view-independent regulariser, counted once (slam_backend.py:229-231): one kernel,
             # value + gradient added (atomically) to the scaling grad arena — on its own stream, next
             # to the views instead of after them
@@ -437,10 +457,12 @@ class MappingWindow:
             with torch.cuda.stream(reg_stream):
                 reg = scale_regulariser(g._scaling, g._scaling.grad)
         terms = []
+        # prune-mode iterations leave the densification statistics alone (utils/slam_backend.py:241-275)
+        rkw = dict(with_stats=False) if (self.render_fn is render_fused and not self.densify_stats) else {}
         for i, v in enumerate(self.local):
             kf = self.kfs[v]
             with (torch.cuda.stream(side[i % len(side)]) if side else contextlib.nullcontext()):
-                pkg = self.render_fn(kf["cam"], g, None, self.bg)
+                pkg = self.render_fn(kf["cam"], g, None, self.bg, **rkw)
                 terms.append(self.loss_fn(pkg["render"], pkg["depth"], kf["cam"], kf["gt_image"],
                                           kf["gt_depth"]))
             stats[v] = pkg
@@ -448,7 +470,7 @@ class MappingWindow:
             main.wait_stream(s)
         for t in terms:
             loss = loss + t
-        if self.rank == 0 and not self.fused_reg:
+        if self.rank == 0 and not self.fused_reg and self.regulariser:
             scaling = g.get_scaling
             loss = loss + 10 * torch.abs(scaling - scaling.mean(dim=1).view(-1, 1)).mean()
         if torch.is_tensor(loss):
@@ -473,9 +495,13 @@ class MappingWindow:
                     g.add_densification_stats(pkg["viewspace_points"], vis)
         return loss, stats
 
-    def _update(self, set_to_none):
+    def _update(self, set_to_none, gaussians=True):
         g = self.g
-        if self.peer is not None:
+        if not gaussians:
+            # the reference's optimizer.step() right after densify_and_prune finds only fresh
+            # Parameters without .grad and changes nothing (utils/slam_backend.py:290-309)
+            pass
+        elif self.peer is not None:
             g.optimizer.step()            # all-reduce + Adam + zero_grad: one kernel over peer memory
         elif self.world > 1:
             if hasattr(g, "flat_grad"):   # ONE message for all six parameter groups
@@ -485,7 +511,7 @@ class MappingWindow:
                     if p.grad is None:
                         p.grad = torch.zeros_like(p)
                     dist.all_reduce(p.grad, op=dist.ReduceOp.SUM, group=self.group)
-        if self.peer is None:
+        if self.peer is None and gaussians:
             g.optimizer.step()
             g.zero_grad()
         if self.kf_optimizer is not None:
@@ -493,7 +519,7 @@ class MappingWindow:
             self._zero_kf_grads(set_to_none)
             if self.optimize_pose:
                 for v in self.local:
-                    if v > 0:
+                    if self._moves(v):
                         cam = self.kfs[v]["cam"]
                         try:
                             cam.update_pose(check_converged=False)
@@ -508,7 +534,7 @@ class MappingWindow:
         return out
 
     # -- eager -------------------------------------------------------------------------
-    def _eager_step(self, set_to_none=True):
+    def _eager_forward_backward(self, set_to_none=True):
         from . import rasterizer as rz
         loss, stats = self._forward_backward()
         if rz._SyncFree.enabled and rz.check_overflow(self._states(stats)):
@@ -517,9 +543,22 @@ class MappingWindow:
             loss, stats = self._forward_backward()
             if rz.check_overflow(self._states(stats)):
                 raise RuntimeError("binning capacity overflow persisted after a retry")
-        self._update(set_to_none)
         self.last = stats
         return loss
+
+    def _eager_step(self, set_to_none=True):
+        loss = self._eager_forward_backward(set_to_none)
+        self._update(set_to_none)
+        return loss
+
+    # the two halves on their own, for a caller that decides between them (backend.py: prune
+    # mode returns after the backward; densify / opacity resets sit between backward and step)
+    def forward_backward(self):
+        self.flush()
+        return self._eager_forward_backward(set_to_none=not self.cuda_graph)
+
+    def update(self, gaussians=True):
+        self._update(not self.cuda_graph, gaussians=gaussians)
 
     # -- CUDA graphs -------------------------------------------------------------------
     def _capture(self):

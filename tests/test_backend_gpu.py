@@ -1,0 +1,141 @@
+"""BackEnd.map / initialize_map (monogs_dev_b200/backend.py) on the real rasterizer: the CUDA-graph
+schedule against the eager one through plain, opacity-reset, densify and prune-mode iterations, and
+an eager run with random extra views.  The order-of-operations parity with the reference loop is
+pinned on the CPU (tests/test_backend_cpu.py); here the same schedule drives libb2gs."""
+import copy
+
+import pytest
+import torch
+
+from monogs_dev_b200 import backend, mapping, rasterizer as rz, synthetic as syn
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+CONFIG = {"Training": dict(monocular=False, init_itr_num=4, init_gaussian_update=3, init_gaussian_reset=2,
+                           init_gaussian_th=0.3, init_gaussian_extent=30, mapping_itr_num=3,
+                           gaussian_update_every=6, gaussian_update_offset=0, gaussian_th=0.55,
+                           gaussian_extent=1.0, gaussian_reset=4, size_threshold=200, window_size=3,
+                           pose_window=2, prune_mode="slam", lr=dict(cam_rot_delta=0.003, cam_trans_delta=0.001))}
+
+
+def _backend(cuda_graph, n_views, config=CONFIG, view_streams=1):
+    sc = syn.make_scene("cfg1_plumbing", device=DEV, n_views=n_views)
+    gtm = mapping.GaussianModel(sc.xyz + 0.01, sc.f_dc + 0.05, sc.f_rest, sc.opacity + 0.1, sc.scaling,
+                                sc.rotation, sh_degree=sc.sh_degree)
+    views = {}
+    with torch.no_grad():
+        for i, cam in enumerate(sc.cameras):
+            pkg = mapping.render(cam, gtm, None, sc.bg)
+            views[i] = dict(cam=cam, gt_image=pkg["render"].clone(), gt_depth=pkg["depth"].clone())
+    gm = mapping.GaussianModel(sc.xyz, sc.f_dc, sc.f_rest, sc.opacity, sc.scaling, sc.rotation,
+                               sh_degree=sc.sh_degree)
+    P = gm._xyz.shape[0]
+    gm.unique_kfIDs = (torch.arange(P, device=DEV) % n_views).int()
+    gm.n_obs = torch.zeros(P, dtype=torch.int32, device=DEV)
+    be = backend.BackEnd(config, gm, sc.bg, cameras_extent=6.0, cuda_graph=cuda_graph, view_streams=view_streams)
+    be.viewpoints = views
+    return be, gm, views
+
+
+def _mismatch(ga, gb, tol=1e-3):
+    """fraction of parameters per group that differ by more than tol * (1 + |a|): Adam normalises
+    the update, so atomics-order noise can flip a step where the gradient is ~0 — compare in the bulk"""
+    out = {}
+    for k in mapping._GROUPS:
+        a, b = ga._params[k].detach(), gb._params[k].detach()
+        if a.numel():
+            out[k] = float(((a - b).abs() > tol * (1 + a.abs())).float().mean())
+    return out
+
+
+def _bulk_equal(ga, gb, frac=2e-3):
+    """the opacity group is compared at 5e-3: with ONE device step count per optimizer (capturable
+    mode) the group that sat out a step after reset_opacity_nonvisible runs one step ahead in its
+    bias correction — a ratio of 0.94 at step 5 (this test resets at iteration 4), 1.0000 at the
+    reference's 2001"""
+    mm = _mismatch(ga, gb)
+    mm["opacity"] = _mismatch(ga, gb, tol=5e-3)["opacity"]
+    assert all(v < frac for v in mm.values()), mm
+    return True
+
+
+def test_graph_schedule_matches_eager_schedule():
+    try:
+        e, ge, ve = _backend(False, 3)
+        g, gg, vg = _backend(True, 3, view_streams=2)
+        window = [2, 1, 0]
+        for be in (e, g):
+            be.set_keyframe_optimizers(window)
+        # iterations 1-3 plain (graph warm-up), 4 opacity reset, 5 plain (first replay)
+        assert e.map(window, iters=5) is False and g.map(window, iters=5) is False
+        assert g._win._g1 is not None and g._win.graph_launches > 0, "graph path not taken"
+        assert _bulk_equal(ge, gg)
+        op = gg._opacity.detach()
+        # every raw opacity went through the reset (inverse_sigmoid(0.4) = -0.405 or an activated
+        # value in (0, 1)) and then one Adam step of at most lr = 0.05
+        assert float(op.min()) > -0.47 and float(op.max()) < 1.06
+        # iteration 6 densifies: same decisions up to threshold noise, fresh arena, window rebuilt
+        n0 = ge._xyz.shape[0]
+        assert e.map(window, iters=1) is True and g.map(window, iters=1) is True
+        assert ge._xyz.shape[0] != n0
+        assert abs(ge._xyz.shape[0] - gg._xyz.shape[0]) <= max(2, n0 // 200)
+        for k in mapping._GROUPS:
+            assert float(gg._params[k].grad.abs().sum()) == 0.0
+        # carry on on the new arena (warm-up, capture, replay); iteration 8 resets again
+        e.map(window, iters=6), g.map(window, iters=6)
+        assert e.iteration_count == g.iteration_count == 12
+        assert g._win._g1 is not None
+        if ge._xyz.shape[0] == gg._xyz.shape[0]:
+            assert _bulk_equal(ge, gg, frac=2e-2)
+        for k in (1, 2):
+            assert torch.allclose(ve[k]["cam"].T, vg[k]["cam"].T, atol=5e-3)
+            assert torch.allclose(ve[k]["cam"].exposure_a, vg[k]["cam"].exposure_a, atol=5e-3)
+        assert torch.equal(vg[0]["cam"].R, torch.eye(3)) and float(vg[0]["cam"].exposure_a) == 0.0
+        assert not torch.equal(vg[2]["cam"].T, torch.zeros(3))
+        assert float(vg[1]["cam"].exposure_a) != 0.0
+        # prune mode: backward only, parameters untouched, gradients left in the arena, masks per view
+        for be, gm in ((e, ge), (g, gg)):
+            before = gm.flat.clone()
+            stats = gm.xyz_gradient_accum.clone()
+            assert be.map(window, prune=True) is False
+            torch.cuda.synchronize()
+            assert torch.equal(gm.flat, before) and float(gm.flat_grad.abs().sum()) > 0
+            assert torch.equal(gm.xyz_gradient_accum, stats)
+            assert set(be.occ_aware_visibility) == set(window)
+            assert all(m.shape[0] == gm._xyz.shape[0] and m.dtype == torch.int64 and int(m.sum()) > 0
+                       for m in be.occ_aware_visibility.values())
+    finally:
+        rz.set_sync_free(False)
+
+
+def test_eager_schedule_with_random_views_and_initialize_map():
+    cfg0 = copy.deepcopy(CONFIG)
+    cfg0["Training"].update(init_itr_num=5, init_gaussian_update=3, init_gaussian_reset=100)
+    be, gm, views = _backend(False, 5, cfg0)
+    P0 = gm._xyz.shape[0]
+    pkg = be.initialize_map(0, views[0])
+    assert be.iteration_count == 5 and pkg["render"].shape[0] == 3
+    assert 0 < gm._xyz.shape[0] != P0                                  # iterations 0 and 3 densified
+    assert float(gm.optimizer.state[gm._xyz]["step"]) == 3.0           # ... and their Adam steps were void
+    assert be.occ_aware_visibility[0].shape[0] == gm._xyz.shape[0]
+    assert torch.equal(views[0]["cam"].R, torch.eye(3))
+    cfg = copy.deepcopy(CONFIG)
+    cfg["Training"].update(gaussian_update_every=1000, gaussian_update_offset=999, gaussian_reset=1000)
+    be2, gm2, views2 = _backend(False, 5, cfg)
+    window = [4, 3, 2]
+    be2.set_keyframe_optimizers(window)
+    first = None
+    for _ in range(6):
+        be2.map(window, iters=1)
+        loss = sum(float(mapping.get_loss_mapping_rgbd_torch(p["render"], p["depth"], views2[window[v]]["cam"],
+                                                              views2[window[v]]["gt_image"],
+                                                              views2[window[v]]["gt_depth"]))
+                   for v, p in be2._win.last.items() if v < 3)
+        first = loss if first is None else first
+    assert loss < first, "window loss did not go down"
+    assert len(be2._win.kfs) == 5                                      # 3 window views + the 2 older keyframes
+    for k in (0, 1):                                                    # random views: rendered, never optimised
+        assert torch.equal(views2[k]["cam"].R, torch.eye(3) if k == 0 else views2[k]["cam"].R)
+        assert float(views2[k]["cam"].exposure_a) == 0.0
+    assert float(views2[4]["cam"].exposure_a) != 0.0 and float(views2[2]["cam"].exposure_a) != 0.0
+    assert float(gm2.denom.max()) >= 6.0                               # statistics of all five views accumulate
