@@ -91,6 +91,9 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
         const int jj = c0 + lane;
         const bool keep = jj < cnt && (s_rec[jj].bm & wmask);
         unsigned mask = __ballot_sync(RF_FULL, keep);
+        // n_touched counts pixels whose transmittance is still above 0.5 after the splat; T only
+        // falls, so once no pixel of the warp is above 0.5 the two ballots per visit are dead code
+        const bool hot = __any_sync(RF_FULL, (!doneA && T.x > 0.5f) || (!doneB && T.y > 0.5f));
         while (mask) {
           const int k = __ffs(mask) - 1;
           mask &= mask - 1;
@@ -128,11 +131,13 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
           lastA = actA ? here : lastA;
           lastB = actB ? here : lastB;
           // n_touched: how many pixels saw this splat with T still above 0.5
-          const unsigned ta = __ballot_sync(RF_FULL, actA && test_T.x > 0.5f);
-          const unsigned tb = __ballot_sync(RF_FULL, actB && test_T.y > 0.5f);
-          if ((ta | tb) != 0u && lane == 0) {   // plain red.shared: one lane, nothing to aggregate
-            asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(cnt_base + 4u * (uint32_t)j),
-                         "r"(__popc(ta) + __popc(tb)) : "memory");
+          if (hot) {
+            const unsigned ta = __ballot_sync(RF_FULL, actA && test_T.x > 0.5f);
+            const unsigned tb = __ballot_sync(RF_FULL, actB && test_T.y > 0.5f);
+            if ((ta | tb) != 0u && lane == 0) {   // plain red.shared: one lane, nothing to aggregate
+              asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(cnt_base + 4u * (uint32_t)j),
+                           "r"(__popc(ta) + __popc(tb)) : "memory");
+            }
           }
         }
         if (__all_sync(RF_FULL, doneA && doneB)) break;  // warp-level early termination
