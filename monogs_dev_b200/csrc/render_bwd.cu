@@ -204,7 +204,7 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
         const f2 cdy2 = mul2(dy, mul2(bc(co.z), dy));
         const f2 quad = fma2(bc(dx), bc(adx), cdy2);
         const f2 power = fma2(quad, bc(-0.5f), mul2(dy, bc(nbdx)));
-        const f2 G = make_float2(expf(power.x), expf(power.y));
+        const f2 G = expf_pair(power);
         const f2 og = mul2(bc(co.w), G);
         const float alphaA = fminf(0.99f, og.x), alphaB = fminf(0.99f, og.y);
         const bool skipA = !(pos < lastA) || power.x > 0.0f || alphaA < 1.0f / 255.0f;

@@ -112,7 +112,7 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
           const f2 power = fma2(quad, bc(-0.5f), mul2(dy, bc(nbdx)));
           bool actA = !doneA && !(power.x > 0.0f), actB = !doneB && !(power.y > 0.0f);
           if (!__any_sync(RF_FULL, actA || actB)) continue;
-          const f2 og = mul2(bc(co.w), make_float2(expf(power.x), expf(power.y)));
+          const f2 og = mul2(bc(co.w), expf_pair(power));
           const float alphaA = fminf(0.99f, og.x), alphaB = fminf(0.99f, og.y);
           actA = actA && !(alphaA < 1.0f / 255.0f);
           actB = actB && !(alphaB < 1.0f / 255.0f);
