@@ -139,3 +139,50 @@ def test_eager_schedule_with_random_views_and_initialize_map():
         assert float(views2[k]["cam"].exposure_a) == 0.0
     assert float(views2[4]["cam"].exposure_a) != 0.0 and float(views2[2]["cam"].exposure_a) != 0.0
     assert float(gm2.denom.max()) >= 6.0                               # statistics of all five views accumulate
+
+
+def test_frontend_tracking_and_keyframe_rules_on_rasterizer():
+    """FrontEnd.tracking (frontend.py) on the real rasterizer: starts from the previous frame's
+    pose, approaches the true one (eager with the reference's convergence break, and the CUDA-graph
+    loop), writes pose and exposure back into the frame's own viewpoint; is_keyframe / add_to_window
+    then consume n_touched / visibility of that render."""
+    from monogs_dev_b200 import frontend
+    try:
+        cfg = copy.deepcopy(CONFIG)
+        cfg["Training"].update(tracking_itr_num=60, kf_translation=0.08, kf_min_translation=0.05, kf_overlap=0.9,
+                               kf_cutoff=0.3, window_size=3)
+        sc = syn.make_scene("cfg1_plumbing", device=DEV, n_views=1)
+        gm = mapping.GaussianModel(sc.xyz, sc.f_dc, sc.f_rest, sc.opacity, sc.scaling, sc.rotation,
+                                   sh_degree=sc.sh_degree)
+        true_w2c = syn.se3_exp(torch.tensor([0.02, -0.015, 0.01, 0.004, -0.006, 0.003]))
+        cam_true = syn.Camera(sc.W, sc.H, 300.0, 300.0, 159.5, 119.5, w2c=true_w2c, device=DEV)
+        with torch.no_grad():
+            gt = mapping.render_pose_only(cam_true, gm, None, sc.bg)
+            first = mapping.render_pose_only(sc.cameras[0], gm, None, sc.bg)
+        poses = []
+        for graph in (False, True):
+            fe = frontend.FrontEnd(cfg, gm, sc.bg, cuda_graph=graph)
+            fe.cameras[0] = dict(cam=sc.cameras[0], gt_image=first["render"], gt_depth=first["depth"])
+            new = dict(cam=syn.Camera(sc.W, sc.H, 300.0, 300.0, 159.5, 119.5, device=DEV),
+                       gt_image=gt["render"].clone(), gt_depth=gt["depth"].clone())
+            pkg = fe.tracking(1, new)
+            cam = fe.cameras[1]["cam"]
+            e0 = float(true_w2c[:3, 3].norm())
+            assert float((cam.T - true_w2c[:3, 3]).norm()) < 0.5 * e0, "tracking did not approach the true pose"
+            assert float(cam.cam_trans_delta.abs().sum()) == 0.0
+            assert float(fe.median_depth) > 0.2
+            poses.append(cam.T.clone())
+            vis = pkg["n_touched"] > 0
+            occ = {0: (first["n_touched"] > 0).long()}
+            # 2.7 cm of motion against a median depth of metres: no keyframe by distance, and the
+            # two views see almost the same Gaussians
+            assert fe.is_keyframe(1, 0, vis, occ) is False
+            fe.cameras[2] = dict(cam=syn.Camera(sc.W, sc.H, 300.0, 300.0, 159.5, 119.5,
+                                                w2c=syn.se3_exp(torch.tensor([2.0, 0, 0, 0, 0, 0.0])), device=DEV))
+            assert fe.is_keyframe(2, 0, vis, occ) is True
+            window, removed = fe.add_to_window(1, vis, occ, [0])
+            assert window == [1, 0] and removed is None
+        assert torch.allclose(poses[0], poses[1], atol=3e-3)
+        assert float(gm.flat_grad.abs().max()) == 0.0
+    finally:
+        rz.set_sync_free(False)
