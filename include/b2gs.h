@@ -205,6 +205,14 @@ B2GS_API int b2gs_debug_export_geom(const B2gsScene* scene, const B2gsWorkspace*
 B2GS_API int b2gs_debug_export_image(const B2gsScene* scene, const B2gsWorkspace* ws, float* final_T,
                             uint32_t* n_contrib, void* stream);
 
+/* Parity/debug helper: the render kernels evaluate exp() of a lane's two pixels with one packed
+ * instruction sequence (csrc/common.cuh: expf_pair) that must return expf()'s bits, since the
+ * reference's skip decisions (CR/forward.cu:346-362) hang on them.  Evaluates both for EVERY float
+ * whose bit pattern lies in [first_bits, last_bits] and writes the number of patterns whose results
+ * differ (either half of the pair) to mismatches[0] (device, uint64). */
+B2GS_API int b2gs_debug_expf_pair_check(uint32_t first_bits, uint32_t last_bits,
+                                        unsigned long long* mismatches, void* stream);
+
 /* mean squared distance to the 3 nearest neighbours (exact). points [P,3] -> out [P]. */
 B2GS_API size_t b2gs_knn_bytes(int32_t P);
 B2GS_API int b2gs_knn3_dist2(const float* points, int32_t P, float* out, void* workspace,

@@ -105,6 +105,7 @@ SYMBOLS = {
                                          C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "b2gs_debug_export_image": (C.c_int, [C.POINTER(B2gsScene), C.POINTER(B2gsWorkspace), C.c_void_p,
                                           C.c_void_p, C.c_void_p]),
+    "b2gs_debug_expf_pair_check": (C.c_int, [C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p]),
     "b2gs_knn_bytes": (C.c_size_t, [C.c_int32]),
     "b2gs_knn3_dist2": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_size_t,
                                   C.c_void_p]),

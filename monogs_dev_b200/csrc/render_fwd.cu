@@ -184,6 +184,38 @@ int launch_render_fwd(const B2gsScene& s, const GeomWS& g, const ImageWS& im, co
 
 }  // namespace b2gs
 
+namespace b2gs {
+__global__ void expf_pair_check_kernel(uint32_t first, uint32_t last, unsigned long long* out) {
+  const unsigned long long span = (unsigned long long)last - first + 1ull;
+  unsigned long long bad = 0;
+  for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < span;
+       i += (unsigned long long)gridDim.x * blockDim.x) {
+    const uint32_t bits = first + (uint32_t)i;
+    const float x = __uint_as_float(bits);
+    const float y = __uint_as_float(first + (uint32_t)((i * 2654435761ull) % span));   // an unrelated partner
+    const float2 e = expf_pair(make_float2(x, y));
+    const float ex = expf(x), ey = expf(y);
+    bad += (__float_as_uint(e.x) != __float_as_uint(ex)) || (__float_as_uint(e.y) != __float_as_uint(ey));
+  }
+  bad = __reduce_add_sync(0xffffffffu, (unsigned)bad);   // < 2^32 per warp: a lane visits < 2^27 patterns
+  if ((threadIdx.x & 31) == 0 && bad) atomicAdd(out, bad);
+}
+}  // namespace b2gs
+
+extern "C" int b2gs_debug_expf_pair_check(uint32_t first_bits, uint32_t last_bits,
+                                          unsigned long long* mismatches, void* stream) {
+  using namespace b2gs;
+  if (!mismatches || last_bits < first_bits) {
+    set_error("b2gs_debug_expf_pair_check: NULL output or empty bit range");
+    return B2GS_ERR_INVALID;
+  }
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  B2GS_CUDA(cudaMemsetAsync(mismatches, 0, sizeof(unsigned long long), st));
+  expf_pair_check_kernel<<<NUM_SMS_HINT * 16, 256, 0, st>>>(first_bits, last_bits, mismatches);
+  B2GS_LAUNCH_CHECK(st, 0);
+  return B2GS_OK;
+}
+
 extern "C" int b2gs_debug_export_image(const B2gsScene* scene, const B2gsWorkspace* ws,
                                        float* final_T, uint32_t* n_contrib, void* stream) {
   using namespace b2gs;

@@ -195,3 +195,21 @@ def test_sync_free_forward_matches_exact_and_flags_overflow():
         assert not rz.check_overflow([out4["state"]]) and torch.equal(out4["color"], out0["color"])
     finally:
         rz.set_sync_free(False)
+
+
+def test_expf_pair_bit_identical_to_expf_exhaustive():
+    """The render kernels' packed two-pixel exp (csrc/common.cuh: expf_pair) must return expf()'s
+    bits — the reference's skip decisions (alpha < 1/255, T < 1e-4) hang on them.  Checked for EVERY
+    float32 in [-104, -0] and [+0, 89] (2.2e9 bit patterns; beyond: 0 / inf), plus the whole range of
+    NaN / inf patterns' neighbourhood through the two sign halves' ends."""
+    import ctypes as C
+    from monogs_dev_b200 import _lib
+    out = torch.zeros(1, dtype=torch.int64, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    import struct
+    f2b = lambda v: struct.unpack("<I", struct.pack("<f", v))[0]
+    for lo, hi in ((f2b(-0.0), f2b(-104.0)), (f2b(0.0), f2b(89.0)), (f2b(89.0), 0x7F800000),
+                   (f2b(-104.0), 0xFF800000)):
+        _lib.check(_lib.lib.b2gs_debug_expf_pair_check(lo, hi, out.data_ptr(), st))
+        assert int(out.item()) == 0, (hex(lo), hex(hi), int(out.item()))
+    assert _lib.lib.b2gs_debug_expf_pair_check(5, 4, out.data_ptr(), st) != 0      # empty range: refused
