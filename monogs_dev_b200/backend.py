@@ -10,8 +10,9 @@ MappingWindow (mapping.py) and the packed-arena GaussianModel (SURVEY.md §8a a2
                                             densify / opacity-reset schedule, pose updates)
   keyframe optimizer set-up    :434-471    (`set_keyframe_optimizers`, inline in BackEnd.run)
 
-Not here: the process / queue plumbing of BackEnd.run and color_refinement's SSIM loss
-(utils/slam_backend.py:320-355; SSIM is outside the §8 path).
+  BackEnd.color_refinement     :320-355    (single random view per iteration, L1 + D-SSIM)
+
+Not here: the process / queue plumbing of BackEnd.run (control plane, out of scope).
 
 Data-parallel windows (one process per GPU): the views of an iteration are sharded by
 MappingWindow; every rank runs this schedule on its replica with identical decisions — the random
@@ -32,6 +33,7 @@ Reference behaviours kept on purpose (each pinned in tests/test_backend_cpu.py):
   * `occ_aware_visibility` is rebuilt from the window views of the LAST iteration only.
 """
 import functools
+import random
 
 import torch
 import torch.distributed as dist
@@ -62,6 +64,7 @@ class BackEnd:
         # randperm source for the two extra views: identical on every rank
         self._gen = torch.Generator().manual_seed(seed)
         self._seed, self._dev_gen = seed, None       # densify_and_split samples: same on every rank
+        self._py_rng = random.Random(seed)           # color_refinement's view choice: same on every rank
         self._win_key, self._win = None, None
         self._kf_flags = {}
         self._vis_iter, self._last_ids = -1, None
@@ -343,6 +346,42 @@ class BackEnd:
             self._set_visibility()
         self.sync_keyframes(list(current_window))
         return gaussian_split
+
+    def color_refinement(self, iteration_total=26000):
+        """:320-355 — one random keyframe per iteration, loss (1 - lambda) L1 + lambda (1 - SSIM) on the
+        raw render (no exposure), Gaussian Adam step, xyz learning-rate schedule on the refinement's own
+        iteration count; densification statistics are left alone except max_radii2D.  With several ranks
+        the iterations are dealt round-robin (one view per iteration does not shard); the gradient
+        exchange of the optimizer step keeps the replicas identical."""
+        from . import mapping
+        from .losses import l1_loss, ssim
+        g = self.gaussians
+        lam = getattr(self.opt_params, "lambda_dssim", 0.2)
+        render = self._render_fn or functools.partial(mapping.render_fused, with_stats=False)
+        ids = list(self.viewpoints.keys())
+        world, rank = self._world_rank()
+        peer = getattr(g, "peer", None)
+        loss = None
+        for iteration in range(1, iteration_total + 1):
+            kf = self.viewpoints[ids[self._py_rng.randint(0, len(ids) - 1)]]
+            if iteration % world == rank:
+                pkg = render(kf["cam"], g, None, self.background)
+                image = pkg["render"]
+                loss = (1.0 - lam) * l1_loss(image, kf["gt_image"]) + lam * (1.0 - ssim(image, kf["gt_image"]))
+                loss.backward()
+                with torch.no_grad():
+                    vis = pkg["visibility_filter"]
+                    mr = g._stats()[2]
+                    mr[vis] = torch.max(mr[vis], pkg["radii"][vis].to(mr.dtype))
+            with torch.no_grad():
+                if world > 1 and peer is None:
+                    dist.all_reduce(g.flat_grad, op=dist.ReduceOp.SUM, group=self._group)
+                g.optimizer.step()
+                if peer is None:
+                    g.zero_grad()
+                g.update_learning_rate(iteration)
+        self._win_key = None
+        return None if loss is None else loss.detach()
 
     def _set_visibility(self):
         """occ_aware_visibility = {kf: n_touched > 0} of the last iteration's window views (:232-236)"""

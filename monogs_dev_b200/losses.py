@@ -134,3 +134,45 @@ def scale_regulariser(raw_scaling, grad_sink=None, weight=10.0):
                                          out.data_ptr(), scratch.data_ptr(), scratch.numel(),
                                          torch.cuda.current_stream().cuda_stream))
     return out
+
+
+# -- colour refinement loss (BackEnd.color_refinement, utils/slam_backend.py:320-355) ---------------
+# Plain torch ops on whatever device the image lives on: this loss runs once per refinement
+# iteration on one view and is outside the §8 hot path (the rasterizer and Adam under it are not).
+
+def l1_loss(network_output, gt):
+    """gaussian_splatting/utils/loss_utils.py:21-22"""
+    return torch.abs(network_output - gt).mean()
+
+
+def _gaussian_window(window_size, sigma, like):
+    x = torch.arange(window_size, dtype=torch.float32) - window_size // 2
+    g = torch.exp(-(x * x) / (2.0 * sigma * sigma))
+    return (g / g.sum()).to(device=like.device, dtype=like.dtype)
+
+
+def ssim(img1, img2, window_size=11, size_average=True):
+    """loss_utils.py:59-101: Gaussian-windowed (11 taps, sigma 1.5, zero padding) SSIM per channel.
+    The 2-D window is the outer product of a 1-D one, so it is applied as a row pass and a column
+    pass (22 taps per pixel instead of 121)."""
+    c = img1.shape[-3]
+    a, b = img1.reshape(-1, c, *img1.shape[-2:]), img2.reshape(-1, c, *img2.shape[-2:])
+    w = _gaussian_window(window_size, 1.5, a)
+    wr = w.view(1, 1, 1, -1).expand(c, 1, 1, window_size).contiguous()
+    wc = w.view(1, 1, -1, 1).expand(c, 1, window_size, 1).contiguous()
+    pad = window_size // 2
+    F = torch.nn.functional
+
+    def blur(t):
+        return F.conv2d(F.conv2d(t, wr, padding=(0, pad), groups=c), wc, padding=(pad, 0), groups=c)
+
+    mu1, mu2 = blur(a), blur(b)
+    mu1_sq, mu2_sq, mu1_mu2 = mu1 * mu1, mu2 * mu2, mu1 * mu2
+    sigma1_sq = blur(a * a) - mu1_sq
+    sigma2_sq = blur(b * b) - mu2_sq
+    sigma12 = blur(a * b) - mu1_mu2
+    C1, C2 = 0.01 ** 2, 0.03 ** 2
+    ssim_map = ((2 * mu1_mu2 + C1) * (2 * sigma12 + C2)) / ((mu1_sq + mu2_sq + C1) * (sigma1_sq + sigma2_sq + C2))
+    if size_average:
+        return ssim_map.mean()
+    return ssim_map.mean(1).mean(1).mean(1)

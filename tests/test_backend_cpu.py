@@ -276,3 +276,44 @@ def test_initialize_map_schedule():
     assert list(be.occ_aware_visibility) == [0]
     assert be.occ_aware_visibility[0].shape[0] == gm._xyz.shape[0]
     assert torch.equal(views[0]["cam"].R, torch.eye(3)) and float(views[0]["cam"].exposure_a) == 0.0
+
+
+def test_ssim_and_l1_match_reference_formula():
+    """losses.ssim applies the 11-tap Gaussian window as two 1-D passes; the reference convolves with
+    the 2-D outer-product window (gaussian_splatting/utils/loss_utils.py:42-101, restated here)."""
+    from math import exp
+    import torch.nn.functional as F
+    from monogs_dev_b200 import losses
+    g = torch.Generator().manual_seed(4)
+    a, b = torch.rand(3, 37, 53, generator=g), torch.rand(3, 37, 53, generator=g)
+    gauss = torch.tensor([exp(-((x - 11 // 2) ** 2) / float(2 * 1.5 ** 2)) for x in range(11)])
+    w1 = (gauss / gauss.sum()).unsqueeze(1)
+    window = w1.mm(w1.t()).float().unsqueeze(0).unsqueeze(0).expand(3, 1, 11, 11).contiguous()
+    conv = lambda t: F.conv2d(t, window, padding=5, groups=3)
+    mu1, mu2 = conv(a), conv(b)
+    s1, s2, s12 = conv(a * a) - mu1.pow(2), conv(b * b) - mu2.pow(2), conv(a * b) - mu1 * mu2
+    ref = (((2 * mu1 * mu2 + 0.01 ** 2) * (2 * s12 + 0.03 ** 2))
+           / ((mu1.pow(2) + mu2.pow(2) + 0.01 ** 2) * (s1 + s2 + 0.03 ** 2))).mean()
+    assert abs(float(losses.ssim(a, b)) - float(ref)) < 2e-6
+    assert abs(float(losses.ssim(a, a)) - 1.0) < 1e-6
+    assert losses.ssim(a[None], b[None], size_average=False).shape == (1,)
+    assert float(losses.l1_loss(a, b)) == float((a - b).abs().mean())
+
+
+def test_color_refinement_steps_gaussians_only():
+    gm, views = build()
+    be = make_backend(gm, views)
+    before = gm.flat.detach().clone()
+    poses = {k: (v["cam"].R.clone(), v["cam"].T.clone()) for k, v in views.items()}
+    first = float(be.color_refinement(iteration_total=1))
+    last = float(be.color_refinement(iteration_total=40))
+    assert not torch.equal(gm.flat.detach(), before) and float(gm.flat_grad.abs().sum()) == 0.0
+    assert float(gm.optimizer.state[gm._xyz]["step"]) == 41.0
+    want_lr = model_io.helper(40, lr_init=gm.lr_init, lr_final=gm.lr_final, lr_delay_mult=gm.lr_delay_mult,
+                              max_steps=gm.max_steps)
+    assert [gr["lr"] for gr in gm.optimizer.param_groups if gr["name"] == "xyz"] == [want_lr]
+    for k, v in views.items():                                  # cameras and exposures are not refined
+        assert torch.equal(v["cam"].R, poses[k][0]) and torch.equal(v["cam"].T, poses[k][1])
+        assert float(v["cam"].exposure_a) == 0.0
+    assert float(gm.denom.sum()) == 0.0 and float(gm.max_radii2D.max()) > 0.0
+    assert last == last and first == first                      # finite

@@ -186,3 +186,18 @@ def test_frontend_tracking_and_keyframe_rules_on_rasterizer():
         assert float(gm.flat_grad.abs().max()) == 0.0
     finally:
         rz.set_sync_free(False)
+
+
+def test_color_refinement_on_rasterizer():
+    """BackEnd.color_refinement: random single views, L1 + D-SSIM on the raw render, Gaussian Adam
+    steps only (fused activations, gradients straight into the arena, statistics untouched)."""
+    be, gm, views = _backend(False, 3)
+    before = gm.flat.clone()
+    gm._stats()
+    l0 = float(be.color_refinement(iteration_total=1))
+    l1 = float(be.color_refinement(iteration_total=30))
+    assert l0 == l0 and l1 == l1 and 0.0 < l1 < 2.0
+    assert not torch.equal(gm.flat, before) and float(gm.flat_grad.abs().sum()) == 0.0
+    assert float(gm.denom.sum()) == 0.0 and float(gm.max_radii2D.max()) > 0.0
+    for v in views.values():
+        assert float(v["cam"].exposure_a) == 0.0 and float(v["cam"].cam_trans_delta.abs().sum()) == 0.0
