@@ -151,8 +151,8 @@ class BackEnd:
         """MappingWindow over the views `ids` (the first n_window are the window, the rest the random
         extras); kept across iterations while views, flags and the parameter arena are unchanged, so
         that a captured step is replayed instead of re-captured."""
-        key = (tuple(ids), n_window, frames_to_optimize, stats, id(self.keyframe_optimizers),
-               getattr(self.gaussians, "flat", torch.empty(0)).data_ptr())
+        arena = lambda: getattr(self.gaussians, "flat", torch.empty(0)).data_ptr()
+        key = (tuple(ids), n_window, frames_to_optimize, stats, id(self.keyframe_optimizers), arena())
         if key == self._win_key:
             return self._win
         if self._win is not None:
@@ -175,8 +175,8 @@ class BackEnd:
                             peer_adam=self._peer, **kw)
         if self.keyframe_optimizers is None:
             self.keyframe_optimizers = win.kf_optimizer
-            key = key[:4] + (id(self.keyframe_optimizers),) + key[5:]
-        self._win_key, self._win = key, win
+        # (the first peer-memory window moves the arenas: the key holds what the NEXT call will see)
+        self._win_key, self._win = key[:4] + (id(self.keyframe_optimizers), arena()), win
         return win
 
     def _gather_touched(self, win, ids, n_window):

@@ -410,9 +410,14 @@ class MappingWindow:
             gaussians._dist_group = group if group is not None else dist.group.WORLD
         self.peer = None
         if peer_adam and self.world > 1 and self.fused_reg:
-            from .peer import PeerArena
-            self.peer = PeerArena(gaussians.flat.device, group)
-            gaussians.enable_peer_arena(self.peer)
+            have = getattr(gaussians, "peer", None)
+            if have is not None and have.world == self.world:
+                self.peer = have                 # an earlier window of this map already moved the arenas
+                gaussians.optimizer.capturable = True
+            else:
+                from .peer import PeerArena
+                self.peer = PeerArena(gaussians.flat.device, group)
+                gaussians.enable_peer_arena(self.peer)
         self.last = {}
         self._g1 = self._g2 = None
         self._ovf = self._status_all = None
