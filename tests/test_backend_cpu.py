@@ -233,7 +233,6 @@ def test_prune_slam_mode_monocular():
     cfg = copy.deepcopy(CONFIG)
     cfg["Training"]["monocular"] = True
     be = make_backend(gm, views, cfg)
-    be.loss_fn = None
     window = [4, 3, 2]
     be.set_keyframe_optimizers(window)
     assert be.initialized is False
@@ -266,7 +265,6 @@ def test_prune_slam_mode_monocular():
 def test_initialize_map_schedule():
     gm, views = build()
     be = make_backend(gm, views)
-    acc_touch = (torch.arange(P) % 3 == 0).long()
     pkg = be.initialize_map(0, views[0])
     assert be.iteration_count == 5 and pkg is not None
     # iteration 0 densifies (step void), iteration 3 (init_gaussian_reset) resets every opacity and
