@@ -4,6 +4,7 @@ FrontEnd (utils/slam_frontend.py), same method names, argument meaning and retur
 `n_touched` outputs on the tracking side.
 
   FrontEnd.tracking        utils/slam_frontend.py:128-196   (pose-only loop on ONE GPU: TrackingLoop)
+  FrontEnd.add_new_keyframe :57-109   (the depth map a new keyframe is seeded from)
   FrontEnd.is_keyframe     :198-226   (translation against the median depth, covisibility IoU)
   FrontEnd.add_to_window   :228-290   (overlap-coefficient cut-off, then the distance heuristic)
   FrontEnd.sync_backend    :307-315
@@ -106,6 +107,37 @@ class FrontEnd:
         return render_pkg
 
     # -- keyframe management ----------------------------------------------------------------------
+    def add_new_keyframe(self, cur_frame_idx, depth=None, opacity=None, init=False, generator=None):
+        """registers the keyframe and returns the [H,W] depth map its Gaussians are seeded from
+        (GaussianModel.extend_from_pcd_seq(depthmap=...)): RGB-D -> the observed depth; monocular ->
+        2 + 0.3 N(0,1) at initialisation, afterwards the rendered depth with outliers (beyond one
+        standard deviation of the opaque pixels' median, or not opaque) set to the median, plus
+        0.2 / 0.5 std of noise; pixels under the RGB boundary threshold are 0 (= not seeded).
+        Stays on the device (the reference returns a numpy array that is uploaded again)."""
+        thr = self.config["Training"]["rgb_boundary_threshold"]
+        self.kf_indices.append(cur_frame_idx)
+        frame = self.cameras[cur_frame_idx]
+        gt_img = frame["gt_image"]
+        valid_rgb = (gt_img.sum(dim=0) > thr)[None]
+        randn = lambda like: torch.randn(like.shape, generator=generator, dtype=like.dtype,
+                                         device=like.device if generator is None else generator.device).to(like.device)
+        if self.monocular:
+            if depth is None:
+                initial_depth = 2 * torch.ones(1, gt_img.shape[1], gt_img.shape[2], device=gt_img.device)
+                initial_depth = initial_depth + randn(initial_depth) * 0.3
+            else:
+                depth = depth.detach().clone()
+                median_depth, std, valid_mask = get_median_depth(depth, opacity, mask=valid_rgb, return_std=True)
+                invalid = torch.logical_or(depth > median_depth + std, depth < median_depth - std)
+                invalid = torch.logical_or(invalid, ~valid_mask)
+                depth[invalid] = median_depth
+                initial_depth = depth + randn(depth) * torch.where(invalid, std * 0.5, std * 0.2)
+            initial_depth[~valid_rgb] = 0
+            return initial_depth[0]
+        initial_depth = frame["gt_depth"].detach().clone().reshape(1, *gt_img.shape[1:])
+        initial_depth[~valid_rgb] = 0
+        return initial_depth[0]
+
     def is_keyframe(self, cur_frame_idx, last_keyframe_idx, cur_frame_visibility_filter, occ_aware_visibility):
         t = self.config["Training"]
         kf_translation, kf_min_translation, kf_overlap = t["kf_translation"], t["kf_min_translation"], t["kf_overlap"]

@@ -136,3 +136,46 @@ def test_tracking_plumbing():
     # sync_backend: poses pushed by the back end replace the front end's
     fe.sync_backend(["sync_backend", gm, {1: torch.ones(P).long()}, [(1, torch.eye(3), torch.tensor([1.0, 2.0, 3.0]))]])
     assert fe.cameras[1]["cam"].T.tolist() == [1.0, 2.0, 3.0] and 1 in fe.occ_aware_visibility
+
+
+def test_add_new_keyframe_depth_maps():
+    import copy
+    cfg = copy.deepcopy(CONFIG)
+    cfg["Training"]["rgb_boundary_threshold"] = 0.01
+    fe = frontend.FrontEnd(cfg, None, torch.zeros(3))
+    frame = cam_at([0, 0, 0])
+    frame["gt_image"][:, 0, :] = 0.0                          # a black row: below the RGB boundary
+    frame["gt_depth"] = torch.full((1, H, W), 3.0)
+    fe.cameras[7] = frame
+    # RGB-D: the observed depth, 0 where the image is black
+    d = fe.add_new_keyframe(7)
+    assert fe.kf_indices == [7] and d.shape == (H, W)
+    assert float(d[0].abs().sum()) == 0.0 and bool((d[1:] == 3.0).all())
+    assert float(frame["gt_depth"].min()) == 3.0              # the frame's own depth is not modified
+    # monocular initialisation: 2 + 0.3 N(0,1)
+    cfg["Training"]["monocular"] = True
+    fm = frontend.FrontEnd(cfg, None, torch.zeros(3))
+    fm.cameras[0] = frame
+    g = torch.Generator().manual_seed(1)
+    d0 = fm.add_new_keyframe(0, init=True, generator=g)
+    want = 2 + 0.3 * torch.randn(1, H, W, generator=torch.Generator().manual_seed(1))
+    want[:, 0, :] = 0
+    assert torch.equal(d0, want[0])
+    # monocular, later keyframes: rendered depth, outliers / translucent pixels replaced by the median
+    depth = torch.full((1, H, W), 2.0)
+    depth[0, 2, 3] = 50.0                                     # outlier
+    depth[0, 3, :] = 2.2
+    opacity = torch.full((1, H, W), 0.99)
+    opacity[0, 4, 4] = 0.2                                    # translucent
+    valid = (depth > 0) & (opacity > 0.95) & (frame["gt_image"].sum(0) > 0.01)[None]
+    med, std = depth[valid].median(), depth[valid].std()
+    g = torch.Generator().manual_seed(2)
+    d1 = fm.add_new_keyframe(0, depth=depth, opacity=opacity, generator=g)
+    noise = torch.randn(1, H, W, generator=torch.Generator().manual_seed(2))
+    inval = (depth > med + std) | (depth < med - std) | ~valid
+    base = depth.clone()
+    base[inval] = med
+    want1 = base + noise * torch.where(inval, std * 0.5, std * 0.2)
+    want1[:, 0, :] = 0
+    assert torch.allclose(d1, want1[0]) and bool(inval[0, 2, 3]) and bool(inval[0, 4, 4])
+    assert abs(float(d1[2, 3]) - float(med)) < 3 * float(std)   # the outlier came back to the median
