@@ -92,7 +92,16 @@ class BackEnd:
         return getattr(self.opt_params, "densify_grad_threshold", 0.0002)
 
     def add_next_kf(self, frame_idx, viewpoint, init=False, scale=2.0, depth_map=None):
-        self.gaussians.extend_from_pcd_seq(viewpoint, kf_id=frame_idx, init=init, scale=scale, depthmap=depth_map)
+        """viewpoint: a frame dict {cam, gt_image, gt_depth} (Camera.from_reference(vp) makes one from a
+        MonoGS Camera) or a camera object carrying original_image / depth itself."""
+        cam = viewpoint
+        if isinstance(viewpoint, dict):
+            cam = viewpoint["cam"]
+            if getattr(cam, "original_image", None) is None:
+                cam.original_image = viewpoint["gt_image"]
+                cam.depth = viewpoint["gt_depth"].reshape(viewpoint["gt_image"].shape[-2:])
+            self.viewpoints.setdefault(frame_idx, viewpoint)
+        self.gaussians.extend_from_pcd_seq(cam, kf_id=frame_idx, init=init, scale=scale, depthmap=depth_map)
         self._win_key = None
 
     def reset(self):

@@ -94,6 +94,36 @@ class Camera:
         self.exposure_a = torch.zeros(1, device=device, requires_grad=True)
         self.exposure_b = torch.zeros(1, device=device, requires_grad=True)
 
+    @classmethod
+    def from_reference(cls, viewpoint, device=None):
+        """wrap a MonoGS `Camera` (utils/camera_utils.py:8-64) for the loop-level entry points:
+        same intrinsics and current pose, the SAME cam_rot_delta / cam_trans_delta / exposure tensors
+        (an optimizer built on the reference object keeps working), uid / original_image / depth /
+        grad_mask carried along.  Returns the frame dict {cam, gt_image, gt_depth} that
+        MappingWindow, TrackingLoop, BackEnd and FrontEnd take."""
+        vp = viewpoint
+        dev = torch.device(device if device is not None else vp.cam_rot_delta.device)
+        w2c = torch.eye(4)
+        w2c[:3, :3], w2c[:3, 3] = vp.R.detach().float().cpu(), vp.T.detach().float().cpu()
+        cam = cls(int(vp.image_width), int(vp.image_height), float(vp.fx), float(vp.fy), float(vp.cx),
+                  float(vp.cy), w2c=w2c, device=dev)
+        cam.FoVx, cam.FoVy = float(vp.FoVx), float(vp.FoVy)
+        if getattr(vp, "projection_matrix", None) is not None:        # already transposed, as stored there
+            cam.projection_matrix = vp.projection_matrix.detach().float().to(dev).contiguous()
+            cam.update_RT(w2c[:3, :3], w2c[:3, 3])
+        for name in ("cam_rot_delta", "cam_trans_delta", "exposure_a", "exposure_b"):
+            setattr(cam, name, getattr(vp, name))
+        cam.uid = getattr(vp, "uid", None)
+        image, depth = getattr(vp, "original_image", None), getattr(vp, "depth", None)
+        cam.original_image, cam.depth, cam.grad_mask = image, depth, getattr(vp, "grad_mask", None)
+        frame = dict(cam=cam, gt_image=None, gt_depth=None)
+        if image is not None:
+            frame["gt_image"] = image.detach().float().to(dev)
+        if depth is not None:                                         # a numpy [H,W] array in the reference
+            frame["gt_depth"] = torch.as_tensor(depth, dtype=torch.float32).to(dev).reshape(
+                1, int(vp.image_height), int(vp.image_width))
+        return frame
+
     def _host(self):
         if self._host_RT is None:       # pose was last changed on the device: read it back
             h = self.state[:12].detach().cpu()

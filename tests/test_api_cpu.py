@@ -58,3 +58,32 @@ def test_camera_conventions():
     cam.update_pose()
     assert torch.allclose(cam.T, w2c[:3, 3] + torch.tensor([0.01, 0.0, 0.0]), atol=1e-6)
     assert float(cam.cam_trans_delta.abs().sum()) == 0.0
+
+
+def test_camera_from_reference_viewpoint():
+    """Camera.from_reference wraps a MonoGS Camera (utils/camera_utils.py:8-64, mimicked here by a
+    namespace with the same attributes): same pose / intrinsics / projection, the SAME parameter
+    tensors, the frame dict the loop-level entry points take."""
+    import math
+    import types
+    import numpy as np
+    from monogs_dev_b200.camera import Camera, projection_matrix, se3_exp
+    W, H = 64, 48
+    w2c = se3_exp(torch.tensor([0.1, -0.2, 0.3, 0.02, 0.01, -0.03]))
+    P = projection_matrix(0.01, 100.0, 31.5, 23.5, 50.0, 52.0, W, H).t().contiguous()
+    par = lambda n: torch.nn.Parameter(torch.zeros(n))
+    vp = types.SimpleNamespace(uid=7, R=w2c[:3, :3].clone(), T=w2c[:3, 3].clone(), fx=50.0, fy=52.0, cx=31.5, cy=23.5,
+                               FoVx=2 * math.atan(W / 100.0), FoVy=2 * math.atan(H / 104.0), image_width=W,
+                               image_height=H, projection_matrix=P, cam_rot_delta=par(3), cam_trans_delta=par(3),
+                               exposure_a=par(1), exposure_b=par(1), original_image=torch.rand(3, H, W),
+                               depth=np.full((H, W), 2.5, dtype=np.float32), grad_mask=None)
+    frame = Camera.from_reference(vp, device="cpu")
+    cam = frame["cam"]
+    assert cam.uid == 7 and cam.cam_rot_delta is vp.cam_rot_delta and cam.exposure_b is vp.exposure_b
+    assert torch.allclose(cam.R, vp.R) and torch.allclose(cam.T, vp.T)
+    # utils/camera_utils.py:94-107: world_view_transform = W2C^T, full_proj = view @ projection, centre
+    assert torch.allclose(cam.world_view_transform, w2c.t(), atol=1e-6)
+    assert torch.allclose(cam.full_proj_transform, w2c.t() @ P, atol=1e-5)
+    assert torch.allclose(cam.camera_center, torch.linalg.inv(w2c.t())[3, :3], atol=1e-6)
+    assert frame["gt_image"].shape == (3, H, W) and frame["gt_depth"].shape == (1, H, W)
+    assert float(frame["gt_depth"].mean()) == 2.5 and cam.original_image is vp.original_image
