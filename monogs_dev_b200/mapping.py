@@ -229,6 +229,15 @@ class GaussianModel:
     get_opacity = property(lambda s: torch.sigmoid(s._opacity))
     get_features = property(lambda s: torch.cat((s._features_dc, s._features_rest), dim=1))
 
+    def get_covariance(self, scaling_modifier=1):
+        """[P,6] upper triangle of R S S^T R^T with the normalised quaternion
+        (build_covariance_from_scaling_rotation, gaussian_model.py:42-49,98-101); only used by
+        render() under pipe.compute_cov3D_python."""
+        from .densify import build_rotation
+        L = build_rotation(self._rotation) * (scaling_modifier * self.get_scaling).unsqueeze(1)   # R @ diag(s)
+        cov = L @ L.transpose(1, 2)
+        return torch.stack([cov[:, 0, 0], cov[:, 0, 1], cov[:, 0, 2], cov[:, 1, 1], cov[:, 1, 2], cov[:, 2, 2]], dim=-1)
+
     def zero_grad(self):
         self.flat_grad.zero_()
 
@@ -269,11 +278,26 @@ def render(viewpoint_camera, pc, pipe=None, bg_color=None, scaling_modifier=1.0,
         projmatrix=cam.full_proj_transform, projmatrix_raw=cam.projection_matrix,
         sh_degree=pc.active_sh_degree, campos=cam.camera_center, prefiltered=False, debug=False)
     rasterizer = GaussianRasterizer(raster_settings=rs)
+    # the two PipelineParams switches (gaussian_renderer/__init__.py:82-111); both default to False
+    scales = rotations = cov3D = None
+    if getattr(pipe, "compute_cov3D_python", False):
+        cov3D = pc.get_covariance(scaling_modifier)
+    else:
+        scales = pc.get_scaling
+        if scales.shape[-1] == 1:              # isotropic model: one scale per Gaussian
+            scales = scales.repeat(1, 3)
+        rotations = pc.get_rotation
     shs, colors = (pc.get_features, None) if override_color is None else (None, override_color)
+    if colors is None and getattr(pipe, "convert_SHs_python", False):
+        from .sh_utils import eval_sh
+        feats = pc.get_features
+        dirs = pc.get_xyz - cam.camera_center.reshape(1, 3)
+        dirs = dirs / dirs.norm(dim=1, keepdim=True)
+        shs, colors = None, torch.clamp_min(eval_sh(pc.active_sh_degree, feats.transpose(1, 2), dirs) + 0.5, 0.0)
     rendered_image, radii, depth, opacity, n_touched = rasterizer(
         means3D=pc.get_xyz, means2D=screenspace_points, shs=shs, colors_precomp=colors,
-        opacities=pc.get_opacity, scales=pc.get_scaling, rotations=pc.get_rotation,
-        cov3D_precomp=None, theta=cam.cam_rot_delta, rho=cam.cam_trans_delta)
+        opacities=pc.get_opacity, scales=scales, rotations=rotations,
+        cov3D_precomp=cov3D, theta=cam.cam_rot_delta, rho=cam.cam_trans_delta)
     return {"render": rendered_image, "viewspace_points": screenspace_points,
             "visibility_filter": radii > 0, "radii": radii, "depth": depth, "opacity": opacity,
             "n_touched": n_touched}

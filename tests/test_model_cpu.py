@@ -178,3 +178,69 @@ def test_ply_reader_ascii_and_errors(tmp_path):
         raise AssertionError("no error")
     except ValueError:
         pass
+
+
+def test_eval_sh_and_covariance_match_oracle():
+    """host-side SH colour (render() under pipe.convert_SHs_python) and get_covariance (under
+    pipe.compute_cov3D_python) against the oracle's restatement of the kernels (CR/forward.cu:22-73,
+    120-154): same basis, same covariance once the quaternion is normalised."""
+    from monogs_dev_b200 import sh_utils
+    from oracle import gs_oracle as O
+    g = torch.Generator().manual_seed(8)
+    d = torch.randn(50, 3, generator=g)
+    d = d / d.norm(dim=1, keepdim=True)
+    for deg in range(4):
+        M = (deg + 1) ** 2
+        assert torch.allclose(sh_utils.sh_basis(deg, d), O._sh_basis(deg, d)[:, :M], atol=1e-7)
+        sh = torch.randn(50, 16, 3, generator=g)                      # [P, M, 3] as the model stores it
+        want = (O._sh_basis(deg, d)[:, :M, None] * sh[:, :M]).sum(1)
+        assert torch.allclose(sh_utils.eval_sh(deg, sh.transpose(1, 2), d), want, atol=1e-6)
+    rgb = torch.rand(5, 3)
+    assert torch.allclose(sh_utils.SH2RGB(sh_utils.RGB2SH(rgb)), rgb, atol=1e-7)
+    try:
+        sh_utils.eval_sh(2, torch.zeros(4, 3, 4), d[:4])
+        raise AssertionError("no error")
+    except ValueError:
+        pass
+    gm, _ = make(P=40)
+    cov = gm.get_covariance(1.5)
+    q = torch.nn.functional.normalize(gm._rotation.detach())
+    want = O.compute_cov3d(torch.exp(gm._scaling.detach()), 1.5, q)
+    assert torch.allclose(cov.detach(), want, rtol=1e-5, atol=1e-7)
+
+
+def test_render_pipeline_switches(monkeypatch):
+    """render() (gaussian_renderer/__init__.py:82-111): by default the rasterizer gets scales /
+    rotations / SH; pipe.compute_cov3D_python hands it the [P,6] covariance instead,
+    pipe.convert_SHs_python the clamped host-side colours; an isotropic model's single scale is
+    repeated.  The rasterizer itself is replaced by a recorder (no CPU rasterizer exists)."""
+    from monogs_dev_b200 import synthetic as syn
+    seen = {}
+
+    class Recorder:
+        def __init__(self, raster_settings):
+            seen["sh_degree"] = raster_settings.sh_degree
+
+        def __call__(self, **kw):
+            seen.update(kw)
+            P = kw["means3D"].shape[0]
+            return torch.zeros(3, 2, 2), torch.zeros(P), torch.zeros(1, 2, 2), torch.zeros(1, 2, 2), torch.zeros(P)
+
+    monkeypatch.setattr(mapping, "GaussianRasterizer", Recorder)
+    gm, _ = make(P=9, sh_degree=1)
+    cam = syn.Camera(8, 6, 10.0, 10.0, 4.0, 3.0)
+    pkg = mapping.render(cam, gm, None, torch.zeros(3))
+    assert set(pkg) == {"render", "viewspace_points", "visibility_filter", "radii", "depth", "opacity", "n_touched"}
+    assert seen["cov3D_precomp"] is None and seen["colors_precomp"] is None and seen["sh_degree"] == 1
+    assert torch.equal(seen["scales"], gm.get_scaling) and torch.equal(seen["shs"], gm.get_features)
+    assert seen["theta"] is cam.cam_rot_delta and seen["rho"] is cam.cam_trans_delta
+    pipe = types.SimpleNamespace(compute_cov3D_python=True, convert_SHs_python=True)
+    mapping.render(cam, gm, pipe, torch.zeros(3), scaling_modifier=2.0)
+    assert seen["scales"] is None and seen["rotations"] is None
+    assert torch.allclose(seen["cov3D_precomp"], gm.get_covariance(2.0))
+    assert seen["shs"] is None and seen["colors_precomp"].shape == (9, 3)
+    assert float(seen["colors_precomp"].min()) >= 0.0
+    iso = mapping.GaussianModel(torch.randn(4, 3), torch.randn(4, 1, 3), torch.randn(4, 0, 3), torch.randn(4, 1),
+                                torch.randn(4, 1), torch.randn(4, 4))
+    mapping.render(cam, iso, None, torch.zeros(3))
+    assert seen["scales"].shape == (4, 3) and torch.equal(seen["scales"][:, 0], seen["scales"][:, 2])
