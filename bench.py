@@ -20,8 +20,15 @@ total work is fixed ("strong" scaling).
                  sample, rank 0, N=1 only
 
 `--impl reference` times the UNMODIFIED reference CUDA rasterizer (oracle/_ref, built for
-sm_100 by oracle/build_ref.py) + torch.optim.Adam through the same loop; if that extension
-cannot be loaded it falls back to the CPU oracle port on a bounded sample.
+sm_100 by oracle/build_ref.py) + torch.optim.Adam through the reference's own loop restated in
+oracle/ref_loop.py (camera properties recomputed per access, torch-op loss, torch update_pose).
+That arm never imports `monogs_dev_b200` (no libb2gs.so in its process) and is single-GPU, as the
+reference is: under torchrun rank 0 alone runs it on the full window, the other ranks exit 0.
+If the extension cannot be loaded it falls back to the CPU oracle port on a bounded sample.
+
+Both arms start from the same seeded scene (synthdata), run the same number of steps and print
+`state_check` = {steps_applied, loss_last, param_sum, param_abs_sum (fp64), pose_sum}: the two
+arms and N = 1/2/4/8 must agree ("the 1-GPU step on the same window").
 """
 import argparse
 import json
@@ -36,9 +43,22 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-WORKLOAD = "cfg3_replica"
-N_VIEWS = 8
+import synthdata
+
+WORKLOADS = {   # name -> (keyframes, description)
+    "cfg3_replica": (8, "cfg3_replica: 1200x680, 500k Gaussians, SH0, 8-keyframe mapping window "
+                        "(fwd+bwd per keyframe, fused Adam, pose Adam)"),
+    "cfg5_large": (16, "cfg5_large: 1920x1080, 4M Gaussians, SH degree 3, 16-keyframe mapping window "
+                       "(fwd+bwd per keyframe, fused Adam, pose Adam)"),
+}
 METRIC = "fwd+bwd render iters/s @1200x680, 500k Gaussians (8-keyframe map-window step)"
+# keyframe optimizer of BackEnd (utils/slam_backend.py:434-471): cam_rot_delta * 0.5, cam_trans_delta * 0.5
+# (configs/rgbd/replica/base_config.yaml:59-61), exposure 0.01 — the same in both arms
+POSE_LR = (0.0015, 0.0005, 0.01, 0.01)
+# executed flop per pixel of the render kernels' inner loops, counted on the source
+FWD_POWER, FWD_BLEND = 9.5, 24.0     # power tree | expf (11) + alpha/test_T (4) + 4 FMA blend + weight (9)
+BWD_HEAD, BWD_BLEND = 22.5, 67.0     # power + expf + alpha | rcp, replay, dL_dalpha, 10 partials, 12-shuffle fold
+GRAPH_WARMUP = 4   # native graph mode: 3 eager sizing steps + the capture; the reference arm runs them too
 
 
 def env_int(k, d):
@@ -98,16 +118,6 @@ def peaks():
     return dict(hbm_gbs=6650.0, sm_max_mhz=1965.0, source="fallback")
 
 
-def perturbed_copy(sc, seed=77):
-    """the 'ground-truth' scene: parameters perturbed by 5 % noise."""
-    g = torch.Generator().manual_seed(seed)
-    n = lambda t: torch.randn(t.shape, generator=g).to(t.device)
-    return dict(xyz=sc.xyz + 0.05 * torch.exp(sc.scaling).mean(1, keepdim=True) * n(sc.xyz),
-                scaling=sc.scaling + 0.05 * n(sc.scaling), rotation=sc.rotation + 0.05 * n(sc.rotation),
-                opacity=sc.opacity + 0.05 * n(sc.opacity), f_dc=sc.f_dc + 0.05 * n(sc.f_dc),
-                f_rest=sc.f_rest)
-
-
 def dist_setup(args):
     world = env_int("WORLD_SIZE", 1)
     rank = env_int("RANK", 0)
@@ -164,24 +174,26 @@ def timed_steps(step_fn, K, world, settle=None):
     return a.elapsed_time(b)
 
 
-def build_window(device, render_fn, model_cls, window_cls, sc):
-    """keyframes with ground truth rendered (untimed) from a 5 %-perturbed copy of the scene."""
+def build_window(device, sc):
+    """native arm: keyframes with ground truth rendered (untimed) from a 5 %-perturbed copy of the scene."""
     from monogs_dev_b200 import mapping
-    gt = perturbed_copy(sc)
+    gt = synthdata.perturbed_params(sc)
     gt_model = mapping.GaussianModel(gt["xyz"], gt["f_dc"], gt["f_rest"], gt["opacity"], gt["scaling"],
-                                     gt["rotation"], sh_degree=sc.sh_degree) if model_cls is None else \
-        model_cls(gt["xyz"], gt["f_dc"], gt["f_rest"], gt["opacity"], gt["scaling"], gt["rotation"],
-                  sh_degree=sc.sh_degree)
-    kfs, host = [], []
+                                     gt["rotation"], sh_degree=sc.sh_degree)
+    kfs = []
     with torch.no_grad():
-        for cam in sc.cameras:
-            pkg = render_fn(cam, gt_model, None, sc.bg)
-            img, dep = pkg["render"].detach().clone(), pkg["depth"].detach().clone()
-            kfs.append(dict(cam=cam, gt_image=img, gt_depth=dep))
-            host.append((img.cpu().pin_memory(), dep.cpu().pin_memory()))
+        for v, cam in enumerate(sc.cameras):
+            pkg = mapping.render_fused(cam, gt_model, None, sc.bg)
+            # keyframe 0 has no optimised parameter at all (utils/slam_backend.py:435-436)
+            kfs.append(dict(cam=cam, gt_image=pkg["render"].detach().clone(), gt_depth=pkg["depth"].detach().clone(),
+                            optimize_pose=v > 0, optimize_exposure=v > 0))
     del gt_model
     torch.cuda.synchronize()
-    return kfs, host
+    return kfs
+
+
+def pinned_host_copies(kfs):
+    return [(kf["gt_image"].cpu().pin_memory(), kf["gt_depth"].cpu().pin_memory()) for kf in kfs]
 
 
 def sum_n_contrib(state, W, H, device):
@@ -199,7 +211,7 @@ def sum_n_contrib(state, W, H, device):
 
 def rooflines(prof, units, pk):
     """per-kernel achieved vs bound.  units: dict of per-launch work:
-    bytes for the HBM-bound kernels, flops for the FP32-pipe-bound ones."""
+    bytes for the HBM-bound kernels, EXECUTED flops for the FP32-pipe-bound ones."""
     fp32_peak = 148 * 128 * 2 * pk["sm_max_mhz"] * 1e6 / 1e12        # TFLOP/s at max SM clock
     table = {}
     for name, (cnt, ms) in prof.items():
@@ -221,19 +233,24 @@ def rooflines(prof, units, pk):
     return table
 
 
+def _ncu_file():
+    import glob
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "*_ncu_render_full.txt")))
+    return files[-1] if files else None
+
+
 def ncu_metrics(kernel):
     """issue-slot and FMA-pipe utilisation of `kernel` from the newest committed `ncu --set full`
-    summary under profiles/ (what the FP32 'frac' does not say: see DESIGN.md §7)."""
-    import glob
+    summary under profiles/ (context next to the measured `frac`; never a bench value)."""
     import re
-    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "*_ncu_render_full.txt")))
-    if not files:
+    f = _ncu_file()
+    if not f:
         return None
     want = {"smsp__issue_active.avg.pct_of_peak_sustained_active": "issue_slot_pct",
             "sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active": "fma_pipe_pct",
             "gpu__time_duration.sum": "ncu_us"}
     out, on = {}, False
-    for line in open(files[-1]):
+    for line in open(f):
         if line.startswith("----"):
             on = kernel + "_kernel" in line
         elif on:
@@ -241,20 +258,19 @@ def ncu_metrics(kernel):
             if m and m.group(1) in want:
                 out[want[m.group(1)]] = round(float(m.group(2)), 1)
     if out:
-        out["source"] = os.path.basename(files[-1])
+        out["source"] = os.path.basename(f)
     return out or None
 
 
 def ncu_traffic(kernel):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel`, from the newest
     `ncu --set full` summary committed under profiles/ (tools/ncu_summary.py); None if absent."""
-    import glob
     import re
-    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "*_ncu_render_full.txt")))
-    if not files:
+    f = _ncu_file()
+    if not f:
         return None
     vals, cur = [], None
-    for line in open(files[-1]):
+    for line in open(f):
         if line.startswith("----"):
             cur = {} if kernel + "_kernel" in line else None
             if cur is not None:
@@ -272,100 +288,141 @@ def cpu_oracle_sample():
     """bounded CPU sample: ONE fwd+bwd of a 1/10-scale config 3 (50k Gaussians, 380x216,
     focal / sqrt(10)) through the PyTorch oracle; scaled to full-size iters/s by 1/10."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
-    from helpers import build_case, run_oracle
+    from oracle import gs_oracle as O
     s = 10 ** 0.5
-    sc, rs, inp, gc, gd = build_case(WORKLOAD, P=50_000, W=380, H=216, fx=600 / s, fy=600 / s,
-                                     cx=189.5, cy=107.5)
+    t = synthdata.scene_tensors("cfg3_replica", P=50_000, W=380, H=216, fx=600 / s, fy=600 / s, cx=189.5, cy=107.5)
+    from oracle import ref_loop
+    cam = ref_loop.RefCamera(0, t.W, t.H, t.fx, t.fy, t.cx, t.cy, device="cpu")
+    from types import SimpleNamespace
+    import math
+    rs = SimpleNamespace(image_height=t.H, image_width=t.W, tanfovx=math.tan(cam.FoVx * 0.5),
+                         tanfovy=math.tan(cam.FoVy * 0.5), bg=torch.zeros(3), scale_modifier=1.0,
+                         viewmatrix=cam.world_view_transform, projmatrix=cam.full_proj_transform,
+                         projmatrix_raw=cam.projection_matrix, sh_degree=t.sh_degree, campos=cam.camera_center,
+                         prefiltered=False, debug=False)
+    gc, gd = synthdata.upstream_grads(t.W, t.H)
     torch.set_num_threads(os.cpu_count() or 1)
-    t = time.time()
-    run_oracle(rs, inp, gc, gd)
-    dt = time.time() - t
+    t0 = time.time()
+    sc = O.scene_from_settings(rs, t.xyz, torch.sigmoid(t.opacity), shs=torch.cat([t.f_dc, t.f_rest], 1).contiguous(),
+                               scales=torch.exp(t.scaling), rotations=torch.nn.functional.normalize(t.rotation))
+    st = O.rasterize_forward(sc)
+    O.rasterize_backward(sc, st, gc, gd)
+    dt = time.time() - t0
     return dict(value=round(1.0 / dt / 10.0, 5), unit="iters/s", cores=torch.get_num_threads(), kind="port",
                 sample="1 fwd+bwd of a 1/10-scale cfg3 view (50k Gaussians, 380x216) in %.1f s on the "
                        "pure-PyTorch oracle; value = measured rate / 10" % dt)
 
 
-def run(args):
-    impl_ref = args.impl == "reference"
+class E2E:
+    """e2e harness shared by both arms (imports neither): every step's ground-truth RGB-D frames
+    come from pinned host memory.  The H2D copy of step k+1 runs on a copy stream while step k
+    computes (double buffering through a staging set; one D2D hand-over per step), and the loss is
+    read back to the host every step, one step late."""
+
+    def __init__(self, win, kfs, host, local_views):
+        self.win, self.kfs, self.host, self.local = win, kfs, host, local_views
+        self.copy_stream = torch.cuda.Stream()
+        self.stage = {v: (torch.empty_like(kfs[v]["gt_image"]), torch.empty_like(kfs[v]["gt_depth"]))
+                      for v in local_views}
+        self.ev_ready, self.ev_free = torch.cuda.Event(), torch.cuda.Event()
+        self.pending = False
+        self.loss_host = [torch.empty(1, dtype=torch.float32).pin_memory() for _ in range(2)]
+        self.loss_ev = [torch.cuda.Event(), torch.cuda.Event()]
+        self.n, self.losses = 0, []
+
+    def prefetch(self):
+        self.copy_stream.wait_event(self.ev_free)
+        with torch.cuda.stream(self.copy_stream):
+            for v in self.local:
+                self.stage[v][0].copy_(self.host[v][0], non_blocking=True)
+                self.stage[v][1].copy_(self.host[v][1], non_blocking=True)
+            self.ev_ready.record(self.copy_stream)
+        self.pending = True
+
+    def step(self):
+        cur = torch.cuda.current_stream()
+        if not self.pending:
+            self.ev_free.record(cur)
+            self.prefetch()
+        cur.wait_event(self.ev_ready)
+        for v in self.local:                      # staging -> the buffers the (captured) step reads
+            self.kfs[v]["gt_image"].copy_(self.stage[v][0], non_blocking=True)
+            self.kfs[v]["gt_depth"].copy_(self.stage[v][1], non_blocking=True)
+        self.ev_free.record(cur)
+        self.prefetch()                           # next step's inputs, overlapped with this step
+        loss = self.win.step()
+        # result read back, device -> host, every step: an async copy into pinned memory that the
+        # host reads after it has enqueued the NEXT step (settle() reads the last one)
+        i = self.n % 2
+        self.loss_host[i].copy_(loss.detach().reshape(1), non_blocking=True)
+        self.loss_ev[i].record(cur)
+        if self.n > 0:
+            self.loss_ev[1 - i].synchronize()
+            self.losses.append(float(self.loss_host[1 - i][0]))
+        self.n += 1
+
+    def settle(self):
+        self.win.flush()
+        if self.n > 0:
+            i = (self.n - 1) % 2
+            self.loss_ev[i].synchronize()
+            self.losses.append(float(self.loss_host[i][0]))
+
+    def reset(self):
+        torch.cuda.synchronize()
+        self.pending = False                      # the timed region issues its own first copy
+        self.n = 0
+        del self.losses[:]
+
+
+def state_check(steps, loss, params, cams_local, world, device):
+    """what the driver compares between the arms and across N: the loss of the last timed step and
+    fp64 checksums of the Gaussian parameters / keyframe poses+exposures after `steps` steps."""
+    ps, pa = synthdata.param_checksum(params)
+    pose = 0.0
+    for cam in cams_local:
+        pose += float(cam.T.detach().double().abs().sum()) + float(cam.exposure_a.detach().double().sum()) \
+            + float(cam.exposure_b.detach().double().sum())
+    return dict(steps_applied=steps, loss_last=round(sum_over_ranks(float(loss), world, device), 8),
+                param_sum=round(ps, 6), param_abs_sum=round(pa, 6),
+                pose_sum=round(sum_over_ranks(pose, world, device), 8))
+
+
+def config_common(name, n_views):
+    return {"workload": WORKLOADS[name][1], "keyframes": n_views, "pose_lr": list(POSE_LR),
+            "seed": synthdata.CONFIGS[name][8], "gt": "render of the 5 %-perturbed scene (seed 77)",
+            "l2_policy": "inputs larger than L2: >400 MB touched per step (GT frames, parameter/moment "
+                         "arenas, per-view workspaces+gradients) vs 126 MB L2"}
+
+
+def run_native(args):
     rank, world, local = dist_setup(args)
     device = torch.device("cuda", local)
     from monogs_dev_b200 import synthetic as syn, mapping, _lib
+    name = args.workload
+    n_views = WORKLOADS[name][0]
     K, W_ = args.steps, max(args.warmup, 3)
+    graph = not args.no_graph
 
-    if impl_ref:
-        from oracle import ref_ext
-        if not ref_ext.available():
-            return run_reference_cpu(args, rank, world)
-        render_fn, model_cls, adam_cls = ref_ext.ref_render, ref_ext.RefGaussianModel, torch.optim.Adam
-        loss_fn, graph = mapping.get_loss_mapping_rgbd_torch, False     # the reference's own torch-op loss
-    else:
-        render_fn, model_cls, adam_cls = mapping.render_fused, mapping.GaussianModel, mapping.FusedAdam
-        loss_fn, graph = mapping.get_loss_mapping_rgbd, not args.no_graph
-
-    sc = syn.make_scene(WORKLOAD, device=device, n_views=N_VIEWS)
-    kfs, host = build_window(device, render_fn, model_cls, None, sc)
-    gm = model_cls(sc.xyz, sc.f_dc, sc.f_rest, sc.opacity, sc.scaling, sc.rotation, sh_degree=sc.sh_degree)
-    win = mapping.MappingWindow(gm, kfs, sc.bg, render_fn=render_fn, adam_cls=adam_cls, loss_fn=loss_fn,
-                                cuda_graph=graph, view_streams=1 if impl_ref else args.view_streams,
-                                peer_adam=(not impl_ref) and world > 1 and not args.no_peer_adam)
+    sc = syn.make_scene(name, device=device, n_views=n_views)
+    kfs = build_window(device, sc)
+    gm = mapping.GaussianModel(sc.xyz, sc.f_dc, sc.f_rest, sc.opacity, sc.scaling, sc.rotation,
+                               sh_degree=sc.sh_degree)
+    win = mapping.MappingWindow(gm, kfs, sc.bg, pose_lr=POSE_LR, cuda_graph=graph, view_streams=args.view_streams,
+                                peer_adam=world > 1 and not args.no_peer_adam)
     local_views = win.local
+    host = pinned_host_copies(kfs)
+    e2e = E2E(win, kfs, host, local_views)
 
-    def step():
-        return win.step()
-
-    # e2e: every step's ground-truth RGB-D frames come from pinned host memory.  The H2D copy of
-    # step k+1 runs on a copy stream while step k computes (double buffering through a staging
-    # set; one D2D hand-over per step), and the loss is read back to the host every step.
-    copy_stream = torch.cuda.Stream()
-    stage = {v: (torch.empty_like(kfs[v]["gt_image"]), torch.empty_like(kfs[v]["gt_depth"])) for v in local_views}
-    ev_ready, ev_free = torch.cuda.Event(), torch.cuda.Event()
-    pending = [False]
-    loss_host = [torch.empty(1, dtype=torch.float32).pin_memory() for _ in range(2)]
-    loss_ev = [torch.cuda.Event(), torch.cuda.Event()]
-    n_e2e, losses_read = [0], []
-
-    def prefetch():
-        copy_stream.wait_event(ev_free)
-        with torch.cuda.stream(copy_stream):
-            for v in local_views:
-                stage[v][0].copy_(host[v][0], non_blocking=True)
-                stage[v][1].copy_(host[v][1], non_blocking=True)
-            ev_ready.record(copy_stream)
-        pending[0] = True
-
-    def step_e2e():
-        cur = torch.cuda.current_stream()
-        if not pending[0]:
-            ev_free.record(cur)
-            prefetch()
-        cur.wait_event(ev_ready)
-        for v in local_views:                      # staging -> the buffers the (captured) step reads
-            kfs[v]["gt_image"].copy_(stage[v][0], non_blocking=True)
-            kfs[v]["gt_depth"].copy_(stage[v][1], non_blocking=True)
-        ev_free.record(cur)
-        prefetch()                                 # next step's inputs, overlapped with this step
+    loss = None
+    for _ in range(W_ + GRAPH_WARMUP):            # graph mode: 3 eager sizing steps + the capture
         loss = win.step()
-        # result read back, device -> host, every step: an async copy into pinned memory that the
-        # host reads after it has enqueued the NEXT step (settle_e2e reads the last one)
-        i = n_e2e[0] % 2
-        loss_host[i].copy_(loss.detach().reshape(1), non_blocking=True)
-        loss_ev[i].record(cur)
-        if n_e2e[0] > 0:
-            loss_ev[1 - i].synchronize()
-            losses_read.append(float(loss_host[1 - i][0]))
-        n_e2e[0] += 1
-
-    def settle_e2e():
-        win.flush()
-        if n_e2e[0] > 0:
-            i = (n_e2e[0] - 1) % 2
-            loss_ev[i].synchronize()
-            losses_read.append(float(loss_host[i][0]))
-
-    for _ in range(W_ + (4 if graph else 0)):      # graph mode: 3 eager sizing steps + the capture
-        step()
     sampler = ClockSampler(local) if rank == 0 else None
     l0 = _lib.lib.b2gs_kernel_launches()
+    last = [loss]
+
+    def step():
+        last[0] = win.step()
     ms = timed_steps(step, K, world, settle=win.flush)
     launches = _lib.lib.b2gs_kernel_launches() - l0
     if graph:      # replays do not pass through the host-side counter: launches captured per step x K
@@ -373,122 +430,206 @@ def run(args):
     clocks = sampler.stop() if sampler else {}
     ms = max_over_ranks(ms, world, device)
     launches = int(sum_over_ranks(launches, world, device))
-    step_e2e()
-    settle_e2e()
-    torch.cuda.synchronize()
-    pending[0] = False                             # the timed region issues its own first copy
-    n_e2e[0] = 0
-    del losses_read[:]
-    ms_e2e = max_over_ranks(timed_steps(step_e2e, K, world, settle=settle_e2e), world, device)
-    assert len(losses_read) == K, "every step's loss must have been read back inside the timed region"
+    check = state_check(W_ + GRAPH_WARMUP + K, last[0], [gm.flat], [kfs[v]["cam"] for v in local_views],
+                        world, device)
+    if getattr(win, "peer", None) is not None:
+        win.peer.check()                          # a barrier time-out would have corrupted the replicas
+
+    e2e.step()
+    e2e.settle()
+    e2e.reset()
+    ms_e2e = max_over_ranks(timed_steps(e2e.step, K, world, settle=e2e.settle), world, device)
+    assert len(e2e.losses) == K, "every step's loss must have been read back inside the timed region"
 
     # headline companion: single-view fwd+bwd only (no optimizer), rank-local, N=1 only
     single = None
     if world == 1:
         def one_view():
-            pkg = render_fn(kfs[0]["cam"], gm, None, sc.bg)
-            loss_fn(pkg["render"], pkg["depth"], kfs[0]["cam"], kfs[0]["gt_image"], kfs[0]["gt_depth"]).backward()
+            pkg = mapping.render_fused(kfs[0]["cam"], gm, None, sc.bg)
+            mapping.get_loss_mapping_rgbd(pkg["render"], pkg["depth"], kfs[0]["cam"], kfs[0]["gt_image"],
+                                          kfs[0]["gt_depth"]).backward()
             gm.zero_grad()
             for t in (kfs[0]["cam"].cam_rot_delta, kfs[0]["cam"].cam_trans_delta,
                       kfs[0]["cam"].exposure_a, kfs[0]["cam"].exposure_b):
                 t.grad = None
         for _ in range(3):
             one_view()
-        n1 = max(20, K * N_VIEWS // 2)
+        n1 = max(20, K * n_views // 2)
         single = n1 / (timed_steps(one_view, n1, 1) / 1e3)
 
-    roof, rooftab = None, {}
-    if not impl_ref:
-        # per-kernel durations: CUDA events on the launching stream, 2 extra (untimed) steps
-        # (views serialised on one stream for this pass: a kernel timed while another view's
-        # kernels share the SMs would not be that kernel's duration)
-        _lib.lib.b2gs_profile_enable(1)
-        vs, win.view_streams = win.view_streams, 1
-        win._eager_step(set_to_none=False); win._eager_step(set_to_none=False)   # eager: events per launch
-        win.view_streams = vs
-        torch.cuda.synchronize()
-        prof = _lib.profile_read()
-        _lib.lib.b2gs_profile_enable(0)
-        pkg = win.last[local_views[0]]
-        st = pkg["render"].grad_fn.state if pkg["render"].grad_fn is not None else None
-        P = sc.P
-        pvis = int((pkg["radii"] > 0).sum().item())
-        pairs = sum_n_contrib(st, sc.W, sc.H, device) if st is not None else 0
-        R = st.num_rendered if st is not None else 0
-        n_par = gm.flat.numel()
-        N = sc.W * sc.H
-        tiles = ((sc.W + 15) // 16) * ((sc.H + 15) // 16)
-        units = {   # algorithmic work per launch
-            "preprocess_fwd": ("hbm", 131.0 * pvis + 20.0 * (P - pvis)),
-            "tile_scan": ("hbm", 16.0 * tiles),
-            "scatter_instances": ("hbm", 12.0 * P + 40.0 * pvis + 8.0 * R),
-            "tile_sort": ("hbm", 24.0 * R),                       # the sort's lower bound: one read + one write of a 12 B pair
-            "render_fwd": ("fp32", 26.0 * pairs),
-            "render_bwd": ("fp32", 80.0 * pairs),
-            "preprocess_bwd": ("hbm", 319.0 * pvis + 60.0 * (P - pvis)),
-            "loss_fwd": ("hbm", 32.0 * N),
-            "loss_bwd": ("hbm", 48.0 * N),
-            "iso_reg": ("hbm", 36.0 * P),
-            "adam": ("hbm", 28.0 * n_par),
-        }
-        rooftab = rooflines(prof, units, peaks())
-        own = {k: v for k, v in prof.items() if k in rooftab}
-        if own:
-            top = max(own, key=lambda k: own[k][1])
-            roof = dict(kernel=top, **rooftab[top])
-            roof["traffic"] = ncu_traffic(top)
-            roof["ncu"] = ncu_metrics(top)
-            tot = sum(v[1] for v in prof.values())
-            roof["share_of_gpu_kernel_time"] = round(prof[top][1] / tot, 3) if tot else None
-        work = dict(P=P, P_visible=pvis, instances=R, effective_pairs=pairs)
-    else:
-        work = {}
+    roof, rooftab, work = native_rooflines(win, gm, sc, kfs, local_views, world, device)
 
     cpu = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline and not impl_ref:
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu = cpu_oracle_sample()
 
     if rank != 0:
         return finish(world, win)
-    views_per_s = N_VIEWS * K / (ms / 1e3)
-    h2d = sum(host[v][0].numel() * 4 + host[v][1].numel() * 4 for v in range(N_VIEWS))
+    h2d = sum(h[0].numel() * 4 + h[1].numel() * 4 for h in host)
     line = {
-        "metric": METRIC, "value": round(views_per_s, 3), "unit": "iters/s", "n_gpus": world, "steps": K,
-        "warmup": W_, "ms_per_step": round(ms / K, 4), "higher_is_better": True, "scaling": "strong",
+        "metric": METRIC, "value": round(n_views * K / (ms / 1e3), 3), "unit": "iters/s", "n_gpus": world,
+        "steps": K, "warmup": W_, "ms_per_step": round(ms / K, 4), "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "cfg3_replica: 1200x680, 500k Gaussians, SH0, 8-keyframe mapping window "
-                               "(fwd+bwd per keyframe, fused Adam, pose Adam)",
-                   "keyframes": N_VIEWS, "parallelism": "keyframes sharded round-robin over %d rank(s)" % world + (
+        "config": {**config_common(name, n_views),
+                   "parallelism": "keyframes sharded round-robin over %d rank(s)" % world + (
                        "; gradient exchange + Adam + zero_grad as one kernel over NVLink peer memory"
                        if getattr(win, "peer", None) is not None else ""),
-                   "launch": ("cuda graphs (2 per step, no host sync inside a step: overflow flags are read back "
+                   "launch": ("cuda graphs (no host sync inside a step: overflow flags are read back "
                               "asynchronously, flush() inside the timed region)" if graph else "eager") +
-                             ("" if impl_ref or args.view_streams < 2 else
+                             ("" if args.view_streams < 2 else
                               ", views issued on %d forked streams" % args.view_streams),
-                   "l2_policy": "inputs larger than L2: >400 MB touched per step (8 GT frames 104 MB, "
-                                "4 parameter/moment arenas 112 MB, per-view workspaces+gradients) vs 126 MB L2",
                    **work},
         "clocks": clocks,
-        "e2e": {"value": round(N_VIEWS * K / (ms_e2e / 1e3), 3), "unit": "iters/s",
+        "state_check": check,
+        "e2e": {"value": round(n_views * K / (ms_e2e / 1e3), 3), "unit": "iters/s",
                 "ms_per_step": round(ms_e2e / K, 4), "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4 * world,
                 "readback": "every step's loss copied to pinned host memory and read by the host one step "
                             "later (after the next step is enqueued); the last one before the region ends"},
         "gpu_launches": launches,
         "single_view_fwd_bwd_iters_s": round(single, 2) if single else None,
+        "roofline": roof, "rooflines_all": rooftab, "cpu_baseline": cpu,
     }
-    if impl_ref:
-        line["impl"] = "reference"
-        line["cpu_baseline"] = {"value": line["value"], "unit": "iters/s", "cores": 0, "kind": "reference",
-                                "sample": "UNMODIFIED reference CUDA rasterizer (oracle/_ref, sm_100 build) + "
-                                          "torch.optim.Adam on the GPU: full workload, not a CPU run "
-                                          "(the reference has no CPU rasterizer)"}
-        line["gpu_launches"] = None
-    else:
-        line["roofline"] = roof
-        line["rooflines_all"] = rooftab
-        line["cpu_baseline"] = cpu
     print(json.dumps(line), flush=True)
     finish(world, win)
+
+
+def native_rooflines(win, gm, sc, kfs, local_views, world, device):
+    """per-kernel durations: CUDA events on the launching stream, 2 extra (untimed) steps with the
+    views serialised on one stream (a kernel timed while another view's kernels share the SMs would
+    not be that kernel's duration).  Work units are read from THIS run: visible Gaussians, the true
+    instance count (status[0], not the workspace capacity), evaluated / contributing pixel-splat
+    pairs counted by the render kernels' debug counters."""
+    from monogs_dev_b200 import _lib, knn
+    _lib.lib.b2gs_profile_enable(1)
+    win.profile_steps(2)
+    if world == 1:
+        knn.distCUDA2(gm._xyz.detach())
+    torch.cuda.synchronize()
+    prof = _lib.profile_read()
+    _lib.lib.b2gs_profile_enable(0)
+    info = win.work_counters(local_views[0])
+    P, N = sc.P, sc.W * sc.H
+    pvis, R = info["visible"], info["instances"]
+    M = (sc.sh_degree + 1) ** 2
+    n_par = gm.flat.numel()
+    tiles = ((sc.W + 15) // 16) * ((sc.H + 15) // 16)
+    # EXECUTED FP32 work of the render kernels (DESIGN.md §4; FMA = 2 flop, a packed fp32x2 op = its two
+    # lanes, MUFU = 1).  A warp visit makes all 64 pixels of the quadrant evaluate `power` (FWD_POWER /
+    # BWD_HEAD flop per pixel); a visit that survives the warp vote runs exp + alpha + blend (forward) or
+    # the gradient arithmetic + 12-shuffle fold (backward) on every pixel, contributing or not.
+    fwd_flop = FWD_POWER * info["fwd_visit_px"] + FWD_BLEND * info["fwd_eval_px"]
+    bwd_flop = BWD_HEAD * info["bwd_visit_px"] + BWD_BLEND * info["bwd_blend_px"]
+    units = {   # algorithmic work per launch (SURVEY.md §8d, DESIGN.md §4)
+        "preprocess_fwd": ("hbm", (119.0 + 12.0 * M) * pvis + 20.0 * (P - pvis)),
+        "scatter_instances": ("hbm", 12.0 * P + 40.0 * pvis + 8.0 * R),
+        "tile_sort": ("hbm", 24.0 * R),               # the sort's lower bound: one read + one write of a 12 B pair
+        "render_fwd": ("fp32", fwd_flop),
+        "render_bwd": ("fp32", bwd_flop),
+        "preprocess_bwd": ("hbm", (283.0 + 36.0 * M) * pvis + 60.0 * (P - pvis)),
+        "loss": ("hbm", 48.0 * N),                    # read render 16 + GT 16, write grads 16
+        "iso_reg": ("hbm", 24.0 * P),
+        "adam": ("hbm", 28.0 * n_par),
+        "adam_peer": ("hbm", 28.0 * n_par / max(world, 1)),
+        "knn_search": ("hbm", 16.0 * P),
+    }
+    rooftab = rooflines(prof, units, peaks())
+    for k in ("render_fwd", "render_bwd"):
+        if k in rooftab:
+            rooftab[k]["ncu"] = ncu_metrics(k)
+    roof = None
+    own = {k: v for k, v in prof.items() if k in rooftab}
+    if own:
+        top = max(own, key=lambda k: own[k][1])
+        roof = dict(kernel=top, **rooftab[top])
+        roof["traffic"] = ncu_traffic(top)
+        tot = sum(v[1] for v in prof.values())
+        roof["share_of_gpu_kernel_time"] = round(prof[top][1] / tot, 3) if tot else None
+        roof["unit_definition"] = (
+            "EXECUTED flops from the kernels' debug counters in this run: forward %.1f/visited pixel + %.1f/"
+            "evaluated pixel; backward %.1f/visited pixel + %.1f/blended pixel (a visit = 64 pixels x 1 splat). "
+            "useful_frac = the same with only contributing pairs charged" % (FWD_POWER, FWD_BLEND, BWD_HEAD, BWD_BLEND))
+        if top in ("render_fwd", "render_bwd"):
+            useful = (FWD_POWER + FWD_BLEND) * info["fwd_contributing"] if top == "render_fwd" else \
+                (BWD_HEAD + BWD_BLEND) * info["bwd_contributing"]
+            roof["useful_frac"] = round(useful / (roof["avg_ms"] * 1e-3) / 1e12 / roof["peak"], 4)
+    work = dict(P=P, P_visible=pvis, instances=R, effective_pairs=info["effective_pairs"],
+                **{k: info[k] for k in ("fwd_visit_px", "fwd_eval_px", "fwd_contributing", "bwd_visit_px",
+                                        "bwd_blend_px", "bwd_contributing")})
+    return roof, rooftab, work
+
+
+def run_reference(args):
+    """the clean reference arm: oracle/_ref (unmodified reference CUDA extension) + oracle/ref_loop.py;
+    `monogs_dev_b200` is never imported in this process."""
+    rank, local = env_int("RANK", 0), env_int("LOCAL_RANK", 0)
+    world = env_int("WORLD_SIZE", 1)
+    if rank != 0:
+        return                                    # the reference is single-GPU: rank 0 runs the whole window
+    from oracle import ref_ext, ref_loop
+    if not ref_ext.available():
+        return run_reference_cpu(args, rank, world)
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    name = args.workload
+    n_views = WORKLOADS[name][0]
+    K, W_ = args.steps, max(args.warmup, 3)
+    t = synthdata.scene_tensors(name, n_views=n_views)
+    bg = torch.zeros(3, device=device)
+    cams = ref_loop.make_cameras(t, device)
+    kfs = ref_loop.build_window_gt(t, cams, bg, device)
+    gm = ref_loop.make_model(t, device)
+    win = ref_loop.RefMappingWindow(gm, kfs, bg, pose_lr=POSE_LR)
+    host = pinned_host_copies(kfs)
+    e2e = E2E(win, kfs, host, list(range(n_views)))
+    loss = None
+    for _ in range(W_ + GRAPH_WARMUP):
+        loss = win.step()
+    sampler = ClockSampler(local)
+    last = [loss]
+
+    def step():
+        last[0] = win.step()
+    ms = timed_steps(step, K, 1)
+    clocks = sampler.stop()
+    check = state_check(W_ + GRAPH_WARMUP + K, last[0], gm.parameters(), cams, 1, device)
+    e2e.step()
+    e2e.settle()
+    e2e.reset()
+    ms_e2e = timed_steps(e2e.step, K, 1, settle=e2e.settle)
+
+    def one_view():
+        pkg = ref_ext.ref_render(cams[0], gm, None, bg)
+        ref_loop.get_loss_mapping_rgbd(pkg["render"], pkg["depth"], cams[0], kfs[0]["gt_image"],
+                                       kfs[0]["gt_depth"]).backward()
+        gm.zero_grad()
+        for p in (cams[0].cam_rot_delta, cams[0].cam_trans_delta, cams[0].exposure_a, cams[0].exposure_b):
+            p.grad = None
+    for _ in range(3):
+        one_view()
+    n1 = max(20, K * n_views // 2)
+    single = n1 / (timed_steps(one_view, n1, 1) / 1e3)
+
+    value = round(n_views * K / (ms / 1e3), 3)
+    h2d = sum(h[0].numel() * 4 + h[1].numel() * 4 for h in host)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": "iters/s", "n_gpus": world, "steps": K,
+        "warmup": W_, "ms_per_step": round(ms / K, 4), "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {**config_common(name, n_views),
+                   "parallelism": "single GPU (the reference has no multi-GPU path): rank 0 runs the whole window",
+                   "launch": "eager, the reference's own loop (oracle/ref_loop.py restates utils/slam_backend.py:156-317)"},
+        "clocks": clocks,
+        "state_check": check,
+        "e2e": {"value": round(n_views * K / (ms_e2e / 1e3), 3), "unit": "iters/s",
+                "ms_per_step": round(ms_e2e / K, 4), "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4},
+        "gpu_launches": None,
+        "single_view_fwd_bwd_iters_s": round(single, 2),
+        "cpu_baseline": {"value": value, "unit": "iters/s", "cores": 0, "kind": "reference",
+                         "sample": "UNMODIFIED reference CUDA rasterizer (oracle/_ref, sm_100 build) + "
+                                   "torch.optim.Adam on ONE GPU: full workload, not a CPU run "
+                                   "(the reference has no CPU rasterizer)"},
+    }
+    print(json.dumps(line), flush=True)
 
 
 def finish(world, win):
@@ -501,7 +642,7 @@ def finish(world, win):
     torch.cuda.synchronize()
     dist.barrier()
     torch.cuda.synchronize()
-    win._g1 = win._g2 = None
+    win.release_graphs()
     sys.stdout.flush()
     sys.stderr.flush()
     os._exit(0)
@@ -512,8 +653,9 @@ def run_reference_cpu(args, rank, world):
     if rank != 0:
         return
     cpu = cpu_oracle_sample()
+    n_views = WORKLOADS["cfg3_replica"][0]
     line = {"impl": "reference", "metric": METRIC, "value": cpu["value"], "unit": "iters/s", "n_gpus": world,
-            "steps": 1, "warmup": 0, "ms_per_step": round(1e3 * N_VIEWS / cpu["value"], 1),
+            "steps": 1, "warmup": 0, "ms_per_step": round(1e3 * n_views / cpu["value"], 1),
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic", "config": {"workload": "cfg3_replica (1/10-scale sample)"},
             "cpu_baseline": cpu,
@@ -530,6 +672,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
+    ap.add_argument("--workload", default="cfg3_replica", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="native arm: eager launches instead of CUDA graphs")
     ap.add_argument("--no-peer-adam", action="store_true",
@@ -541,7 +684,9 @@ def main():
         if args.impl == "reference":
             return run_reference_cpu(args, env_int("RANK", 0), env_int("WORLD_SIZE", 1))
         raise SystemExit("bench.py needs a CUDA device: the product has no CPU fallback")
-    run(args)
+    if args.impl == "reference":
+        return run_reference(args)
+    run_native(args)
 
 
 if __name__ == "__main__":

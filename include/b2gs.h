@@ -276,6 +276,15 @@ B2GS_API int b2gs_backproject_rgbd(int32_t W, int32_t H, const float* image, con
  * ranks (the result is left in the flag), so data-parallel replicas agree. */
 B2GS_API void b2gs_set_update_guard(const int32_t* device_flag);
 
+/* Debug work counters (measurement only, bench.py roofline): while `device_counters` (8 device
+ * uint64, or NULL to clear) is set for the calling host thread, the render kernels launch a counting
+ * instantiation and ADD to it:  [0] forward warp visits (a warp = 64 pixels looking at one splat of
+ * its tile's list), [1] forward visits that evaluate exp + blend, [2] forward contributing
+ * pixel-splat pairs (alpha >= 1/255, not terminated: the pairs CR/forward.cu:359-371 blends),
+ * [4] backward warp visits, [5] backward visits that run the gradient arithmetic, [6] backward
+ * contributing pairs (CR/backward.cu:700-757). */
+B2GS_API void b2gs_debug_set_counters(uint64_t* device_counters);
+
 /* ---- fused per-pixel losses (utils/slam_utils.py:56-128) ---------------------------------
  * mode: 0 mapping rgbd (get_loss_mapping_rgbd :113-128), 1 tracking rgbd (:74-88),
  *       2 mapping rgb / monocular (:101-110), 3 tracking rgb / monocular (:64-72).

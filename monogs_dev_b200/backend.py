@@ -64,6 +64,7 @@ class BackEnd:
         # randperm source for the two extra views: identical on every rank
         self._gen = torch.Generator().manual_seed(seed)
         self._seed, self._dev_gen = seed, None       # densify_and_split samples: same on every rank
+        self._seed_gen = torch.Generator().manual_seed(seed + 2)   # keyframe seeding: same on every rank
         self._py_rng = random.Random(seed)           # color_refinement's view choice: same on every rank
         self._win_key, self._win = None, None
         self._kf_flags = {}
@@ -101,7 +102,11 @@ class BackEnd:
                 cam.original_image = viewpoint["gt_image"]
                 cam.depth = viewpoint["gt_depth"].reshape(viewpoint["gt_image"].shape[-2:])
             self.viewpoints.setdefault(frame_idx, viewpoint)
-        self.gaussians.extend_from_pcd_seq(cam, kf_id=frame_idx, init=init, scale=scale, depthmap=depth_map)
+        # the random down-sample subset (and the monocular depth noise) must be the SAME on every rank
+        # of a data-parallel run: replicas that seed different Gaussians keep equal sizes and are then
+        # silently mixed by the gradient exchange.  A host generator seeded alike on all ranks.
+        self.gaussians.extend_from_pcd_seq(cam, kf_id=frame_idx, init=init, scale=scale, depthmap=depth_map,
+                                           generator=self._seed_gen)
         self._win_key = None
 
     def reset(self):

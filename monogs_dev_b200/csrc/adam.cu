@@ -150,6 +150,9 @@ __global__ void peer_barrier_kernel(const __grid_constant__ PeerTable pt, uint32
   if (guard && t == 0) {
     uint32_t any = 0;
     for (int r = 0; r < pt.world; ++r) any |= *(volatile uint32_t*)(pt.signal[pt.rank] + PEER_MAX + r);
+    // a timed-out barrier means some peer's gradients may not be final: discard the update (the
+    // host reads fail_flag with the overflow flags and raises, mapping.MappingWindow._settle)
+    any |= *(volatile uint32_t*)fail;
     *guard = (int32_t)any;
   }
 }
@@ -159,8 +162,9 @@ constexpr int PEER_CHUNK = 1024;   // floats per ownership chunk = one float4 pe
 __global__ void __launch_bounds__(256)
 adam_peer_kernel(const __grid_constant__ AdamTable t, const __grid_constant__ PeerTable pt, float w1,
                  float beta2, float w2, float eps, float beta1, const long long* __restrict__ step_dev,
-                 const int32_t* __restrict__ guard) {
+                 const int32_t* __restrict__ guard, const uint32_t* __restrict__ fail) {
   if (guard && *guard) return;   // some rank overflowed: every rank discards this step
+  if (*fail) return;             // a barrier timed out: peers' arenas may not be final
   const long long chunk = (long long)blockIdx.x * pt.world + pt.rank;   // chunks this rank owns
   if (chunk >= t.first_chunk[t.num]) return;
   int s = 0;
@@ -269,7 +273,8 @@ static int adam_impl(const B2gsAdamSegment* segments, int32_t num_segments, int6
     t.num = k;
     if (chunks > 0) {
       if (chunks > 0x7fffffffLL) { set_error("b2gs_adam_step: too many elements"); return B2GS_ERR_INVALID; }
-      B2GS_PROF("adam", st);
+      // the camera / exposure optimizer is a handful of floats: latency, not bandwidth — its own name
+      B2GS_PROF(chunks * ADAM_CHUNK < 65536 ? "adam_small" : "adam", st);
       adam_kernel<<<(unsigned)chunks, 256, 0, st>>>(t, w1, beta2, w2, bc2_sqrt, eps, beta1, step_dev,
                                                         update_guard());
       B2GS_LAUNCH_CHECK(st, 0);
@@ -333,10 +338,14 @@ extern "C" int b2gs_adam_step_peer(const B2gsAdamSegment* segments, int32_t num_
   }
   t.first_chunk[num_segments] = chunks;
   t.num = num_segments;
-  adam_tick_kernel<<<1, 1, 0, st>>>(reinterpret_cast<long long*>(step_counter), guard);
-  B2GS_LAUNCH_CHECK(st, 0);
-  // every rank's gradients are final ...
+  // every rank's gradients are final ...  (the barrier also leaves the OR of all ranks' guard words
+  // in *guard, and sets it when a peer timed out: the update below is then skipped on every rank)
   peer_barrier_kernel<<<1, 32, 0, st>>>(pt, peers->fail_flag, guard);
+  B2GS_LAUNCH_CHECK(st, 0);
+  // ... and only now may the step counter advance: with the rank-local guard value a rank whose own
+  // forward did not overflow would tick while an overflowed rank does not, and the replicas' bias
+  // corrections would diverge for good
+  adam_tick_kernel<<<1, 1, 0, st>>>(reinterpret_cast<long long*>(step_counter), guard);
   B2GS_LAUNCH_CHECK(st, 0);
   if (chunks > 0) {
     const long long blocks = (chunks + pt.world - 1) / pt.world;
@@ -344,7 +353,8 @@ extern "C" int b2gs_adam_step_peer(const B2gsAdamSegment* segments, int32_t num_
     B2GS_PROF("adam_peer", st);
     adam_peer_kernel<<<(unsigned)blocks, 256, 0, st>>>(t, pt, (float)(1.0 - (double)beta1), beta2,
                                                       (float)(1.0 - (double)beta2), eps, beta1,
-                                                      reinterpret_cast<const long long*>(step_counter), guard);
+                                                      reinterpret_cast<const long long*>(step_counter), guard,
+                                                      peers->fail_flag);
     B2GS_LAUNCH_CHECK(st, 0);
   }
   // ... and every replica / gradient arena has been written by all of its chunk owners

@@ -18,6 +18,8 @@ static std::atomic<unsigned long long> g_launches{0};
 
 static thread_local const int32_t* g_guard = nullptr;
 const int32_t* update_guard() { return g_guard; }
+static thread_local unsigned long long* g_counters = nullptr;
+unsigned long long* debug_counters() { return g_counters; }
 
 void note_launches(int n) { g_launches.fetch_add((unsigned long long)n, std::memory_order_relaxed); }
 
@@ -109,6 +111,9 @@ using namespace b2gs;
 extern "C" int b2gs_version(void) { return 100; }
 extern "C" const char* b2gs_last_error(void) { return g_err; }
 extern "C" void b2gs_set_update_guard(const int32_t* device_flag) { b2gs::g_guard = device_flag; }
+extern "C" void b2gs_debug_set_counters(uint64_t* device_counters) {
+  b2gs::g_counters = reinterpret_cast<unsigned long long*>(device_counters);
+}
 
 extern "C" uint64_t b2gs_kernel_launches(void) { return g_launches.load(std::memory_order_relaxed); }
 

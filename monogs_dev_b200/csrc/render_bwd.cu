@@ -1,8 +1,12 @@
 // render_bwd.cu — backward of the alpha blend, one CTA per 16x16 tile, back to front.
 // Replaces renderCUDA<3> backward + render_cuda_reduce_sum (CR/backward.cu:541-787).
 //
-// Per-pixel arithmetic follows the reference recurrences (T recovered by division,
-// accum_rec / last_alpha / last_color replay, CR/backward.cu:700-757).  What is
+// Per-pixel arithmetic follows the reference recurrences (CR/backward.cu:700-757) with two
+// algebraic rewrites that stay within the 1e-4 gradient tolerance but are NOT operation for
+// operation: T / (1 - alpha) is T * rcp(1 - alpha) (MUFU.RCP + one Newton step, <= 1 ulp), and the
+// replay accum = last_alpha * last_colour + (1 - last_alpha) * accum is kept in the incremental
+// form accum += last_alpha * (last_colour - accum).  `power` / exp / the skip tests ARE the
+// forward's operation tree bit for bit, so both passes take the same decisions.  What is
 // redesigned is the reduction of the 10 per-splat partials:
 //   reference: per splat per tile 3 block barriers + a 256-wide, 8-level shared
 //              memory tree over 13 floats + 10 atomics from thread 0;
@@ -87,15 +91,19 @@ __device__ __forceinline__ float hsum(f2 a) { return a.x + a.y; }
 
 constexpr int RB_THREADS = 128;   // 4 warps x (8x8 pixels, two per lane) = one 16x16 tile
 
+// COUNT: debug instantiation that also counts the work it executes (b2gs_debug_set_counters):
+// [4] warp visits, [5] warp visits that run the blend / gradient arithmetic, [6] contributing pairs
+template <bool COUNT>
 __global__ void __launch_bounds__(RB_THREADS)
 render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W,
                   int H, int gx, const float* __restrict__ bg, const float2* __restrict__ xy,
                   const float4* __restrict__ conic_o, const float4* __restrict__ rgbd,
                   const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib,
                   const float* __restrict__ dL_dpixels, const float* __restrict__ dL_dpixels_depth,
-                  float* __restrict__ acc) {
+                  float* __restrict__ acc, unsigned long long* __restrict__ counters) {
   __shared__ SplatRec s_rec[RB_BATCH];
   __shared__ int s_max;
+  unsigned c_visit = 0, c_full = 0, c_contrib = 0;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int tile = blockIdx.x;
@@ -209,7 +217,9 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
         const float alphaA = fminf(0.99f, og.x), alphaB = fminf(0.99f, og.y);
         const bool skipA = !(pos < lastA) || power.x > 0.0f || alphaA < 1.0f / 255.0f;
         const bool skipB = !(pos < lastB) || power.y > 0.0f || alphaB < 1.0f / 255.0f;
+        if (COUNT) ++c_visit;
         if (__all_sync(FULL, skipA && skipB)) continue;
+        if (COUNT) { ++c_full; c_contrib += (unsigned)!skipA + (unsigned)!skipB; }
 
         const f2 alpha = make_float2(skipA ? 0.f : alphaA, skipB ? 0.f : alphaB);
         const f2 Gs = make_float2(skipA ? 0.f : G.x, skipB ? 0.f : G.y);
@@ -258,15 +268,29 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
       }
     }
   }
+  if (COUNT) {
+    c_contrib = __reduce_add_sync(FULL, c_contrib);
+    if (lane == 0) {
+      atomicAdd(&counters[4], (unsigned long long)c_visit);
+      atomicAdd(&counters[5], (unsigned long long)c_full);
+      atomicAdd(&counters[6], (unsigned long long)c_contrib);
+    }
+  }
 }
 
 int launch_render_bwd(const B2gsScene& s, const GeomWS& g, const ImageWS& im, const BinWS& b,
                       const B2gsBackwardIO& io, float* acc, cudaStream_t st) {
   const int gx = (s.W + TILE - 1) / TILE, gy = (s.H + TILE - 1) / TILE;
   B2GS_PROF("render_bwd", st);
-  render_bwd_kernel<<<gx * gy, RB_THREADS, 0, st>>>(im.ranges, b.point_list, s.W, s.H, gx, s.bg, g.xy,
-                                                    g.conic_o, g.rgbd, im.final_T, im.n_contrib,
-                                                    io.dL_dcolor, io.dL_ddepth, acc);
+  unsigned long long* cnt = debug_counters();
+  if (cnt)
+    render_bwd_kernel<true><<<gx * gy, RB_THREADS, 0, st>>>(im.ranges, b.point_list, s.W, s.H, gx, s.bg, g.xy,
+                                                            g.conic_o, g.rgbd, im.final_T, im.n_contrib,
+                                                            io.dL_dcolor, io.dL_ddepth, acc, cnt);
+  else
+    render_bwd_kernel<false><<<gx * gy, RB_THREADS, 0, st>>>(im.ranges, b.point_list, s.W, s.H, gx, s.bg, g.xy,
+                                                             g.conic_o, g.rgbd, im.final_T, im.n_contrib,
+                                                             io.dL_dcolor, io.dL_ddepth, acc, nullptr);
   B2GS_LAUNCH_CHECK(st, s.debug);
   return B2GS_OK;
 }

@@ -1,18 +1,19 @@
-// render_fwd.cu — forward alpha blending, one CTA per 16x16 tile.
+// render_fwd.cu — forward alpha blending, one CTA (128 threads) per 16x16 tile.
 // Replaces renderCUDA<3> forward (CR/forward.cu:263-392).
 //
-// Differences in structure (results identical up to fp32 rounding of identical
-// expressions):
-//  * a warp covers an 8x4 pixel block (not 16x2) so that its 32 lanes see
-//    nearly the same splats -> warp-level early termination and coherent skips;
-//  * the tile's batch of splats is staged in shared memory as packed 16 B
-//    records (conic+opacity, rgb+depth): no per-pair global colour fetch
-//    (CR/forward.cu:365 reads features[] from global for every contributing pair);
-//  * each warp first culls the staged batch against its own 8x4 block (cull.cuh, one
-//    lane per splat) and only iterates over the survivors' bit mask;
-//  * n_touched (CR/forward.cu:369-371) is kept as per-lane bit flags, counted with
-//    ballots only for splats that were touched, into shared memory, and flushed with
-//    ONE global atomic per (tile, splat) instead of one per (pixel, splat).
+// Structure (per-pixel results identical to the reference: same operation tree for `power`,
+// the library's expf bit for bit, the reference's skip / termination tests):
+//  * a warp covers an 8x8 quadrant of the tile, each lane TWO pixels (rows r and r+4); the
+//    per-pixel arithmetic of the pair is packed fp32x2 (FFMA2 / FMUL2 / FADD2: one issue slot
+//    for both pixels, each half an IEEE single-rounding op);
+//  * a batch of the tile's list is staged in shared memory as one 48 B SplatRec per splat
+//    (conic+opacity, rgb+depth, mean, id, block mask): a visit is one address and three
+//    broadcast loads, no per-pair global colour fetch (CR/forward.cu:365);
+//  * the block mask (cull.cuh) was computed once by the instance scatter and arrives in the low
+//    byte of the sorted list word; a warp only walks the splats whose mask reaches its quadrant;
+//  * warp-level early termination; n_touched (CR/forward.cu:369-371) is two ballots per visit
+//    while some pixel of the warp still has T > 0.5, one red.shared from lane 0, and ONE global
+//    atomic per (tile, splat) instead of one per (pixel, splat).
 #include "common.cuh"
 #include "cull.cuh"
 
@@ -30,14 +31,19 @@ __device__ __forceinline__ f2 mul2(f2 a, f2 b) { return __fmul2_rn(a, b); }
 __device__ __forceinline__ f2 add2(f2 a, f2 b) { return __fadd2_rn(a, b); }
 __device__ __forceinline__ f2 fma2(f2 a, f2 b, f2 c) { return __ffma2_rn(a, b, c); }
 
+// COUNT: debug instantiation that also counts the work it executes (b2gs_debug_set_counters):
+// [0] warp visits, [1] warp visits that evaluate exp / blend, [2] contributing pixel-splat pairs
+template <bool COUNT>
 __global__ void __launch_bounds__(RF_THREADS)
 render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W,
                   int H, int gx, const float2* __restrict__ xy, const float4* __restrict__ conic_o,
                   const float4* __restrict__ rgbd, const float* __restrict__ bg,
                   float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
                   float* __restrict__ out_color, float* __restrict__ out_depth,
-                  float* __restrict__ out_opacity, int* __restrict__ n_touched) {
+                  float* __restrict__ out_opacity, int* __restrict__ n_touched,
+                  unsigned long long* __restrict__ counters) {
   __shared__ SplatRec s_rec[RF_BATCH];
+  unsigned c_visit = 0, c_full = 0, c_contrib = 0;
   __shared__ int s_cnt[RF_BATCH];
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -111,7 +117,9 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
           const f2 quad = fma2(bc(dx), bc(adx), cdy2);
           const f2 power = fma2(quad, bc(-0.5f), mul2(dy, bc(nbdx)));
           bool actA = !doneA && !(power.x > 0.0f), actB = !doneB && !(power.y > 0.0f);
+          if (COUNT) ++c_visit;
           if (!__any_sync(RF_FULL, actA || actB)) continue;
+          if (COUNT) ++c_full;
           const f2 og = mul2(bc(co.w), expf_pair(power));
           const float alphaA = fminf(0.99f, og.x), alphaB = fminf(0.99f, og.y);
           actA = actA && !(alphaA < 1.0f / 255.0f);
@@ -127,6 +135,7 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
           C2 = fma2(bc(cd.z), w, C2);
           D = fma2(bc(cd.w), w, D);
           T = make_float2(actA ? test_T.x : T.x, actB ? test_T.y : T.y);
+          if (COUNT) c_contrib += (unsigned)actA + (unsigned)actB;
           const uint32_t here = (uint32_t)(base + j + 1);
           lastA = actA ? here : lastA;
           lastB = actB ? here : lastB;
@@ -150,6 +159,14 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     }
   }
 
+  if (COUNT) {
+    c_contrib = __reduce_add_sync(RF_FULL, c_contrib);
+    if (lane == 0) {
+      atomicAdd(&counters[0], (unsigned long long)c_visit);
+      atomicAdd(&counters[1], (unsigned long long)c_full);
+      atomicAdd(&counters[2], (unsigned long long)c_contrib);
+    }
+  }
   const size_t plane = (size_t)H * W;
   if (insideA) {
     final_T[pixA] = T.x;
@@ -175,9 +192,16 @@ int launch_render_fwd(const B2gsScene& s, const GeomWS& g, const ImageWS& im, co
                       const B2gsForwardOut& out, cudaStream_t st) {
   const int gx = (s.W + TILE - 1) / TILE, gy = (s.H + TILE - 1) / TILE;
   B2GS_PROF("render_fwd", st);
-  render_fwd_kernel<<<gx * gy, RF_THREADS, 0, st>>>(im.ranges, b.point_list, s.W, s.H, gx, g.xy, g.conic_o,
-                                             g.rgbd, s.bg, im.final_T, im.n_contrib, out.color,
-                                             out.depth, out.opacity, out.n_touched);
+  unsigned long long* cnt = debug_counters();
+  if (cnt)
+    render_fwd_kernel<true><<<gx * gy, RF_THREADS, 0, st>>>(im.ranges, b.point_list, s.W, s.H, gx, g.xy,
+                                                            g.conic_o, g.rgbd, s.bg, im.final_T, im.n_contrib,
+                                                            out.color, out.depth, out.opacity, out.n_touched, cnt);
+  else
+    render_fwd_kernel<false><<<gx * gy, RF_THREADS, 0, st>>>(im.ranges, b.point_list, s.W, s.H, gx, g.xy,
+                                                             g.conic_o, g.rgbd, s.bg, im.final_T, im.n_contrib,
+                                                             out.color, out.depth, out.opacity, out.n_touched,
+                                                             nullptr);
   B2GS_LAUNCH_CHECK(st, s.debug);
   return B2GS_OK;
 }

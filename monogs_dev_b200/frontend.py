@@ -73,7 +73,7 @@ class FrontEnd:
     # -- tracking ---------------------------------------------------------------------------------
     def _tracking_loop(self, viewpoint):
         if self._loop is None or self._loop.g is not self.gaussians:
-            from .synthetic import Camera
+            from .camera import Camera
             c = viewpoint
             cam = Camera(c.image_width, c.image_height, c.fx, c.fy, c.cx, c.cy, device=self.background.device)
             lr = self.config["Training"]["lr"]

@@ -625,7 +625,8 @@ class MappingWindow:
         self.graph_launches = (l1 - l0) + self._l2      # libb2gs kernels per replayed step
         if self._status_all is not None:
             self._flag_host = [(torch.empty(self._status_all.shape, dtype=torch.int32).pin_memory(),
-                                torch.empty(1, dtype=torch.int32).pin_memory()) for _ in range(3)]
+                                torch.empty(1, dtype=torch.int32).pin_memory(),
+                                torch.zeros(1, dtype=torch.int32).pin_memory()) for _ in range(3)]
 
     def _launch(self):
         """one replay of the captured step + an asynchronous read-back of its overflow flags"""
@@ -635,12 +636,14 @@ class MappingWindow:
         self._g1.replay()
         self._g2.replay()
         if self._status_all is not None:
-            st, ov = self._flag_host[self._launched % 3]
+            st, ov, fl = self._flag_host[self._launched % 3]
             st.copy_(self._status_all, non_blocking=True)      # this rank's views: sizes the retry
             ov.copy_(self._ovf, non_blocking=True)             # after G2: the OR over all ranks
+            if self.peer is not None:
+                fl.copy_(self.peer.fail, non_blocking=True)    # did a peer barrier time out?
             ev = torch.cuda.Event()
             ev.record()
-            self._pending.append((ev, st, ov))
+            self._pending.append((ev, st, ov, fl))
         self._launched += 1
 
     def _settle(self, keep):
@@ -651,15 +654,18 @@ class MappingWindow:
         from . import rasterizer as rz
         over = False
         while len(self._pending) > keep:
-            ev, st, ov = self._pending.pop(0)
+            ev, st, ov, fl = self._pending.pop(0)
             ev.synchronize()
+            if int(fl[0]):
+                raise RuntimeError("libb2gs peer barrier timed out: a rank died or fell out of step; the "
+                                   "replicas were left untouched by that step but the window cannot continue")
             rz.note_overflow(self._gstates, st.tolist())
             over = over or bool(int(ov[0]))
         if not over:
             return
         torch.cuda.synchronize()
         lost = 1 + len(self._pending)           # every launch since the overflowing one was discarded
-        for ev, st, ov in self._pending:
+        for ev, st, ov, fl in self._pending:
             rz.note_overflow(self._gstates, st.tolist())
         self._pending.clear()
         for _ in range(lost):
@@ -669,7 +675,7 @@ class MappingWindow:
             self._capture()                     # larger capacities are now in rz._SyncFree.cap
             self._launch()
             torch.cuda.synchronize()
-            ev, st, ov = self._pending.pop(0)
+            ev, st, ov, fl = self._pending.pop(0)
             rz.note_overflow(self._gstates, st.tolist())
             if int(ov[0]):
                 raise RuntimeError("binning capacity overflow persisted after re-capture")
@@ -702,6 +708,56 @@ class MappingWindow:
         loss = self._graph_step() if self.cuda_graph else self._eager_step()
         self._steps += 1
         return loss
+
+    def release_graphs(self):
+        """drop the captured graphs (they pin communicator resources in multi-rank runs)."""
+        self._g1 = self._g2 = None
+
+    # -- measurement helpers (bench.py) ------------------------------------------------------
+    def profile_steps(self, n):
+        """`n` extra EAGER steps with the views serialised on one stream, for per-kernel CUDA-event
+        timing (b2gs_profile_enable): a kernel timed while another view's kernels share the SMs
+        would not be that kernel's duration."""
+        self.flush()
+        vs, self.view_streams = self.view_streams, 1
+        try:
+            for _ in range(n):
+                self._eager_step(set_to_none=False)
+        finally:
+            self.view_streams = vs
+
+    def work_counters(self, v):
+        """the work one fwd+bwd of keyframe `v` executes, read from the run itself: visible
+        Gaussians, the true instance count, sum of n_contrib, and the render kernels' debug
+        counters (b2gs_debug_set_counters).  Leaves parameters and gradients untouched."""
+        import ctypes as C
+        from . import _lib
+        self.flush()
+        kf, g, dev = self.kfs[v], self.g, self.bg.device
+        cnt = torch.zeros(8, dtype=torch.int64, device=dev)
+        _lib.lib.b2gs_debug_set_counters(cnt.data_ptr())
+        try:
+            pkg = self.render_fn(kf["cam"], g, None, self.bg, **(
+                dict(with_stats=False) if self.render_fn is render_fused else {}))
+            self.loss_fn(pkg["render"], pkg["depth"], kf["cam"], kf["gt_image"], kf["gt_depth"]).backward()
+            torch.cuda.synchronize()
+        finally:
+            _lib.lib.b2gs_debug_set_counters(None)
+        g.zero_grad()
+        self._zero_kf_grads(False)
+        st = pkg["render"].grad_fn.state
+        inst = int(st.status[0].item()) if st.status is not None else int(st.num_rendered)
+        sc = _lib.B2gsScene()
+        sc.P, sc.W, sc.H = 1, int(kf["cam"].image_width), int(kf["cam"].image_height)
+        ws = _lib.B2gsWorkspace(None, 0, _lib.ptr(st.image), st.image.numel(), None, 0)
+        nc = torch.zeros(sc.W * sc.H, dtype=torch.int32, device=dev)
+        _lib.check(_lib.lib.b2gs_debug_export_image(C.byref(sc), C.byref(ws), None, nc.data_ptr(),
+                                                    torch.cuda.current_stream().cuda_stream))
+        c = cnt.tolist()
+        return dict(visible=int((pkg["radii"] > 0).sum().item()), instances=inst,
+                    effective_pairs=int(nc.long().sum().item()),
+                    fwd_visit_px=64 * c[0], fwd_eval_px=64 * c[1], fwd_contributing=c[2],
+                    bwd_visit_px=64 * c[4], bwd_blend_px=64 * c[5], bwd_contributing=c[6])
 
 
 def render_pose_only(viewpoint_camera, pc, pipe=None, bg_color=None, scaling_modifier=1.0):

@@ -1,0 +1,153 @@
+"""Loop-level parity ON THE BENCHED PATH, at full BASELINE sizes, against the clean reference loop.
+
+product:   render_fused (raw parameters, fused activations, in-kernel gradient accumulation and
+           densification statistics) + fused loss kernels + CUDA graphs + 8 view streams + FusedAdam
+           + device pose update                       — exactly what bench.py times
+reference: oracle/ref_loop.py (utils/slam_backend.py:156-317 / utils/slam_frontend.py:128-196
+           restated, pinned by tests/test_ref_loop_cpu.py) over the UNMODIFIED reference CUDA
+           extension (oracle/_ref) + torch.optim.Adam — exactly what bench.py --impl reference times
+
+Both sides start from the same synthdata tensors and the same ground-truth frames.
+
+Tolerances (stated here, used below):
+  * per-step loss: 1e-5 relative;
+  * Gaussian parameters after the steps: |a - b| <= 1e-5 * (|b| + mean|b| of the group) for all but
+    OUTLIER_FRAC of the elements — Adam divides the gradient by its own magnitude, so where the
+    gradient is at the level of the float-atomics summation noise (or a radius flips by one pixel
+    because exp / sigmoid / normalize differ from torch's by an ulp) the update can differ by up to
+    2 * lr per step; those outliers are bounded by 2.5 * lr * steps;
+  * keyframe poses / exposures: 1e-4 absolute;
+  * densification statistics: `denom` equal and `max_radii2D` equal on all but 1e-4 of the
+    Gaussians, `xyz_gradient_accum` within 1e-4 relative of its scale.
+"""
+import pytest
+import torch
+
+import synthdata
+from monogs_dev_b200 import mapping, rasterizer as rz
+from monogs_dev_b200.camera import Camera
+from oracle import ref_ext, ref_loop
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+POSE_LR = (0.0015, 0.0005, 0.01, 0.01)
+OUTLIER_FRAC = 2e-3
+LRS = dict(xyz=0.00016 * 6.0, f_dc=0.0025, f_rest=0.0025 / 20.0, opacity=0.05, scaling=0.001 * 6.0, rotation=0.001)
+
+
+def _need_ref():
+    if not ref_ext.available():
+        pytest.skip("reference extension (oracle/_ref) not built")
+
+
+def _product_window(t, kfs_r, bg, **kw):
+    to = lambda x: x.to(DEV).contiguous()
+    gm = mapping.GaussianModel(to(t.xyz), to(t.f_dc), to(t.f_rest), to(t.opacity), to(t.scaling), to(t.rotation),
+                               sh_degree=t.sh_degree)
+    kfs = []
+    for v, m in enumerate(t.w2c):
+        cam = Camera(t.W, t.H, t.fx, t.fy, t.cx, t.cy, w2c=m, device=DEV)
+        kfs.append(dict(cam=cam, gt_image=kfs_r[v]["gt_image"].clone(), gt_depth=kfs_r[v]["gt_depth"].clone(),
+                        optimize_pose=v > 0, optimize_exposure=v > 0))
+    return gm, kfs, mapping.MappingWindow(gm, kfs, bg, pose_lr=POSE_LR, **kw)
+
+
+def _compare_models(gm, gr, steps, report):
+    groups = dict(xyz=gr._xyz, f_dc=gr._features_dc, f_rest=gr._features_rest, opacity=gr._opacity,
+                  scaling=gr._scaling, rotation=gr._rotation)
+    for k, b in groups.items():
+        a = gm._params[k].detach()
+        if a.numel() == 0:
+            continue
+        b = b.detach()
+        diff = (a - b).abs()
+        tol = 1e-5 * (b.abs() + b.abs().mean())
+        frac = float((diff > tol).float().mean())
+        worst = float(diff.max())
+        report.append(f"{k}: off-fraction {frac:.2e}, max |diff| {worst:.3e} (lr {LRS[k]:.2e})")
+        assert frac < OUTLIER_FRAC, f"{k}: {frac:.3e} of the elements differ by more than 1e-5 rel"
+        assert worst <= 2.5 * LRS[k] * steps + 1e-6, f"{k}: outlier {worst:.3e} beyond 2.5 * lr * steps"
+
+
+@pytest.mark.parametrize("graph", [True])
+def test_cfg3_mapping_window_matches_reference_loop(graph):
+    _need_ref()
+    steps = 6                        # graph mode: 3 eager sizing steps, the capture, 2 replays
+    try:
+        t = synthdata.scene_tensors("cfg3_replica", n_views=8)
+        bg = torch.zeros(3, device=DEV)
+        cams_r = ref_loop.make_cameras(t, DEV)
+        kfs_r = ref_loop.build_window_gt(t, cams_r, bg, DEV)
+        gr = ref_loop.make_model(t, DEV)
+        win_r = ref_loop.RefMappingWindow(gr, kfs_r, bg, pose_lr=POSE_LR)
+        gm, kfs_p, win_p = _product_window(t, kfs_r, bg, cuda_graph=graph, view_streams=8)
+        report = []
+        for s in range(steps):
+            lr_, lp_ = float(win_r.step()), float(win_p.step())
+            report.append(f"step {s}: loss ref {lr_:.8f} product {lp_:.8f} rel {abs(lp_ - lr_) / abs(lr_):.2e}")
+            assert abs(lp_ - lr_) <= 1e-5 * abs(lr_), report[-1]
+        win_p.flush()
+        torch.cuda.synchronize()
+        if graph:
+            assert win_p._g1 is not None and win_p.graph_launches > 0, "graph path not taken"
+        _compare_models(gm, gr, steps, report)
+        for v in range(1, 8):
+            cp, cr = kfs_p[v]["cam"], cams_r[v]
+            dT = float((cp.T.to(DEV) - cr.T).abs().max())
+            dR = float((cp.R.to(DEV) - cr.R).abs().max())
+            da = abs(float(cp.exposure_a) - float(cr.exposure_a)), abs(float(cp.exposure_b) - float(cr.exposure_b))
+            report.append(f"kf {v}: |dT| {dT:.2e} |dR| {dR:.2e} |d exposure| {da[0]:.2e} {da[1]:.2e}")
+            assert dT <= 1e-4 and dR <= 1e-4 and max(da) <= 1e-4, report[-1]
+        # keyframe 0 is never moved and has no exposure parameter
+        assert torch.equal(kfs_p[0]["cam"].T, t.w2c[0][:3, 3]) and float(kfs_p[0]["cam"].exposure_a) == 0.0
+        # densification statistics
+        den_bad = float((gm.denom != gr.denom).float().mean())
+        rad_bad = float((gm.max_radii2D != gr.max_radii2D).float().mean())
+        acc_scale = float(gr.xyz_gradient_accum.abs().max())
+        acc_bad = float(((gm.xyz_gradient_accum - gr.xyz_gradient_accum).abs() >
+                         1e-4 * gr.xyz_gradient_accum.abs() + 1e-4 * acc_scale).float().mean())
+        report.append(f"densify stats: denom off {den_bad:.2e}, max_radii2D off {rad_bad:.2e}, accum off {acc_bad:.2e}")
+        print("\n".join(report))
+        assert den_bad < 1e-4 and rad_bad < 1e-4 and acc_bad < 1e-3, report[-1]
+    finally:
+        rz.set_sync_free(False)
+
+
+def test_cfg2_tracking_loop_matches_reference_loop():
+    """BASELINE config 2: 100 tracking iterations on a 640x480 frame over 100k frozen Gaussians,
+    captured-graph TrackingLoop vs utils/slam_frontend.py:163-193 restated."""
+    _need_ref()
+    try:
+        t = synthdata.scene_tensors("cfg2_tracking", n_views=1)
+        bg = torch.zeros(3, device=DEV)
+        true_w2c = synthdata.se3_exp(torch.tensor([0.02, -0.015, 0.01, 0.004, -0.006, 0.003]))
+        gr = ref_loop.make_model(t, DEV)
+        cam_true = ref_loop.RefCamera(0, t.W, t.H, t.fx, t.fy, t.cx, t.cy, w2c=true_w2c, device=DEV)
+        with torch.no_grad():
+            gt = ref_ext.ref_render(cam_true, gr, None, bg)
+        gt_image, gt_depth = gt["render"].detach().clone(), gt["depth"].detach().clone()
+        cam_r = ref_loop.RefCamera(1, t.W, t.H, t.fx, t.fy, t.cx, t.cy, device=DEV)
+        loop_r = ref_loop.RefTrackingLoop(gr, cam_r, bg, iters=100)
+        loop_r.load_frame(torch.eye(3), torch.zeros(3), gt_image, gt_depth)
+        loop_r.track()
+        to = lambda x: x.to(DEV).contiguous()
+        gm = mapping.GaussianModel(to(t.xyz), to(t.f_dc), to(t.f_rest), to(t.opacity), to(t.scaling),
+                                   to(t.rotation), sh_degree=t.sh_degree)
+        cam_p = Camera(t.W, t.H, t.fx, t.fy, t.cx, t.cy, device=DEV)
+        loop_p = mapping.TrackingLoop(gm, cam_p, bg, iters=100, cuda_graph=True)
+        loop_p.load_frame(torch.eye(3), torch.zeros(3), gt_image, gt_depth)
+        loop_p.track()
+        torch.cuda.synchronize()
+        dT = float((cam_p.T.to(DEV) - cam_r.T).abs().max())
+        dR = float((cam_p.R.to(DEV) - cam_r.R).abs().max())
+        e0 = float(true_w2c[:3, 3].norm())
+        err = float((cam_r.T.cpu() - true_w2c[:3, 3]).norm())
+        print(f"tracking: |dT| {dT:.2e} |dR| {dR:.2e}; reference pose error {err:.3e} of {e0:.3e}; "
+              f"loss ref {float(loop_r.loss):.6f} product {float(loop_p.loss):.6f}")
+        assert err < 0.5 * e0, "the reference loop itself did not approach the true pose"
+        assert dT <= 1e-4 and dR <= 1e-4
+        assert abs(float(cam_p.exposure_a) - float(cam_r.exposure_a)) <= 1e-4
+        assert abs(float(loop_p.loss) - float(loop_r.loss)) <= 1e-4 * abs(float(loop_r.loss))
+        assert float(gm.flat_grad.abs().max()) == 0.0, "a gradient leaked into the frozen map"
+    finally:
+        rz.set_sync_free(False)

@@ -177,7 +177,7 @@ def test_knn_oracle_small():
     assert torch.allclose(out[3], torch.tensor((0 + 9 + 10) / 3.0))   # duplicate point -> 0 counts
 
 
-GOLDENS = sorted(glob.glob(os.path.join(GOLDEN, "*.pt")))
+GOLDENS = sorted(glob.glob(os.path.join(GOLDEN, "ref_*.pt")))     # rasterizer goldens (make_golden.py)
 
 
 @pytest.mark.skipif(not GOLDENS, reason="no golden vectors committed yet (tests/golden/make_golden.py)")
