@@ -502,8 +502,14 @@ def native_rooflines(win, gm, sc, kfs, local_views, world, device):
     from monogs_dev_b200 import _lib, knn
     _lib.lib.b2gs_profile_enable(1)
     win.profile_steps(2)
-    if world == 1:
+    knn_evals = 0
+    if world == 1:       # distCUDA2 is not part of a mapping step: one call on the scene's points, for its line
+        cnt = torch.zeros(8, dtype=torch.int64, device=device)
+        _lib.lib.b2gs_debug_set_counters(cnt.data_ptr())
         knn.distCUDA2(gm._xyz.detach())
+        torch.cuda.synchronize()
+        _lib.lib.b2gs_debug_set_counters(None)
+        knn_evals = int(cnt[7])
     torch.cuda.synchronize()
     prof = _lib.profile_read()
     _lib.lib.b2gs_profile_enable(0)
@@ -526,11 +532,9 @@ def native_rooflines(win, gm, sc, kfs, local_views, world, device):
         "render_fwd": ("fp32", fwd_flop),
         "render_bwd": ("fp32", bwd_flop),
         "preprocess_bwd": ("hbm", (283.0 + 36.0 * M) * pvis + 60.0 * (P - pvis)),
-        "loss": ("hbm", 48.0 * N),                    # read render 16 + GT 16, write grads 16
-        "iso_reg": ("hbm", 24.0 * P),
-        "adam": ("hbm", 28.0 * n_par),
+        "adam": ("hbm", 32.0 * n_par),                # read p,g,m,v; write p,m,v and the cleared g
         "adam_peer": ("hbm", 28.0 * n_par / max(world, 1)),
-        "knn_search": ("hbm", 16.0 * P),
+        "knn_search": ("fp32", 8.0 * knn_evals),      # 3 sub, 3 mul/fma, compare-exchange chain ~ 8 flop / evaluation
     }
     rooftab = rooflines(prof, units, peaks())
     for k in ("render_fwd", "render_bwd"):

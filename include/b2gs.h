@@ -103,6 +103,8 @@ typedef struct B2gsWorkspace {
   void* binning; size_t binning_bytes;/* >= b2gs_binning_bytes(R,W,H); may be NULL in forward_plan */
 } B2gsWorkspace;
 
+struct B2gsFusedLoss;    /* defined with the loss entry points below */
+
 typedef struct B2gsForwardOut {
   float* color;      /* device [3,H,W] */
   float* depth;      /* device [1,H,W] */
@@ -112,6 +114,14 @@ typedef struct B2gsForwardOut {
   uint32_t* status;  /* device [2], optional (b2gs_forward only): [0] = number of (Gaussian, tile)
                       * instances, [1] = 1 if that exceeded the binning capacity (then the image
                       * is background only and the caller must retry with a larger workspace) */
+  /* optional, loop-level fusion; all may be NULL / 0:
+   * fused_loss: the mapping / tracking loss of this view and its gradient are computed in the
+   *   render kernel's epilogue from the pixel values it holds in registers (no separate pass over
+   *   the image, no torch autograd node): see B2gsFusedLoss.
+   * bwd_scratch: the backward's scratch buffer; the forward then clears the accumulator rows of
+   *   the visible Gaussians itself and b2gs_backward(scratch_zeroed = 1) skips its memset. */
+  const struct B2gsFusedLoss* fused_loss;
+  void* bwd_scratch; size_t bwd_scratch_bytes;
 } B2gsForwardOut;
 
 typedef struct B2gsBackwardIO {
@@ -141,6 +151,16 @@ typedef struct B2gsBackwardIO {
   float* densify_grad_accum;   /* [P] */
   float* densify_denom;        /* [P] */
   float* max_radii2D;          /* [P] */
+  int32_t scratch_zeroed;      /* the forward was given this scratch as out->bwd_scratch */
+  /* defer_tau != 0: dL_dtau may be NULL; the per-block partial rows (8 floats: tau[6], the
+   * regulariser partial, pad) stay in the scratch for b2gs_window_finalize
+   * (b2gs_backward_tau_partials tells where). */
+  int32_t defer_tau;
+  /* iso_reg_weight != 0 (needs raw_params + accumulate): this call also adds the gradient of the
+   * isotropic-scale regulariser  weight * mean|exp(s) - mean_row exp(s)|  (utils/slam_backend.py:
+   * 229-231) to dL_dscales for EVERY Gaussian, visible or not, and leaves per-block partial sums of
+   * its value in slot 6 of the tau partial rows.  Give it to exactly one view of a step. */
+  float iso_reg_weight;
 } B2gsBackwardIO;
 
 B2GS_API int b2gs_version(void);
@@ -159,6 +179,8 @@ B2GS_API size_t b2gs_geom_bytes(int32_t P);
 B2GS_API size_t b2gs_image_bytes(int32_t W, int32_t H);
 B2GS_API size_t b2gs_binning_bytes(int64_t R, int32_t W, int32_t H);
 B2GS_API size_t b2gs_backward_scratch_bytes(int32_t P);
+/* where b2gs_backward(defer_tau) leaves its per-block partial rows inside `scratch`, and how many */
+B2GS_API const float* b2gs_backward_tau_partials(const void* scratch, int32_t P, int32_t* blocks);
 
 /* Two-call form (exact sizing, like the reference: one small D2H read + sync).
  * Phase 1: per-Gaussian preprocessing, per-tile instance counts, tile ranges.
@@ -254,6 +276,56 @@ B2GS_API int b2gs_adam_step_peer(const B2gsAdamSegment* segments, int32_t num_se
                         int64_t* step_counter, float beta1, float beta2, float eps,
                         const B2gsPeerArena* peers, void* stream);
 
+/* ---- the scalar tail of a window / tracking step (csrc/window.cu) ----------------------------
+ * One entry per local view: where its fused-loss partials (B2gsFusedLoss.partials, `loss_rows` =
+ * tiles) and its backward partial rows (b2gs_backward_tau_partials) are, and where the results go. */
+typedef struct B2gsViewFinalize {
+  const float* loss_partials; int32_t loss_rows;   /* NULL: this view has no loss term */
+  int32_t N; int32_t mode; float alpha;            /* as in B2gsLossArgs */
+  const float* exposure_a;                         /* device scalar or NULL */
+  const float* tau_partials; int32_t tau_rows;     /* NULL: no pose gradient wanted */
+  float reg_scale;    /* iso_reg_weight / (3P) if this view's backward carried the regulariser, else 0 */
+  const uint32_t* status;   /* [2] of this view's b2gs_forward, or NULL */
+  float* loss;              /* [1] out: loss of the view (+ the regulariser value if reg_scale != 0) */
+  float* dL_dtau;           /* [6] out (rho, theta), may be NULL */
+  float* dL_dexposure;      /* [2] out (a, b), may be NULL */
+} B2gsViewFinalize;
+/* loss_total[0] = sum of the views' losses (view order), guard[0] = OR of the views' overflow flags
+ * (either may be NULL).  `ticket`: one zero-initialised device word, left zero.  <= 32 views. */
+B2GS_API int b2gs_window_finalize(const B2gsViewFinalize* views, int32_t n_views, float* loss_total,
+                         int32_t* guard, uint32_t* ticket, void* stream);
+
+/* Adam (torch.optim.Adam semantics, one shared 1-based step count) over the camera parameters of
+ * every local keyframe + update_pose + zeroed deltas, ONE launch; honours the update guard. */
+typedef struct B2gsPoseCam {
+  float* cam_state; const float* projmatrix_raw;   /* as in b2gs_pose_update */
+  float* rot_delta; float* trans_delta; float* exposure_a; float* exposure_b;
+  const float* dL_dtau;        /* [6] (rho, theta) */
+  const float* dL_dexposure;   /* [2] */
+  float* moments;              /* [16] exp_avg[8], exp_avg_sq[8] in the order rot, trans, a, b */
+  float lr_rot, lr_trans, lr_exposure_a, lr_exposure_b;
+  int32_t optimize_pose, optimize_exposure;
+} B2gsPoseCam;
+/* step_counter: device int64, incremented by the call (after use: the kernels read count + 1);
+ * extra_tick: optional second device counter incremented alongside (the Gaussian optimizer's, when
+ * b2gs_adam_step_fused ran with B2GS_ADAM_NO_TICK).  `ticket` as above. */
+B2GS_API int b2gs_pose_step(const B2gsPoseCam* cams, int32_t n_cams, int64_t* step_counter,
+                   int64_t* extra_tick, float beta1, float beta2, float eps, uint32_t* ticket,
+                   void* stream);
+
+/* b2gs_adam_step_dev / b2gs_adam_step_peer with options:
+ *   B2GS_ADAM_ZERO_GRAD  clear each gradient element after reading it (optimizer.zero_grad fused);
+ *   B2GS_ADAM_NO_TICK    use step_counter + 1 and leave the counter alone (the caller ticks it after
+ *                        the update, e.g. b2gs_pose_step(extra_tick)) — saves the 1-thread tick launch. */
+#define B2GS_ADAM_ZERO_GRAD 1
+#define B2GS_ADAM_NO_TICK 2
+B2GS_API int b2gs_adam_step_fused(const B2gsAdamSegment* segments, int32_t num_segments,
+                         int64_t* step_counter, float beta1, float beta2, float eps, int32_t flags,
+                         void* stream);
+B2GS_API int b2gs_adam_step_peer_fused(const B2gsAdamSegment* segments, int32_t num_segments,
+                              int64_t* step_counter, float beta1, float beta2, float eps,
+                              const B2gsPeerArena* peers, int32_t flags, void* stream);
+
 /* RGB-D keyframe back-projection (the seed point cloud of new Gaussians; feeds b2gs_knn3_dist2).
  * Replaces GaussianModel.create_pcd_from_image_and_depth's host round trip through open3d 0.17
  * (GS/scene/gaussian_model.py:107-156: RGBDImage.create_from_color_and_depth(depth_scale=1,
@@ -277,12 +349,12 @@ B2GS_API int b2gs_backproject_rgbd(int32_t W, int32_t H, const float* image, con
 B2GS_API void b2gs_set_update_guard(const int32_t* device_flag);
 
 /* Debug work counters (measurement only, bench.py roofline): while `device_counters` (8 device
- * uint64, or NULL to clear) is set for the calling host thread, the render kernels launch a counting
+ * uint64, or NULL to clear) is set (process-wide), the render kernels launch a counting
  * instantiation and ADD to it:  [0] forward warp visits (a warp = 64 pixels looking at one splat of
  * its tile's list), [1] forward visits that evaluate exp + blend, [2] forward contributing
  * pixel-splat pairs (alpha >= 1/255, not terminated: the pairs CR/forward.cu:359-371 blends),
  * [4] backward warp visits, [5] backward visits that run the gradient arithmetic, [6] backward
- * contributing pairs (CR/backward.cu:700-757). */
+ * contributing pairs (CR/backward.cu:700-757), [7] kNN search: point-to-point distance evaluations. */
 B2GS_API void b2gs_debug_set_counters(uint64_t* device_counters);
 
 /* ---- fused per-pixel losses (utils/slam_utils.py:56-128) ---------------------------------
@@ -304,6 +376,17 @@ typedef struct B2gsLossArgs {
   const float* exposure_b;        /* [1] or NULL */
   const float* grad_mask;         /* [N] or NULL: viewpoint.grad_mask (tracking modes) */
 } B2gsLossArgs;
+/* The same loss fused into the forward render (B2gsForwardOut.fused_loss), upstream gradient 1:
+ * args.image / depth / opacity are ignored (the kernel uses the pixel it has just blended).
+ * Writes dL/dimage, dL/ddepth for the backward and, per 16x16 tile, the four partial sums
+ * (sum |rgb term|, sum |depth term|, dL/d exposure_a / exp(a), dL/d exposure_b) that
+ * b2gs_window_finalize turns into the loss value and the exposure gradients. */
+typedef struct B2gsFusedLoss {
+  B2gsLossArgs args;
+  float* dL_dimage;   /* [3,N] */
+  float* dL_ddepth;   /* [N] */
+  float* partials;    /* [tiles,4] */
+} B2gsFusedLoss;
 B2GS_API size_t b2gs_loss_scratch_bytes(int32_t N);
 B2GS_API int b2gs_loss_forward(const B2gsLossArgs* args, float* loss, void* scratch,
                       size_t scratch_bytes, void* stream);

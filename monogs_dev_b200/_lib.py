@@ -37,6 +37,7 @@ class B2gsForwardOut(C.Structure):
     _fields_ = [
         ("color", C.c_void_p), ("depth", C.c_void_p), ("opacity", C.c_void_p),
         ("radii", C.c_void_p), ("n_touched", C.c_void_p), ("status", C.c_void_p),
+        ("fused_loss", C.c_void_p), ("bwd_scratch", C.c_void_p), ("bwd_scratch_bytes", C.c_size_t),
     ]
 
 
@@ -49,6 +50,7 @@ class B2gsBackwardIO(C.Structure):
         ("scratch", C.c_void_p), ("scratch_bytes", C.c_size_t),
         ("accumulate", C.c_int32), ("dL_dsh_rest", C.c_void_p), ("densify_grad_accum", C.c_void_p),
         ("densify_denom", C.c_void_p), ("max_radii2D", C.c_void_p),
+        ("scratch_zeroed", C.c_int32), ("defer_tau", C.c_int32), ("iso_reg_weight", C.c_float),
     ]
 
 
@@ -61,11 +63,35 @@ class B2gsLossArgs(C.Structure):
     ]
 
 
+class B2gsFusedLoss(C.Structure):
+    _fields_ = [("args", B2gsLossArgs), ("dL_dimage", C.c_void_p), ("dL_ddepth", C.c_void_p),
+                ("partials", C.c_void_p)]
+
+
 class B2gsAdamSegment(C.Structure):
     _fields_ = [
         ("param", C.c_void_p), ("grad", C.c_void_p), ("exp_avg", C.c_void_p),
         ("exp_avg_sq", C.c_void_p), ("n", C.c_int64), ("lr", C.c_float),
         ("lr_dev", C.c_void_p),
+    ]
+
+
+class B2gsViewFinalize(C.Structure):
+    _fields_ = [
+        ("loss_partials", C.c_void_p), ("loss_rows", C.c_int32), ("N", C.c_int32), ("mode", C.c_int32),
+        ("alpha", C.c_float), ("exposure_a", C.c_void_p), ("tau_partials", C.c_void_p), ("tau_rows", C.c_int32),
+        ("reg_scale", C.c_float), ("status", C.c_void_p), ("loss", C.c_void_p), ("dL_dtau", C.c_void_p),
+        ("dL_dexposure", C.c_void_p),
+    ]
+
+
+class B2gsPoseCam(C.Structure):
+    _fields_ = [
+        ("cam_state", C.c_void_p), ("projmatrix_raw", C.c_void_p), ("rot_delta", C.c_void_p),
+        ("trans_delta", C.c_void_p), ("exposure_a", C.c_void_p), ("exposure_b", C.c_void_p),
+        ("dL_dtau", C.c_void_p), ("dL_dexposure", C.c_void_p), ("moments", C.c_void_p),
+        ("lr_rot", C.c_float), ("lr_trans", C.c_float), ("lr_exposure_a", C.c_float),
+        ("lr_exposure_b", C.c_float), ("optimize_pose", C.c_int32), ("optimize_exposure", C.c_int32),
     ]
 
 
@@ -88,6 +114,7 @@ SYMBOLS = {
     "b2gs_image_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
     "b2gs_binning_bytes": (C.c_size_t, [C.c_int64, C.c_int32, C.c_int32]),
     "b2gs_backward_scratch_bytes": (C.c_size_t, [C.c_int32]),
+    "b2gs_backward_tau_partials": (C.c_void_p, [C.c_void_p, C.c_int32, C.POINTER(C.c_int32)]),
     "b2gs_forward_plan": (C.c_int, [C.POINTER(B2gsScene), C.POINTER(B2gsWorkspace),
                                     C.POINTER(B2gsForwardOut), C.c_void_p, C.POINTER(C.c_int64)]),
     "b2gs_forward_render": (C.c_int, [C.POINTER(B2gsScene), C.POINTER(B2gsWorkspace),
@@ -128,6 +155,15 @@ SYMBOLS = {
                                         C.c_void_p, C.c_void_p]),
     "b2gs_adam_step_peer": (C.c_int, [C.POINTER(B2gsAdamSegment), C.c_int32, C.c_void_p, C.c_float,
                                       C.c_float, C.c_float, C.POINTER(B2gsPeerArena), C.c_void_p]),
+    "b2gs_adam_step_fused": (C.c_int, [C.POINTER(B2gsAdamSegment), C.c_int32, C.c_void_p, C.c_float,
+                                       C.c_float, C.c_float, C.c_int32, C.c_void_p]),
+    "b2gs_adam_step_peer_fused": (C.c_int, [C.POINTER(B2gsAdamSegment), C.c_int32, C.c_void_p, C.c_float,
+                                            C.c_float, C.c_float, C.POINTER(B2gsPeerArena), C.c_int32,
+                                            C.c_void_p]),
+    "b2gs_window_finalize": (C.c_int, [C.POINTER(B2gsViewFinalize), C.c_int32, C.c_void_p, C.c_void_p,
+                                       C.c_void_p, C.c_void_p]),
+    "b2gs_pose_step": (C.c_int, [C.POINTER(B2gsPoseCam), C.c_int32, C.c_void_p, C.c_void_p, C.c_float,
+                                 C.c_float, C.c_float, C.c_void_p, C.c_void_p]),
 }
 
 

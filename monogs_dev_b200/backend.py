@@ -182,7 +182,7 @@ class BackEnd:
         if self.keyframe_optimizers is not None:
             kw["kf_optimizer"] = self.keyframe_optimizers
         lr = self.config["Training"]["lr"]
-        win = MappingWindow(self.gaussians, kfs, self.background,
+        win = MappingWindow(self.gaussians, kfs, self.background, lean=False,
                             pose_lr=(lr["cam_rot_delta"] * 0.5, lr["cam_trans_delta"] * 0.5, 0.01, 0.01),
                             group=self._group, render_fn=self._render_fn, adam_cls=self._adam, loss_fn=self._loss_fn,
                             cuda_graph=self._graph, densify_stats=stats, view_streams=self._streams,
@@ -277,7 +277,7 @@ class BackEnd:
         kf["optimize_pose"] = kf["optimize_exposure"] = False
         from . import mapping
         loss = self._loss_fn or mapping.get_loss_mapping_rgbd
-        return MappingWindow(self.gaussians, [kf], self.background, optimize_pose=False, group=self._group,
+        return MappingWindow(self.gaussians, [kf], self.background, optimize_pose=False, group=self._group, lean=False,
                              render_fn=self._render_fn, adam_cls=self._adam,
                              loss_fn=functools.partial(loss, initialization=True),
                              cuda_graph=False, densify_stats=True, regulariser=False)

@@ -40,8 +40,9 @@ __device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, 
 __global__ void __launch_bounds__(256)
 adam_kernel(const __grid_constant__ AdamTable t, float w1, float beta2, float w2, float bc2_sqrt,
             float eps, float beta1, const long long* __restrict__ step_dev,
-            const int32_t* __restrict__ guard) {
+            const int32_t* __restrict__ guard, int flags) {
   if (guard && *guard) return;   // the step is being discarded (b2gs_set_update_guard)
+  const bool zero = flags & B2GS_ADAM_ZERO_GRAD;
   // which segment does this block's chunk belong to?
   int s = 0;
   const long long chunk = blockIdx.x;
@@ -52,14 +53,14 @@ adam_kernel(const __grid_constant__ AdamTable t, float w1, float beta2, float w2
   long long end = begin + ADAM_CHUNK;
   if (end > n) end = n;
   float* __restrict__ p = t.p[s];
-  const float* __restrict__ g = t.g[s];
+  float* __restrict__ g = const_cast<float*>(t.g[s]);
   float* __restrict__ m = t.m[s];
   float* __restrict__ v = t.v[s];
   float neg_step = t.neg_step_size[s];
   if (step_dev != nullptr) {
     // CUDA-graph capturable form: the step count lives on the device (incremented by
     // adam_tick_kernel just before); same double-precision scalar prep as the host path
-    const double step = (double)*step_dev;
+    const double step = (double)(*step_dev + ((flags & B2GS_ADAM_NO_TICK) ? 1 : 0));
     const double bc1 = 1.0 - pow((double)beta1, step);
     bc2_sqrt = (float)sqrt(1.0 - pow((double)beta2, step));
     const float lr = t.lr_dev[s] ? t.lr_dev[s][0] : t.lr[s];
@@ -81,17 +82,20 @@ adam_kernel(const __grid_constant__ AdamTable t, float w1, float beta2, float w2
       *reinterpret_cast<float4*>(p + i) = pp;
       *reinterpret_cast<float4*>(m + i) = mm;
       *reinterpret_cast<float4*>(v + i) = vv;
+      if (zero) *reinterpret_cast<float4*>(g + i) = make_float4(0.f, 0.f, 0.f, 0.f);
     }
     for (long long i = end4 + threadIdx.x; i < end; i += blockDim.x) {
       float pp = p[i], mm = m[i], vv = v[i];
       adam_one(pp, g[i], mm, vv, w1, beta2, w2, bc2_sqrt, eps, neg_step);
       p[i] = pp; m[i] = mm; v[i] = vv;
+      if (zero) g[i] = 0.f;
     }
   } else {
     for (long long i = begin + threadIdx.x; i < end; i += blockDim.x) {
       float pp = p[i], mm = m[i], vv = v[i];
       adam_one(pp, g[i], mm, vv, w1, beta2, w2, bc2_sqrt, eps, neg_step);
       p[i] = pp; m[i] = mm; v[i] = vv;
+      if (zero) g[i] = 0.f;
     }
   }
 }
@@ -162,7 +166,7 @@ constexpr int PEER_CHUNK = 1024;   // floats per ownership chunk = one float4 pe
 __global__ void __launch_bounds__(256)
 adam_peer_kernel(const __grid_constant__ AdamTable t, const __grid_constant__ PeerTable pt, float w1,
                  float beta2, float w2, float eps, float beta1, const long long* __restrict__ step_dev,
-                 const int32_t* __restrict__ guard, const uint32_t* __restrict__ fail) {
+                 const int32_t* __restrict__ guard, const uint32_t* __restrict__ fail, int flags) {
   if (guard && *guard) return;   // some rank overflowed: every rank discards this step
   if (*fail) return;             // a barrier timed out: peers' arenas may not be final
   const long long chunk = (long long)blockIdx.x * pt.world + pt.rank;   // chunks this rank owns
@@ -177,7 +181,7 @@ adam_peer_kernel(const __grid_constant__ AdamTable t, const __grid_constant__ Pe
   float* __restrict__ m = t.m[s];
   float* __restrict__ v = t.v[s];
   const long long poff = t.p[s] - pt.param[pt.rank], goff = t.g[s] - pt.grad[pt.rank];
-  const double step = (double)*step_dev;
+  const double step = (double)(*step_dev + ((flags & B2GS_ADAM_NO_TICK) ? 1 : 0));
   const double bc1 = 1.0 - pow((double)beta1, step);
   const float bc2_sqrt = (float)sqrt(1.0 - pow((double)beta2, step));
   const float lr = t.lr_dev[s] ? t.lr_dev[s][0] : t.lr[s];
@@ -232,14 +236,14 @@ adam_peer_kernel(const __grid_constant__ AdamTable t, const __grid_constant__ Pe
 using namespace b2gs;
 
 static int adam_impl(const B2gsAdamSegment* segments, int32_t num_segments, int64_t step,
-                     long long* step_dev, float beta1, float beta2, float eps, void* stream) {
+                     long long* step_dev, float beta1, float beta2, float eps, void* stream, int flags = 0) {
   if (num_segments < 0 || (num_segments > 0 && !segments)) {
     set_error("b2gs_adam_step: bad segments");
     return B2GS_ERR_INVALID;
   }
   if (step < 1) { set_error("b2gs_adam_step: step must be >= 1"); return B2GS_ERR_INVALID; }
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  if (step_dev) {
+  if (step_dev && !(flags & B2GS_ADAM_NO_TICK)) {
     adam_tick_kernel<<<1, 1, 0, st>>>(step_dev, update_guard());
     B2GS_LAUNCH_CHECK(st, 0);
   }
@@ -274,9 +278,11 @@ static int adam_impl(const B2gsAdamSegment* segments, int32_t num_segments, int6
     if (chunks > 0) {
       if (chunks > 0x7fffffffLL) { set_error("b2gs_adam_step: too many elements"); return B2GS_ERR_INVALID; }
       // the camera / exposure optimizer is a handful of floats: latency, not bandwidth — its own name
-      B2GS_PROF(chunks * ADAM_CHUNK < 65536 ? "adam_small" : "adam", st);
+      long long total = 0;
+      for (int q = 0; q < k; ++q) total += t.n[q];
+      B2GS_PROF(total < 65536 ? "adam_small" : "adam", st);
       adam_kernel<<<(unsigned)chunks, 256, 0, st>>>(t, w1, beta2, w2, bc2_sqrt, eps, beta1, step_dev,
-                                                        update_guard());
+                                                        update_guard(), flags);
       B2GS_LAUNCH_CHECK(st, 0);
     }
     done += k;
@@ -297,9 +303,23 @@ extern "C" int b2gs_adam_step_dev(const B2gsAdamSegment* segments, int32_t num_s
                    beta2, eps, stream);
 }
 
+extern "C" int b2gs_adam_step_fused(const B2gsAdamSegment* segments, int32_t num_segments,
+                                    int64_t* step_counter, float beta1, float beta2, float eps,
+                                    int32_t flags, void* stream) {
+  if (!step_counter) { set_error("b2gs_adam_step_fused: NULL step counter"); return B2GS_ERR_INVALID; }
+  return adam_impl(segments, num_segments, 1, reinterpret_cast<long long*>(step_counter), beta1, beta2,
+                   eps, stream, flags);
+}
+
 extern "C" int b2gs_adam_step_peer(const B2gsAdamSegment* segments, int32_t num_segments,
                                    int64_t* step_counter, float beta1, float beta2, float eps,
                                    const B2gsPeerArena* peers, void* stream) {
+  return b2gs_adam_step_peer_fused(segments, num_segments, step_counter, beta1, beta2, eps, peers, 0, stream);
+}
+
+extern "C" int b2gs_adam_step_peer_fused(const B2gsAdamSegment* segments, int32_t num_segments,
+                                         int64_t* step_counter, float beta1, float beta2, float eps,
+                                         const B2gsPeerArena* peers, int32_t flags, void* stream) {
   if (!step_counter || !peers) { set_error("b2gs_adam_step_peer: NULL step counter / peers"); return B2GS_ERR_INVALID; }
   if (peers->world < 1 || peers->world > PEER_MAX || peers->rank < 0 || peers->rank >= peers->world ||
       !peers->param_base || !peers->grad_base || !peers->signal || !peers->fail_flag) {
@@ -345,8 +365,10 @@ extern "C" int b2gs_adam_step_peer(const B2gsAdamSegment* segments, int32_t num_
   // ... and only now may the step counter advance: with the rank-local guard value a rank whose own
   // forward did not overflow would tick while an overflowed rank does not, and the replicas' bias
   // corrections would diverge for good
-  adam_tick_kernel<<<1, 1, 0, st>>>(reinterpret_cast<long long*>(step_counter), guard);
-  B2GS_LAUNCH_CHECK(st, 0);
+  if (!(flags & B2GS_ADAM_NO_TICK)) {
+    adam_tick_kernel<<<1, 1, 0, st>>>(reinterpret_cast<long long*>(step_counter), guard);
+    B2GS_LAUNCH_CHECK(st, 0);
+  }
   if (chunks > 0) {
     const long long blocks = (chunks + pt.world - 1) / pt.world;
     if (blocks > 0x7fffffffLL) { set_error("b2gs_adam_step_peer: too many elements"); return B2GS_ERR_INVALID; }
@@ -354,7 +376,7 @@ extern "C" int b2gs_adam_step_peer(const B2gsAdamSegment* segments, int32_t num_
     adam_peer_kernel<<<(unsigned)blocks, 256, 0, st>>>(t, pt, (float)(1.0 - (double)beta1), beta2,
                                                       (float)(1.0 - (double)beta2), eps, beta1,
                                                       reinterpret_cast<const long long*>(step_counter), guard,
-                                                      peers->fail_flag);
+                                                      peers->fail_flag, flags);
     B2GS_LAUNCH_CHECK(st, 0);
   }
   // ... and every replica / gradient arena has been written by all of its chunk owners

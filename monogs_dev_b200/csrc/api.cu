@@ -18,8 +18,9 @@ static std::atomic<unsigned long long> g_launches{0};
 
 static thread_local const int32_t* g_guard = nullptr;
 const int32_t* update_guard() { return g_guard; }
-static thread_local unsigned long long* g_counters = nullptr;
-unsigned long long* debug_counters() { return g_counters; }
+// process-wide, not thread-local: the backward runs on autograd's device thread
+static std::atomic<unsigned long long*> g_counters{nullptr};
+unsigned long long* debug_counters() { return g_counters.load(std::memory_order_relaxed); }
 
 void note_launches(int n) { g_launches.fetch_add((unsigned long long)n, std::memory_order_relaxed); }
 
@@ -112,7 +113,7 @@ extern "C" int b2gs_version(void) { return 100; }
 extern "C" const char* b2gs_last_error(void) { return g_err; }
 extern "C" void b2gs_set_update_guard(const int32_t* device_flag) { b2gs::g_guard = device_flag; }
 extern "C" void b2gs_debug_set_counters(uint64_t* device_counters) {
-  b2gs::g_counters = reinterpret_cast<unsigned long long*>(device_counters);
+  b2gs::g_counters.store(reinterpret_cast<unsigned long long*>(device_counters), std::memory_order_relaxed);
 }
 
 extern "C" uint64_t b2gs_kernel_launches(void) { return g_launches.load(std::memory_order_relaxed); }
@@ -170,6 +171,10 @@ extern "C" size_t b2gs_backward_scratch_bytes(int32_t P) {
   const size_t blocks = ((size_t)(P > 0 ? P : 1) + 127) / 128;
   return align_up(((size_t)(P > 0 ? P : 1) * ACC_STRIDE + blocks * 8) * sizeof(float), 256);
 }
+extern "C" const float* b2gs_backward_tau_partials(const void* scratch, int32_t P, int32_t* blocks) {
+  if (blocks) *blocks = (int32_t)(((size_t)(P > 0 ? P : 1) + 127) / 128);
+  return reinterpret_cast<const float*>(scratch) + (size_t)(P > 0 ? P : 0) * ACC_STRIDE;
+}
 
 // shared front half: preprocess (+ per-tile instance counts) and the tile scan
 static int forward_front(const B2gsScene& s, const B2gsWorkspace* ws, const B2gsForwardOut* out,
@@ -190,9 +195,17 @@ static int forward_front(const B2gsScene& s, const B2gsWorkspace* ws, const B2gs
   }
   const size_t tiles = (size_t)((s.W + TILE - 1) / TILE) * ((s.H + TILE - 1) / TILE);
   B2GS_CUDA(cudaMemsetAsync(im.cursor, 0, sizeof(uint32_t) * tiles * CURSOR_STRIDE, st));
-  int rc = launch_preprocess_fwd(s, g, im, out->radii, out->n_touched, st);
+  float* acc_zero = nullptr;
+  if (out->bwd_scratch) {
+    if (out->bwd_scratch_bytes < b2gs_backward_scratch_bytes(s.P)) {
+      set_error("bwd_scratch too small: %zu < %zu", out->bwd_scratch_bytes, b2gs_backward_scratch_bytes(s.P));
+      return B2GS_ERR_WORKSPACE;
+    }
+    acc_zero = reinterpret_cast<float*>(out->bwd_scratch);
+  }
+  int rc = launch_preprocess_fwd(s, g, im, out->radii, out->n_touched, acc_zero, st);
   if (rc) return rc;
-  rc = launch_tile_scan(s, im, cap, st);
+  rc = launch_tile_scan(s, im, cap, cap >= 0 ? out->status : nullptr, st);
   if (rc) return rc;
   *g_out = g;
   *im_out = im;
@@ -237,6 +250,14 @@ extern "C" int b2gs_forward_plan(const B2gsScene* scene, const B2gsWorkspace* ws
 static int forward_back(const B2gsScene& s, const B2gsWorkspace* ws, const B2gsForwardOut* out,
                         const GeomWS& g, const ImageWS& im, int64_t cap, cudaStream_t st) {
   if (!out->color || !out->depth || !out->opacity) { set_error("image outputs must be non-NULL"); return B2GS_ERR_INVALID; }
+  if (out->fused_loss) {
+    const B2gsFusedLoss& f = *out->fused_loss;
+    if (f.args.N != s.W * s.H || f.args.mode < 0 || f.args.mode > 3 || !f.args.gt_image || !f.dL_dimage ||
+        !f.dL_ddepth || !f.partials || (!(f.args.mode & 2) && !f.args.gt_depth)) {
+      set_error("fused_loss: N must be W*H, mode 0..3, gt / gradient / partial pointers non-NULL");
+      return B2GS_ERR_INVALID;
+    }
+  }
   BinWS b = carve_bin(ws->binning, cap, nullptr);
   int rc = launch_binning(s, g, im, b, cap, st);
   if (rc) return rc;
@@ -298,11 +319,9 @@ extern "C" int b2gs_forward(const B2gsScene* scene, const B2gsWorkspace* ws,
     rc = forward_front(s, ws, out, cap, st, &g, &im);
     if (rc) return rc;
   }
-  rc = forward_back(s, ws, out, g, im, cap, st);
-  if (rc) return rc;
-  if (out->status)
-    B2GS_CUDA(cudaMemcpyAsync(out->status, im.status, 2 * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
-  return B2GS_OK;
+  if (s.P == 0 && out->status)   // (otherwise the tile scan has written it)
+    B2GS_CUDA(cudaMemsetAsync(out->status, 0, 2 * sizeof(uint32_t), st));
+  return forward_back(s, ws, out, g, im, cap, st);
 }
 
 extern "C" int b2gs_backward(const B2gsScene* scene, const B2gsWorkspace* ws, int64_t R,
@@ -312,9 +331,14 @@ extern "C" int b2gs_backward(const B2gsScene* scene, const B2gsWorkspace* ws, in
   if (!ws || !io) { set_error("NULL ws/io"); return B2GS_ERR_INVALID; }
   const B2gsScene& s = *scene;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  if (!io->dL_dtau) { set_error("dL_dtau must be non-NULL"); return B2GS_ERR_INVALID; }
+  if (!io->dL_dtau && !io->defer_tau) { set_error("dL_dtau must be non-NULL"); return B2GS_ERR_INVALID; }
+  if (io->iso_reg_weight != 0.f && !(s.raw_params && io->accumulate && io->dL_dscales)) {
+    set_error("iso_reg_weight needs raw_params, accumulate and dL_dscales");
+    return B2GS_ERR_INVALID;
+  }
   if (s.P == 0) {
-    B2GS_CUDA(cudaMemsetAsync(io->dL_dtau, 0, 6 * sizeof(float), st));
+    if (io->dL_dtau) B2GS_CUDA(cudaMemsetAsync(io->dL_dtau, 0, 6 * sizeof(float), st));
+    if (io->defer_tau && io->scratch) B2GS_CUDA(cudaMemsetAsync(io->scratch, 0, io->scratch_bytes, st));
     return B2GS_OK;
   }
   if (!io->dL_dcolor || !io->dL_ddepth || !io->radii || !io->dL_dmeans3D || !io->dL_dopacity) {
@@ -334,7 +358,8 @@ extern "C" int b2gs_backward(const B2gsScene* scene, const B2gsWorkspace* ws, in
   ImageWS im = carve_image(ws->image, s.W, s.H, nullptr);
   BinWS b = carve_bin(ws->binning, R, nullptr);
   float* acc = reinterpret_cast<float*>(io->scratch);
-  B2GS_CUDA(cudaMemsetAsync(acc, 0, (size_t)s.P * ACC_STRIDE * sizeof(float), st));
+  if (!io->scratch_zeroed)
+    B2GS_CUDA(cudaMemsetAsync(acc, 0, (size_t)s.P * ACC_STRIDE * sizeof(float), st));
   if (R > 0) {
     rc = launch_render_bwd(s, g, im, b, *io, acc, st);
     if (rc) return rc;

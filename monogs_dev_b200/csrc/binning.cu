@@ -69,7 +69,8 @@ constexpr int SCAN_THREADS = 1024;
 
 __global__ void __launch_bounds__(SCAN_THREADS)
 tile_scan_kernel(uint32_t tiles, long long cap, uint32_t* __restrict__ cursor,
-                 uint2* __restrict__ ranges, uint32_t* __restrict__ status) {
+                 uint2* __restrict__ ranges, uint32_t* __restrict__ status,
+                 uint32_t* __restrict__ status_out) {
   __shared__ uint32_t s_total;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const uint32_t per = (tiles + SCAN_THREADS - 1) / SCAN_THREADS;
@@ -111,6 +112,10 @@ tile_scan_kernel(uint32_t tiles, long long cap, uint32_t* __restrict__ cursor,
       const bool over = wi >= (1ull << 31) || (cap >= 0 && wi > (unsigned long long)cap);
       status[0] = (uint32_t)min(wi, 0xffffffffull);
       status[1] = over ? 1u : 0u;
+      if (status_out) {
+        status_out[0] = (uint32_t)min(wi, 0xffffffffull);
+        status_out[1] = over ? 1u : 0u;
+      }
       s_total = over ? 0xffffffffu : 0u;
     }
   }
@@ -138,11 +143,12 @@ tile_scan_kernel(uint32_t tiles, long long cap, uint32_t* __restrict__ cursor,
   }
 }
 
-int launch_tile_scan(const B2gsScene& s, const ImageWS& im, int64_t cap, cudaStream_t st) {
+int launch_tile_scan(const B2gsScene& s, const ImageWS& im, int64_t cap, uint32_t* status_out,
+                     cudaStream_t st) {
   const int gx = (s.W + TILE - 1) / TILE, gy = (s.H + TILE - 1) / TILE;
   B2GS_PROF("tile_scan", st);
   tile_scan_kernel<<<1, SCAN_THREADS, 0, st>>>((uint32_t)(gx * gy), (long long)cap, im.cursor,
-                                               im.ranges, im.status);
+                                               im.ranges, im.status, status_out);
   B2GS_LAUNCH_CHECK(st, s.debug);
   return B2GS_OK;
 }

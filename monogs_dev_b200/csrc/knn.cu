@@ -219,8 +219,10 @@ struct LeafVisitor {
   int lane;
   float px, py, pz;
   float best[3];
+  unsigned visits;   // leaves scanned by this warp (debug work counter)
 
   __device__ __forceinline__ void leaf(int b0, int count, bool own) {
+    visits += (unsigned)count;
     __syncwarp();
     s_c[lane] = pts[(size_t)b0 * 32 + lane];
     __syncwarp();
@@ -235,7 +237,7 @@ struct LeafVisitor {
 __global__ void __launch_bounds__(256)
 knn_search_kernel(int P, int n0, int n1, int n2, const float4* __restrict__ pts,
                   const Box* __restrict__ l0, const Box* __restrict__ l1, const Box* __restrict__ l2,
-                  float* __restrict__ out) {
+                  float* __restrict__ out, unsigned long long* __restrict__ counters) {
   __shared__ float4 s_stage[8][32];
   const int warp_in_block = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int my0 = blockIdx.x * 8 + warp_in_block;  // leaf owned by this warp
@@ -249,6 +251,7 @@ knn_search_kernel(int P, int n0, int n1, int n2, const float4* __restrict__ pts,
   v.pts = pts; v.s_c = s_stage[warp_in_block]; v.lane = lane;
   v.px = me.x; v.py = me.y; v.pz = me.z;
   v.best[0] = v.best[1] = v.best[2] = FLT_MAX;
+  v.visits = 0;
   // padding lanes must never keep a box alive
   const float NEVER = -1.f;
 
@@ -284,6 +287,8 @@ knn_search_kernel(int P, int n0, int n1, int n2, const float4* __restrict__ pts,
     visit_l2(b2, -1);
   }
   if (valid) out[__float_as_uint(me.w)] = (v.best[0] + v.best[1] + v.best[2]) / 3.0f;
+  // every lane evaluates one distance per candidate point of a visited leaf
+  if (counters && lane == 0) atomicAdd(&counters[7], 32ull * v.visits);
 }
 
 }  // namespace b2gs
@@ -321,7 +326,8 @@ extern "C" int b2gs_knn3_dist2(const float* points, int32_t P, float* out, void*
   knn_parent_kernel<<<(k.n1 * 32 + 255) / 256, 256, 0, st>>>(k.n0, k.l0, k.l1);
   knn_parent_kernel<<<(k.n2 * 32 + 255) / 256, 256, 0, st>>>(k.n1, k.l1, k.l2);
   B2GS_PROF("knn_search", st);
-  knn_search_kernel<<<(k.n0 + 7) / 8, 256, 0, st>>>(P, k.n0, k.n1, k.n2, k.pts, k.l0, k.l1, k.l2, out);
+  knn_search_kernel<<<(k.n0 + 7) / 8, 256, 0, st>>>(P, k.n0, k.n1, k.n2, k.pts, k.l0, k.l1, k.l2, out,
+                                                    debug_counters());
   B2GS_LAUNCH_CHECK(st, 0);
   note_launches(3);
   return B2GS_OK;

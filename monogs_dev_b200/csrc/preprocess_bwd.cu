@@ -10,6 +10,13 @@
 // memset of the outputs), and reduces the pose gradient dL_dtau in-kernel:
 // warp shuffle -> shared -> one partial row per block -> a fixed-order final sum
 // (deterministic given the accumulator).
+//
+// Provenance note: the closed-form derivative chains in here RESTATE the reference's formulas —
+// the conic / cov2D -> cov3D -> T -> J -> t chain follows CR/backward.cu:204-271 term by term
+// (same intermediate names, so the two can be read side by side) and the SH gradient block
+// follows CR/backward.cu:59-128.  Everything around them is new: the fusion of three reference
+// kernels, the packed accumulator row, the cross-product form of the pose Jacobian, the fused
+// activations, the in-kernel tau reduction, the accumulate / statistics / regulariser sinks.
 #include "common.cuh"
 #include "gsmath.cuh"
 
@@ -136,9 +143,9 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
                       const float* __restrict__ shs_rest, const float* __restrict__ opacities,
                       int accumulate, float* __restrict__ dL_dsh_rest,
                       float* __restrict__ st_grad_accum, float* __restrict__ st_denom,
-                      float* __restrict__ st_max_radii) {
+                      float* __restrict__ st_max_radii, float iso_w) {
   __shared__ float s_view[16], s_proj[16];
-  __shared__ float s_tau[4][6];
+  __shared__ float s_tau[4][7];
   if (threadIdx.x < 16) s_view[threadIdx.x] = viewmatrix[threadIdx.x];
   else if (threadIdx.x < 32) s_proj[threadIdx.x - 16] = projmatrix[threadIdx.x - 16];
   __syncthreads();
@@ -452,17 +459,33 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
     if (st_max_radii) atomicMax(reinterpret_cast<int*>(st_max_radii) + idx, __float_as_int((float)radii[idx]));
   }
 
-  // ---- dL_dtau: warp -> block -> one partial row per block ----
+  // ---- isotropic-scale regulariser (utils/slam_backend.py:229-231), every Gaussian, visible or
+  // not: value partial + gradient wrt the raw log-scales added to the gradient arena ----
+  float reg = 0.f;
+  if (RAW && iso_w != 0.f && idx < P) {
+    const float s0 = expf(scales[3 * idx]), s1 = expf(scales[3 * idx + 1]), s2 = expf(scales[3 * idx + 2]);
+    const float m = (s0 + s1 + s2) / 3.0f;
+    const float d0 = s0 - m, d1 = s1 - m, d2 = s2 - m;
+    reg = fabsf(d0) + fabsf(d1) + fabsf(d2);
+    const float g0 = (float)(d0 > 0.f) - (float)(d0 < 0.f), g1 = (float)(d1 > 0.f) - (float)(d1 < 0.f),
+                g2 = (float)(d2 > 0.f) - (float)(d2 < 0.f);
+    const float gm = (g0 + g1 + g2) / 3.0f;          // through the mean
+    atomicAdd(&dL_dscales[3 * idx], iso_w * (g0 - gm) * s0);   // d exp(x) = exp(x) dx
+    atomicAdd(&dL_dscales[3 * idx + 1], iso_w * (g1 - gm) * s1);
+    atomicAdd(&dL_dscales[3 * idx + 2], iso_w * (g2 - gm) * s2);
+  }
+
+  // ---- dL_dtau (+ the regulariser partial): warp -> block -> one partial row per block ----
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
-  for (int k = 0; k < 6; ++k) {
-    float v = tau[k];
+  for (int k = 0; k < 7; ++k) {
+    float v = k < 6 ? tau[k] : reg;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
     if (lane == 0) s_tau[warp][k] = v;
   }
   __syncthreads();
-  if (threadIdx.x < 6) {
+  if (threadIdx.x < 7) {
     float v = 0.f;
 #pragma unroll
     for (int w = 0; w < 4; ++w) v += s_tau[w][threadIdx.x];
@@ -510,10 +533,13 @@ int launch_preprocess_bwd(const B2gsScene& s, const GeomWS& g, const B2gsBackwar
       s.tan_fovx, s.tan_fovy, acc, io.dL_dmeans3D, io.dL_dmeans2D, io.dL_dopacity, io.dL_dcolors,
       s.shs ? io.dL_dsh : nullptr, io.dL_dscales, io.dL_drotations, io.dL_dcov3D, partials,
       s.shs_rest, s.opacities, io.accumulate, io.dL_dsh_rest, io.densify_grad_accum,
-      io.densify_denom, io.max_radii2D);
+      io.densify_denom, io.max_radii2D,
+      io.iso_reg_weight != 0.f ? io.iso_reg_weight / (3.0f * (float)s.P) : 0.f);
   B2GS_LAUNCH_CHECK(st, s.debug);
-  tau_finalize_kernel<<<1, 256, 0, st>>>(blocks, partials, io.dL_dtau);
-  B2GS_LAUNCH_CHECK(st, s.debug);
+  if (io.dL_dtau) {   // defer_tau callers hand the partial rows to b2gs_window_finalize instead
+    tau_finalize_kernel<<<1, 256, 0, st>>>(blocks, partials, io.dL_dtau);
+    B2GS_LAUNCH_CHECK(st, s.debug);
+  }
   return B2GS_OK;
 }
 

@@ -67,7 +67,8 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
                       int H, float tan_fovx, float tan_fovy, float focal_x, float focal_y, int gx,
                       int gy, int prefiltered,
                       const float* __restrict__ shs_rest, int32_t* __restrict__ radii,
-                      int32_t* __restrict__ n_touched, uint32_t* __restrict__ tile_count, GeomWS g) {
+                      int32_t* __restrict__ n_touched, uint32_t* __restrict__ tile_count, GeomWS g,
+                      float* __restrict__ acc_zero) {
   __shared__ float s_view[16], s_proj[16];
   __shared__ WarpRects s_rects[8];
   if (threadIdx.x < 16) s_view[threadIdx.x] = viewmatrix[threadIdx.x];
@@ -168,6 +169,11 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
     g.rect[idx] = make_ushort4((unsigned short)x0, (unsigned short)y0, (unsigned short)x1,
                                (unsigned short)y1);
     g.clamped[idx] = clamp_bits;
+    if (acc_zero) {   // the render backward accumulates into this row; culled rows are never read
+      float4* row = reinterpret_cast<float4*>(acc_zero + (size_t)idx * ACC_STRIDE);
+      const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+      row[0] = z; row[1] = z; row[2] = z;
+    }
   }
 
   // instances per tile: the T counters become the tile ranges (binning.cu) — replaces the
@@ -191,7 +197,7 @@ __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D,
 }
 
 int launch_preprocess_fwd(const B2gsScene& s, const GeomWS& g, const ImageWS& im, int32_t* radii,
-                          int32_t* n_touched, cudaStream_t st) {
+                          int32_t* n_touched, float* acc_zero, cudaStream_t st) {
   // focal lengths exactly as the reference derives them (CR/rasterizer_impl.cu:225-226)
   const float focal_y = s.H / (2.0f * s.tan_fovy);
   const float focal_x = s.W / (2.0f * s.tan_fovx);
@@ -203,7 +209,7 @@ int launch_preprocess_fwd(const B2gsScene& s, const GeomWS& g, const ImageWS& im
       s.P, s.D, s.M, s.means3D, s.scales, s.scale_modifier, s.rotations, s.opacities, s.shs,
       s.cov3D_precomp, s.colors_precomp, s.viewmatrix, s.projmatrix, s.campos, s.W, s.H,
       s.tan_fovx, s.tan_fovy, focal_x, focal_y, gx, gy, s.prefiltered, s.shs_rest, radii,
-      n_touched, im.cursor, g);
+      n_touched, im.cursor, g, acc_zero);
   B2GS_LAUNCH_CHECK(st, s.debug);
   return B2GS_OK;
 }

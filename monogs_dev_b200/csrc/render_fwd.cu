@@ -16,6 +16,8 @@
 //    atomic per (tile, splat) instead of one per (pixel, splat).
 #include "common.cuh"
 #include "cull.cuh"
+#include "loss_terms.cuh"
+#include <string.h>
 
 namespace b2gs {
 
@@ -33,7 +35,10 @@ __device__ __forceinline__ f2 fma2(f2 a, f2 b, f2 c) { return __ffma2_rn(a, b, c
 
 // COUNT: debug instantiation that also counts the work it executes (b2gs_debug_set_counters):
 // [0] warp visits, [1] warp visits that evaluate exp / blend, [2] contributing pixel-splat pairs
-template <bool COUNT>
+// LOSS: the view's mapping / tracking loss and its gradient wrt the pixel are formed in the epilogue
+// from the blended values still in registers (B2gsFusedLoss); per-tile partial sums go to
+// fl.partials for b2gs_window_finalize.
+template <bool COUNT, bool LOSS>
 __global__ void __launch_bounds__(RF_THREADS)
 render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W,
                   int H, int gx, const float2* __restrict__ xy, const float4* __restrict__ conic_o,
@@ -41,7 +46,7 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
                   float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
                   float* __restrict__ out_color, float* __restrict__ out_depth,
                   float* __restrict__ out_opacity, int* __restrict__ n_touched,
-                  unsigned long long* __restrict__ counters) {
+                  unsigned long long* __restrict__ counters, const __grid_constant__ B2gsFusedLoss fl) {
   __shared__ SplatRec s_rec[RF_BATCH];
   unsigned c_visit = 0, c_full = 0, c_contrib = 0;
   __shared__ int s_cnt[RF_BATCH];
@@ -186,6 +191,43 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     out_depth[pixB] = D.y;
     out_opacity[pixB] = 1 - T.y;
   }
+  if (LOSS) {
+    // loss + its gradient for this tile's pixels (loss_terms.cuh), upstream gradient 1
+    __shared__ float s_loss[RF_THREADS / 32][4];
+    float ea, eb;
+    exposure(fl.args, ea, eb);
+    const bool mono = fl.args.mode & 2;
+    const float w_rgb = (mono ? 1.f : fl.args.alpha) / (3.0f * (float)fl.args.N);
+    const float w_dep = mono ? 0.f : (1.f - fl.args.alpha) / (float)fl.args.N;
+    float red[4] = {0.f, 0.f, 0.f, 0.f};
+    if (insideA) {
+      const PixelLoss r = pixel_loss(fl.args, ea, eb, w_rgb, w_dep, pixA, C0.x + T.x * bg[0], C1.x + T.x * bg[1],
+                                     C2.x + T.x * bg[2], D.x, 1 - T.x);
+      fl.dL_dimage[0 * plane + pixA] = r.g[0]; fl.dL_dimage[1 * plane + pixA] = r.g[1];
+      fl.dL_dimage[2 * plane + pixA] = r.g[2]; fl.dL_ddepth[pixA] = r.gd;
+      red[0] += r.rgb; red[1] += r.dep; red[2] += r.ga; red[3] += r.gb;
+    }
+    if (insideB) {
+      const PixelLoss r = pixel_loss(fl.args, ea, eb, w_rgb, w_dep, pixB, C0.y + T.y * bg[0], C1.y + T.y * bg[1],
+                                     C2.y + T.y * bg[2], D.y, 1 - T.y);
+      fl.dL_dimage[0 * plane + pixB] = r.g[0]; fl.dL_dimage[1 * plane + pixB] = r.g[1];
+      fl.dL_dimage[2 * plane + pixB] = r.g[2]; fl.dL_ddepth[pixB] = r.gd;
+      red[0] += r.rgb; red[1] += r.dep; red[2] += r.ga; red[3] += r.gb;
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+#pragma unroll
+      for (int d = 16; d > 0; d >>= 1) red[k] += __shfl_xor_sync(RF_FULL, red[k], d);
+      if (lane == 0) s_loss[warp][k] = red[k];
+    }
+    __syncthreads();
+    if (tid < 4) {
+      float v = 0.f;
+#pragma unroll
+      for (int w = 0; w < RF_THREADS / 32; ++w) v += s_loss[w][tid];   // fixed order: deterministic
+      fl.partials[4 * (size_t)tile + tid] = v;
+    }
+  }
 }
 
 int launch_render_fwd(const B2gsScene& s, const GeomWS& g, const ImageWS& im, const BinWS& b,
@@ -193,15 +235,19 @@ int launch_render_fwd(const B2gsScene& s, const GeomWS& g, const ImageWS& im, co
   const int gx = (s.W + TILE - 1) / TILE, gy = (s.H + TILE - 1) / TILE;
   B2GS_PROF("render_fwd", st);
   unsigned long long* cnt = debug_counters();
-  if (cnt)
-    render_fwd_kernel<true><<<gx * gy, RF_THREADS, 0, st>>>(im.ranges, b.point_list, s.W, s.H, gx, g.xy,
-                                                            g.conic_o, g.rgbd, s.bg, im.final_T, im.n_contrib,
-                                                            out.color, out.depth, out.opacity, out.n_touched, cnt);
-  else
-    render_fwd_kernel<false><<<gx * gy, RF_THREADS, 0, st>>>(im.ranges, b.point_list, s.W, s.H, gx, g.xy,
-                                                             g.conic_o, g.rgbd, s.bg, im.final_T, im.n_contrib,
-                                                             out.color, out.depth, out.opacity, out.n_touched,
-                                                             nullptr);
+  B2gsFusedLoss fl;
+  memset(&fl, 0, sizeof(fl));
+  if (out.fused_loss) fl = *out.fused_loss;
+#define B2GS_RF_LAUNCH(C_, L_)                                                                        \
+  render_fwd_kernel<C_, L_><<<gx * gy, RF_THREADS, 0, st>>>(                                          \
+      im.ranges, b.point_list, s.W, s.H, gx, g.xy, g.conic_o, g.rgbd, s.bg, im.final_T, im.n_contrib,  \
+      out.color, out.depth, out.opacity, out.n_touched, cnt, fl)
+  if (out.fused_loss) {
+    if (cnt) B2GS_RF_LAUNCH(true, true); else B2GS_RF_LAUNCH(false, true);
+  } else {
+    if (cnt) B2GS_RF_LAUNCH(true, false); else B2GS_RF_LAUNCH(false, false);
+  }
+#undef B2GS_RF_LAUNCH
   B2GS_LAUNCH_CHECK(st, s.debug);
   return B2GS_OK;
 }

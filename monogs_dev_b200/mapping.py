@@ -373,14 +373,28 @@ class MappingWindow:
     def __init__(self, gaussians, keyframes, bg, pose_lr=(0.003, 0.001, 0.01, 0.01),
                  optimize_pose=True, group=None, render_fn=None, adam_cls=FusedAdam,
                  loss_fn=None, cuda_graph=False, densify_stats=True, view_streams=1, peer_adam=False,
-                 kf_optimizer=None, regulariser=True):
+                 kf_optimizer=None, regulariser=True, lean=None):
         """keyframe dict flags (optional): `optimize_pose` (default: every view but the first, as
         viewpoint.uid == 0 is never moved, utils/slam_backend.py:315-316,434-436) and
         `optimize_exposure` (default True; the reference gives keyframe 0 and the two random
         views of an iteration no optimised parameter at all, :196-227,434-471).
         kf_optimizer: an existing optimizer over the camera parameters (BackEnd.keyframe_optimizers
-        outlives a map() call); by default one is built for the local views."""
+        outlives a map() call); by default one is built for the local views.
+        lean: run the step as straight libb2gs calls (window.LeanWindow: loss fused into the render
+        epilogue, one finalize kernel, Adam + zero_grad fused, one camera kernel — no autograd graph,
+        no torch kernel inside a step).  Default: whenever the window is the stock one (packed-arena
+        GaussianModel on the GPU, FusedAdam, default renderer / RGB-D mapping loss, no external
+        keyframe optimizer); lean=False keeps the autograd route over the same kernels."""
         self.g, self.kfs, self.bg = gaussians, keyframes, bg
+        stock = (isinstance(gaussians, GaussianModel) and gaussians.flat.is_cuda and render_fn is None
+                 and loss_fn is None and adam_cls is FusedAdam and kf_optimizer is None
+                 and isinstance(gaussians.optimizer, FusedAdam)
+                 and all(hasattr(kf["cam"], "state") for kf in keyframes))
+        if lean and not stock:
+            raise RuntimeError("lean=True needs the stock window (GaussianModel on CUDA, FusedAdam, default "
+                               "render / loss functions, no external keyframe optimizer)")
+        self._lean = None
+        use_lean = stock if lean is None else bool(lean)
         self.regulariser = bool(regulariser)     # BackEnd.initialize_map has no isotropic term (:86-139)
         self.render_fn = render_fn or (render_fused if isinstance(gaussians, GaussianModel) else render)
         self.loss_fn = loss_fn or get_loss_mapping_rgbd
@@ -395,7 +409,7 @@ class MappingWindow:
         if self.densify_stats and hasattr(gaussians, "_stats"):
             gaussians._stats()
         groups = []
-        for v in self.local:       # utils/slam_backend.py:434-471 (one Adam over the kf params)
+        for v in ([] if use_lean else self.local):       # utils/slam_backend.py:434-471 (one Adam over the kf params)
             cam = keyframes[v]["cam"]
             if self._moves(v):
                 groups += [dict(params=[cam.cam_rot_delta], lr=pose_lr[0]),
@@ -442,6 +456,12 @@ class MappingWindow:
                 from .peer import PeerArena
                 self.peer = PeerArena(gaussians.flat.device, group)
                 gaussians.enable_peer_arena(self.peer)
+        if use_lean:
+            from .window import LeanWindow
+            self._lean = LeanWindow(gaussians, keyframes, self.local, bg, pose_lr, self._moves,
+                                    lambda v: bool(self.kfs[v].get("optimize_exposure", True)),
+                                    densify_stats=self.densify_stats, regulariser=self.regulariser,
+                                    rank=self.rank)
         self.last = {}
         self._g1 = self._g2 = None
         self._ovf = self._status_all = None
@@ -461,6 +481,14 @@ class MappingWindow:
 
     # -- the two halves of a step ------------------------------------------------------
     def _forward_backward(self):
+        if self._lean is not None:
+            side = []
+            if self.view_streams > 1 and len(self.local) > 1:
+                if self._side is None:
+                    self._side = [torch.cuda.Stream(self.bg.device) for _ in range(self.view_streams)]
+                side = self._side
+            loss = self._lean.forward_backward(side)
+            return loss, {v: self._lean.package(v) for v in self.local}
         g = self.g
         loss = 0
         stats = {}
@@ -526,6 +554,8 @@ class MappingWindow:
 
     def _update(self, set_to_none, gaussians=True):
         g = self.g
+        if self._lean is not None:
+            return self._lean.update(peer=self.peer, world=self.world, group=self.group, gaussians=gaussians)
         if not gaussians:
             # the reference's optimizer.step() right after densify_and_prune finds only fresh
             # Parameters without .grad and changes nothing (utils/slam_backend.py:290-309)
@@ -565,6 +595,16 @@ class MappingWindow:
     # -- eager -------------------------------------------------------------------------
     def _eager_forward_backward(self, set_to_none=True):
         from . import rasterizer as rz
+        if self._lean is not None:
+            for attempt in range(3):
+                loss, stats = self._forward_backward()
+                if not self._lean.note_overflow(self._lean.status_all.tolist()):    # one host sync per step
+                    break
+                self.g.zero_grad()              # discard the background-only pass, redo it with more room
+                if attempt == 2:
+                    raise RuntimeError("binning capacity overflow persisted after two retries")
+            self.last = stats
+            return loss
         loss, stats = self._forward_backward()
         if rz._SyncFree.enabled and rz.check_overflow(self._states(stats)):
             self.g.zero_grad()              # discard the background-only pass and redo it
@@ -598,6 +638,19 @@ class MappingWindow:
         dev = self.bg.device
         if self._ovf is None:
             self._ovf = torch.zeros(1, dtype=torch.int32, device=dev)
+        if self._lean is not None:
+            # the whole step as ONE graph: views -> finalize -> [exchange] -> Adam -> camera step
+            self._lean.ensure()
+            self._g1, self._g2 = torch.cuda.CUDAGraph(), None
+            with torch.cuda.graph(self._g1):
+                self._loss, self._stats = self._forward_backward()
+                self._update(set_to_none=False)
+            self._status_all, self._ovf, self._gstates = self._lean.status_all, self._lean.guard, None
+            self.graph_launches = self._lean.launches_fb + self._lean.launches_up
+            self._flag_host = [(torch.empty(self._status_all.shape, dtype=torch.int32).pin_memory(),
+                                torch.empty(1, dtype=torch.int32).pin_memory(),
+                                torch.zeros(1, dtype=torch.int32).pin_memory()) for _ in range(3)]
+            return
         l0 = lib.b2gs_kernel_launches()
         self._g1 = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self._g1):
@@ -634,7 +687,8 @@ class MappingWindow:
             if opt is not None:
                 opt.sync_lr()
         self._g1.replay()
-        self._g2.replay()
+        if self._g2 is not None:
+            self._g2.replay()
         if self._status_all is not None:
             st, ov, fl = self._flag_host[self._launched % 3]
             st.copy_(self._status_all, non_blocking=True)      # this rank's views: sizes the retry
@@ -659,14 +713,14 @@ class MappingWindow:
             if int(fl[0]):
                 raise RuntimeError("libb2gs peer barrier timed out: a rank died or fell out of step; the "
                                    "replicas were left untouched by that step but the window cannot continue")
-            rz.note_overflow(self._gstates, st.tolist())
+            self._note(st.tolist())
             over = over or bool(int(ov[0]))
         if not over:
             return
         torch.cuda.synchronize()
         lost = 1 + len(self._pending)           # every launch since the overflowing one was discarded
         for ev, st, ov, fl in self._pending:
-            rz.note_overflow(self._gstates, st.tolist())
+            self._note(st.tolist())
         self._pending.clear()
         for _ in range(lost):
             self.g.zero_grad()
@@ -676,9 +730,15 @@ class MappingWindow:
             self._launch()
             torch.cuda.synchronize()
             ev, st, ov, fl = self._pending.pop(0)
-            rz.note_overflow(self._gstates, st.tolist())
+            self._note(st.tolist())
             if int(ov[0]):
                 raise RuntimeError("binning capacity overflow persisted after re-capture")
+
+    def _note(self, vals):
+        from . import rasterizer as rz
+        if self._lean is not None:
+            return self._lean.note_overflow(vals)
+        return rz.note_overflow(self._gstates, vals)
 
     def flush(self):
         """settle every launched step (one host sync): afterwards all of them have been applied."""
@@ -695,7 +755,7 @@ class MappingWindow:
                 loss = self._eager_step(set_to_none=False)
             torch.cuda.current_stream().wait_stream(s)
             return loss
-        if self._g1 is None:
+        if self._g1 is None or (self._lean is not None and self._lean.ensure()):
             self._capture()
         # no host sync inside the step: the flags of the step launched two calls ago are looked at
         # now (its event completed long ago, the GPU is busy with the previous step meanwhile)

@@ -123,7 +123,7 @@ def test_capturable_adam_in_graph_matches_torch():
         assert float((x - y).abs().max()) <= 2e-6 * float(y.abs().max()) + 1e-7
 
 
-def _window(cuda_graph, view_streams=1, n_views=3):
+def _window(cuda_graph, view_streams=1, n_views=3, lean=None):
     sc = syn.make_scene("cfg1_plumbing", device=DEV, n_views=n_views)
     gt = dict(xyz=sc.xyz + 0.01, scaling=sc.scaling, rotation=sc.rotation, opacity=sc.opacity + 0.1,
               f_dc=sc.f_dc + 0.05, f_rest=sc.f_rest)
@@ -136,14 +136,38 @@ def _window(cuda_graph, view_streams=1, n_views=3):
             kfs.append(dict(cam=cam, gt_image=pkg["render"].clone(), gt_depth=pkg["depth"].clone()))
     gm = mapping.GaussianModel(sc.xyz, sc.f_dc, sc.f_rest, sc.opacity, sc.scaling, sc.rotation,
                                sh_degree=sc.sh_degree)
-    return mapping.MappingWindow(gm, kfs, sc.bg, cuda_graph=cuda_graph, view_streams=view_streams), gm, kfs
+    return mapping.MappingWindow(gm, kfs, sc.bg, cuda_graph=cuda_graph, view_streams=view_streams, lean=lean), gm, kfs
 
 
-@pytest.mark.parametrize("view_streams", [1, 2])
-def test_graph_mapping_step_matches_eager(view_streams):
+def test_lean_window_matches_autograd_route():
+    """window.LeanWindow (loss fused into the render epilogue, window_finalize, Adam + zero_grad fused,
+    one camera kernel) == the autograd route over the same kernels (render_fused + fused loss kernels +
+    FusedAdam + per-keyframe pose update), eager, 3 views, 6 steps."""
+    w0, g0, k0 = _window(False, lean=False)
+    w1, g1, k1 = _window(False, lean=True)
+    assert w1._lean is not None and w0._lean is None
+    for s in range(6):
+        a, b = float(w0.step()), float(w1.step())
+        assert abs(a - b) <= 2e-6 * abs(a) * (1 + 4 * s), (s, a, b)     # same arithmetic up to reduction order
+    diff = (g0.flat - g1.flat).abs()
+    assert float((diff > 1e-4 * (1 + g0.flat.abs())).float().mean()) < 1e-3
+    for a, b in zip(k0[1:], k1[1:]):
+        assert torch.allclose(a["cam"].T, b["cam"].T, atol=1e-4)
+        assert torch.allclose(a["cam"].exposure_a, b["cam"].exposure_a, atol=1e-4)
+        assert torch.allclose(a["cam"].exposure_b, b["cam"].exposure_b, atol=1e-4)
+    assert float(g1.flat_grad.abs().max()) == 0.0, "Adam must leave the gradient arena cleared"
+    assert torch.equal(g0.denom, g1.denom) and torch.equal(g0.max_radii2D, g1.max_radii2D)
+    assert torch.allclose(g0.xyz_gradient_accum, g1.xyz_gradient_accum, rtol=1e-3,
+                          atol=1e-5 * float(g0.xyz_gradient_accum.abs().max()))
+    pk = w1.last[0]
+    assert pk["render"].shape == k1[0]["gt_image"].shape and int((pk["radii"] > 0).sum()) > 0
+
+
+@pytest.mark.parametrize("view_streams,lean", [(1, True), (2, True), (2, False)])
+def test_graph_mapping_step_matches_eager(view_streams, lean):
     try:
-        w0, g0, k0 = _window(False)
-        w1, g1, k1 = _window(True, view_streams)
+        w0, g0, k0 = _window(False, lean=lean)
+        w1, g1, k1 = _window(True, view_streams, lean=lean)
         l0 = [float(w0.step()) for _ in range(8)]
         l1 = [float(w1.step()) for _ in range(8)]
         assert w1._g1 is not None and w1.graph_launches > 0, "graph path not taken"
@@ -161,6 +185,9 @@ def test_graph_mapping_step_matches_eager(view_streams):
         # host notices two calls later (or at flush), re-captures and runs the discarded steps again
         w1.flush()
         before = g1.flat.clone()
+        if w1._lean is not None:
+            for v in w1.local:
+                w1._lean._alloc_binning(v, 64)
         for key in list(rz._SyncFree.cap):
             rz._SyncFree.cap[key] = 64
         w1._g1 = None
