@@ -271,6 +271,13 @@ typedef struct B2gsPeerArena {
   float* const* grad_base;    /* [world] base of every rank's gradient arena */
   uint32_t* const* signal;    /* [world] every rank's signal pad: >= 32 zero-initialised uint32 */
   uint32_t* fail_flag;        /* local device word, set to 1 if a barrier timed out (about 4 s) */
+  /* optional NVLink-switch multicast mappings of the SAME two arenas (CUDA multicast objects bound on
+   * every rank, e.g. torch symmetric memory's handle.multicast_ptr): when both are non-NULL the
+   * owner of a chunk reads the gradient sum with one multimem.ld_reduce (the switch adds the ranks'
+   * copies) and broadcasts the new parameters / the cleared gradients with multimem.st — per-rank
+   * link traffic drops from 3 (world-1)/world to 3/world of the arena.  NULL: plain peer loads/stores. */
+  float* param_mc;
+  float* grad_mc;
 } B2gsPeerArena;
 B2GS_API int b2gs_adam_step_peer(const B2gsAdamSegment* segments, int32_t num_segments,
                         int64_t* step_counter, float beta1, float beta2, float eps,

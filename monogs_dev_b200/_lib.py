@@ -100,6 +100,7 @@ class B2gsPeerArena(C.Structure):
         ("world", C.c_int32), ("rank", C.c_int32),
         ("param_base", C.POINTER(C.c_void_p)), ("grad_base", C.POINTER(C.c_void_p)),
         ("signal", C.POINTER(C.c_void_p)), ("fail_flag", C.c_void_p),
+        ("param_mc", C.c_void_p), ("grad_mc", C.c_void_p),
     ]
 
 

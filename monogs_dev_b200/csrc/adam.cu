@@ -120,8 +120,23 @@ struct PeerTable {
   float* param[PEER_MAX];
   float* grad[PEER_MAX];
   uint32_t* signal[PEER_MAX];
+  float* param_mc;   // multicast views of the arenas (NVLS), or nullptr
+  float* grad_mc;
   int world, rank;
 };
+
+// NVLink-switch multicast accesses (sm_90+): one load returns the SUM over every rank's copy
+// (the switch reduces in flight), one store lands in every rank's copy.
+__device__ __forceinline__ float4 multimem_ld_reduce_add(const float* mc_addr) {
+  float4 r;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(mc_addr) : "memory");
+  return r;
+}
+__device__ __forceinline__ void multimem_st(float* mc_addr, float4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
+               :: "l"(mc_addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
 
 // All-to-all flag barrier between the ranks' streams (one thread per peer).  Slot [src] on the
 // destination's pad: 0 -> 1 by the arriving rank, 1 -> 0 by the owner; CAS on both sides makes
@@ -190,7 +205,21 @@ adam_peer_kernel(const __grid_constant__ AdamTable t, const __grid_constant__ Pe
 
   const bool vec = (((poff | goff) & 3) == 0) && ((((uintptr_t)m | (uintptr_t)v) & 15) == 0);
   const long long i = begin + 4LL * threadIdx.x;
-  if (vec && i + 4 <= end) {
+  if (vec && i + 4 <= end && pt.param_mc != nullptr) {
+    // NVLS: the switch sums the ranks' gradient copies and replicates the stores
+    float4 gg = multimem_ld_reduce_add(pt.grad_mc + goff + i);
+    float4 pp = *reinterpret_cast<const float4*>(pt.param[pt.rank] + poff + i);
+    float4 mm = *reinterpret_cast<float4*>(m + i);
+    float4 vv = *reinterpret_cast<float4*>(v + i);
+    adam_one(pp.x, gg.x, mm.x, vv.x, w1, beta2, w2, bc2_sqrt, eps, neg_step);
+    adam_one(pp.y, gg.y, mm.y, vv.y, w1, beta2, w2, bc2_sqrt, eps, neg_step);
+    adam_one(pp.z, gg.z, mm.z, vv.z, w1, beta2, w2, bc2_sqrt, eps, neg_step);
+    adam_one(pp.w, gg.w, mm.w, vv.w, w1, beta2, w2, bc2_sqrt, eps, neg_step);
+    *reinterpret_cast<float4*>(m + i) = mm;
+    *reinterpret_cast<float4*>(v + i) = vv;
+    multimem_st(pt.param_mc + poff + i, pp);
+    multimem_st(pt.grad_mc + goff + i, make_float4(0.f, 0.f, 0.f, 0.f));
+  } else if (vec && i + 4 <= end) {
     // all peers' loads in flight together (one NVLink round trip), then the sum in rank order
     float4 x[PEER_MAX];
 #pragma unroll
@@ -336,6 +365,7 @@ extern "C" int b2gs_adam_step_peer_fused(const B2gsAdamSegment* segments, int32_
   PeerTable pt;
   memset(&pt, 0, sizeof(pt));
   pt.world = peers->world; pt.rank = peers->rank;
+  if (peers->param_mc && peers->grad_mc && pt.world > 1) { pt.param_mc = peers->param_mc; pt.grad_mc = peers->grad_mc; }
   for (int r = 0; r < pt.world; ++r) {
     pt.param[r] = peers->param_base[r]; pt.grad[r] = peers->grad_base[r]; pt.signal[r] = peers->signal[r];
     if (!pt.param[r] || !pt.grad[r] || !pt.signal[r]) { set_error("b2gs_adam_step_peer: NULL peer pointer"); return B2GS_ERR_INVALID; }

@@ -223,7 +223,9 @@ static int forward_empty(const B2gsScene& s, const B2gsWorkspace* ws, cudaStream
   const size_t tiles = (size_t)((s.W + TILE - 1) / TILE) * ((s.H + TILE - 1) / TILE);
   B2GS_CUDA(cudaMemsetAsync(im.ranges, 0, sizeof(uint2) * tiles, st));
   B2GS_CUDA(cudaMemsetAsync(im.status, 0, sizeof(uint32_t) * 8, st));
-  return B2GS_OK;
+  // tile order of the per-tile kernels: run the scan on all-zero counters (identity-like order)
+  B2GS_CUDA(cudaMemsetAsync(im.cursor, 0, sizeof(uint32_t) * tiles * CURSOR_STRIDE, st));
+  return launch_tile_scan(s, im, 0, nullptr, st);
 }
 
 extern "C" int b2gs_forward_plan(const B2gsScene* scene, const B2gsWorkspace* ws,

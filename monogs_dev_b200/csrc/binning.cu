@@ -47,6 +47,7 @@ ImageWS carve_image(void* base, int32_t W, int32_t H, size_t* total) {
   im.ranges = c.take<uint2>(tiles);
   im.cursor = c.take<uint32_t>(tiles * CURSOR_STRIDE);
   im.status = c.take<uint32_t>(8);
+  im.order = c.take<uint32_t>(tiles);
   if (total) *total = c.total();
   return im;
 }
@@ -66,12 +67,24 @@ BinWS carve_bin(void* base, int64_t cap, size_t* total) {
 // reference leaves empty tiles at (0,0), CR/rasterizer_impl.cu:313-321), turns the
 // counters into scatter cursors, publishes num_rendered and the overflow flag.
 constexpr int SCAN_THREADS = 1024;
+constexpr int SCAN_CLASSES = 64;
+// length class of a tile: half octaves of its instance count, LONGEST = class 0
+__device__ __forceinline__ uint32_t length_class(uint32_t c) {
+  if (c == 0) return SCAN_CLASSES - 1;
+  const int msb = 31 - __clz(c);
+  const uint32_t half = msb > 0 ? (c >> (msb - 1)) & 1u : 0u;
+  const int k = 2 * msb + (int)half;           // 0 .. 63, growing with c
+  return (uint32_t)(SCAN_CLASSES - 2 - min(k, SCAN_CLASSES - 2));
+}
 
 __global__ void __launch_bounds__(SCAN_THREADS)
 tile_scan_kernel(uint32_t tiles, long long cap, uint32_t* __restrict__ cursor,
                  uint2* __restrict__ ranges, uint32_t* __restrict__ status,
-                 uint32_t* __restrict__ status_out) {
+                 uint32_t* __restrict__ status_out, uint32_t* __restrict__ order) {
   __shared__ uint32_t s_total;
+  __shared__ uint32_t s_class[SCAN_CLASSES];   // tiles per length class, then the class cursors
+  if (threadIdx.x < SCAN_CLASSES) s_class[threadIdx.x] = 0u;
+  __syncthreads();
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const uint32_t per = (tiles + SCAN_THREADS - 1) / SCAN_THREADS;
   const uint32_t lo = min(tiles, (uint32_t)tid * per), hi = min(tiles, lo + per);
@@ -85,9 +98,16 @@ tile_scan_kernel(uint32_t tiles, long long cap, uint32_t* __restrict__ cursor,
 #pragma unroll
     for (uint32_t k = 0; k < SCAN_REG; ++k) cnt[k] = (lo + k < hi) ? cursor[(lo + k) * CURSOR_STRIDE] : 0u;
 #pragma unroll
-    for (uint32_t k = 0; k < SCAN_REG; ++k) mine += cnt[k];
+    for (uint32_t k = 0; k < SCAN_REG; ++k) {
+      mine += cnt[k];
+      if (lo + k < hi) atomicAdd(&s_class[length_class(cnt[k])], 1u);
+    }
   } else {
-    for (uint32_t t = lo; t < hi; ++t) mine += cursor[t * CURSOR_STRIDE];
+    for (uint32_t t = lo; t < hi; ++t) {
+      const uint32_t c = cursor[t * CURSOR_STRIDE];
+      mine += c;
+      atomicAdd(&s_class[length_class(c)], 1u);
+    }
   }
   // block-wide exclusive scan of `mine` (64-bit: the total may exceed 2^32)
   unsigned long long incl = mine;
@@ -108,6 +128,18 @@ tile_scan_kernel(uint32_t tiles, long long cap, uint32_t* __restrict__ cursor,
       if (lane >= d) wi += n;
     }
     s_w64[lane] = wi - w;  // exclusive prefix of the warp
+    // class histogram -> class start offsets (two values per lane)
+    {
+      const uint32_t a = s_class[2 * lane], b = s_class[2 * lane + 1];
+      uint32_t incl2 = a + b;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t n = __shfl_up_sync(0xffffffffu, incl2, d);
+        if (lane >= d) incl2 += n;
+      }
+      s_class[2 * lane] = incl2 - a - b;
+      s_class[2 * lane + 1] = incl2 - b;
+    }
     if (lane == 31) {
       const bool over = wi >= (1ull << 31) || (cap >= 0 && wi > (unsigned long long)cap);
       status[0] = (uint32_t)min(wi, 0xffffffffull);
@@ -129,6 +161,7 @@ tile_scan_kernel(uint32_t tiles, long long cap, uint32_t* __restrict__ cursor,
       if (t < hi) {
         ranges[t] = (c && !over) ? make_uint2(run, run + c) : make_uint2(0u, 0u);
         cursor[t * CURSOR_STRIDE] = run;
+        order[atomicAdd(&s_class[length_class(c)], 1u)] = t;
       }
       run += c;
     }
@@ -139,6 +172,7 @@ tile_scan_kernel(uint32_t tiles, long long cap, uint32_t* __restrict__ cursor,
     // on overflow every tile is rendered empty; the caller sees status[1] and retries
     ranges[t] = (c && !over) ? make_uint2(run, run + c) : make_uint2(0u, 0u);
     cursor[t * CURSOR_STRIDE] = run;
+    order[atomicAdd(&s_class[length_class(c)], 1u)] = t;
     run += c;
   }
 }
@@ -148,7 +182,7 @@ int launch_tile_scan(const B2gsScene& s, const ImageWS& im, int64_t cap, uint32_
   const int gx = (s.W + TILE - 1) / TILE, gy = (s.H + TILE - 1) / TILE;
   B2GS_PROF("tile_scan", st);
   tile_scan_kernel<<<1, SCAN_THREADS, 0, st>>>((uint32_t)(gx * gy), (long long)cap, im.cursor,
-                                               im.ranges, im.status, status_out);
+                                               im.ranges, im.status, status_out, im.order);
   B2GS_LAUNCH_CHECK(st, s.debug);
   return B2GS_OK;
 }
@@ -283,10 +317,10 @@ __device__ __forceinline__ void merge_level(const uint64_t* __restrict__ in, uin
 }
 
 __global__ void __launch_bounds__(SORT_THREADS)
-tile_sort_kernel(const uint2* __restrict__ ranges, uint64_t* __restrict__ keys,
-                 uint32_t* __restrict__ point_list) {
+tile_sort_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ order,
+                 uint64_t* __restrict__ keys, uint32_t* __restrict__ point_list) {
   __shared__ uint64_t s_keys[SORT_SMEM_KEYS];
-  const uint2 r = ranges[blockIdx.x];
+  const uint2 r = ranges[order[blockIdx.x]];
   const uint32_t n = r.y - r.x;
   if (n == 0) return;
   uint64_t* seg = keys + r.x;
@@ -334,7 +368,7 @@ int launch_binning(const B2gsScene& s, const GeomWS& g, const ImageWS& im, const
     B2GS_LAUNCH_CHECK(st, s.debug);
   }
   B2GS_PROF("tile_sort", st);
-  tile_sort_kernel<<<gx * gy, SORT_THREADS, 0, st>>>(im.ranges, b.keys, b.point_list);
+  tile_sort_kernel<<<gx * gy, SORT_THREADS, 0, st>>>(im.ranges, im.order, b.keys, b.point_list);
   B2GS_LAUNCH_CHECK(st, s.debug);
   return B2GS_OK;
 }

@@ -24,7 +24,7 @@ constexpr int LOSS_MAX_BLOCKS = 148 * 8;
 __device__ __forceinline__ PixelTerms pixel_terms(const B2gsLossArgs& a, float ea, float eb, int i) {
   const size_t N = (size_t)a.N;
   return pixel_terms_of(a, ea, eb, i, a.image[i], a.image[N + i], a.image[2 * N + i],
-                        (a.mode & 2) ? 0.f : a.depth[i], (a.mode & 1) ? a.opacity[i] : 1.f);
+                        (a.mode & 2) ? 0.f : a.depth[i], (a.mode & 1) ? a.opacity[i] : 1.f, load_gt(a, i));
 }
 
 __device__ __forceinline__ float block_sum(float v, float* s_red) {

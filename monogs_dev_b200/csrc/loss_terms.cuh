@@ -17,12 +17,20 @@ struct PixelTerms {
 __device__ __forceinline__ float sgnf(float x) { return (float)(x > 0.f) - (float)(x < 0.f); }
 
 // mode bit 0: tracking (opacity weighting, opacity>0.95 depth mask, grad_mask); bit 1: monocular.
-// c0..c2 / dep / op: the rendered pixel (from memory in loss.cu, from registers in render_fwd.cu).
-__device__ __forceinline__ PixelTerms pixel_terms_of(const B2gsLossArgs& a, float ea, float eb, int i,
-                                                    float c0, float c1, float c2, float dep, float op_in) {
-  PixelTerms t;
+// c0..c2 / dep / op: the rendered pixel (from memory in loss.cu, from registers in render_fwd.cu);
+// gt: the ground-truth pixel (r, g, b, depth) — render_fwd.cu fetches it before its blend loop so
+// that the loads are long done when the epilogue needs them.
+__device__ __forceinline__ float4 load_gt(const B2gsLossArgs& a, int i) {
   const size_t N = (size_t)a.N;
-  const float g0 = a.gt_image[i], g1 = a.gt_image[N + i], g2 = a.gt_image[2 * N + i];
+  return make_float4(a.gt_image[i], a.gt_image[N + i], a.gt_image[2 * N + i],
+                     (a.mode & 2) ? 0.f : a.gt_depth[i]);
+}
+
+__device__ __forceinline__ PixelTerms pixel_terms_of(const B2gsLossArgs& a, float ea, float eb, int i,
+                                                    float c0, float c1, float c2, float dep, float op_in,
+                                                    float4 gt) {
+  PixelTerms t;
+  const float g0 = gt.x, g1 = gt.y, g2 = gt.z;
   // gt_image.sum(dim=0) > threshold  (torch sums channel 0 + 1 + 2 in this order)
   float m = ((g0 + g1) + g2) > a.rgb_boundary_threshold ? 1.f : 0.f;
   const bool tracking = a.mode & 1;
@@ -40,7 +48,7 @@ __device__ __forceinline__ PixelTerms pixel_terms_of(const B2gsLossArgs& a, floa
   t.md = 0.f;
   t.dd = 0.f;
   if (!(a.mode & 2)) {
-    const float gd = a.gt_depth[i];
+    const float gd = gt.w;
     float md = gd > 0.01f ? 1.f : 0.f;
     if (tracking) md *= (op > 0.95f ? 1.f : 0.f);
     t.md = md;
@@ -64,8 +72,8 @@ struct PixelLoss {
 
 __device__ __forceinline__ PixelLoss pixel_loss(const B2gsLossArgs& a, float ea, float eb, float w_rgb,
                                                 float w_dep, int i, float c0, float c1, float c2,
-                                                float dep, float op) {
-  const PixelTerms t = pixel_terms_of(a, ea, eb, i, c0, c1, c2, dep, op);
+                                                float dep, float op, float4 gt) {
+  const PixelTerms t = pixel_terms_of(a, ea, eb, i, c0, c1, c2, dep, op, gt);
   PixelLoss r;
   const float img[3] = {c0, c1, c2};
   r.ga = 0.f; r.gb = 0.f;

@@ -154,7 +154,27 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
 
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   float tau[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-  const bool live = idx < P && radii[idx] > 0;
+  // all per-Gaussian inputs are requested before the first dependent use (radius -> accumulator row
+  // -> mean -> rotation / scale -> opacity ... would otherwise be a chain of DRAM round trips; the
+  // kernel is latency-bound).  Rows of culled Gaussians are fetched in vain: ~30 % of 100 B.
+  int radius_in = 0;
+  float4 a0 = {0.f, 0.f, 0.f, 0.f}, a1 = a0, a2 = a0, q_in = make_float4(1.f, 0.f, 0.f, 0.f);
+  float3 mean = {0.f, 0.f, 0.f}, s_in = {0.f, 0.f, 0.f};
+  float op_raw = 0.f;
+  uint8_t clamp_in = 0;
+  if (idx < P) {
+    radius_in = radii[idx];
+    const float4* arow = reinterpret_cast<const float4*>(acc + (size_t)idx * ACC_STRIDE);
+    a0 = arow[0]; a1 = arow[1]; a2 = arow[2];
+    mean = {means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]};
+    if (cov3D_precomp == nullptr) {
+      q_in = reinterpret_cast<const float4*>(rotations)[idx];
+      s_in = {scales[3 * idx], scales[3 * idx + 1], scales[3 * idx + 2]};
+    }
+    if (RAW) op_raw = opacities[idx];
+    if (shs != nullptr) clamp_in = clamped[idx];
+  }
+  const bool live = radius_in > 0;
 
   if (idx < P && !live && !accumulate) {
     // culled: every gradient row is zero (reference: torch::zeros, DGR/rasterize_points.cu:160-170)
@@ -173,15 +193,12 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
   }
 
   if (live) {
-    const float4* arow = reinterpret_cast<const float4*>(acc + (size_t)idx * ACC_STRIDE);
-    const float4 a0 = arow[0], a1 = arow[1], a2 = arow[2];
     const float dmean2D_x = a0.x, dmean2D_y = a0.y;
     const float3 dL_dconic = {a0.z, a0.w, a1.x};
     const float dL_dop = a1.y;
     const V3 dL_dcol = {a1.z, a1.w, a2.x};
     const float dL_ddepth = a2.y;
 
-    const float3 mean = {means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]};
     float cov6[6];
     float4 q = make_float4(1.f, 0.f, 0.f, 0.f);
     float sx = 0.f, sy = 0.f, sz = 0.f, q_norm = 1.f;
@@ -189,8 +206,8 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
 #pragma unroll
       for (int i = 0; i < 6; ++i) cov6[i] = cov3D_precomp[6 * idx + i];
     } else {
-      q = reinterpret_cast<const float4*>(rotations)[idx];
-      sx = scales[3 * idx]; sy = scales[3 * idx + 1]; sz = scales[3 * idx + 2];
+      q = q_in;
+      sx = s_in.x; sy = s_in.y; sz = s_in.z;
       if (RAW) {  // same activations as the forward (gsmath.cuh)
         q = act_normalize(q, q_norm);
         sx = expf(sx); sy = expf(sy); sz = expf(sz);
@@ -350,7 +367,7 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
         d_dc = RAW ? dL_dsh + (size_t)idx * 3 : dL_dsh + (size_t)idx * M * 3;
         d_rest = RAW ? dL_dsh_rest + (size_t)idx * (M - 1) * 3 : d_dc + 3;
       }
-      const V3 dm = sh_backward(D, M, dc, rest, V3{mean.x, mean.y, mean.z}, campos, clamped[idx],
+      const V3 dm = sh_backward(D, M, dc, rest, V3{mean.x, mean.y, mean.z}, campos, clamp_in,
                                 dL_dcol, d_dc, d_rest, accumulate != 0);
       dmean.x += dm.x; dmean.y += dm.y; dmean.z += dm.z;
       tau[0] += -dm.x; tau[1] += -dm.y; tau[2] += -dm.z;
@@ -431,7 +448,7 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
     }
     float d_op = dL_dop;
     if (RAW) {  // d sigmoid(x) = o (1 - o) dx
-      const float o = act_sigmoid(opacities[idx]);
+      const float o = act_sigmoid(op_raw);
       d_op *= o * (1.f - o);
     }
     if (accumulate) {
@@ -456,14 +473,14 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
     if (st_denom) atomicAdd(&st_denom[idx], 1.f);
     // radii >= 0: the int order of the bit patterns is the float order; atomic so that views
     // running on concurrent streams can share the statistics arrays
-    if (st_max_radii) atomicMax(reinterpret_cast<int*>(st_max_radii) + idx, __float_as_int((float)radii[idx]));
+    if (st_max_radii) atomicMax(reinterpret_cast<int*>(st_max_radii) + idx, __float_as_int((float)radius_in));
   }
 
   // ---- isotropic-scale regulariser (utils/slam_backend.py:229-231), every Gaussian, visible or
   // not: value partial + gradient wrt the raw log-scales added to the gradient arena ----
   float reg = 0.f;
   if (RAW && iso_w != 0.f && idx < P) {
-    const float s0 = expf(scales[3 * idx]), s1 = expf(scales[3 * idx + 1]), s2 = expf(scales[3 * idx + 2]);
+    const float s0 = expf(s_in.x), s1 = expf(s_in.y), s2 = expf(s_in.z);
     const float m = (s0 + s1 + s2) / 3.0f;
     const float d0 = s0 - m, d1 = s1 - m, d2 = s2 - m;
     reg = fabsf(d0) + fabsf(d1) + fabsf(d2);

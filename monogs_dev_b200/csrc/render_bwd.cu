@@ -95,7 +95,8 @@ constexpr int RB_THREADS = 128;   // 4 warps x (8x8 pixels, two per lane) = one 
 // [4] warp visits, [5] warp visits that run the blend / gradient arithmetic, [6] contributing pairs
 template <bool COUNT>
 __global__ void __launch_bounds__(RB_THREADS)
-render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W,
+render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ order,
+                  const uint32_t* __restrict__ point_list, int W,
                   int H, int gx, const float* __restrict__ bg, const float2* __restrict__ xy,
                   const float4* __restrict__ conic_o, const float4* __restrict__ rgbd,
                   const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib,
@@ -106,7 +107,7 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   unsigned c_visit = 0, c_full = 0, c_contrib = 0;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int tile = blockIdx.x;
+  const int tile = (int)order[blockIdx.x];   // longest lists first (tile_scan_kernel)
   const int tile_x = tile % gx, tile_y = tile / gx;
   // warp -> 8x8 quadrant of the tile; lane -> column lane & 7, rows lane >> 3 and (lane >> 3) + 4:
   // the upper pixel lies in the 8x4 cull block 4 * (warp >> 1) + (warp & 1), the lower one in the
@@ -284,11 +285,11 @@ int launch_render_bwd(const B2gsScene& s, const GeomWS& g, const ImageWS& im, co
   B2GS_PROF("render_bwd", st);
   unsigned long long* cnt = debug_counters();
   if (cnt)
-    render_bwd_kernel<true><<<gx * gy, RB_THREADS, 0, st>>>(im.ranges, b.point_list, s.W, s.H, gx, s.bg, g.xy,
+    render_bwd_kernel<true><<<gx * gy, RB_THREADS, 0, st>>>(im.ranges, im.order, b.point_list, s.W, s.H, gx, s.bg, g.xy,
                                                             g.conic_o, g.rgbd, im.final_T, im.n_contrib,
                                                             io.dL_dcolor, io.dL_ddepth, acc, cnt);
   else
-    render_bwd_kernel<false><<<gx * gy, RB_THREADS, 0, st>>>(im.ranges, b.point_list, s.W, s.H, gx, s.bg, g.xy,
+    render_bwd_kernel<false><<<gx * gy, RB_THREADS, 0, st>>>(im.ranges, im.order, b.point_list, s.W, s.H, gx, s.bg, g.xy,
                                                              g.conic_o, g.rgbd, im.final_T, im.n_contrib,
                                                              io.dL_dcolor, io.dL_ddepth, acc, nullptr);
   B2GS_LAUNCH_CHECK(st, s.debug);

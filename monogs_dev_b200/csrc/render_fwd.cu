@@ -40,7 +40,8 @@ __device__ __forceinline__ f2 fma2(f2 a, f2 b, f2 c) { return __ffma2_rn(a, b, c
 // fl.partials for b2gs_window_finalize.
 template <bool COUNT, bool LOSS>
 __global__ void __launch_bounds__(RF_THREADS)
-render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W,
+render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ order,
+                  const uint32_t* __restrict__ point_list, int W,
                   int H, int gx, const float2* __restrict__ xy, const float4* __restrict__ conic_o,
                   const float4* __restrict__ rgbd, const float* __restrict__ bg,
                   float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
@@ -52,7 +53,7 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   __shared__ int s_cnt[RF_BATCH];
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int tile = blockIdx.x;
+  const int tile = (int)order[blockIdx.x];   // longest lists first (tile_scan_kernel)
   const int tile_x = tile % gx, tile_y = tile / gx;
   // warp -> 8x8 quadrant of the tile; lane -> column lane & 7, rows lane >> 3 and (lane >> 3) + 4:
   // the upper pixel lies in the 8x4 cull block 4 * (warp >> 1) + (warp & 1), the lower one in the
@@ -68,6 +69,12 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   const uint2 range = ranges[tile];
   const int n = (int)(range.y - range.x);
 
+  // fused loss: this lane's two ground-truth pixels, requested now, consumed in the epilogue
+  float4 gtA = make_float4(0.f, 0.f, 0.f, 0.f), gtB = gtA;
+  if (LOSS) {
+    if (insideA) gtA = load_gt(fl.args, pixA);
+    if (insideB) gtB = load_gt(fl.args, pixB);
+  }
   const uint32_t cnt_base = (uint32_t)__cvta_generic_to_shared(s_cnt);
   bool doneA = !insideA, doneB = !insideB;
   f2 T = bc(1.0f);
@@ -202,14 +209,14 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     float red[4] = {0.f, 0.f, 0.f, 0.f};
     if (insideA) {
       const PixelLoss r = pixel_loss(fl.args, ea, eb, w_rgb, w_dep, pixA, C0.x + T.x * bg[0], C1.x + T.x * bg[1],
-                                     C2.x + T.x * bg[2], D.x, 1 - T.x);
+                                     C2.x + T.x * bg[2], D.x, 1 - T.x, gtA);
       fl.dL_dimage[0 * plane + pixA] = r.g[0]; fl.dL_dimage[1 * plane + pixA] = r.g[1];
       fl.dL_dimage[2 * plane + pixA] = r.g[2]; fl.dL_ddepth[pixA] = r.gd;
       red[0] += r.rgb; red[1] += r.dep; red[2] += r.ga; red[3] += r.gb;
     }
     if (insideB) {
       const PixelLoss r = pixel_loss(fl.args, ea, eb, w_rgb, w_dep, pixB, C0.y + T.y * bg[0], C1.y + T.y * bg[1],
-                                     C2.y + T.y * bg[2], D.y, 1 - T.y);
+                                     C2.y + T.y * bg[2], D.y, 1 - T.y, gtB);
       fl.dL_dimage[0 * plane + pixB] = r.g[0]; fl.dL_dimage[1 * plane + pixB] = r.g[1];
       fl.dL_dimage[2 * plane + pixB] = r.g[2]; fl.dL_ddepth[pixB] = r.gd;
       red[0] += r.rgb; red[1] += r.dep; red[2] += r.ga; red[3] += r.gb;
@@ -240,7 +247,8 @@ int launch_render_fwd(const B2gsScene& s, const GeomWS& g, const ImageWS& im, co
   if (out.fused_loss) fl = *out.fused_loss;
 #define B2GS_RF_LAUNCH(C_, L_)                                                                        \
   render_fwd_kernel<C_, L_><<<gx * gy, RF_THREADS, 0, st>>>(                                          \
-      im.ranges, b.point_list, s.W, s.H, gx, g.xy, g.conic_o, g.rgbd, s.bg, im.final_T, im.n_contrib,  \
+      im.ranges, im.order, b.point_list, s.W, s.H, gx, g.xy, g.conic_o, g.rgbd, s.bg, im.final_T,     \
+      im.n_contrib,                                                                                  \
       out.color, out.depth, out.opacity, out.n_touched, cnt, fl)
   if (out.fused_loss) {
     if (cnt) B2GS_RF_LAUNCH(true, true); else B2GS_RF_LAUNCH(false, true);

@@ -30,47 +30,47 @@ struct FinalizeTable {
   int n;
 };
 
-__device__ __forceinline__ double block_sum_d(double x, double* s_red) {
-#pragma unroll
-  for (int d = 16; d > 0; d >>= 1) x += __shfl_xor_sync(0xffffffffu, x, d);
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  __syncthreads();
-  if (lane == 0) s_red[warp] = x;
-  __syncthreads();
-  double r = 0.0;
-  if (threadIdx.x == 0)
-    for (int w = 0; w < WF_THREADS / 32; ++w) r += s_red[w];   // fixed order
-  return r;  // valid in thread 0
-}
-
 __global__ void __launch_bounds__(WF_THREADS)
 window_finalize_kernel(const __grid_constant__ FinalizeTable t, float* __restrict__ loss_total,
                        int32_t* __restrict__ guard, uint32_t* __restrict__ ticket) {
-  __shared__ double s_red[WF_THREADS / 32];
+  __shared__ double s_red[WF_THREADS / 32][11];
   __shared__ bool s_last;
   const B2gsViewFinalize& v = t.v[blockIdx.x];
-  double acc[4] = {0.0, 0.0, 0.0, 0.0};
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  // r[0..3]: loss partial sums, r[4..10]: tau[6] + regulariser.  Every thread's share is summed in a
+  // fixed order and the cross-thread reduction order is fixed too: deterministic given the partials.
+  double r[11] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
   if (v.loss_partials) {
+    const float4* lp = reinterpret_cast<const float4*>(v.loss_partials);
+#pragma unroll 4
     for (int i = threadIdx.x; i < v.loss_rows; i += WF_THREADS) {
-      const float4 p = reinterpret_cast<const float4*>(v.loss_partials)[i];
-      acc[0] += p.x; acc[1] += p.y; acc[2] += p.z; acc[3] += p.w;
+      const float4 p = __ldcg(lp + i);
+      r[0] += p.x; r[1] += p.y; r[2] += p.z; r[3] += p.w;
     }
   }
-  double tau[7] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
   if (v.tau_partials) {
+    const float4* tp = reinterpret_cast<const float4*>(v.tau_partials);
+#pragma unroll 4
     for (int i = threadIdx.x; i < v.tau_rows; i += WF_THREADS) {
-      const float4 a = reinterpret_cast<const float4*>(v.tau_partials)[2 * i];
-      const float4 b = reinterpret_cast<const float4*>(v.tau_partials)[2 * i + 1];
-      tau[0] += a.x; tau[1] += a.y; tau[2] += a.z; tau[3] += a.w;
-      tau[4] += b.x; tau[5] += b.y; tau[6] += b.z;
+      const float4 a = __ldcg(tp + 2 * i), b = __ldcg(tp + 2 * i + 1);
+      r[4] += a.x; r[5] += a.y; r[6] += a.z; r[7] += a.w;
+      r[8] += b.x; r[9] += b.y; r[10] += b.z;
     }
   }
-  double r[11];
 #pragma unroll
-  for (int k = 0; k < 4; ++k) r[k] = block_sum_d(acc[k], s_red);
+  for (int k = 0; k < 11; ++k) {
 #pragma unroll
-  for (int k = 0; k < 7; ++k) r[4 + k] = block_sum_d(tau[k], s_red);
+    for (int d = 16; d > 0; d >>= 1) r[k] += __shfl_xor_sync(0xffffffffu, r[k], d);
+    if (lane == 0) s_red[warp][k] = r[k];
+  }
+  __syncthreads();
   if (threadIdx.x == 0) {
+#pragma unroll
+    for (int k = 0; k < 11; ++k) {
+      double x = 0.0;
+      for (int w = 0; w < WF_THREADS / 32; ++w) x += s_red[w][k];   // fixed order
+      r[k] = x;
+    }
     const bool mono = v.mode & 2;
     const double l_rgb = r[0] / (3.0 * (double)v.N), l_dep = r[1] / (double)v.N;
     // monocular: l1.mean() alone (utils/slam_utils.py:72,109); rgbd: alpha blend (:88,128)
@@ -88,19 +88,18 @@ window_finalize_kernel(const __grid_constant__ FinalizeTable t, float* __restric
     }
     __threadfence();
     s_last = atomicAdd(ticket, 1u) == (uint32_t)(t.n - 1);
-  }
-  __syncthreads();
-  if (s_last && threadIdx.x == 0) {
-    __threadfence();
-    double total = 0.0;
-    uint32_t over = 0;
-    for (int k = 0; k < t.n; ++k) {       // view order: deterministic
-      if (t.v[k].loss) total += (double)*(volatile float*)t.v[k].loss;
-      if (t.v[k].status) over |= t.v[k].status[1];
+    if (s_last) {
+      __threadfence();
+      double total = 0.0;
+      uint32_t over = 0;
+      for (int k = 0; k < t.n; ++k) {       // view order: deterministic
+        if (t.v[k].loss) total += (double)*(volatile float*)t.v[k].loss;
+        if (t.v[k].status) over |= *(volatile const uint32_t*)(t.v[k].status + 1);
+      }
+      if (loss_total) loss_total[0] = (float)total;
+      if (guard) guard[0] = (int32_t)over;
+      *ticket = 0u;                          // ready for the next launch
     }
-    if (loss_total) loss_total[0] = (float)total;
-    if (guard) guard[0] = (int32_t)over;
-    *ticket = 0u;                          // ready for the next launch
   }
 }
 
@@ -126,11 +125,18 @@ __global__ void __launch_bounds__(32)
 pose_step_kernel(const __grid_constant__ PoseTable t, long long* __restrict__ step_counter,
                  long long* __restrict__ extra_tick, float beta1, float beta2, float eps, int do_tick,
                  const int32_t* __restrict__ guard, uint32_t* __restrict__ ticket) {
-  if (guard && *guard) return;   // the step is being discarded: no update, no tick
-  const double step = (double)(*step_counter + 1);
-  if ((int)blockIdx.x < t.n) {
-    const B2gsPoseCam& c = t.c[blockIdx.x];
-    const int k = threadIdx.x;
+  // every load of the kernel is issued up front (this kernel is pure latency): lane k < 8 its
+  // parameter / gradient / moments, lanes 8..19 the camera block's R | T for the pose update
+  __shared__ float s_rt[12];
+  const int k = threadIdx.x;
+  const bool have = (int)blockIdx.x < t.n;
+  const B2gsPoseCam& c = t.c[have ? blockIdx.x : 0];
+  const int32_t g_word = guard ? *guard : 0;
+  const long long step_ll = *step_counter;
+  if (have && k >= 8 && k < 20 && c.optimize_pose) s_rt[k - 8] = c.cam_state[k - 8];
+  if (g_word) return;            // the step is being discarded: no update, no tick
+  const double step = (double)(step_ll + 1);
+  if (have) {
     if (k < 8) {
       // 0-2 rot (theta <- dL_dtau[3:6]), 3-5 trans (rho <- dL_dtau[0:3]), 6 exposure_a, 7 exposure_b
       const bool pose = k < 6;

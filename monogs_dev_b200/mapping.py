@@ -454,7 +454,8 @@ class MappingWindow:
                 gaussians.optimizer.capturable = True
             else:
                 from .peer import PeerArena
-                self.peer = PeerArena(gaussians.flat.device, group)
+                # peer_adam="nomc": plain peer loads / stores even where NVLS multicast is available
+                self.peer = PeerArena(gaussians.flat.device, group, multicast=peer_adam != "nomc")
                 gaussians.enable_peer_arena(self.peer)
         if use_lean:
             from .window import LeanWindow

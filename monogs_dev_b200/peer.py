@@ -15,7 +15,7 @@ from . import _lib
 
 
 class PeerArena:
-    def __init__(self, device, group=None):
+    def __init__(self, device, group=None, multicast=True):
         import torch.distributed._symmetric_memory as symm
         if not dist.is_initialized():
             raise RuntimeError("PeerArena needs an initialised process group")
@@ -33,6 +33,8 @@ class PeerArena:
         self._sig.zero_()
         self._sig_h = symm.rendezvous(self._sig, self.group)
         self.fail = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self.want_multicast = bool(multicast)
+        self.multicast = False           # set by alloc(): the arenas have an NVLS multicast mapping
         self._arena = self._arena_h = None
         self._struct = None
         self.total = 0
@@ -50,7 +52,15 @@ class PeerArena:
         self._pb = (C.c_void_p * W)(*[int(p) for p in self._arena_h.buffer_ptrs])
         self._gb = (C.c_void_p * W)(*[int(p) + 4 * n for p in self._arena_h.buffer_ptrs])
         self._sb = (C.c_void_p * W)(*[int(p) for p in self._sig_h.buffer_ptrs])
-        self._struct = _lib.B2gsPeerArena(W, self.rank, self._pb, self._gb, self._sb, self.fail.data_ptr())
+        mc = 0
+        if self.want_multicast:
+            try:
+                mc = int(self._arena_h.multicast_ptr or 0) if self._arena_h.has_multicast_support else 0
+            except Exception:
+                mc = 0
+        self.multicast = mc != 0
+        self._struct = _lib.B2gsPeerArena(W, self.rank, self._pb, self._gb, self._sb, self.fail.data_ptr(),
+                                          mc if mc else None, (mc + 4 * n) if mc else None)
         return self._arena[:total], self._arena[n:n + total]
 
     def struct(self):

@@ -14,7 +14,7 @@ graph = len(sys.argv) > 2 and sys.argv[2] == "graph"
 
 def make(peer):
     sc = syn.make_scene(name, device=dev, n_views=4)
-    kfs, _ = bench.build_window(dev, mapping.render_fused, mapping.GaussianModel, None, sc)
+    kfs = bench.build_window(dev, sc)
     gm = mapping.GaussianModel(sc.xyz, sc.f_dc, sc.f_rest, sc.opacity, sc.scaling, sc.rotation, sh_degree=sc.sh_degree)
     return mapping.MappingWindow(gm, kfs, sc.bg, cuda_graph=graph, view_streams=2, peer_adam=peer), gm
 
