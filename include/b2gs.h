@@ -333,6 +333,38 @@ B2GS_API int b2gs_adam_step_peer_fused(const B2gsAdamSegment* segments, int32_t 
                               int64_t* step_counter, float beta1, float beta2, float eps,
                               const B2gsPeerArena* peers, int32_t flags, void* stream);
 
+/* ---- densify_and_prune on the packed arenas (csrc/densify.cu) --------------------------------
+ * Replaces GaussianModel.densify_and_prune and everything under it (GS/scene/gaussian_model.py:
+ * 468-555, 593-689) with plan -> (one host read of the totals) -> apply.  Groups: the parameter
+ * tensors of the model, `width[g]` floats per Gaussian, with their Adam moments.  The new arenas
+ * receive [kept originals | kept clones | kept children (copy-major)], the reference's final order;
+ * new rows get zero moments, kept rows keep theirs. */
+typedef struct B2gsDensifyArgs {
+  int32_t P, n_groups;                       /* <= 8 groups */
+  const float* param[8]; const float* exp_avg[8]; const float* exp_avg_sq[8];
+  int32_t width[8];
+  int32_t xyz, opacity, scaling, rotation;   /* which groups they are (widths 3 / 1 / 3 / 4) */
+  const float* grad_accum; const float* denom;   /* [P] densification statistics */
+  float max_grad, min_opacity;
+  float dense_threshold;                     /* percent_dense * scene_extent, rounded once by the caller */
+  float world_size_threshold;                /* 0.1 * extent */
+  int32_t max_screen_size_on;                /* the reference's `if max_screen_size:` */
+  int32_t N; float split_divisor;            /* children per split parent, 0.8 * N */
+  const int32_t* aux[2];                     /* optional int32 [P] arrays that ride along (unique_kfIDs, n_obs) */
+} B2gsDensifyArgs;
+B2GS_API size_t b2gs_densify_bytes(int32_t P);
+/* totals (device, 8 x uint64): [0] kept originals, [1] kept clones, [2] kept split parents (each has
+ * N kept children), [3] clones selected, [4] split parents selected.  New size = [0] + [1] + N * [2]. */
+B2GS_API int b2gs_densify_plan(const B2gsDensifyArgs* args, void* workspace, size_t workspace_bytes,
+                      uint64_t* totals, void* stream);
+/* totals_host: the five counts read back.  samples: device [N * totals[4], 3] unit normals, row
+ * k * totals[4] + r belongs to copy k of the r-th split parent (torch.normal's draw order,
+ * gaussian_model.py:606-611).  new_*: HOST arrays of n_groups device pointers (the new arenas),
+ * new_aux: 2 device pointers or NULL. */
+B2GS_API int b2gs_densify_apply(const B2gsDensifyArgs* args, const void* workspace, const int64_t* totals_host,
+                       const float* samples, float* const* new_param, float* const* new_exp_avg,
+                       float* const* new_exp_avg_sq, int32_t* const* new_aux, void* stream);
+
 /* RGB-D keyframe back-projection (the seed point cloud of new Gaussians; feeds b2gs_knn3_dist2).
  * Replaces GaussianModel.create_pcd_from_image_and_depth's host round trip through open3d 0.17
  * (GS/scene/gaussian_model.py:107-156: RGBDImage.create_from_color_and_depth(depth_scale=1,

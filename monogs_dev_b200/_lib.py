@@ -95,6 +95,19 @@ class B2gsPoseCam(C.Structure):
     ]
 
 
+class B2gsDensifyArgs(C.Structure):
+    _fields_ = [
+        ("P", C.c_int32), ("n_groups", C.c_int32),
+        ("param", C.c_void_p * 8), ("exp_avg", C.c_void_p * 8), ("exp_avg_sq", C.c_void_p * 8),
+        ("width", C.c_int32 * 8),
+        ("xyz", C.c_int32), ("opacity", C.c_int32), ("scaling", C.c_int32), ("rotation", C.c_int32),
+        ("grad_accum", C.c_void_p), ("denom", C.c_void_p),
+        ("max_grad", C.c_float), ("min_opacity", C.c_float), ("dense_threshold", C.c_float),
+        ("world_size_threshold", C.c_float), ("max_screen_size_on", C.c_int32),
+        ("N", C.c_int32), ("split_divisor", C.c_float), ("aux", C.c_void_p * 2),
+    ]
+
+
 class B2gsPeerArena(C.Structure):
     _fields_ = [
         ("world", C.c_int32), ("rank", C.c_int32),
@@ -161,6 +174,11 @@ SYMBOLS = {
     "b2gs_adam_step_peer_fused": (C.c_int, [C.POINTER(B2gsAdamSegment), C.c_int32, C.c_void_p, C.c_float,
                                             C.c_float, C.c_float, C.POINTER(B2gsPeerArena), C.c_int32,
                                             C.c_void_p]),
+    "b2gs_densify_bytes": (C.c_size_t, [C.c_int32]),
+    "b2gs_densify_plan": (C.c_int, [C.POINTER(B2gsDensifyArgs), C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]),
+    "b2gs_densify_apply": (C.c_int, [C.POINTER(B2gsDensifyArgs), C.c_void_p, C.POINTER(C.c_int64), C.c_void_p,
+                                     C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
+                                     C.POINTER(C.c_void_p), C.c_void_p]),
     "b2gs_window_finalize": (C.c_int, [C.POINTER(B2gsViewFinalize), C.c_int32, C.c_void_p, C.c_void_p,
                                        C.c_void_p, C.c_void_p]),
     "b2gs_pose_step": (C.c_int, [C.POINTER(B2gsPoseCam), C.c_int32, C.c_void_p, C.c_void_p, C.c_float,

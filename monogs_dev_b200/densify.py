@@ -61,9 +61,68 @@ def prune_points(g, mask):
 
 
 @torch.no_grad()
+def _densify_and_prune_kernels(g, max_grad, min_opacity, extent, max_screen_size, N, samples, generator):
+    """densify_and_prune as libb2gs kernels (csrc/densify.cu): plan -> one host read of the totals ->
+    the surviving rows of every group of the parameter / exp_avg / exp_avg_sq arenas written straight
+    to their final position in freshly allocated arenas."""
+    import ctypes as C
+    from . import _lib
+    from ._lib import lib, check, ptr
+    acc, den, _ = g._stats()
+    dev = g.flat.device
+    P = g._xyz.shape[0]
+    par, mom, steps = _state(g)
+    a = _lib.B2gsDensifyArgs()
+    a.P, a.n_groups = P, len(_GROUPS)
+    for i, k in enumerate(_GROUPS):
+        a.param[i], a.exp_avg[i], a.exp_avg_sq[i] = ptr(par[k]), ptr(mom[k][0]), ptr(mom[k][1])
+        a.width[i] = par[k].numel() // max(P, 1)
+    a.xyz, a.opacity, a.scaling, a.rotation = (_GROUPS.index(k) for k in ("xyz", "opacity", "scaling", "rotation"))
+    a.grad_accum, a.denom = acc.data_ptr(), den.data_ptr()
+    a.max_grad, a.min_opacity = float(max_grad), float(min_opacity)
+    a.dense_threshold = g.percent_dense * extent              # rounded to fp32 once, as torch rounds the scalar
+    a.world_size_threshold = 0.1 * extent
+    a.max_screen_size_on, a.N, a.split_divisor = int(bool(max_screen_size)), int(N), 0.8 * N
+    aux_old = [getattr(g, n, None) for n in ("unique_kfIDs", "n_obs")]
+    aux_old = [t.to(dev).int().contiguous() if t is not None else None for t in aux_old]
+    for i, t in enumerate(aux_old):
+        a.aux[i] = ptr(t)
+    with torch.cuda.device(dev):
+        st = torch.cuda.current_stream().cuda_stream
+        ws = torch.empty(lib.b2gs_densify_bytes(P), dtype=torch.uint8, device=dev)
+        totals = torch.zeros(8, dtype=torch.int64, device=dev)
+        check(lib.b2gs_densify_plan(C.byref(a), ws.data_ptr(), ws.numel(), totals.data_ptr(), st))
+        tot = totals.cpu().tolist()                           # the one host sync: sizes the new arenas
+        n_o, n_c, n_s, nc, ns = tot[:5]
+        P_new = n_o + n_c + N * n_s
+        if ns and samples is None:
+            samples = torch.randn(N * ns, 3, device=dev, generator=generator)
+        samples = samples.to(dev).float().contiguous() if ns else None
+        old = (g.flat, g.flat_m, g.flat_v)                    # the kernels read these: keep them alive
+        shapes = {k: (P_new,) + tuple(par[k].shape[1:]) for k in _GROUPS}
+        g._allocate(None, None, steps, shapes=shapes, device=dev)
+        new_p = (C.c_void_p * 8)(*[ptr(g._params[k]) for k in _GROUPS])
+        new_m = (C.c_void_p * 8)(*[ptr(g.optimizer.state[g._params[k]]["exp_avg"]) for k in _GROUPS])
+        new_v = (C.c_void_p * 8)(*[ptr(g.optimizer.state[g._params[k]]["exp_avg_sq"]) for k in _GROUPS])
+        aux_new = [torch.empty(P_new, dtype=torch.int32, device=dev) if t is not None else None for t in aux_old]
+        new_a = (C.c_void_p * 2)(*[ptr(t) for t in aux_new])
+        th = (C.c_int64 * 8)(*tot)
+        check(lib.b2gs_densify_apply(C.byref(a), ws.data_ptr(), th, ptr(samples), new_p, new_m, new_v, new_a, st))
+    for n, t in zip(("unique_kfIDs", "n_obs"), aux_new):
+        if t is not None:
+            setattr(g, n, t)
+    g._stats()                                                # zeros of the new size
+    del old
+    return nc, ns, (P - ns + nc + N * ns) - P_new
+
+
+@torch.no_grad()
 def densify_and_prune(g, max_grad, min_opacity, extent, max_screen_size, N=2, samples=None, generator=None):
     """Returns (n_clone, n_split, n_pruned_final).  `samples` ([n_split * N, 3] unit normals) can be
-    injected for parity tests; otherwise drawn on the device."""
+    injected for parity tests; otherwise drawn on the device.  On the GPU the whole sequence runs as
+    three libb2gs kernels; the torch index plan below is the host-logic (CPU) path."""
+    if g.flat.is_cuda and getattr(g, "peer", None) is None:
+        return _densify_and_prune_kernels(g, max_grad, min_opacity, extent, max_screen_size, N, samples, generator)
     acc, den, max_radii = g._stats()
     P = g._xyz.shape[0]
     dev = g.flat.device

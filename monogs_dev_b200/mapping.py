@@ -51,11 +51,16 @@ class GaussianModel:
         self._allocate(dict(xyz=xyz, f_dc=f_dc, f_rest=f_rest, opacity=opacity, scaling=scaling,
                             rotation=rotation))
 
-    def _allocate(self, src, moments=None, steps=None):
+    def _allocate(self, src, moments=None, steps=None, shapes=None, device=None):
         """(re)build the four packed arenas (parameters, gradients, Adam m / v) from per-group
         tensors; used at construction and after densify / prune (the reference re-wraps six
-        nn.Parameters and twelve moment tensors, GS/scene/gaussian_model.py:468-555)."""
-        dev = src["xyz"].device
+        nn.Parameters and twelve moment tensors, GS/scene/gaussian_model.py:468-555).
+        src=None with `shapes` (group -> shape) and `device`: arenas are allocated and wired up but
+        left for the caller to fill (the densify kernels write the new rows in place)."""
+        if src is None:
+            src = {k: torch.empty(tuple(shapes[k]), device="meta") for k in _GROUPS}
+        fill = src["xyz"].device.type != "meta"
+        dev = src["xyz"].device if fill else torch.device(device)
         capturable = bool(getattr(self.optimizer, "capturable", False))
         step_dev = getattr(self.optimizer, "_step_dev", None)     # device step count survives re-allocation
         if self.optimizer is not None:
@@ -76,7 +81,8 @@ class GaussianModel:
         self._params = {}
         for k, o, n in zip(_GROUPS, offs, sizes):
             view = self.flat[o:o + n].view(src[k].shape)
-            view.copy_(src[k])
+            if fill:
+                view.copy_(src[k])
             p = torch.nn.Parameter(view)
             p.grad = self.flat_grad[o:o + n].view(src[k].shape)
             self._params[k] = p
