@@ -222,7 +222,6 @@ static int forward_empty(const B2gsScene& s, const B2gsWorkspace* ws, cudaStream
   }
   const size_t tiles = (size_t)((s.W + TILE - 1) / TILE) * ((s.H + TILE - 1) / TILE);
   B2GS_CUDA(cudaMemsetAsync(im.ranges, 0, sizeof(uint2) * tiles, st));
-  B2GS_CUDA(cudaMemsetAsync(im.ranges_c, 0, sizeof(uint2) * tiles, st));
   B2GS_CUDA(cudaMemsetAsync(im.status, 0, sizeof(uint32_t) * 8, st));
   // tile order of the per-tile kernels: run the scan on all-zero counters (identity-like order)
   B2GS_CUDA(cudaMemsetAsync(im.cursor, 0, sizeof(uint32_t) * tiles * CURSOR_STRIDE, st));
@@ -292,13 +291,19 @@ extern "C" int b2gs_forward_render(const B2gsScene* scene, const B2gsWorkspace* 
 }
 
 extern "C" int64_t b2gs_binning_capacity(size_t binning_bytes) {
-  // inverse of b2gs_binning_bytes: point_list (4 B) + keys (8 B) + splat record (48 B) per instance
-  int64_t n = (int64_t)(binning_bytes / 60);
+  // inverse of b2gs_binning_bytes: point_list (4 B) + keys (8 B) per instance
+  int64_t n = (int64_t)(binning_bytes / 12);
   while (n > 0) {
     size_t need = 0;
     carve_bin(nullptr, n, &need);
     if (need <= binning_bytes) break;
-    n -= (int64_t)((need - binning_bytes + 59) / 60);
+    n -= (int64_t)((need - binning_bytes + 11) / 12);
+  }
+  for (;;) {   // the step above may undershoot by the alignment slack of the three segments
+    size_t need = 0;
+    carve_bin(nullptr, n + 1, &need);
+    if (need > binning_bytes) break;
+    ++n;
   }
   return n > 0 ? n : 0;
 }

@@ -45,7 +45,6 @@ ImageWS carve_image(void* base, int32_t W, int32_t H, size_t* total) {
   im.final_T = c.take<float>(N);
   im.n_contrib = c.take<uint32_t>(N);
   im.ranges = c.take<uint2>(tiles);
-  im.ranges_c = c.take<uint2>(tiles);
   im.cursor = c.take<uint32_t>(tiles * CURSOR_STRIDE);
   im.status = c.take<uint32_t>(8);
   im.order = c.take<uint32_t>(tiles);
@@ -59,7 +58,6 @@ BinWS carve_bin(void* base, int64_t cap, size_t* total) {
   size_t n = (size_t)(cap > 0 ? cap : 1);
   b.point_list = c.take<uint32_t>(n);
   b.keys = c.take<uint64_t>(n);
-  b.recs = c.take<SplatRec>(n);
   if (total) *total = c.total();
   return b;
 }
@@ -318,63 +316,13 @@ __device__ __forceinline__ void merge_level(const uint64_t* __restrict__ in, uin
   }
 }
 
-// Epilogue of the per-tile sort: the sorted list word (id << 8 | block mask) of every position goes
-// to point_list (the reference's list, bit for bit: parity export); the splats whose mask reaches
-// at least one block of the tile are gathered ONCE, here, into contiguous SplatRec records in list
-// order — the render kernels then stage a batch with one bulk-async copy instead of per-thread
-// gathers, forward and backward, and never see the ~35 % of the instances that touch no block.
-__device__ __forceinline__ void emit_records(const uint64_t* __restrict__ a, uint32_t n, uint32_t start,
-                                             uint32_t* __restrict__ point_list, SplatRec* __restrict__ recs,
-                                             const float2* __restrict__ xy, const float4* __restrict__ conic_o,
-                                             const float4* __restrict__ rgbd, uint2* __restrict__ range_c) {
-  __shared__ uint32_t s_wsum[SORT_THREADS / 32];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  uint32_t base = 0;
-  for (uint32_t c0 = 0; c0 < n; c0 += SORT_THREADS) {
-    const uint32_t i = c0 + threadIdx.x;
-    const uint32_t v = i < n ? (uint32_t)a[i] : 0u;
-    if (i < n) point_list[start + i] = v;
-    const bool keep = (v & 0xffu) != 0u;
-    const uint32_t b = __ballot_sync(0xffffffffu, keep);
-    if (lane == 0) s_wsum[warp] = __popc(b);
-    __syncthreads();
-    uint32_t before = 0, total = 0;
-#pragma unroll
-    for (int w = 0; w < SORT_THREADS / 32; ++w) {
-      const uint32_t c = s_wsum[w];
-      before += w < warp ? c : 0u;
-      total += c;
-    }
-    if (keep) {
-      const uint32_t id = v >> 8;
-      SplatRec r;
-      r.co = conic_o[id];
-      r.cd = rgbd[id];
-      r.xy = xy[id];
-      r.id = (int)id;
-      r.bm = (v & 0xffu) | (i << 8);
-      recs[start + base + before + __popc(b & ((1u << lane) - 1u))] = r;
-    }
-    base += total;
-    __syncthreads();
-  }
-  if (threadIdx.x == 0) *range_c = make_uint2(start, start + base);
-}
-
 __global__ void __launch_bounds__(SORT_THREADS)
 tile_sort_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ order,
-                 uint64_t* __restrict__ keys, uint32_t* __restrict__ point_list,
-                 SplatRec* __restrict__ recs, const float2* __restrict__ xy,
-                 const float4* __restrict__ conic_o, const float4* __restrict__ rgbd,
-                 uint2* __restrict__ ranges_c) {
+                 uint64_t* __restrict__ keys, uint32_t* __restrict__ point_list) {
   __shared__ uint64_t s_keys[SORT_SMEM_KEYS];
-  const uint32_t tile = order[blockIdx.x];
-  const uint2 r = ranges[tile];
+  const uint2 r = ranges[order[blockIdx.x]];
   const uint32_t n = r.y - r.x;
-  if (n == 0) {
-    if (threadIdx.x == 0) ranges_c[tile] = make_uint2(0u, 0u);
-    return;
-  }
+  if (n == 0) return;
   uint64_t* seg = keys + r.x;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   if (n <= MERGE_KEYS) {
@@ -394,26 +342,23 @@ tile_sort_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
     }
     B2GS_MERGE(32u) B2GS_MERGE(64u) B2GS_MERGE(128u) B2GS_MERGE(256u) B2GS_MERGE(512u) B2GS_MERGE(1024u)
 #undef B2GS_MERGE
-    emit_records(a, n, r.x, point_list, recs, xy, conic_o, rgbd, ranges_c + tile);
+    for (uint32_t i = threadIdx.x; i < n; i += SORT_THREADS) point_list[r.x + i] = (uint32_t)a[i];
   } else if (n <= SORT_SMEM_KEYS) {
     for (uint32_t i = threadIdx.x; i < n; i += SORT_THREADS) s_keys[i] = seg[i];
     __syncthreads();
     bitonic_sort_block(s_keys, n);
-    emit_records(s_keys, n, r.x, point_list, recs, xy, conic_o, rgbd, ranges_c + tile);
+    for (uint32_t i = threadIdx.x; i < n; i += SORT_THREADS) point_list[r.x + i] = (uint32_t)s_keys[i];
   } else {
     __syncthreads();
     bitonic_sort_block(seg, n);
-    emit_records(seg, n, r.x, point_list, recs, xy, conic_o, rgbd, ranges_c + tile);
+    for (uint32_t i = threadIdx.x; i < n; i += SORT_THREADS) point_list[r.x + i] = (uint32_t)seg[i];
   }
 }
 
 int launch_binning(const B2gsScene& s, const GeomWS& g, const ImageWS& im, const BinWS& b,
                    int64_t cap, cudaStream_t st) {
   const int gx = (s.W + TILE - 1) / TILE, gy = (s.H + TILE - 1) / TILE;
-  if (cap <= 0 || s.P == 0) {   // no instance anywhere: every tile's record range is empty
-    B2GS_CUDA(cudaMemsetAsync(im.ranges_c, 0, sizeof(uint2) * (size_t)gx * gy, st));
-    return B2GS_OK;
-  }
+  if (cap <= 0 || s.P == 0) return B2GS_OK;
   {
     B2GS_PROF("scatter_instances", st);
     scatter_instances_kernel<<<(s.P + 255) / 256, 256, 0, st>>>(s.P, (uint32_t)gx, g.tiles_touched,
@@ -423,8 +368,7 @@ int launch_binning(const B2gsScene& s, const GeomWS& g, const ImageWS& im, const
     B2GS_LAUNCH_CHECK(st, s.debug);
   }
   B2GS_PROF("tile_sort", st);
-  tile_sort_kernel<<<gx * gy, SORT_THREADS, 0, st>>>(im.ranges, im.order, b.keys, b.point_list, b.recs, g.xy,
-                                                     g.conic_o, g.rgbd, im.ranges_c);
+  tile_sort_kernel<<<gx * gy, SORT_THREADS, 0, st>>>(im.ranges, im.order, b.keys, b.point_list);
   B2GS_LAUNCH_CHECK(st, s.debug);
   return B2GS_OK;
 }

@@ -17,17 +17,12 @@
 //              over all 32 lanes: 5+3+2+1+1 shuffles instead of 50) and the 10
 //              lanes that end up owning a total issue one red.global.add.f32 each
 //              into a packed 48 B accumulator row per splat.
-//   Staging: the tile's splats arrive as contiguous 48 B records (written once by the tile sort's
-//   epilogue, only the splats that reach a block of the tile) through double-buffered bulk-async
-//   copies (cp.async.bulk + mbarrier, bulk.cuh): one instruction from one thread per 256-splat
-//   batch, the next batch in flight while this one is processed; ONE block barrier per batch (buffer
-//   reuse) and no load latency behind it.  Each warp walks the records whose block-mask bits reach
-//   its 8x8 quadrant (one lane tests one record, the warp iterates the survivors' ballot).
-//   Splats behind every pixel's last contributor are never staged: the block starts at
-//   max(n_contrib) over the tile, each warp at its own max.
+//   Before any per-pixel work each warp culls the staged batch against its own 8x4
+//   block (cull.cuh): one lane tests one splat, the warp walks the survivors' bit mask.
+//   Splats behind every pixel's last contributor are never staged: the block
+//   starts at max(n_contrib) over the tile, each warp at its own max.
 #include "common.cuh"
 #include "cull.cuh"
-#include "bulk.cuh"
 
 namespace b2gs {
 
@@ -99,17 +94,15 @@ constexpr int RB_THREADS = 128;   // 4 warps x (8x8 pixels, two per lane) = one 
 // COUNT: debug instantiation that also counts the work it executes (b2gs_debug_set_counters):
 // [4] warp visits, [5] warp visits that run the blend / gradient arithmetic, [6] contributing pairs
 template <bool COUNT>
-__global__ void __launch_bounds__(RB_THREADS, 7)
-render_bwd_kernel(const uint2* __restrict__ ranges_c, const uint32_t* __restrict__ order,
-                  const SplatRec* __restrict__ recs, int W,
-                  int H, int gx, const float* __restrict__ bg,
+__global__ void __launch_bounds__(RB_THREADS)
+render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ order,
+                  const uint32_t* __restrict__ point_list, int W,
+                  int H, int gx, const float* __restrict__ bg, const float2* __restrict__ xy,
+                  const float4* __restrict__ conic_o, const float4* __restrict__ rgbd,
                   const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib,
                   const float* __restrict__ dL_dpixels, const float* __restrict__ dL_dpixels_depth,
                   float* __restrict__ acc, unsigned long long* __restrict__ counters) {
-  // two staging buffers filled by the copy engine (bulk.cuh): the next (shallower) batch of the
-  // tile's compacted splat records lands while the current one is processed
-  __shared__ __align__(128) SplatRec s_rec[2][RB_BATCH];
-  __shared__ __align__(8) uint64_t s_bar[2];
+  __shared__ SplatRec s_rec[RB_BATCH];
   __shared__ int s_max;
   unsigned c_visit = 0, c_full = 0, c_contrib = 0;
 
@@ -127,14 +120,10 @@ render_bwd_kernel(const uint2* __restrict__ ranges_c, const uint32_t* __restrict
   const f2 npixfy = make_float2(-(float)pyA, -(float)pyB);
   const uint32_t wmask = 0x5u << (4 * (warp >> 1) + (warp & 1));
 
-  const uint2 range = ranges_c[tile];
-  const int n = (int)(range.y - range.x);
-  const SplatRec* const src = recs + range.x;
+  const uint2 range = ranges[tile];
 
   const f2 T_final = make_float2(insideA ? final_Ts[pixA] : 0.f, insideB ? final_Ts[pixB] : 0.f);
   f2 T = T_final;
-  // n_contrib: 1-based position of the pixel's last contributor in the tile's FULL sorted list
-  // (the reference's number); a record carries its own position there (bm >> 8)
   const int lastA = insideA ? (int)n_contrib[pixA] : 0, lastB = insideB ? (int)n_contrib[pixB] : 0;
 
   // accum_c: blended colour behind the current splat; diff_c: (colour - accum) of the previous list
@@ -174,60 +163,46 @@ render_bwd_kernel(const uint2* __restrict__ ranges_c, const uint32_t* __restrict
   const int slot = fold10_slot(lane);
   float* const slot_row = slot >= 0 ? acc + slot : nullptr;
 
-  // deepest contributor over the warp / the tile (positions in the full list)
+  // deepest contributor over the warp / the tile
   const int warp_max = __reduce_max_sync(FULL, max(lastA, lastB));
-  if (tid == 0) {
-    s_max = 0;
-    mbar_init(&s_bar[0], 1);
-    mbar_init(&s_bar[1], 1);
-    mbar_init_fence();
-  }
+  if (tid == 0) s_max = 0;
   __syncthreads();
   if (lane == 0 && warp_max > 0) atomicMax(&s_max, warp_max);
   __syncthreads();
-  const int tile_max = s_max;  // list positions [0, tile_max) matter
-  // m = how many of the tile's records lie at positions < tile_max (records are in list order, so
-  // they are the first m): counted 128 at a time, stopping at the first chunk that is not all-in
-  int m = 0;
-  for (int c0 = 0; c0 < n; c0 += RB_THREADS) {
-    const int i = c0 + tid;
-    const int in = __syncthreads_count(i < n && (int)(src[i].bm >> 8) < tile_max);
-    m += in;
-    if (in < RB_THREADS) break;
-  }
-  const int nb = (m + RB_BATCH - 1) / RB_BATCH;
-  // batch b (b = 0 is the DEEPEST) holds records [lo_b, lo_b + cnt_b), lo_b = max(0, m - (b+1) B)
-  auto issue = [&](int b) {
-    const int hi = m - b * RB_BATCH, lo = max(0, hi - RB_BATCH);
-    const uint32_t bytes = (uint32_t)(hi - lo) * (uint32_t)sizeof(SplatRec);
-    mbar_expect_tx(&s_bar[b & 1], bytes);
-    bulk_g2s(s_rec[b & 1], src + lo, bytes, &s_bar[b & 1]);
-  };
-  if (tid == 0) {
-    if (nb > 0) issue(0);
-    if (nb > 1) issue(1);
-  }
+  const int tile_max = s_max;  // positions [0, tile_max) of the range matter
 
-  for (int b = 0; b < nb; ++b) {
-    const int hi = m - b * RB_BATCH, lo = max(0, hi - RB_BATCH);
-    const int cnt = hi - lo;
-    const SplatRec* const batch = s_rec[b & 1];
-    mbar_wait(&s_bar[b & 1], (uint32_t)(b >> 1) & 1u);     // batch b has landed
+  for (int base = 0; base < tile_max; base += RB_BATCH) {
+    const int cnt = min(RB_BATCH, tile_max - base);
+    if (base) __syncthreads();
+    for (int t = tid; t < cnt; t += RB_THREADS) {
+      const int pos = tile_max - 1 - (base + t);
+      const uint32_t v = point_list[range.x + pos];   // id << 8 | block mask
+      const int id = (int)(v >> 8);
+      SplatRec& r = s_rec[t];
+      r.id = id;
+      r.bm = v & 0xffu;
+      if (v & 0xffu) {        // a splat that reaches no block of the tile is never visited
+        r.co = conic_o[id];
+        r.cd = rgbd[id];
+        r.xy = xy[id];
+      }
+    }
+    __syncthreads();
 
-    // back to front: lane l of group g looks at local entry cnt - 1 - (32 g + l)
-    for (int c0 = 0; c0 < cnt; c0 += 32) {
-      const int e = cnt - 1 - (c0 + lane);
-      // one lane per splat: can it reach this warp's 8x8 quadrant at all (cull.cuh), and does it lie
-      // in front of the warp's deepest contributor?
-      uint32_t bmw = 0;
-      if (e >= 0) bmw = batch[e].bm;
-      const bool keep = e >= 0 && (bmw & wmask) && (int)(bmw >> 8) < warp_max;
+    // entry j is at position tile_max-1-(base+j); this warp needs pos < warp_max
+    int j0 = tile_max - base - warp_max;
+    if (j0 < 0) j0 = 0;
+    for (int c0 = j0 & ~31; c0 < cnt; c0 += 32) {
+      // one lane per splat: can it reach this warp's 8x8 quadrant at all? (cull.cuh)
+      const int jj = c0 + lane;
+      const bool keep = jj >= j0 && jj < cnt && (s_rec[jj].bm & wmask);
       unsigned mask = __ballot_sync(FULL, keep);
       while (mask) {
         const int k = __ffs(mask) - 1;
         mask &= mask - 1;
-        const SplatRec& r = batch[cnt - 1 - (c0 + k)];
-        const int pos = (int)(r.bm >> 8);
+        const int j = c0 + k;
+        const int pos = tile_max - 1 - (base + j);
+        const SplatRec& r = s_rec[j];
         const float2 p = r.xy;
         const float4 co = r.co;
         // power: the forward's operation tree, operation for operation (render_fwd.cu), so that
@@ -293,8 +268,6 @@ render_bwd_kernel(const uint2* __restrict__ ranges_c, const uint32_t* __restrict
         warp_fold10_and_red(v, lane, slot_row, (size_t)r.id * ACC_STRIDE);
       }
     }
-    __syncthreads();                                      // every warp is done with buffer b & 1
-    if (tid == 0 && b + 2 < nb) issue(b + 2);
   }
   if (COUNT) {
     c_contrib = __reduce_add_sync(FULL, c_contrib);
@@ -312,12 +285,12 @@ int launch_render_bwd(const B2gsScene& s, const GeomWS& g, const ImageWS& im, co
   B2GS_PROF("render_bwd", st);
   unsigned long long* cnt = debug_counters();
   if (cnt)
-    render_bwd_kernel<true><<<gx * gy, RB_THREADS, 0, st>>>(im.ranges_c, im.order, b.recs, s.W, s.H, gx, s.bg,
-                                                            im.final_T, im.n_contrib,
+    render_bwd_kernel<true><<<gx * gy, RB_THREADS, 0, st>>>(im.ranges, im.order, b.point_list, s.W, s.H, gx, s.bg, g.xy,
+                                                            g.conic_o, g.rgbd, im.final_T, im.n_contrib,
                                                             io.dL_dcolor, io.dL_ddepth, acc, cnt);
   else
-    render_bwd_kernel<false><<<gx * gy, RB_THREADS, 0, st>>>(im.ranges_c, im.order, b.recs, s.W, s.H, gx, s.bg,
-                                                             im.final_T, im.n_contrib,
+    render_bwd_kernel<false><<<gx * gy, RB_THREADS, 0, st>>>(im.ranges, im.order, b.point_list, s.W, s.H, gx, s.bg, g.xy,
+                                                             g.conic_o, g.rgbd, im.final_T, im.n_contrib,
                                                              io.dL_dcolor, io.dL_ddepth, acc, nullptr);
   B2GS_LAUNCH_CHECK(st, s.debug);
   return B2GS_OK;

@@ -17,7 +17,6 @@
 #include "common.cuh"
 #include "cull.cuh"
 #include "loss_terms.cuh"
-#include "bulk.cuh"
 #include <string.h>
 
 namespace b2gs {
@@ -41,17 +40,17 @@ __device__ __forceinline__ f2 fma2(f2 a, f2 b, f2 c) { return __ffma2_rn(a, b, c
 // fl.partials for b2gs_window_finalize.
 template <bool COUNT, bool LOSS>
 __global__ void __launch_bounds__(RF_THREADS)
-render_fwd_kernel(const uint2* __restrict__ ranges_c, const uint32_t* __restrict__ order,
-                  const SplatRec* __restrict__ recs, int W,
-                  int H, int gx, const float* __restrict__ bg,
+render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ order,
+                  const uint32_t* __restrict__ point_list, int W,
+                  int H, int gx, const float2* __restrict__ xy, const float4* __restrict__ conic_o,
+                  const float4* __restrict__ rgbd, const float* __restrict__ bg,
                   float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
                   float* __restrict__ out_color, float* __restrict__ out_depth,
                   float* __restrict__ out_opacity, int* __restrict__ n_touched,
                   unsigned long long* __restrict__ counters, const __grid_constant__ B2gsFusedLoss fl) {
-  // two staging buffers filled by the copy engine (bulk.cuh): batch k+1 lands while batch k is blended
-  __shared__ __align__(128) SplatRec s_rec[2][RF_BATCH];
-  __shared__ __align__(8) uint64_t s_bar[2];
+  __shared__ SplatRec s_rec[RF_BATCH];
   unsigned c_visit = 0, c_full = 0, c_contrib = 0;
+  __shared__ int s_cnt[RF_BATCH];
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int tile = (int)order[blockIdx.x];   // longest lists first (tile_scan_kernel)
@@ -67,27 +66,8 @@ render_fwd_kernel(const uint2* __restrict__ ranges_c, const uint32_t* __restrict
   const f2 npixfy = make_float2(-(float)pyA, -(float)pyB);
   const uint32_t wmask = 0x5u << (4 * (warp >> 1) + (warp & 1));
 
-  const uint2 range = ranges_c[tile];
+  const uint2 range = ranges[tile];
   const int n = (int)(range.y - range.x);
-  const int nb = (n + RF_BATCH - 1) / RF_BATCH;
-  const SplatRec* const src = recs + range.x;
-
-  if (tid == 0) {
-    mbar_init(&s_bar[0], 1);
-    mbar_init(&s_bar[1], 1);
-    mbar_init_fence();
-  }
-  __syncthreads();
-  // thread 0 is the producer: arm the buffer's barrier with the byte count, issue one bulk copy
-  auto issue = [&](int b) {
-    const uint32_t bytes = (uint32_t)min(RF_BATCH, n - b * RF_BATCH) * (uint32_t)sizeof(SplatRec);
-    mbar_expect_tx(&s_bar[b & 1], bytes);
-    bulk_g2s(s_rec[b & 1], src + (size_t)b * RF_BATCH, bytes, &s_bar[b & 1]);
-  };
-  if (tid == 0) {
-    if (nb > 0) issue(0);
-    if (nb > 1) issue(1);
-  }
 
   // fused loss: this lane's two ground-truth pixels, requested now, consumed in the epilogue
   float4 gtA = make_float4(0.f, 0.f, 0.f, 0.f), gtB = gtA;
@@ -95,23 +75,39 @@ render_fwd_kernel(const uint2* __restrict__ ranges_c, const uint32_t* __restrict
     if (insideA) gtA = load_gt(fl.args, pixA);
     if (insideB) gtB = load_gt(fl.args, pixB);
   }
+  const uint32_t cnt_base = (uint32_t)__cvta_generic_to_shared(s_cnt);
   bool doneA = !insideA, doneB = !insideB;
   f2 T = bc(1.0f);
   f2 C0 = bc(0.f), C1 = bc(0.f), C2 = bc(0.f), D = bc(0.f);
   uint32_t lastA = 0, lastB = 0;
 
-  int b = 0;
-  for (; b < nb; ++b) {
-    const int cnt = min(RF_BATCH, n - b * RF_BATCH);
-    const SplatRec* const batch = s_rec[b & 1];
-    mbar_wait(&s_bar[b & 1], (uint32_t)(b >> 1) & 1u);     // batch b has landed
+  for (int base = 0; base < n; base += RF_BATCH) {
+    // whole tile finished?  (also the barrier that protects the staging buffers)
+    if (__syncthreads_count(doneA && doneB) == RF_THREADS) break;
+    const int cnt = min(RF_BATCH, n - base);
+    for (int t = tid; t < RF_BATCH; t += RF_THREADS) {
+      if (t < cnt) {
+        const uint32_t v = point_list[range.x + base + t];   // id << 8 | block mask
+        const int id = (int)(v >> 8);
+        SplatRec& r = s_rec[t];
+        r.bm = v & 0xffu;
+        r.id = id;
+        if (v & 0xffu) {      // a splat that reaches no block of the tile is never visited
+          r.co = conic_o[id];
+          r.cd = rgbd[id];
+          r.xy = xy[id];
+        }
+      }
+      s_cnt[t] = 0;
+    }
+    __syncthreads();
 
     if (!__all_sync(RF_FULL, doneA && doneB)) {
       for (int c0 = 0; c0 < cnt; c0 += 32) {
         // can the splat reach this warp's quadrant at all?  (bits computed once by the binning
         // stage, cull.cuh: splat_block_mask)
         const int jj = c0 + lane;
-        const bool keep = jj < cnt && (batch[jj].bm & wmask);
+        const bool keep = jj < cnt && (s_rec[jj].bm & wmask);
         unsigned mask = __ballot_sync(RF_FULL, keep);
         // n_touched counts pixels whose transmittance is still above 0.5 after the splat; T only
         // falls, so once no pixel of the warp is above 0.5 the two ballots per visit are dead code
@@ -119,7 +115,8 @@ render_fwd_kernel(const uint2* __restrict__ ranges_c, const uint32_t* __restrict
         while (mask) {
           const int k = __ffs(mask) - 1;
           mask &= mask - 1;
-          const SplatRec& r = batch[c0 + k];
+          const int j = c0 + k;
+          const SplatRec& r = s_rec[j];
           const float2 p = r.xy;
           const float4 co = r.co;
           // power = -0.5f * (a dx dx + c dy dy) - b dx dy in the operation tree the reference's
@@ -151,29 +148,28 @@ render_fwd_kernel(const uint2* __restrict__ ranges_c, const uint32_t* __restrict
           D = fma2(bc(cd.w), w, D);
           T = make_float2(actA ? test_T.x : T.x, actB ? test_T.y : T.y);
           if (COUNT) c_contrib += (unsigned)actA + (unsigned)actB;
-          // the reference's contributor count: 1-based position in the tile's FULL sorted list
-          const uint32_t here = (r.bm >> 8) + 1u;
+          const uint32_t here = (uint32_t)(base + j + 1);
           lastA = actA ? here : lastA;
           lastB = actB ? here : lastB;
-          // n_touched: how many pixels saw this splat with T still above 0.5 — one fire-and-forget
-          // red.global per (warp, splat) while the warp is "hot"
+          // n_touched: how many pixels saw this splat with T still above 0.5
           if (hot) {
             const unsigned ta = __ballot_sync(RF_FULL, actA && test_T.x > 0.5f);
             const unsigned tb = __ballot_sync(RF_FULL, actB && test_T.y > 0.5f);
-            if ((ta | tb) != 0u && lane == 0) atomicAdd(&n_touched[r.id], __popc(ta) + __popc(tb));
+            if ((ta | tb) != 0u && lane == 0) {   // plain red.shared: one lane, nothing to aggregate
+              asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(cnt_base + 4u * (uint32_t)j),
+                           "r"(__popc(ta) + __popc(tb)) : "memory");
+            }
           }
         }
         if (__all_sync(RF_FULL, doneA && doneB)) break;  // warp-level early termination
       }
     }
-    // every warp is done with buffer b & 1 (and: is the whole tile finished?)
-    const bool all_done = __syncthreads_count(doneA && doneB) == RF_THREADS;
-    if (all_done) { ++b; break; }
-    if (tid == 0 && b + 2 < nb) issue(b + 2);
+    __syncthreads();
+    for (int t = tid; t < cnt; t += RF_THREADS) {
+      const int c = s_cnt[t];
+      if (c) atomicAdd(&n_touched[s_rec[t].id], c);
+    }
   }
-  // a copy issued for a batch that was never consumed must land before the CTA gives its shared
-  // memory back (batch b, if issued: the producer runs at most one batch ahead of the consumers)
-  if (b < nb) mbar_wait(&s_bar[b & 1], (uint32_t)(b >> 1) & 1u);
 
   if (COUNT) {
     c_contrib = __reduce_add_sync(RF_FULL, c_contrib);
@@ -251,7 +247,8 @@ int launch_render_fwd(const B2gsScene& s, const GeomWS& g, const ImageWS& im, co
   if (out.fused_loss) fl = *out.fused_loss;
 #define B2GS_RF_LAUNCH(C_, L_)                                                                        \
   render_fwd_kernel<C_, L_><<<gx * gy, RF_THREADS, 0, st>>>(                                          \
-      im.ranges_c, im.order, b.recs, s.W, s.H, gx, s.bg, im.final_T, im.n_contrib,                    \
+      im.ranges, im.order, b.point_list, s.W, s.H, gx, g.xy, g.conic_o, g.rgbd, s.bg, im.final_T,     \
+      im.n_contrib,                                                                                  \
       out.color, out.depth, out.opacity, out.n_touched, cnt, fl)
   if (out.fused_loss) {
     if (cnt) B2GS_RF_LAUNCH(true, true); else B2GS_RF_LAUNCH(false, true);

@@ -54,6 +54,57 @@ def test_fused_loss_matches_torch_ops(kind):
     assert torch.allclose(a[5], b[5], rtol=1e-4, atol=1e-8), "dL/dexposure_b"
 
 
+@pytest.mark.parametrize("name", ["mapping_rgbd", "mapping_rgb", "mapping_rgbd_init", "tracking_rgbd", "tracking_rgb"])
+def test_fused_loss_kernels_match_reference_modules_golden(name):
+    """csrc/loss.cu against values + autograd gradients produced by the reference's OWN
+    utils/slam_utils.py (tests/golden/make_loop_golden.py -> loop_golden.pt): pins §8f row 2."""
+    import os
+    from helpers import GOLDEN
+    G = torch.load(os.path.join(GOLDEN, "loop_golden.pt"), weights_only=False)
+    i, c = G["loss_inputs"], G["loss_cases"][name]
+    H, W = i["image"].shape[-2:]
+    cam = syn.Camera(W, H, 100.0, 100.0, W / 2, H / 2, device=DEV)
+    cam.exposure_a.data.fill_(i["exposure_a"]); cam.exposure_b.data.fill_(i["exposure_b"])
+    im, de, op = (i[k].to(DEV).clone().requires_grad_(True) for k in ("image", "depth", "opacity"))
+    gt_i, gt_d, gmask = i["gt_image"].to(DEV), i["gt_depth"].to(DEV), i["grad_mask"].to(DEV)
+    if name == "mapping_rgbd":
+        loss = losses.get_loss_mapping_rgbd(im, de, cam, gt_i, gt_d)
+    elif name == "mapping_rgbd_init":
+        loss = losses.get_loss_mapping_rgbd(im, de, cam, gt_i, gt_d, initialization=True)
+    elif name == "mapping_rgb":
+        loss = losses.get_loss_mapping_rgb(im, cam, gt_i)
+    elif name == "tracking_rgbd":
+        loss = losses.get_loss_tracking_rgbd(im, de, op, cam, gt_i, gt_d, grad_mask=gmask)
+    else:
+        loss = losses.get_loss_tracking_rgb(im, op, cam, gt_i, grad_mask=gmask)
+    (c["upstream"] * loss).backward()
+    z = lambda t, like: t.cpu() if t is not None else torch.zeros_like(like).cpu()
+    assert torch.allclose(loss.detach().cpu(), c["loss"], rtol=2e-6), name
+    assert torch.allclose(z(im.grad, im), c["d_image"], rtol=1e-5, atol=1e-10), name
+    assert torch.allclose(z(de.grad, de), c["d_depth"], rtol=1e-5, atol=1e-10), name
+    # q1 (the rasterizer drops dL/dopacity) is the rasterizer's business: the loss kernel returns it
+    assert torch.allclose(z(op.grad, op), c["d_opacity"], rtol=1e-5, atol=1e-9), name
+    assert torch.allclose(z(cam.exposure_a.grad, cam.exposure_a), c["d_exposure_a"], rtol=1e-4, atol=1e-8), name
+    assert torch.allclose(z(cam.exposure_b.grad, cam.exposure_b), c["d_exposure_b"], rtol=1e-4, atol=1e-8), name
+
+
+def test_device_pose_update_matches_reference_modules_golden():
+    """b2gs_pose_update against utils/pose_utils.update_pose + utils/camera_utils.Camera run from the
+    reference's own modules (loop_golden.pt)."""
+    import os
+    from helpers import GOLDEN
+    G = torch.load(os.path.join(GOLDEN, "loop_golden.pt"), weights_only=False)
+    k = G["intrinsics"]
+    for p in G["poses"]:
+        cam = syn.Camera(k["W"], k["H"], k["fx"], k["fy"], k["cx"], k["cy"], w2c=p["w2c"], device=DEV)
+        cam.cam_trans_delta.data.copy_(p["tau"][:3]); cam.cam_rot_delta.data.copy_(p["tau"][3:])
+        assert cam.update_pose() == p["converged"]
+        assert torch.allclose(cam.R, p["R"], atol=2e-6) and torch.allclose(cam.T, p["T"], atol=2e-6)
+        assert torch.allclose(cam.world_view_transform.cpu(), p["view"], atol=2e-6)
+        assert torch.allclose(cam.full_proj_transform.cpu(), p["full"], atol=2e-5)
+        assert torch.allclose(cam.camera_center.cpu(), p["center"], atol=5e-6)
+
+
 def test_fused_loss_monocular_and_initialization():
     image, depth, opacity, gt_image, gt_depth, cam = _loss_inputs()
     mask = (gt_image.sum(0) > 0.01).view(1, *gt_image.shape[1:])

@@ -127,12 +127,12 @@ def test_cfg3_mapping_window_matches_reference_loop(graph):
             if s == 0:
                 # densification statistics of ONE step from identical parameters: nothing has drifted yet
                 torch.cuda.synchronize()
-                d0 = float((gm.denom != gr.denom).float().mean())
-                r0 = float((gm.max_radii2D != gr.max_radii2D).float().mean())
                 sc0 = float(gr.xyz_gradient_accum.abs().max())
-                a0 = float(((gm.xyz_gradient_accum - gr.xyz_gradient_accum).abs() >
-                            1e-4 * gr.xyz_gradient_accum.abs() + 1e-4 * sc0).float().mean())
-                stats0 = (d0, r0, a0)
+                off0 = lambda g: (float((g.denom != gr.denom).float().mean()),
+                                  float((g.max_radii2D != gr.max_radii2D).float().mean()),
+                                  float(((g.xyz_gradient_accum - gr.xyz_gradient_accum).abs() >
+                                         1e-4 * gr.xyz_gradient_accum.abs() + 1e-4 * sc0).float().mean()))
+                stats0, stats0_twin = off0(gm), off0(gr2)
             rel, rel_t = abs(lp_ - lr_) / abs(lr_), abs(lr2_ - lr_) / abs(lr_)
             report.append(f"step {s}: loss ref {lr_:.8f} product {lp_:.8f} rel {rel:.2e} (reference twin rel {rel_t:.2e})")
             if rel > max(1e-5, 4 * rel_t):
@@ -162,11 +162,14 @@ def test_cfg3_mapping_window_matches_reference_loop(graph):
                     float(((g.xyz_gradient_accum - gr.xyz_gradient_accum).abs() >
                            1e-4 * gr.xyz_gradient_accum.abs() + 1e-4 * acc_scale).float().mean()))
         sp, st = stat_off(gm), stat_off(gr2)
-        report.append(f"densify stats after step 0: denom off {stats0[0]:.2e}, max_radii2D off {stats0[1]:.2e}, accum off {stats0[2]:.2e}")
+        report.append(f"densify stats after step 0: denom off {stats0[0]:.2e} (twin {stats0_twin[0]:.2e}), max_radii2D off "
+                      f"{stats0[1]:.2e} (twin {stats0_twin[1]:.2e}), accum off {stats0[2]:.2e} (twin {stats0_twin[2]:.2e})")
         report.append(f"densify stats after {steps} steps: denom off {sp[0]:.2e} (twin {st[0]:.2e}), max_radii2D off {sp[1]:.2e} "
                       f"(twin {st[1]:.2e}), accum off {sp[2]:.2e} (twin {st[2]:.2e})")
         print("\n".join(report[steps:]))
-        assert stats0[0] < 1e-5 and stats0[1] < 1e-5 and stats0[2] < 1e-4, report[-2]
+        # one step from identical parameters: visibility / radii equal; the accumulated |dL_dmeans2D| is a sum of
+        # float atomics (1e-4 relative on most elements, the twin's own scatter as the bound for the rest)
+        assert stats0[0] < 1e-5 and stats0[1] < 1e-5 and stats0[2] < max(1e-4, 4 * stats0_twin[2]), report[-2]
         assert sp[0] < max(1e-4, 4 * st[0]) and sp[1] < max(1e-4, 4 * st[1]) and sp[2] < max(1e-3, 4 * st[2]), report[-1]
     finally:
         rz.set_sync_free(False)
