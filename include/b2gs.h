@@ -130,9 +130,9 @@ typedef struct B2gsBackwardIO {
   const int32_t* radii;    /* device [P], from the forward */
   /* outputs: every row is written by the library (zeros for culled Gaussians);
    * pointers marked optional may be NULL to skip that output. */
-  float* dL_dmeans3D;   /* [P,3] */
+  float* dL_dmeans3D;   /* [P,3]; may be NULL (pose-only backward) */
   float* dL_dmeans2D;   /* [P,3] optional (z always 0; x,y scaled by W/2, H/2 — CR/backward.cu:643-644) */
-  float* dL_dopacity;   /* [P] */
+  float* dL_dopacity;   /* [P]; may be NULL (pose-only backward) */
   float* dL_dcolors;    /* [P,3] optional: gradient wrt colors_precomp */
   float* dL_dsh;        /* [P,M,3] optional: gradient wrt shs */
   float* dL_dscales;    /* [P,3] optional */
@@ -298,7 +298,9 @@ typedef struct B2gsViewFinalize {
   float* dL_dexposure;      /* [2] out (a, b), may be NULL */
 } B2gsViewFinalize;
 /* loss_total[0] = sum of the views' losses (view order), guard[0] = OR of the views' overflow flags
- * (either may be NULL).  `ticket`: one zero-initialised device word, left zero.  <= 32 views. */
+ * (either may be NULL).  `ticket`: FOUR zero-initialised device words: [0] is the launch's ticket
+ * (left zero), [2] accumulates the OR of every launch's overflow flag until the caller clears it (a
+ * tracking loop replays many iterations and looks once per frame).  <= 32 views. */
 B2GS_API int b2gs_window_finalize(const B2gsViewFinalize* views, int32_t n_views, float* loss_total,
                          int32_t* guard, uint32_t* ticket, void* stream);
 
@@ -312,6 +314,7 @@ typedef struct B2gsPoseCam {
   float* moments;              /* [16] exp_avg[8], exp_avg_sq[8] in the order rot, trans, a, b */
   float lr_rot, lr_trans, lr_exposure_a, lr_exposure_b;
   int32_t optimize_pose, optimize_exposure;
+  float* tau_norm;             /* optional [1]: |(rho, theta)| of this update (update_pose's convergence test) */
 } B2gsPoseCam;
 /* step_counter: device int64, incremented by the call (after use: the kernels read count + 1);
  * extra_tick: optional second device counter incremented alongside (the Gaussian optimizer's, when

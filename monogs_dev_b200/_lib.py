@@ -92,6 +92,7 @@ class B2gsPoseCam(C.Structure):
         ("dL_dtau", C.c_void_p), ("dL_dexposure", C.c_void_p), ("moments", C.c_void_p),
         ("lr_rot", C.c_float), ("lr_trans", C.c_float), ("lr_exposure_a", C.c_float),
         ("lr_exposure_b", C.c_float), ("optimize_pose", C.c_int32), ("optimize_exposure", C.c_int32),
+        ("tau_norm", C.c_void_p),
     ]
 
 

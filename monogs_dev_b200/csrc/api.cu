@@ -349,7 +349,7 @@ extern "C" int b2gs_backward(const B2gsScene* scene, const B2gsWorkspace* ws, in
     if (io->defer_tau && io->scratch) B2GS_CUDA(cudaMemsetAsync(io->scratch, 0, io->scratch_bytes, st));
     return B2GS_OK;
   }
-  if (!io->dL_dcolor || !io->dL_ddepth || !io->radii || !io->dL_dmeans3D || !io->dL_dopacity) {
+  if (!io->dL_dcolor || !io->dL_ddepth || !io->radii) {
     set_error("backward: required pointer is NULL");
     return B2GS_ERR_INVALID;
   }

@@ -178,9 +178,9 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
 
   if (idx < P && !live && !accumulate) {
     // culled: every gradient row is zero (reference: torch::zeros, DGR/rasterize_points.cu:160-170)
-    dL_dmeans3D[3 * idx] = 0.f; dL_dmeans3D[3 * idx + 1] = 0.f; dL_dmeans3D[3 * idx + 2] = 0.f;
+    if (dL_dmeans3D) { dL_dmeans3D[3 * idx] = 0.f; dL_dmeans3D[3 * idx + 1] = 0.f; dL_dmeans3D[3 * idx + 2] = 0.f; }
     if (dL_dmeans2D) { dL_dmeans2D[3 * idx] = 0.f; dL_dmeans2D[3 * idx + 1] = 0.f; dL_dmeans2D[3 * idx + 2] = 0.f; }
-    dL_dopacity[idx] = 0.f;
+    if (dL_dopacity) dL_dopacity[idx] = 0.f;
     if (dL_dcolors) { dL_dcolors[3 * idx] = 0.f; dL_dcolors[3 * idx + 1] = 0.f; dL_dcolors[3 * idx + 2] = 0.f; }
     if (dL_dsh && !RAW) for (int k = 0; k < 3 * M; ++k) dL_dsh[(size_t)idx * M * 3 + k] = 0.f;
     if (dL_dsh && RAW) {
@@ -451,16 +451,21 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
       const float o = act_sigmoid(op_raw);
       d_op *= o * (1.f - o);
     }
+    // (pose-only callers — tracking — pass NULL for the per-Gaussian outputs they do not want)
     if (accumulate) {
-      atomicAdd(&dL_dmeans3D[3 * idx], dmean.x);
-      atomicAdd(&dL_dmeans3D[3 * idx + 1], dmean.y);
-      atomicAdd(&dL_dmeans3D[3 * idx + 2], dmean.z);
-      atomicAdd(&dL_dopacity[idx], d_op);
+      if (dL_dmeans3D) {
+        atomicAdd(&dL_dmeans3D[3 * idx], dmean.x);
+        atomicAdd(&dL_dmeans3D[3 * idx + 1], dmean.y);
+        atomicAdd(&dL_dmeans3D[3 * idx + 2], dmean.z);
+      }
+      if (dL_dopacity) atomicAdd(&dL_dopacity[idx], d_op);
     } else {
-      dL_dmeans3D[3 * idx] = dmean.x;
-      dL_dmeans3D[3 * idx + 1] = dmean.y;
-      dL_dmeans3D[3 * idx + 2] = dmean.z;
-      dL_dopacity[idx] = d_op;
+      if (dL_dmeans3D) {
+        dL_dmeans3D[3 * idx] = dmean.x;
+        dL_dmeans3D[3 * idx + 1] = dmean.y;
+        dL_dmeans3D[3 * idx + 2] = dmean.z;
+      }
+      if (dL_dopacity) dL_dopacity[idx] = d_op;
     }
     if (dL_dmeans2D) {
       dL_dmeans2D[3 * idx] = dmean2D_x;

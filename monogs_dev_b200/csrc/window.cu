@@ -98,6 +98,7 @@ window_finalize_kernel(const __grid_constant__ FinalizeTable t, float* __restric
       }
       if (loss_total) loss_total[0] = (float)total;
       if (guard) guard[0] = (int32_t)over;
+      ticket[2] |= over;                     // sticky: "some launch since the caller cleared it overflowed"
       *ticket = 0u;                          // ready for the next launch
     }
   }
@@ -151,7 +152,7 @@ pose_step_kernel(const __grid_constant__ PoseTable t, long long* __restrict__ st
     }
     __syncwarp();
     if (k == 0 && c.optimize_pose)
-      pose_update_device(c.cam_state, c.projmatrix_raw, c.rot_delta, c.trans_delta, nullptr);
+      pose_update_device(c.cam_state, c.projmatrix_raw, c.rot_delta, c.trans_delta, c.tau_norm);
   }
   if (threadIdx.x == 0 && do_tick) {
     __threadfence();

@@ -857,8 +857,20 @@ class TrackingLoop:
     its convergence test); binning overflow is checked once per frame and the frame re-run."""
 
     def __init__(self, gaussians, camera, bg, lr_rot=0.003, lr_trans=0.001, lr_exposure=0.01, iters=100,
-                 cuda_graph=False, render_fn=None, loss_fn=None, adam_cls=FusedAdam):
+                 cuda_graph=False, render_fn=None, loss_fn=None, adam_cls=FusedAdam, lean=None, grad_mask=None):
+        """lean (default: whenever the loop is the stock one — packed-arena GaussianModel on the GPU,
+        camera.Camera, default renderer / RGB-D tracking loss, FusedAdam): an iteration is five libb2gs
+        launches sequences with no autograd graph and no torch kernel — b2gs_forward with the tracking
+        loss fused into the render epilogue, a pose-only b2gs_backward (no per-Gaussian output),
+        b2gs_window_finalize, b2gs_pose_step (window.LeanWindow(pose_only=True)).
+        grad_mask: optional [1,H,W] viewpoint.grad_mask buffer (utils/slam_utils.py:70)."""
         self.g, self.cam, self.bg, self.iters = gaussians, camera, bg, iters
+        stock = (isinstance(gaussians, GaussianModel) and gaussians.flat.is_cuda and render_fn is None
+                 and loss_fn is None and adam_cls is FusedAdam and hasattr(camera, "state"))
+        if lean and not stock:
+            raise RuntimeError("lean=True needs the stock tracking loop")
+        self._lean = None
+        use_lean = stock if lean is None else bool(lean)
         self.render_fn = render_fn or render_pose_only
         self.loss_fn = loss_fn or get_loss_tracking_rgbd
         self.cuda_graph = bool(cuda_graph)
@@ -868,7 +880,13 @@ class TrackingLoop:
         groups = [dict(params=[camera.cam_rot_delta], lr=lr_rot), dict(params=[camera.cam_trans_delta], lr=lr_trans),
                   dict(params=[camera.exposure_a], lr=lr_exposure), dict(params=[camera.exposure_b], lr=lr_exposure)]
         kw = dict(capturable=True) if (self.cuda_graph and adam_cls is FusedAdam) else {}
-        self.opt = adam_cls(groups, lr=0.0, eps=1e-8, **kw)
+        self.opt = None if use_lean else adam_cls(groups, lr=0.0, eps=1e-8, **kw)
+        if use_lean:
+            from .window import LeanWindow
+            from .losses import TRACKING_RGBD
+            self._kf = dict(cam=camera, gt_image=self.gt_image, gt_depth=self.gt_depth, grad_mask=grad_mask)
+            self._lean = LeanWindow(gaussians, [self._kf], [0], bg, (lr_rot, lr_trans, lr_exposure, lr_exposure),
+                                    lambda v: True, lambda v: True, mode=TRACKING_RGBD, pose_only=True)
         self._graph = None
         self.graph_launches = 0
         self.pkg = None
@@ -894,6 +912,8 @@ class TrackingLoop:
         return pkg, loss.detach(), conv
 
     def _reset_optimizer(self):
+        if self._lean is not None:
+            return self._lean.reset_camera_optimizer()
         for st in self.opt.state.values():
             if "exp_avg" in st:
                 st["exp_avg"].zero_()
@@ -912,11 +932,53 @@ class TrackingLoop:
             self.cam.exposure_a.fill_(exposure[0]); self.cam.exposure_b.fill_(exposure[1])
         self._reset_optimizer()
 
+    def _track_lean(self, iters, check_converged):
+        L = self._lean
+        L.ensure()
+        done = 0
+        if not self.cuda_graph:
+            while done < iters:
+                self.loss = L.forward_backward()
+                L.update(gaussians=False)
+                done += 1
+                if check_converged and float(L.tau_norm[0]) < 1e-4:      # the reference's per-iteration sync
+                    break
+        else:
+            if self._graph is None or L.ensure():
+                torch.cuda.synchronize()
+                self._graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(self._graph):
+                    self.loss = L.forward_backward()
+                    L.update(gaussians=False)
+                self.graph_launches = L.launches_fb + L.launches_up
+            for _ in range(iters):
+                self._graph.replay()
+        # one host sync per frame: did any iteration run out of binning capacity?  (an overflowed
+        # iteration rendered background only and skipped its own pose step on the device)
+        if int(L.tickets[2].item()):
+            L.tickets[2:3].zero_()
+            L.note_overflow([[int(L.status_all[0, 0].item()) * 2, 1]])
+            self._graph = None
+            self.cam.state.copy_(self._snap[0]); self.cam._host_RT = None
+            with torch.no_grad():
+                for p, q in zip((self.cam.cam_rot_delta, self.cam.cam_trans_delta, self.cam.exposure_a,
+                                 self.cam.exposure_b), self._snap[1]):
+                    p.copy_(q)
+            self._reset_optimizer()
+            return self._track_lean(iters, check_converged)
+        self.pkg = L.package(0)
+        self.pkg["visibility_filter"] = self.pkg["radii"] > 0      # once per frame, outside the iteration loop
+        return self.pkg
+
     def track(self, iters=None, check_converged=False):
         """runs the loop on the loaded frame; returns the last render package."""
         from . import rasterizer as rz
         from ._lib import lib
         iters = self.iters if iters is None else iters
+        if self._lean is not None:
+            self._snap = (self.cam.state.clone(), [p.detach().clone() for p in (
+                self.cam.cam_rot_delta, self.cam.cam_trans_delta, self.cam.exposure_a, self.cam.exposure_b)])
+            return self._track_lean(iters, check_converged)
         if not self.cuda_graph:
             for _ in range(iters):
                 self.pkg, self.loss, conv = self._iteration(check_converged)

@@ -40,8 +40,14 @@ class _View:
 
 class LeanWindow:
     def __init__(self, gaussians, keyframes, local, bg, pose_lr, moves, exposures, densify_stats=True,
-                 regulariser=True, rank=0, alpha=0.95, rgb_boundary_threshold=0.01, mode=MAPPING_RGBD):
+                 regulariser=True, rank=0, alpha=0.95, rgb_boundary_threshold=0.01, mode=MAPPING_RGBD,
+                 pose_only=False):
+        """pose_only: the map is frozen (tracking, utils/slam_frontend.py:128-196): the backward writes
+        no per-Gaussian gradient at all, only the pose / exposure gradients of the views."""
         self.g, self.kfs, self.local, self.bg = gaussians, keyframes, list(local), bg
+        self.pose_only = bool(pose_only)
+        if self.pose_only:
+            densify_stats = regulariser = False
         self.pose_lr, self.moves, self.exposures = pose_lr, moves, exposures
         self.densify_stats, self.regulariser, self.rank = densify_stats, regulariser, rank
         self.alpha, self.thr, self.mode = float(alpha), float(rgb_boundary_threshold), int(mode)
@@ -56,12 +62,19 @@ class LeanWindow:
         self.kf_grads = torch.zeros(n, 8, device=self.dev)   # per view: dL_dtau[6], dL_dexposure[2]
         self.kf_moments = torch.zeros(n, 16, device=self.dev)
         self.kf_step = torch.zeros(1, dtype=torch.int64, device=self.dev)
+        self.tau_norm = torch.zeros(n, device=self.dev)      # |tau| of each view's last pose update
         self.cap = {}                                        # view -> binning capacity (instances)
         self.views = {}
         self._arena_key = None
         self.launches_fb = self.launches_up = 0
 
     # -- (re)build: the argument structs hold raw pointers into the arenas ------------------------
+    def reset_camera_optimizer(self):
+        """a fresh keyframe / pose optimizer (zero moments, step 0), as torch.optim.Adam(opt_params)
+        is rebuilt per tracked frame (utils/slam_frontend.py:132-161)"""
+        self.kf_moments.zero_()
+        self.kf_step.zero_()
+
     def _key(self):
         g = self.g
         kf = tuple((self.kfs[v]["gt_image"].data_ptr(), self.kfs[v]["cam"].state.data_ptr(),
@@ -75,7 +88,7 @@ class LeanWindow:
         M = 1 + g._features_rest.shape[1]
         u8 = dict(dtype=torch.uint8, device=dev)
         f32 = dict(dtype=torch.float32, device=dev)
-        sinks = g.grad_sinks(self.densify_stats)
+        sinks = None if self.pose_only else g.grad_sinks(self.densify_stats)
         reg_view = self.local[0] if (self.regulariser and self.rank == 0 and self.local) else None
         self._keep = []
         for i, v in enumerate(self.local):
@@ -121,6 +134,7 @@ class LeanWindow:
             fl.args.gt_image, fl.args.gt_depth = kf["gt_image"].data_ptr(), ptr(kf.get("gt_depth"))
             fl.args.exposure_a = None if init else cam.exposure_a.data_ptr()
             fl.args.exposure_b = None if init else cam.exposure_b.data_ptr()
+            fl.args.grad_mask = ptr(kf.get("grad_mask"))      # tracking modes (viewpoint.grad_mask)
             fl.dL_dimage, fl.dL_ddepth, fl.partials = V.dL_dimage.data_ptr(), V.dL_ddepth.data_ptr(), V.partials.data_ptr()
             V.fused = fl
             V.gt = (kf["gt_image"], kf.get("gt_depth"))      # the captured pointers must stay alive
@@ -130,13 +144,14 @@ class LeanWindow:
                                         V.scratch.numel())
             io = _lib.B2gsBackwardIO()
             io.dL_dcolor, io.dL_ddepth, io.radii = V.dL_dimage.data_ptr(), V.dL_ddepth.data_ptr(), V.radii.data_ptr()
-            io.dL_dmeans3D, io.dL_dopacity = sinks.xyz.data_ptr(), sinks.opacity.data_ptr()
-            io.dL_dsh, io.dL_dsh_rest = sinks.f_dc.data_ptr(), ptr(sinks.f_rest)
-            io.dL_dscales, io.dL_drotations = sinks.scaling.data_ptr(), sinks.rotation.data_ptr()
+            if sinks is not None:
+                io.dL_dmeans3D, io.dL_dopacity = sinks.xyz.data_ptr(), sinks.opacity.data_ptr()
+                io.dL_dsh, io.dL_dsh_rest = sinks.f_dc.data_ptr(), ptr(sinks.f_rest)
+                io.dL_dscales, io.dL_drotations = sinks.scaling.data_ptr(), sinks.rotation.data_ptr()
+                io.densify_grad_accum, io.densify_denom = ptr(sinks.xyz_gradient_accum), ptr(sinks.denom)
+                io.max_radii2D = ptr(sinks.max_radii2D)
             io.scratch, io.scratch_bytes = V.scratch.data_ptr(), V.scratch.numel()
-            io.accumulate, io.scratch_zeroed, io.defer_tau = 1, 1, 1
-            io.densify_grad_accum, io.densify_denom = ptr(sinks.xyz_gradient_accum), ptr(sinks.denom)
-            io.max_radii2D = ptr(sinks.max_radii2D)
+            io.accumulate, io.scratch_zeroed, io.defer_tau = int(sinks is not None), 1, 1
             io.iso_reg_weight = 10.0 if v == reg_view else 0.0
             V.io = io
             nb = C.c_int32(0)
@@ -157,13 +172,14 @@ class LeanWindow:
             pc.moments = self.kf_moments[i].data_ptr()
             pc.lr_rot, pc.lr_trans, pc.lr_exposure_a, pc.lr_exposure_b = [float(x) for x in self.pose_lr]
             pc.optimize_pose, pc.optimize_exposure = int(self.moves(v)), int(self.exposures(v) and not init)
+            pc.tau_norm = self.tau_norm[i:i + 1].data_ptr()
             V.pose = pc
             V.cam = cam
             self.views[v] = V
         n = len(self.local)
         self._fin_arr = (_lib.B2gsViewFinalize * max(n, 1))(*[self.views[v].fin for v in self.local])
         self._pose_arr = (_lib.B2gsPoseCam * max(n, 1))(*[self.views[v].pose for v in self.local])
-        self._segs = self._segments()
+        self._segs = None if self.pose_only else self._segments()
         self._arena_key = self._key()
         for v in self.local:                                  # binning workspaces at the known capacities
             self._alloc_binning(v, self.cap.get(v))
@@ -260,12 +276,13 @@ class LeanWindow:
         state-changing kernel guarded by the overflow word of this step."""
         self.ensure()
         g = self.g
-        opt = g.optimizer
+        gaussians = gaussians and not self.pose_only
+        opt = g.optimizer if gaussians else None
         n0 = lib.b2gs_kernel_launches()
-        b1, b2 = self._betas
+        b1, b2 = self._betas if gaussians else (0.9, 0.999)
         with torch.cuda.device(self.dev):
             st = torch.cuda.current_stream().cuda_stream
-            if world > 1 and peer is None:
+            if world > 1 and peer is None and gaussians:
                 dist.all_reduce(g.flat_grad, op=dist.ReduceOp.SUM, group=group)
                 dist.all_reduce(self.guard, op=dist.ReduceOp.MAX, group=group)
             lib.b2gs_set_update_guard(self.guard.data_ptr())

@@ -326,6 +326,34 @@ def test_tracking_loop_recovers_pose_and_graph_matches_eager():
         rz.set_sync_free(False)
 
 
+def test_lean_tracking_loop_matches_autograd_route():
+    """TrackingLoop(lean=True) — tracking loss fused into the render epilogue, pose-only backward with no
+    per-Gaussian output, window_finalize, one pose_step kernel — against the autograd route over the
+    same kernels (render_pose_only + fused loss kernels + FusedAdam + b2gs_pose_update), 12 iterations."""
+    sc = syn.make_scene("cfg1_plumbing", device=DEV, n_views=1)
+    gm = mapping.GaussianModel(sc.xyz, sc.f_dc, sc.f_rest, sc.opacity, sc.scaling, sc.rotation, sh_degree=sc.sh_degree)
+    true_w2c = syn.se3_exp(torch.tensor([0.02, -0.015, 0.01, 0.004, -0.006, 0.003]))
+    cam_true = syn.Camera(sc.W, sc.H, 300.0, 300.0, 159.5, 119.5, w2c=true_w2c, device=DEV)
+    with torch.no_grad():
+        gt = mapping.render_pose_only(cam_true, gm, None, sc.bg)
+    res = []
+    for lean, graph in ((False, False), (True, False), (True, True)):
+        cam = syn.Camera(sc.W, sc.H, 300.0, 300.0, 159.5, 119.5, device=DEV)
+        loop = mapping.TrackingLoop(gm, cam, sc.bg, iters=12, cuda_graph=graph, lean=lean)
+        assert (loop._lean is not None) == lean
+        loop.load_frame(torch.eye(3), torch.zeros(3), gt["render"], gt["depth"])
+        pkg = loop.track()
+        torch.cuda.synchronize()
+        res.append((cam.R.clone(), cam.T.clone(), float(cam.exposure_a.detach()), float(cam.exposure_b.detach()), float(loop.loss)))
+        assert pkg["render"].shape == gt["render"].shape and pkg["visibility_filter"].dtype == torch.bool
+    for r in res[1:]:
+        assert torch.allclose(r[0], res[0][0], atol=2e-5) and torch.allclose(r[1], res[0][1], atol=2e-5), (r, res[0])
+        assert abs(r[2] - res[0][2]) < 2e-5 and abs(r[3] - res[0][3]) < 2e-5
+        assert abs(r[4] - res[0][4]) <= 1e-4 * abs(res[0][4])
+    assert float(gm.flat_grad.abs().max()) == 0.0
+    rz.set_sync_free(False)
+
+
 def test_densify_prune_config4_size_on_gpu():
     """BASELINE config 4: one densify_and_prune(max_grad=2e-4, min_opacity=0.7, extent=6.0,
     max_screen_size=20) on a 2M-Gaussian model with synthetic statistics, on the device."""

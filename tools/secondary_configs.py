@@ -90,30 +90,24 @@ def tracking():
         row["native_graph_ms_per_iter" if graph else "native_eager_ms_per_iter"] = best
     rz.set_sync_free(False)
     if ref_ext.available():
-        # the reference's loop (utils/slam_frontend.py:163-193): render -> torch loss -> backward ->
-        # torch Adam on the 4 camera tensors -> update_pose
-        cam = syn.Camera(sc.W, sc.H, cam0.fx, cam0.fy, cam0.cx, cam0.cy, device=DEV)
-        rgm = ref_ext.RefGaussianModel(sc.xyz, sc.f_dc, sc.f_rest, sc.opacity, sc.scaling, sc.rotation,
-                                       sh_degree=sc.sh_degree)
-        for p in rgm.parameters():
-            p.requires_grad_(False)
-        opt = torch.optim.Adam([dict(params=[cam.cam_rot_delta], lr=0.003), dict(params=[cam.cam_trans_delta], lr=0.001),
-                                dict(params=[cam.exposure_a], lr=0.01), dict(params=[cam.exposure_b], lr=0.01)])
-        kf = dict(gt_image=gt["render"], gt_depth=gt["depth"])
-
-        def it():
-            pkg = ref_ext.ref_render(cam, rgm, None, sc.bg)
-            loss = mapping.get_loss_tracking_rgbd_torch(pkg["render"], pkg["depth"], pkg["opacity"], cam,
-                                                        kf["gt_image"], kf["gt_depth"])
-            loss.backward()
-            opt.step()
-            opt.zero_grad()
-            try:
-                cam.update_pose(check_converged=False)
-            except TypeError:
-                cam.update_pose()
+        # the reference's loop (utils/slam_frontend.py:163-193) as restated in oracle/ref_loop.py: reference
+        # rasterizer, torch loss, torch Adam on the 4 camera tensors, torch update_pose, reference camera
+        from oracle import ref_loop
+        import synthdata
+        t = synthdata.scene_tensors("cfg2_tracking", n_views=1)
+        rgm = ref_loop.make_model(t, DEV)
+        rcam = ref_loop.RefCamera(1, t.W, t.H, t.fx, t.fy, t.cx, t.cy, device=DEV)
+        rloop = ref_loop.RefTrackingLoop(rgm, rcam, sc.bg, iters=100)
         try:
-            row["reference_ms_per_iter"] = timeit(it, 100, 5)
+            best = 1e9
+            for rep in range(2):
+                rloop.load_frame(torch.eye(3, device=DEV), torch.zeros(3, device=DEV), gt["render"], gt["depth"])
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                rloop.track()
+                torch.cuda.synchronize()
+                best = min(best, (time.perf_counter() - t0) * 1e3 / 100)
+            row["reference_ms_per_iter"] = best
             row["speedup"] = row["reference_ms_per_iter"] / row["native_graph_ms_per_iter"]
         except Exception as e:       # the reference-side loop is a convenience, never a blocker
             row["reference_error"] = repr(e)[:200]
