@@ -165,11 +165,11 @@ typedef struct B2gsBackwardIO {
 
 B2GS_API int b2gs_version(void);
 B2GS_API const char* b2gs_last_error(void);
-/* number of the library's own (hand-written) kernels launched so far in this process;
- * CUB sort/scan launches are not counted. */
+/* number of the library's kernels launched so far in this process (every kernel in the library is
+ * hand-written: no CUB / Thrust / cuBLAS call anywhere). */
 B2GS_API uint64_t b2gs_kernel_launches(void);
 
-/* Per-kernel timing: while enabled, every kernel (and CUB call) of the library is
+/* Per-kernel timing: while enabled, every kernel of the library is
  * bracketed by CUDA events on its launching stream.  b2gs_profile_read synchronises,
  * writes "name count total_ms" lines into buf and clears the records. */
 B2GS_API void b2gs_profile_enable(int on);

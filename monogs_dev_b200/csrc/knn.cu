@@ -15,9 +15,12 @@
 //  * one warp owns one 32-point leaf: pruning decisions are warp votes (no
 //    divergence), candidate leaves are loaded coalesced and broadcast from shared
 //    memory, the warp's own leaf / 1024-box / 32768-box are visited first so the
-//    pruning radius is tight before the global sweep.
+//    pruning radius is tight before the global sweep;
+//  * the Morton sort (thrust::sort_by_key there, KNN/simple_knn.cu:210-213) is an own
+//    stable LSD radix sort of the 30-bit codes: 4 passes of 8 bits, per pass a per-tile
+//    digit histogram, one scan, and a stable scatter whose in-tile ranks come from
+//    warp match_any votes (no library call anywhere in the library).
 #include "common.cuh"
-#include <cub/cub.cuh>
 #include <float.h>
 
 namespace b2gs {
@@ -32,9 +35,13 @@ struct KnnWS {
   uint32_t* idx_s;     // [P]
   float4* pts;         // [P] sorted points, w = original index bits
   Box* l0; Box* l1; Box* l2;
-  void* temp; size_t temp_bytes;
-  int n0, n1, n2;
+  uint32_t* hist;      // [256][tiles] digit counts of one radix pass, then their exclusive scan
+  int n0, n1, n2, tiles;
 };
+
+constexpr int RS_THREADS = 256;                       // 8 warps
+constexpr int RS_PER_WARP = 512;                      // consecutive keys owned by one warp
+constexpr int RS_TILE = (RS_THREADS / 32) * RS_PER_WARP;   // 4096 keys per block
 
 static KnnWS carve_knn(void* base, int32_t P, size_t* total) {
   Carver c(base);
@@ -52,10 +59,8 @@ static KnnWS carve_knn(void* base, int32_t P, size_t* total) {
   k.l0 = c.take<Box>(k.n0);
   k.l1 = c.take<Box>(k.n1);
   k.l2 = c.take<Box>(k.n2);
-  k.temp_bytes = 0;
-  cub::DeviceRadixSort::SortPairs(nullptr, k.temp_bytes, (const uint32_t*)nullptr, (uint32_t*)nullptr,
-                                  (const uint32_t*)nullptr, (uint32_t*)nullptr, (int)n);
-  k.temp = c.take<char>(k.temp_bytes);
+  k.tiles = (int)((n + RS_TILE - 1) / RS_TILE);
+  k.hist = c.take<uint32_t>((size_t)256 * k.tiles);
   if (total) *total = c.total();
   return k;
 }
@@ -127,6 +132,118 @@ __global__ void __launch_bounds__(256) knn_morton_kernel(int P, const float* __r
   }
   codes[i] = code;
   iota[i] = (uint32_t)i;
+}
+
+// ---- stable LSD radix sort of (code, index) pairs, 8 bits per pass ------------------------------
+// A block owns a tile of 4096 consecutive pairs, a warp 512 consecutive ones, so "tile order" is
+// warp-major and a pair's rank among equal digits is  (pairs of earlier tiles) + (earlier warps of the
+// tile) + (earlier rounds of the warp) + (lower lanes of the round) — every term a count, no sort
+// inside.  Lanes with the same digit find each other with __match_any_sync.
+__global__ void __launch_bounds__(RS_THREADS)
+radix_hist_kernel(int n, int shift, const uint32_t* __restrict__ keys, uint32_t* __restrict__ hist, int tiles) {
+  __shared__ uint32_t s_cnt[256];
+  s_cnt[threadIdx.x] = 0u;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const long long base = (long long)blockIdx.x * RS_TILE + (long long)warp * RS_PER_WARP;
+#pragma unroll 4
+  for (int r = 0; r < RS_PER_WARP / 32; ++r) {
+    const long long i = base + r * 32 + lane;
+    const bool ok = i < n;
+    const uint32_t d = ok ? (keys[i] >> shift) & 255u : 256u;     // 256: padding lanes group together
+    const uint32_t m = __match_any_sync(0xffffffffu, d);
+    if (ok && lane == __ffs(m) - 1) atomicAdd(&s_cnt[d], (uint32_t)__popc(m));
+  }
+  __syncthreads();
+  hist[(size_t)threadIdx.x * tiles + blockIdx.x] = s_cnt[threadIdx.x];
+}
+
+// one CTA: exclusive scan of hist in (digit-major, tile-minor) order = global start of every
+// (digit, tile) bucket
+__global__ void __launch_bounds__(1024) radix_scan_kernel(int total, uint32_t* __restrict__ hist) {
+  __shared__ uint32_t s_w[32];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int per = (total + 1023) / 1024;
+  const int lo = min(total, tid * per), hi = min(total, lo + per);
+  uint32_t mine = 0;
+  for (int i = lo; i < hi; ++i) mine += hist[i];
+  uint32_t incl = mine;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const uint32_t v = __shfl_up_sync(0xffffffffu, incl, d);
+    if (lane >= d) incl += v;
+  }
+  if (lane == 31) s_w[warp] = incl;
+  __syncthreads();
+  if (warp == 0) {
+    const uint32_t w = s_w[lane];
+    uint32_t wi = w;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t v = __shfl_up_sync(0xffffffffu, wi, d);
+      if (lane >= d) wi += v;
+    }
+    s_w[lane] = wi - w;
+  }
+  __syncthreads();
+  uint32_t run = s_w[warp] + incl - mine;
+  for (int i = lo; i < hi; ++i) {
+    const uint32_t c = hist[i];
+    hist[i] = run;
+    run += c;
+  }
+}
+
+__global__ void __launch_bounds__(RS_THREADS)
+radix_scatter_kernel(int n, int shift, const uint32_t* __restrict__ keys, const uint32_t* __restrict__ vals,
+                     const uint32_t* __restrict__ hist, int tiles, uint32_t* __restrict__ keys_out,
+                     uint32_t* __restrict__ vals_out) {
+  __shared__ uint32_t s_cnt[RS_THREADS / 32][256];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int d = lane; d < 256; d += 32) s_cnt[warp][d] = 0u;
+  __syncwarp();
+  const long long base = (long long)blockIdx.x * RS_TILE + (long long)warp * RS_PER_WARP;
+  constexpr int ROUNDS = RS_PER_WARP / 32;
+  uint32_t key[ROUNDS], val[ROUNDS];
+#pragma unroll
+  for (int r = 0; r < ROUNDS; ++r) {
+    const long long i = base + r * 32 + lane;
+    const bool ok = i < n;
+    key[r] = ok ? keys[i] : 0xffffffffu;
+    val[r] = ok ? vals[i] : 0u;
+    const uint32_t d = ok ? (key[r] >> shift) & 255u : 256u;
+    const uint32_t m = __match_any_sync(0xffffffffu, d);
+    if (ok && lane == __ffs(m) - 1) s_cnt[warp][d] += (uint32_t)__popc(m);   // one lane per digit group
+    __syncwarp();
+  }
+  __syncthreads();
+  {  // per digit: bucket start of this tile, then the warps of the tile in order
+    const int d = threadIdx.x;
+    uint32_t run = hist[(size_t)d * tiles + blockIdx.x];
+#pragma unroll
+    for (int w = 0; w < RS_THREADS / 32; ++w) {
+      const uint32_t c = s_cnt[w][d];
+      s_cnt[w][d] = run;
+      run += c;
+    }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int r = 0; r < ROUNDS; ++r) {
+    const long long i = base + r * 32 + lane;
+    const bool ok = i < n;
+    const uint32_t d = ok ? (key[r] >> shift) & 255u : 256u;
+    const uint32_t m = __match_any_sync(0xffffffffu, d);
+    uint32_t dst = 0;
+    if (ok) dst = s_cnt[warp][d] + (uint32_t)__popc(m & ((1u << lane) - 1u));
+    __syncwarp();
+    if (ok && lane == __ffs(m) - 1) s_cnt[warp][d] += (uint32_t)__popc(m);
+    __syncwarp();
+    if (ok) {
+      keys_out[dst] = key[r];
+      vals_out[dst] = val[r];
+    }
+  }
 }
 
 // gather into Morton order + leaf boxes (one warp per 32-point leaf)
@@ -319,10 +436,22 @@ extern "C" int b2gs_knn3_dist2(const float* points, int32_t P, float* out, void*
   knn_morton_kernel<<<blocks, 256, 0, st>>>(P, points, k.bbox, k.morton, k.iota);
   B2GS_LAUNCH_CHECK(st, 0);
   note_launches(2);
-  size_t tb = k.temp_bytes;
-  B2GS_CUDA(cub::DeviceRadixSort::SortPairs(k.temp, tb, (const uint32_t*)k.morton, k.morton_s,
-                                            (const uint32_t*)k.iota, k.idx_s, P, 0, 30, st));
-  knn_leaf_kernel<<<(k.n0 * 32 + 255) / 256, 256, 0, st>>>(P, points, k.idx_s, k.pts, k.l0);
+  {
+    // 30-bit codes: 4 passes of 8 bits, ping-ponging (morton, iota) <-> (morton_s, idx_s); an even
+    // number of passes leaves the sorted pairs in (morton, iota)
+    B2GS_PROF("knn_morton_sort", st);
+    uint32_t *ka = k.morton, *va = k.iota, *kb = k.morton_s, *vb = k.idx_s;
+    for (int shift = 0; shift < 32; shift += 8) {
+      radix_hist_kernel<<<k.tiles, RS_THREADS, 0, st>>>(P, shift, ka, k.hist, k.tiles);
+      radix_scan_kernel<<<1, 1024, 0, st>>>(256 * k.tiles, k.hist);
+      radix_scatter_kernel<<<k.tiles, RS_THREADS, 0, st>>>(P, shift, ka, va, k.hist, k.tiles, kb, vb);
+      uint32_t* t = ka; ka = kb; kb = t;
+      t = va; va = vb; vb = t;
+    }
+    B2GS_LAUNCH_CHECK(st, 0);
+    note_launches(11);
+  }
+  knn_leaf_kernel<<<(k.n0 * 32 + 255) / 256, 256, 0, st>>>(P, points, k.iota, k.pts, k.l0);
   knn_parent_kernel<<<(k.n1 * 32 + 255) / 256, 256, 0, st>>>(k.n0, k.l0, k.l1);
   knn_parent_kernel<<<(k.n2 * 32 + 255) / 256, 256, 0, st>>>(k.n1, k.l1, k.l2);
   B2GS_PROF("knn_search", st);
