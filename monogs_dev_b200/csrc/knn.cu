@@ -35,7 +35,8 @@ struct KnnWS {
   uint32_t* idx_s;     // [P]
   float4* pts;         // [P] sorted points, w = original index bits
   Box* l0; Box* l1; Box* l2;
-  uint32_t* hist;      // [256][tiles] digit counts of one radix pass, then their exclusive scan
+  uint32_t* hist;      // [256][tiles] digit counts of one radix pass, then their per-digit exclusive scan
+  uint32_t* totals;    // [256] keys per digit
   int n0, n1, n2, tiles;
 };
 
@@ -61,6 +62,7 @@ static KnnWS carve_knn(void* base, int32_t P, size_t* total) {
   k.l2 = c.take<Box>(k.n2);
   k.tiles = (int)((n + RS_TILE - 1) / RS_TILE);
   k.hist = c.take<uint32_t>((size_t)256 * k.tiles);
+  k.totals = c.take<uint32_t>(256);
   if (total) *total = c.total();
   return k;
 }
@@ -158,47 +160,44 @@ radix_hist_kernel(int n, int shift, const uint32_t* __restrict__ keys, uint32_t*
   hist[(size_t)threadIdx.x * tiles + blockIdx.x] = s_cnt[threadIdx.x];
 }
 
-// one CTA: exclusive scan of hist in (digit-major, tile-minor) order = global start of every
-// (digit, tile) bucket
-__global__ void __launch_bounds__(1024) radix_scan_kernel(int total, uint32_t* __restrict__ hist) {
-  __shared__ uint32_t s_w[32];
+// one CTA per digit: exclusive scan of that digit's row of per-tile counts (coalesced), row total to
+// totals[digit]; the scatter blocks turn the 256 totals into digit bases themselves
+constexpr int RS_SCAN_THREADS = 512;
+__global__ void __launch_bounds__(RS_SCAN_THREADS)
+radix_scan_kernel(int tiles, uint32_t* __restrict__ hist, uint32_t* __restrict__ totals) {
+  __shared__ uint32_t s_w[RS_SCAN_THREADS / 32];
+  __shared__ uint32_t s_carry;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int per = (total + 1023) / 1024;
-  const int lo = min(total, tid * per), hi = min(total, lo + per);
-  uint32_t mine = 0;
-  for (int i = lo; i < hi; ++i) mine += hist[i];
-  uint32_t incl = mine;
-#pragma unroll
-  for (int d = 1; d < 32; d <<= 1) {
-    const uint32_t v = __shfl_up_sync(0xffffffffu, incl, d);
-    if (lane >= d) incl += v;
-  }
-  if (lane == 31) s_w[warp] = incl;
+  uint32_t* row = hist + (size_t)blockIdx.x * tiles;
+  if (tid == 0) s_carry = 0u;
   __syncthreads();
-  if (warp == 0) {
-    const uint32_t w = s_w[lane];
-    uint32_t wi = w;
+  for (int t0 = 0; t0 < tiles; t0 += RS_SCAN_THREADS) {
+    const int t = t0 + tid;
+    const uint32_t c = t < tiles ? row[t] : 0u;
+    uint32_t incl = c;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
-      const uint32_t v = __shfl_up_sync(0xffffffffu, wi, d);
-      if (lane >= d) wi += v;
+      const uint32_t v = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += v;
     }
-    s_w[lane] = wi - w;
+    if (lane == 31) s_w[warp] = incl;
+    __syncthreads();
+    uint32_t before = s_carry;
+    for (int w = 0; w < warp; ++w) before += s_w[w];
+    if (t < tiles) row[t] = before + incl - c;
+    __syncthreads();
+    if (tid == RS_SCAN_THREADS - 1) s_carry = before + incl;
+    __syncthreads();
   }
-  __syncthreads();
-  uint32_t run = s_w[warp] + incl - mine;
-  for (int i = lo; i < hi; ++i) {
-    const uint32_t c = hist[i];
-    hist[i] = run;
-    run += c;
-  }
+  if (tid == 0) totals[blockIdx.x] = s_carry;
 }
 
 __global__ void __launch_bounds__(RS_THREADS)
 radix_scatter_kernel(int n, int shift, const uint32_t* __restrict__ keys, const uint32_t* __restrict__ vals,
-                     const uint32_t* __restrict__ hist, int tiles, uint32_t* __restrict__ keys_out,
-                     uint32_t* __restrict__ vals_out) {
+                     const uint32_t* __restrict__ hist, const uint32_t* __restrict__ totals, int tiles,
+                     uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out) {
   __shared__ uint32_t s_cnt[RS_THREADS / 32][256];
+  __shared__ uint32_t s_wsum[RS_THREADS / 32];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   for (int d = lane; d < 256; d += 32) s_cnt[warp][d] = 0u;
   __syncwarp();
@@ -217,9 +216,21 @@ radix_scatter_kernel(int n, int shift, const uint32_t* __restrict__ keys, const 
     __syncwarp();
   }
   __syncthreads();
-  {  // per digit: bucket start of this tile, then the warps of the tile in order
+  {  // per digit: digit base (exclusive scan of the 256 totals) + this tile's offset in the digit's
+     // row, then the warps of the tile in order
     const int d = threadIdx.x;
-    uint32_t run = hist[(size_t)d * tiles + blockIdx.x];
+    const uint32_t tot = totals[d];
+    uint32_t incl = tot;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += v;
+    }
+    if (lane == 31) s_wsum[warp] = incl;
+    __syncthreads();
+    uint32_t digit_base = incl - tot;
+    for (int w = 0; w < warp; ++w) digit_base += s_wsum[w];
+    uint32_t run = digit_base + hist[(size_t)d * tiles + blockIdx.x];
 #pragma unroll
     for (int w = 0; w < RS_THREADS / 32; ++w) {
       const uint32_t c = s_cnt[w][d];
@@ -443,8 +454,8 @@ extern "C" int b2gs_knn3_dist2(const float* points, int32_t P, float* out, void*
     uint32_t *ka = k.morton, *va = k.iota, *kb = k.morton_s, *vb = k.idx_s;
     for (int shift = 0; shift < 32; shift += 8) {
       radix_hist_kernel<<<k.tiles, RS_THREADS, 0, st>>>(P, shift, ka, k.hist, k.tiles);
-      radix_scan_kernel<<<1, 1024, 0, st>>>(256 * k.tiles, k.hist);
-      radix_scatter_kernel<<<k.tiles, RS_THREADS, 0, st>>>(P, shift, ka, va, k.hist, k.tiles, kb, vb);
+      radix_scan_kernel<<<256, RS_SCAN_THREADS, 0, st>>>(k.tiles, k.hist, k.totals);
+      radix_scatter_kernel<<<k.tiles, RS_THREADS, 0, st>>>(P, shift, ka, va, k.hist, k.totals, k.tiles, kb, vb);
       uint32_t* t = ka; ka = kb; kb = t;
       t = va; va = vb; vb = t;
     }
