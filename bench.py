@@ -409,7 +409,8 @@ def run_native(args):
     gm = mapping.GaussianModel(sc.xyz, sc.f_dc, sc.f_rest, sc.opacity, sc.scaling, sc.rotation,
                                sh_degree=sc.sh_degree)
     win = mapping.MappingWindow(gm, kfs, sc.bg, pose_lr=POSE_LR, cuda_graph=graph, view_streams=args.view_streams,
-                                peer_adam=world > 1 and not args.no_peer_adam)
+                                peer_adam=(args.peer_mode if args.peer_mode == "nomc" else True)
+                                if (world > 1 and not args.no_peer_adam) else False)
     local_views = win.local
     host = pinned_host_copies(kfs)
     e2e = E2E(win, kfs, host, local_views)
@@ -472,7 +473,8 @@ def run_native(args):
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {**config_common(name, n_views),
                    "parallelism": "keyframes sharded round-robin over %d rank(s)" % world + (
-                       "; gradient exchange + Adam + zero_grad as one kernel over NVLink peer memory"
+                       "; gradient exchange + Adam + zero_grad as one kernel over NVLink peer memory" + (
+                           " (NVLS multicast: multimem.ld_reduce / multimem.st)" if win.peer.multicast else " (plain P2P)")
                        if getattr(win, "peer", None) is not None else ""),
                    "launch": ("cuda graphs (no host sync inside a step: overflow flags are read back "
                               "asynchronously, flush() inside the timed region)" if graph else "eager") +
@@ -681,6 +683,9 @@ def main():
     ap.add_argument("--no-graph", action="store_true", help="native arm: eager launches instead of CUDA graphs")
     ap.add_argument("--no-peer-adam", action="store_true",
                     help="native arm, N>1: NCCL all-reduce + replicated Adam instead of the peer-memory step")
+    ap.add_argument("--peer-mode", default="mc", choices=["mc", "nomc"],
+                    help="native arm, N>1: peer-memory Adam over NVLS multicast (multimem.ld_reduce / multimem.st) "
+                         "where available, or plain peer loads / stores")
     ap.add_argument("--view-streams", type=int, default=8,
                     help="native arm: side streams the window's views are issued on (1 = serial)")
     args = ap.parse_args()
