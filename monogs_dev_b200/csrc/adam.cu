@@ -196,11 +196,17 @@ adam_peer_kernel(const __grid_constant__ AdamTable t, const __grid_constant__ Pe
   float* __restrict__ m = t.m[s];
   float* __restrict__ v = t.v[s];
   const long long poff = t.p[s] - pt.param[pt.rank], goff = t.g[s] - pt.grad[pt.rank];
-  const double step = (double)(*step_dev + ((flags & B2GS_ADAM_NO_TICK) ? 1 : 0));
-  const double bc1 = 1.0 - pow((double)beta1, step);
-  const float bc2_sqrt = (float)sqrt(1.0 - pow((double)beta2, step));
-  const float lr = t.lr_dev[s] ? t.lr_dev[s][0] : t.lr[s];
-  const float neg_step = (float)(-((double)lr / bc1));
+  // bias corrections: double-precision pow once per block, not once per thread
+  __shared__ float s_bc[2];
+  if (threadIdx.x == 0) {
+    const double step = (double)(*step_dev + ((flags & B2GS_ADAM_NO_TICK) ? 1 : 0));
+    const double bc1 = 1.0 - pow((double)beta1, step);
+    const float lr = t.lr_dev[s] ? t.lr_dev[s][0] : t.lr[s];
+    s_bc[0] = (float)sqrt(1.0 - pow((double)beta2, step));
+    s_bc[1] = (float)(-((double)lr / bc1));
+  }
+  __syncthreads();
+  const float bc2_sqrt = s_bc[0], neg_step = s_bc[1];
   const int W = pt.world;
 
   const bool vec = (((poff | goff) & 3) == 0) && ((((uintptr_t)m | (uintptr_t)v) & 15) == 0);
@@ -218,7 +224,6 @@ adam_peer_kernel(const __grid_constant__ AdamTable t, const __grid_constant__ Pe
     *reinterpret_cast<float4*>(m + i) = mm;
     *reinterpret_cast<float4*>(v + i) = vv;
     multimem_st(pt.param_mc + poff + i, pp);
-    multimem_st(pt.grad_mc + goff + i, make_float4(0.f, 0.f, 0.f, 0.f));
   } else if (vec && i + 4 <= end) {
     // all peers' loads in flight together (one NVLink round trip), then the sum in rank order
     float4 x[PEER_MAX];
@@ -241,17 +246,13 @@ adam_peer_kernel(const __grid_constant__ AdamTable t, const __grid_constant__ Pe
     adam_one(pp.w, gg.w, mm.w, vv.w, w1, beta2, w2, bc2_sqrt, eps, neg_step);
     *reinterpret_cast<float4*>(m + i) = mm;
     *reinterpret_cast<float4*>(v + i) = vv;
-    const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
     for (int r = 0; r < PEER_MAX; ++r)
-      if (r < W) {
-        __stcg(reinterpret_cast<float4*>(pt.param[r] + poff + i), pp);
-        __stcg(reinterpret_cast<float4*>(pt.grad[r] + goff + i), zero);
-      }
+      if (r < W) __stcg(reinterpret_cast<float4*>(pt.param[r] + poff + i), pp);
   } else {
     for (long long j = i; j < end && j < i + 4; ++j) {
       float g = 0.f;
-      for (int r = 0; r < W; ++r) { g = __fadd_rn(g, __ldcg(pt.grad[r] + goff + j)); __stcg(pt.grad[r] + goff + j, 0.f); }
+      for (int r = 0; r < W; ++r) g = __fadd_rn(g, __ldcg(pt.grad[r] + goff + j));
       float pp = pt.param[pt.rank][poff + j], mm = m[j], vv = v[j];
       adam_one(pp, g, mm, vv, w1, beta2, w2, bc2_sqrt, eps, neg_step);
       m[j] = mm; v[j] = vv;
@@ -409,8 +410,31 @@ extern "C" int b2gs_adam_step_peer_fused(const B2gsAdamSegment* segments, int32_
                                                       peers->fail_flag, flags);
     B2GS_LAUNCH_CHECK(st, 0);
   }
-  // ... and every replica / gradient arena has been written by all of its chunk owners
+  // ... and every replica has been written, every gradient arena read, by all of its chunk owners
   peer_barrier_kernel<<<1, 32, 0, st>>>(pt, peers->fail_flag, nullptr);
   B2GS_LAUNCH_CHECK(st, 0);
+  // zero_grad: every rank clears ITS OWN gradient arena (local HBM writes) now that all owners have
+  // read it — clearing it through the owners' remote stores would put a second arena's worth of
+  // zeros on every rank's NVLink ingress next to the parameter broadcast
+  {
+    const float* lo = nullptr; const float* hi = nullptr;
+    for (int k = 0; k < num_segments; ++k) {
+      if (segments[k].n <= 0) continue;
+      const float* a = segments[k].grad; const float* b = a + segments[k].n;
+      if (!lo || a < lo) lo = a;
+      if (!hi || b > hi) hi = b;
+    }
+    const float* base = pt.grad[pt.rank];
+    // the segments must form one arena (pads of < 4 floats between them): then it is one memset
+    long long covered = 0;
+    for (int k = 0; k < num_segments; ++k) covered += (segments[k].n + 3) / 4 * 4;
+    if (lo && (hi - lo) <= covered && lo >= base) {
+      B2GS_CUDA(cudaMemsetAsync(const_cast<float*>(lo), 0, (size_t)(hi - lo) * sizeof(float), st));
+    } else {
+      for (int k = 0; k < num_segments; ++k)
+        if (segments[k].n > 0)
+          B2GS_CUDA(cudaMemsetAsync(const_cast<float*>(segments[k].grad), 0, (size_t)segments[k].n * sizeof(float), st));
+    }
+  }
   return B2GS_OK;
 }
