@@ -122,6 +122,11 @@ typedef struct B2gsForwardOut {
    *   the visible Gaussians itself and b2gs_backward(scratch_zeroed = 1) skips its memset. */
   const struct B2gsFusedLoss* fused_loss;
   void* bwd_scratch; size_t bwd_scratch_bytes;
+  /* optional cudaEvent_t recorded on the stream after the binning stage (preprocess, scan, scatter,
+   * sort) and before the render kernel: lets a caller that issues several views on several streams
+   * start the NEXT view's HBM-bound front end when this view's issue-bound render begins, instead
+   * of all front ends first and all renders after (window.py: the views form a software pipeline). */
+  void* event_after_binning;
 } B2gsForwardOut;
 
 typedef struct B2gsBackwardIO {
@@ -159,8 +164,11 @@ typedef struct B2gsBackwardIO {
   /* iso_reg_weight != 0 (needs raw_params + accumulate): this call also adds the gradient of the
    * isotropic-scale regulariser  weight * mean|exp(s) - mean_row exp(s)|  (utils/slam_backend.py:
    * 229-231) to dL_dscales for EVERY Gaussian, visible or not, and leaves per-block partial sums of
-   * its value in slot 6 of the tau partial rows.  Give it to exactly one view of a step. */
+   * its value in slot 6 of the tau partial rows.  Give it to exactly one view of a step — or, with
+   * data-parallel ranks, to one view per rank with iso_reg_stride = world and iso_reg_offset = rank:
+   * the call then covers only the Gaussians i with i % stride == offset (stride 0 means all). */
   float iso_reg_weight;
+  int32_t iso_reg_stride, iso_reg_offset;
 } B2gsBackwardIO;
 
 B2GS_API int b2gs_version(void);

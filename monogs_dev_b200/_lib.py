@@ -38,6 +38,7 @@ class B2gsForwardOut(C.Structure):
         ("color", C.c_void_p), ("depth", C.c_void_p), ("opacity", C.c_void_p),
         ("radii", C.c_void_p), ("n_touched", C.c_void_p), ("status", C.c_void_p),
         ("fused_loss", C.c_void_p), ("bwd_scratch", C.c_void_p), ("bwd_scratch_bytes", C.c_size_t),
+        ("event_after_binning", C.c_void_p),
     ]
 
 
@@ -51,6 +52,7 @@ class B2gsBackwardIO(C.Structure):
         ("accumulate", C.c_int32), ("dL_dsh_rest", C.c_void_p), ("densify_grad_accum", C.c_void_p),
         ("densify_denom", C.c_void_p), ("max_radii2D", C.c_void_p),
         ("scratch_zeroed", C.c_int32), ("defer_tau", C.c_int32), ("iso_reg_weight", C.c_float),
+        ("iso_reg_stride", C.c_int32), ("iso_reg_offset", C.c_int32),
     ]
 
 

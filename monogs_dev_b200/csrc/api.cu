@@ -263,6 +263,8 @@ static int forward_back(const B2gsScene& s, const B2gsWorkspace* ws, const B2gsF
   BinWS b = carve_bin(ws->binning, cap, nullptr);
   int rc = launch_binning(s, g, im, b, cap, st);
   if (rc) return rc;
+  if (out->event_after_binning)
+    B2GS_CUDA(cudaEventRecord(reinterpret_cast<cudaEvent_t>(out->event_after_binning), st));
   return launch_render_fwd(s, g, im, b, *out, st);
 }
 

@@ -143,7 +143,7 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
                       const float* __restrict__ shs_rest, const float* __restrict__ opacities,
                       int accumulate, float* __restrict__ dL_dsh_rest,
                       float* __restrict__ st_grad_accum, float* __restrict__ st_denom,
-                      float* __restrict__ st_max_radii, float iso_w) {
+                      float* __restrict__ st_max_radii, float iso_w, int iso_stride, int iso_offset) {
   __shared__ float s_view[16], s_proj[16];
   __shared__ float s_tau[4][7];
   if (threadIdx.x < 16) s_view[threadIdx.x] = viewmatrix[threadIdx.x];
@@ -484,7 +484,7 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
   // ---- isotropic-scale regulariser (utils/slam_backend.py:229-231), every Gaussian, visible or
   // not: value partial + gradient wrt the raw log-scales added to the gradient arena ----
   float reg = 0.f;
-  if (RAW && iso_w != 0.f && idx < P) {
+  if (RAW && iso_w != 0.f && idx < P && (iso_stride <= 1 || idx % iso_stride == iso_offset)) {
     const float s0 = expf(s_in.x), s1 = expf(s_in.y), s2 = expf(s_in.z);
     const float m = (s0 + s1 + s2) / 3.0f;
     const float d0 = s0 - m, d1 = s1 - m, d2 = s2 - m;
@@ -556,7 +556,8 @@ int launch_preprocess_bwd(const B2gsScene& s, const GeomWS& g, const B2gsBackwar
       s.shs ? io.dL_dsh : nullptr, io.dL_dscales, io.dL_drotations, io.dL_dcov3D, partials,
       s.shs_rest, s.opacities, io.accumulate, io.dL_dsh_rest, io.densify_grad_accum,
       io.densify_denom, io.max_radii2D,
-      io.iso_reg_weight != 0.f ? io.iso_reg_weight / (3.0f * (float)s.P) : 0.f);
+      io.iso_reg_weight != 0.f ? io.iso_reg_weight / (3.0f * (float)s.P) : 0.f, io.iso_reg_stride,
+      io.iso_reg_offset);
   B2GS_LAUNCH_CHECK(st, s.debug);
   if (io.dL_dtau) {   // defer_tau callers hand the partial rows to b2gs_window_finalize instead
     tau_finalize_kernel<<<1, 256, 0, st>>>(blocks, partials, io.dL_dtau);

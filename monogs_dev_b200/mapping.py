@@ -468,7 +468,7 @@ class MappingWindow:
             self._lean = LeanWindow(gaussians, keyframes, self.local, bg, pose_lr, self._moves,
                                     lambda v: bool(self.kfs[v].get("optimize_exposure", True)),
                                     densify_stats=self.densify_stats, regulariser=self.regulariser,
-                                    rank=self.rank)
+                                    rank=self.rank, world=self.world)
         self.last = {}
         self._g1 = self._g2 = None
         self._ovf = self._status_all = None

@@ -41,15 +41,17 @@ class _View:
 class LeanWindow:
     def __init__(self, gaussians, keyframes, local, bg, pose_lr, moves, exposures, densify_stats=True,
                  regulariser=True, rank=0, alpha=0.95, rgb_boundary_threshold=0.01, mode=MAPPING_RGBD,
-                 pose_only=False):
+                 pose_only=False, world=1):
         """pose_only: the map is frozen (tracking, utils/slam_frontend.py:128-196): the backward writes
         no per-Gaussian gradient at all, only the pose / exposure gradients of the views."""
         self.g, self.kfs, self.local, self.bg = gaussians, keyframes, list(local), bg
         self.pose_only = bool(pose_only)
+        import os
+        self.stagger = os.environ.get("B2GS_STAGGER", "1") != "0"
         if self.pose_only:
             densify_stats = regulariser = False
         self.pose_lr, self.moves, self.exposures = pose_lr, moves, exposures
-        self.densify_stats, self.regulariser, self.rank = densify_stats, regulariser, rank
+        self.densify_stats, self.regulariser, self.rank, self.world = densify_stats, regulariser, rank, max(1, world)
         self.alpha, self.thr, self.mode = float(alpha), float(rgb_boundary_threshold), int(mode)
         self.dev = bg.device
         n = max(len(self.local), 1)
@@ -89,7 +91,11 @@ class LeanWindow:
         u8 = dict(dtype=torch.uint8, device=dev)
         f32 = dict(dtype=torch.float32, device=dev)
         sinks = None if self.pose_only else g.grad_sinks(self.densify_stats)
-        reg_view = self.local[0] if (self.regulariser and self.rank == 0 and self.local) else None
+        # the view-independent regulariser is counted once per step: every rank's first local view
+        # carries the Gaussians i with i % world == rank (its cost is spread over the ranks)
+        # (fewer keyframes than ranks: some rank has no view to carry its slice -> rank 0 takes all)
+        spread = len(self.kfs) >= self.world
+        reg_view = self.local[0] if (self.regulariser and self.local and (spread or self.rank == 0)) else None
         self._keep = []
         for i, v in enumerate(self.local):
             kf = self.kfs[v]
@@ -153,6 +159,7 @@ class LeanWindow:
             io.scratch, io.scratch_bytes = V.scratch.data_ptr(), V.scratch.numel()
             io.accumulate, io.scratch_zeroed, io.defer_tau = int(sinks is not None), 1, 1
             io.iso_reg_weight = 10.0 if v == reg_view else 0.0
+            io.iso_reg_stride, io.iso_reg_offset = (self.world, self.rank) if spread else (0, 0)
             V.io = io
             nb = C.c_int32(0)
             tau_ptr = lib.b2gs_backward_tau_partials(V.scratch.data_ptr(), P, C.byref(nb))
@@ -175,6 +182,7 @@ class LeanWindow:
             pc.tau_norm = self.tau_norm[i:i + 1].data_ptr()
             V.pose = pc
             V.cam = cam
+            V.event = old.event if old is not None and hasattr(old, "event") else torch.cuda.Event()
             self.views[v] = V
         n = len(self.local)
         self._fin_arr = (_lib.B2gsViewFinalize * max(n, 1))(*[self.views[v].fin for v in self.local])
@@ -258,9 +266,21 @@ class LeanWindow:
             side = list(side) if len(self.local) > 1 else []
             for s in side:
                 s.wait_stream(main)
+            prev_ev = None
             for i, v in enumerate(self.local):
                 V = self.views[v]
-                st = (side[i % len(side)] if side else main).cuda_stream
+                stream = side[i % len(side)] if side else main
+                st = stream.cuda_stream
+                # software pipeline over the views: view i's front end (preprocess .. sort: HBM- and
+                # latency-bound) starts when view i-1 has finished ITS front end, i.e. runs under view
+                # i-1's issue-bound render kernels, instead of all front ends competing first
+                if side and self.stagger and prev_ev is not None:
+                    stream.wait_event(prev_ev)
+                if side and self.stagger:
+                    V.out.event_after_binning = V.event.cuda_event
+                    prev_ev = V.event
+                else:
+                    V.out.event_after_binning = None
                 check(lib.b2gs_forward(C.byref(V.scene), C.byref(V.ws), C.byref(V.out), st))
                 check(lib.b2gs_backward(C.byref(V.scene), C.byref(V.ws), V.cap_real, C.byref(V.io), st))
             for s in side:
