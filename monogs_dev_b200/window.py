@@ -47,7 +47,9 @@ class LeanWindow:
         self.g, self.kfs, self.local, self.bg = gaussians, keyframes, list(local), bg
         self.pose_only = bool(pose_only)
         import os
-        self.stagger = os.environ.get("B2GS_STAGGER", "1") != "0"
+        # software pipeline over the views (B2gsForwardOut.event_after_binning): measured SLOWER than
+        # letting all views' kernels compete (cfg3, N=1: 4.77 vs 4.60 ms per step) -> opt-in only
+        self.stagger = os.environ.get("B2GS_STAGGER", "0") == "1"
         if self.pose_only:
             densify_stats = regulariser = False
         self.pose_lr, self.moves, self.exposures = pose_lr, moves, exposures
@@ -182,7 +184,11 @@ class LeanWindow:
             pc.tau_norm = self.tau_norm[i:i + 1].data_ptr()
             V.pose = pc
             V.cam = cam
-            V.event = old.event if old is not None and hasattr(old, "event") else torch.cuda.Event()
+            if old is not None and hasattr(old, "event"):
+                V.event = old.event
+            else:
+                V.event = torch.cuda.Event()
+                V.event.record()      # torch creates the CUDA event lazily: the library needs the handle
             self.views[v] = V
         n = len(self.local)
         self._fin_arr = (_lib.B2gsViewFinalize * max(n, 1))(*[self.views[v].fin for v in self.local])
