@@ -183,6 +183,11 @@ B2GS_API uint64_t b2gs_kernel_launches(void);
 B2GS_API void b2gs_profile_enable(int on);
 B2GS_API int b2gs_profile_read(char* buf, int cap);
 
+/* Programmatic dependent launch between the consecutive kernels of a call / a step (default on;
+ * environment B2GS_PDL=0 or b2gs_set_pdl(0) turns it off): hides the launch latency between
+ * dependent kernels, in eager streams and as programmatic edges of a captured CUDA graph. */
+B2GS_API void b2gs_set_pdl(int on);
+
 B2GS_API size_t b2gs_geom_bytes(int32_t P);
 B2GS_API size_t b2gs_image_bytes(int32_t W, int32_t H);
 B2GS_API size_t b2gs_binning_bytes(int64_t R, int32_t W, int32_t H);

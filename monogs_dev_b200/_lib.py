@@ -166,6 +166,7 @@ SYMBOLS = {
                                  C.c_float, C.c_float, C.c_void_p]),
     "b2gs_set_update_guard": (None, [C.c_void_p]),
     "b2gs_debug_set_counters": (None, [C.c_void_p]),
+    "b2gs_set_pdl": (None, [C.c_int]),
     "b2gs_backproject_rgbd": (C.c_int, [C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                         C.c_double, C.c_double, C.c_double, C.c_double,
                                         C.POINTER(C.c_double), C.c_float, C.c_void_p, C.c_void_p,

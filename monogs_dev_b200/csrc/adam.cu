@@ -41,6 +41,7 @@ __global__ void __launch_bounds__(256)
 adam_kernel(const __grid_constant__ AdamTable t, float w1, float beta2, float w2, float bc2_sqrt,
             float eps, float beta1, const long long* __restrict__ step_dev,
             const int32_t* __restrict__ guard, int flags) {
+  pdl_wait();
   if (guard && *guard) return;   // the step is being discarded (b2gs_set_update_guard)
   const bool zero = flags & B2GS_ADAM_ZERO_GRAD;
   // which segment does this block's chunk belong to?
@@ -101,6 +102,7 @@ adam_kernel(const __grid_constant__ AdamTable t, float w1, float beta2, float w2
 }
 
 __global__ void adam_tick_kernel(long long* step, const int32_t* __restrict__ guard) {
+  pdl_wait();
   if (guard && *guard) return;
   *step += 1;
 }
@@ -146,6 +148,7 @@ __device__ __forceinline__ void multimem_st(float* mc_addr, float4 v) {
 // whether this step's update is discarded.
 __global__ void peer_barrier_kernel(const __grid_constant__ PeerTable pt, uint32_t* __restrict__ fail,
                                     int32_t* __restrict__ guard) {
+  pdl_wait();
   const int t = threadIdx.x;
   const bool peer = t < pt.world && t != pt.rank;
   if (guard && t < pt.world) {
@@ -182,6 +185,7 @@ __global__ void __launch_bounds__(256)
 adam_peer_kernel(const __grid_constant__ AdamTable t, const __grid_constant__ PeerTable pt, float w1,
                  float beta2, float w2, float eps, float beta1, const long long* __restrict__ step_dev,
                  const int32_t* __restrict__ guard, const uint32_t* __restrict__ fail, int flags) {
+  pdl_wait();
   if (guard && *guard) return;   // some rank overflowed: every rank discards this step
   if (*fail) return;             // a barrier timed out: peers' arenas may not be final
   const long long chunk = (long long)blockIdx.x * pt.world + pt.rank;   // chunks this rank owns
@@ -274,7 +278,7 @@ static int adam_impl(const B2gsAdamSegment* segments, int32_t num_segments, int6
   if (step < 1) { set_error("b2gs_adam_step: step must be >= 1"); return B2GS_ERR_INVALID; }
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   if (step_dev && !(flags & B2GS_ADAM_NO_TICK)) {
-    adam_tick_kernel<<<1, 1, 0, st>>>(step_dev, update_guard());
+    B2GS_LAUNCH(adam_tick_kernel, 1, 1, st, step_dev, update_guard());
     B2GS_LAUNCH_CHECK(st, 0);
   }
   // scalar prep in double, as torch does in Python (torch/optim/adam.py)
@@ -311,8 +315,8 @@ static int adam_impl(const B2gsAdamSegment* segments, int32_t num_segments, int6
       long long total = 0;
       for (int q = 0; q < k; ++q) total += t.n[q];
       B2GS_PROF(total < 65536 ? "adam_small" : "adam", st);
-      adam_kernel<<<(unsigned)chunks, 256, 0, st>>>(t, w1, beta2, w2, bc2_sqrt, eps, beta1, step_dev,
-                                                        update_guard(), flags);
+      B2GS_LAUNCH(adam_kernel, (unsigned)chunks, 256, st, t, w1, beta2, w2, bc2_sqrt, eps, beta1,
+                  (const long long*)step_dev, update_guard(), flags);
       B2GS_LAUNCH_CHECK(st, 0);
     }
     done += k;
@@ -391,27 +395,26 @@ extern "C" int b2gs_adam_step_peer_fused(const B2gsAdamSegment* segments, int32_
   t.num = num_segments;
   // every rank's gradients are final ...  (the barrier also leaves the OR of all ranks' guard words
   // in *guard, and sets it when a peer timed out: the update below is then skipped on every rank)
-  peer_barrier_kernel<<<1, 32, 0, st>>>(pt, peers->fail_flag, guard);
+  B2GS_LAUNCH(peer_barrier_kernel, 1, 32, st, pt, peers->fail_flag, guard);
   B2GS_LAUNCH_CHECK(st, 0);
   // ... and only now may the step counter advance: with the rank-local guard value a rank whose own
   // forward did not overflow would tick while an overflowed rank does not, and the replicas' bias
   // corrections would diverge for good
   if (!(flags & B2GS_ADAM_NO_TICK)) {
-    adam_tick_kernel<<<1, 1, 0, st>>>(reinterpret_cast<long long*>(step_counter), guard);
+    B2GS_LAUNCH(adam_tick_kernel, 1, 1, st, reinterpret_cast<long long*>(step_counter), (const int32_t*)guard);
     B2GS_LAUNCH_CHECK(st, 0);
   }
   if (chunks > 0) {
     const long long blocks = (chunks + pt.world - 1) / pt.world;
     if (blocks > 0x7fffffffLL) { set_error("b2gs_adam_step_peer: too many elements"); return B2GS_ERR_INVALID; }
     B2GS_PROF("adam_peer", st);
-    adam_peer_kernel<<<(unsigned)blocks, 256, 0, st>>>(t, pt, (float)(1.0 - (double)beta1), beta2,
-                                                      (float)(1.0 - (double)beta2), eps, beta1,
-                                                      reinterpret_cast<const long long*>(step_counter), guard,
-                                                      peers->fail_flag, flags);
+    B2GS_LAUNCH(adam_peer_kernel, (unsigned)blocks, 256, st, t, pt, (float)(1.0 - (double)beta1), beta2,
+                (float)(1.0 - (double)beta2), eps, beta1, reinterpret_cast<const long long*>(step_counter),
+                (const int32_t*)guard, (const uint32_t*)peers->fail_flag, flags);
     B2GS_LAUNCH_CHECK(st, 0);
   }
   // ... and every replica has been written, every gradient arena read, by all of its chunk owners
-  peer_barrier_kernel<<<1, 32, 0, st>>>(pt, peers->fail_flag, nullptr);
+  B2GS_LAUNCH(peer_barrier_kernel, 1, 32, st, pt, peers->fail_flag, (int32_t*)nullptr);
   B2GS_LAUNCH_CHECK(st, 0);
   // zero_grad: every rank clears ITS OWN gradient arena (local HBM writes) now that all owners have
   // read it — clearing it through the owners' remote stores would put a second arena's worth of

@@ -10,6 +10,7 @@
 #include <map>
 #include <stdarg.h>
 #include <string.h>
+#include <stdlib.h>
 
 namespace b2gs {
 
@@ -21,6 +22,17 @@ const int32_t* update_guard() { return g_guard; }
 // process-wide, not thread-local: the backward runs on autograd's device thread
 static std::atomic<unsigned long long*> g_counters{nullptr};
 unsigned long long* debug_counters() { return g_counters.load(std::memory_order_relaxed); }
+
+static int pdl_from_env() {
+  const char* e = getenv("B2GS_PDL");
+  return (e && e[0] == '0') ? 0 : 1;
+}
+static std::atomic<int> g_pdl{-1};
+bool pdl_enabled() {
+  int v = g_pdl.load(std::memory_order_relaxed);
+  if (v < 0) { v = pdl_from_env(); g_pdl.store(v, std::memory_order_relaxed); }
+  return v != 0;
+}
 
 void note_launches(int n) { g_launches.fetch_add((unsigned long long)n, std::memory_order_relaxed); }
 
@@ -115,6 +127,8 @@ extern "C" void b2gs_set_update_guard(const int32_t* device_flag) { b2gs::g_guar
 extern "C" void b2gs_debug_set_counters(uint64_t* device_counters) {
   b2gs::g_counters.store(reinterpret_cast<unsigned long long*>(device_counters), std::memory_order_relaxed);
 }
+
+extern "C" void b2gs_set_pdl(int on) { b2gs::g_pdl.store(on ? 1 : 0, std::memory_order_relaxed); }
 
 extern "C" uint64_t b2gs_kernel_launches(void) { return g_launches.load(std::memory_order_relaxed); }
 

@@ -83,6 +83,7 @@ tile_scan_kernel(uint32_t tiles, long long cap, uint32_t* __restrict__ cursor,
                  uint32_t* __restrict__ status_out, uint32_t* __restrict__ order) {
   __shared__ uint32_t s_total;
   __shared__ uint32_t s_class[SCAN_CLASSES];   // tiles per length class, then the class cursors
+  pdl_wait();
   if (threadIdx.x < SCAN_CLASSES) s_class[threadIdx.x] = 0u;
   __syncthreads();
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -181,8 +182,8 @@ int launch_tile_scan(const B2gsScene& s, const ImageWS& im, int64_t cap, uint32_
                      cudaStream_t st) {
   const int gx = (s.W + TILE - 1) / TILE, gy = (s.H + TILE - 1) / TILE;
   B2GS_PROF("tile_scan", st);
-  tile_scan_kernel<<<1, SCAN_THREADS, 0, st>>>((uint32_t)(gx * gy), (long long)cap, im.cursor,
-                                               im.ranges, im.status, status_out, im.order);
+  B2GS_LAUNCH(tile_scan_kernel, 1, SCAN_THREADS, st, (uint32_t)(gx * gy), (long long)cap, im.cursor, im.ranges,
+              im.status, status_out, im.order);
   B2GS_LAUNCH_CHECK(st, s.debug);
   return B2GS_OK;
 }
@@ -202,6 +203,7 @@ scatter_instances_kernel(int P, uint32_t gx, const uint32_t* __restrict__ tiles_
   __shared__ WarpRects s_rects[8];
   __shared__ SplatCullBox s_cull[8][32];
   __shared__ uint32_t s_depth[8][32];
+  pdl_wait();
   if (status[1]) return;  // overflow: nothing may be written
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -320,6 +322,7 @@ __global__ void __launch_bounds__(SORT_THREADS)
 tile_sort_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ order,
                  uint64_t* __restrict__ keys, uint32_t* __restrict__ point_list) {
   __shared__ uint64_t s_keys[SORT_SMEM_KEYS];
+  pdl_wait();
   const uint2 r = ranges[order[blockIdx.x]];
   const uint32_t n = r.y - r.x;
   if (n == 0) return;
@@ -361,14 +364,15 @@ int launch_binning(const B2gsScene& s, const GeomWS& g, const ImageWS& im, const
   if (cap <= 0 || s.P == 0) return B2GS_OK;
   {
     B2GS_PROF("scatter_instances", st);
-    scatter_instances_kernel<<<(s.P + 255) / 256, 256, 0, st>>>(s.P, (uint32_t)gx, g.tiles_touched,
+    B2GS_LAUNCH(scatter_instances_kernel, (s.P + 255) / 256, 256, st, s.P, (uint32_t)gx, (const uint32_t*)g.tiles_touched,
                                                                g.rect, g.xy, g.conic_o, g.rgbd, im.cursor,
                                                                im.status,
                                                                b.keys);
     B2GS_LAUNCH_CHECK(st, s.debug);
   }
   B2GS_PROF("tile_sort", st);
-  tile_sort_kernel<<<gx * gy, SORT_THREADS, 0, st>>>(im.ranges, im.order, b.keys, b.point_list);
+  B2GS_LAUNCH(tile_sort_kernel, gx * gy, SORT_THREADS, st, (const uint2*)im.ranges, (const uint32_t*)im.order, b.keys,
+              b.point_list);
   B2GS_LAUNCH_CHECK(st, s.debug);
   return B2GS_OK;
 }

@@ -146,6 +146,7 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
                       float* __restrict__ st_max_radii, float iso_w, int iso_stride, int iso_offset) {
   __shared__ float s_view[16], s_proj[16];
   __shared__ float s_tau[4][7];
+  pdl_wait();
   if (threadIdx.x < 16) s_view[threadIdx.x] = viewmatrix[threadIdx.x];
   else if (threadIdx.x < 32) s_proj[threadIdx.x - 16] = projmatrix[threadIdx.x - 16];
   __syncthreads();
@@ -549,7 +550,7 @@ int launch_preprocess_bwd(const B2gsScene& s, const GeomWS& g, const B2gsBackwar
   float* partials = const_cast<float*>(acc) + (size_t)s.P * ACC_STRIDE;  // scratch tail
   B2GS_PROF("preprocess_bwd", st);
   auto kern = s.raw_params ? preprocess_bwd_kernel<true> : preprocess_bwd_kernel<false>;
-  kern<<<blocks, 128, 0, st>>>(
+  B2GS_LAUNCH(kern, blocks, 128, st,
       s.P, s.D, s.M, s.means3D, io.radii, s.shs, g.clamped, s.scales, s.rotations, s.scale_modifier,
       s.cov3D_precomp, s.viewmatrix, s.projmatrix, s.projmatrix_raw, s.campos, focal_x, focal_y,
       s.tan_fovx, s.tan_fovy, acc, io.dL_dmeans3D, io.dL_dmeans2D, io.dL_dopacity, io.dL_dcolors,

@@ -71,6 +71,7 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
                       float* __restrict__ acc_zero) {
   __shared__ float s_view[16], s_proj[16];
   __shared__ WarpRects s_rects[8];
+  pdl_wait();
   if (threadIdx.x < 16) s_view[threadIdx.x] = viewmatrix[threadIdx.x];
   else if (threadIdx.x < 32) s_proj[threadIdx.x - 16] = projmatrix[threadIdx.x - 16];
   __syncthreads();
@@ -222,7 +223,7 @@ int launch_preprocess_fwd(const B2gsScene& s, const GeomWS& g, const ImageWS& im
   const int blocks = (s.P + 255) / 256;
   B2GS_PROF("preprocess_fwd", st);
   auto kern = s.raw_params ? preprocess_fwd_kernel<true> : preprocess_fwd_kernel<false>;
-  kern<<<blocks, 256, 0, st>>>(
+  B2GS_LAUNCH(kern, blocks, 256, st,
       s.P, s.D, s.M, s.means3D, s.scales, s.scale_modifier, s.rotations, s.opacities, s.shs,
       s.cov3D_precomp, s.colors_precomp, s.viewmatrix, s.projmatrix, s.campos, s.W, s.H,
       s.tan_fovx, s.tan_fovy, focal_x, focal_y, gx, gy, s.prefiltered, s.shs_rest, radii,

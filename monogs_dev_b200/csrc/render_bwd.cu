@@ -105,6 +105,7 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   __shared__ SplatRec s_rec[RB_BATCH];
   __shared__ int s_max;
   unsigned c_visit = 0, c_full = 0, c_contrib = 0;
+  pdl_wait();
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int tile = (int)order[blockIdx.x];   // longest lists first (tile_scan_kernel)
@@ -285,11 +286,11 @@ int launch_render_bwd(const B2gsScene& s, const GeomWS& g, const ImageWS& im, co
   B2GS_PROF("render_bwd", st);
   unsigned long long* cnt = debug_counters();
   if (cnt)
-    render_bwd_kernel<true><<<gx * gy, RB_THREADS, 0, st>>>(im.ranges, im.order, b.point_list, s.W, s.H, gx, s.bg, g.xy,
+    B2GS_LAUNCH(render_bwd_kernel<true>, gx * gy, RB_THREADS, st, im.ranges, im.order, b.point_list, s.W, s.H, gx, s.bg, g.xy,
                                                             g.conic_o, g.rgbd, im.final_T, im.n_contrib,
                                                             io.dL_dcolor, io.dL_ddepth, acc, cnt);
   else
-    render_bwd_kernel<false><<<gx * gy, RB_THREADS, 0, st>>>(im.ranges, im.order, b.point_list, s.W, s.H, gx, s.bg, g.xy,
+    B2GS_LAUNCH(render_bwd_kernel<false>, gx * gy, RB_THREADS, st, im.ranges, im.order, b.point_list, s.W, s.H, gx, s.bg, g.xy,
                                                              g.conic_o, g.rgbd, im.final_T, im.n_contrib,
                                                              io.dL_dcolor, io.dL_ddepth, acc, nullptr);
   B2GS_LAUNCH_CHECK(st, s.debug);

@@ -51,6 +51,7 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   __shared__ SplatRec s_rec[RF_BATCH];
   unsigned c_visit = 0, c_full = 0, c_contrib = 0;
   __shared__ int s_cnt[RF_BATCH];
+  pdl_wait();
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int tile = (int)order[blockIdx.x];   // longest lists first (tile_scan_kernel)
@@ -246,7 +247,7 @@ int launch_render_fwd(const B2gsScene& s, const GeomWS& g, const ImageWS& im, co
   memset(&fl, 0, sizeof(fl));
   if (out.fused_loss) fl = *out.fused_loss;
 #define B2GS_RF_LAUNCH(C_, L_)                                                                        \
-  render_fwd_kernel<C_, L_><<<gx * gy, RF_THREADS, 0, st>>>(                                          \
+  B2GS_LAUNCH((render_fwd_kernel<C_, L_>), gx * gy, RF_THREADS, st,                                  \
       im.ranges, im.order, b.point_list, s.W, s.H, gx, g.xy, g.conic_o, g.rgbd, s.bg, im.final_T,     \
       im.n_contrib,                                                                                  \
       out.color, out.depth, out.opacity, out.n_touched, cnt, fl)

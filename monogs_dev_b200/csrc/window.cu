@@ -35,6 +35,7 @@ window_finalize_kernel(const __grid_constant__ FinalizeTable t, float* __restric
                        int32_t* __restrict__ guard, uint32_t* __restrict__ ticket) {
   __shared__ double s_red[WF_THREADS / 32][11];
   __shared__ bool s_last;
+  pdl_wait();
   const B2gsViewFinalize& v = t.v[blockIdx.x];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   // r[0..3]: loss partial sums, r[4..10]: tau[6] + regulariser.  Every thread's share is summed in a
@@ -129,6 +130,7 @@ pose_step_kernel(const __grid_constant__ PoseTable t, long long* __restrict__ st
   // every load of the kernel is issued up front (this kernel is pure latency): lane k < 8 its
   // parameter / gradient / moments, lanes 8..19 the camera block's R | T for the pose update
   __shared__ float s_rt[12];
+  pdl_wait();
   const int k = threadIdx.x;
   const bool have = (int)blockIdx.x < t.n;
   const B2gsPoseCam& c = t.c[have ? blockIdx.x : 0];
@@ -188,7 +190,7 @@ extern "C" int b2gs_window_finalize(const B2gsViewFinalize* views, int32_t n_vie
   t.n = n_views;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   B2GS_PROF("window_finalize", st);
-  window_finalize_kernel<<<n_views, WF_THREADS, 0, st>>>(t, loss_total, guard, ticket);
+  B2GS_LAUNCH(window_finalize_kernel, n_views, WF_THREADS, st, t, loss_total, guard, ticket);
   B2GS_LAUNCH_CHECK(st, 0);
   return B2GS_OK;
 }
@@ -220,9 +222,8 @@ extern "C" int b2gs_pose_step(const B2gsPoseCam* cams, int32_t n_cams, int64_t* 
     done += k;
     const int last = done >= n_cams;
     B2GS_PROF("pose_step", st);
-    pose_step_kernel<<<k > 0 ? k : 1, 32, 0, st>>>(t, reinterpret_cast<long long*>(step_counter),
-                                                   reinterpret_cast<long long*>(extra_tick), beta1, beta2,
-                                                   eps, last, update_guard(), ticket);
+    B2GS_LAUNCH(pose_step_kernel, k > 0 ? k : 1, 32, st, t, reinterpret_cast<long long*>(step_counter),
+                reinterpret_cast<long long*>(extra_tick), beta1, beta2, eps, last, update_guard(), ticket);
     B2GS_LAUNCH_CHECK(st, 0);
   } while (done < n_cams);
   return B2GS_OK;

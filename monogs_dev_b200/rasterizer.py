@@ -81,11 +81,13 @@ class RasterState:
     `num_rendered` is the binning capacity the backward must carve with: the exact
     instance count in the default two-call mode, the workspace capacity in sync-free mode
     (then `status` is the device [2] = (instances, overflow flag) the caller must check)."""
-    __slots__ = ("geom", "image", "binning", "num_rendered", "status", "key")
+    __slots__ = ("geom", "image", "binning", "num_rendered", "status", "key", "scene", "keep")
 
     def __init__(self):
         self.status = None
         self.key = None
+        self.scene = None      # the forward's B2gsScene (same pointers in backward: not rebuilt)
+        self.keep = None
 
 
 class _SyncFree:
@@ -158,6 +160,7 @@ def _forward_native(rs, means3D, sh, colors, opac, scales, rots, cov3D, sh_rest=
         keep = []
         scene = _scene_struct(rs, P, M, means3D, sh, colors, opac, scales, rots, cov3D, keep,
                               sh_rest=sh_rest, raw=raw)
+        st.scene, st.keep = scene, (keep, means3D, sh, colors, opac, scales, rots, cov3D, sh_rest)
         ws = _lib.B2gsWorkspace(st.geom.data_ptr(), st.geom.numel(), st.image.data_ptr(),
                                 st.image.numel(), None, 0)
         out = _lib.B2gsForwardOut(color.data_ptr(), depth.data_ptr(), opacity.data_ptr(),
@@ -245,22 +248,30 @@ class _RasterizeGaussians(torch.autograd.Function):
         def run():
             with torch.cuda.device(dev):
                 stream = torch.cuda.current_stream().cuda_stream
-                g_means3D = torch.empty(P, 3, **f32)
-                g_means2D = torch.empty(P, 3, **f32)
-                g_opac = torch.empty(P, 1, **f32)
-                g_colors = torch.empty(P, 3, **f32) if (colors is not None and need[3]) else None
-                g_sh = torch.empty(P, M, 3, **f32) if (sh is not None and need[2]) else None
+                # every gradient output is a slice of ONE allocation (rows 16 B aligned): the drop-in
+                # path at small P is bound by host time, and nine torch.empty calls are a third of it
                 want_sr = scales is not None and (need[5] or need[6])
-                g_scales = torch.empty(P, 3, **f32) if want_sr else None
-                g_rots = torch.empty(P, 4, **f32) if want_sr else None
-                g_cov3D = torch.empty(P, 6, **f32) if (cov3D is not None and need[7]) else None
-                g_tau = torch.empty(6, **f32)
+                widths = [3, 3, 1, 3 if (colors is not None and need[3]) else 0,
+                          3 * M if (sh is not None and need[2]) else 0, 3 if want_sr else 0, 4 if want_sr else 0,
+                          6 if (cov3D is not None and need[7]) else 0]
+                offs, total = [], 0
+                for w in widths:
+                    offs.append(total)
+                    total += (P * w + 3) // 4 * 4
+                flat = torch.empty(total + 8, **f32)
+                cut = lambda k, *shape: flat[offs[k]:offs[k] + P * widths[k]].view(*shape) if widths[k] else None
+                g_means3D, g_means2D, g_opac = cut(0, P, 3), cut(1, P, 3), cut(2, P, 1)
+                g_colors, g_sh = cut(3, P, 3), cut(4, P, M, 3)
+                g_scales, g_rots, g_cov3D = cut(5, P, 3), cut(6, P, 4), cut(7, P, 6)
+                g_tau = flat[total:total + 6]
                 if P == 0:
                     g_tau.zero_()
                     return g_means3D, g_means2D, g_sh, g_colors, g_opac, g_scales, g_rots, g_cov3D, g_tau
                 scratch = torch.empty(lib.b2gs_backward_scratch_bytes(P), dtype=torch.uint8, device=dev)
-                keep = []
-                scene = _scene_struct(rs, P, M, means3D, sh, colors, opac, scales, rots, cov3D, keep)
+                scene = st.scene        # built by the forward from the very tensors saved for backward
+                if scene is None:
+                    keep = []
+                    scene = _scene_struct(rs, P, M, means3D, sh, colors, opac, scales, rots, cov3D, keep)
                 ws = _lib.B2gsWorkspace(ptr(st.geom), st.geom.numel(), ptr(st.image),
                                         st.image.numel(), ptr(st.binning), st.binning.numel())
                 io = _lib.B2gsBackwardIO(
