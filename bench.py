@@ -559,8 +559,8 @@ def native_rooflines(win, gm, sc, kfs, local_views, world, device):
                 (BWD_HEAD + BWD_BLEND) * info["bwd_contributing"]
             roof["useful_frac"] = round(useful / (roof["avg_ms"] * 1e-3) / 1e12 / roof["peak"], 4)
     work = dict(P=P, P_visible=pvis, instances=R, effective_pairs=info["effective_pairs"],
-                **{k: info[k] for k in ("fwd_visit_px", "fwd_eval_px", "fwd_contributing", "bwd_visit_px",
-                                        "bwd_blend_px", "bwd_contributing")})
+                **{k: info[k] for k in ("fwd_visit_px", "fwd_eval_px", "fwd_contributing", "fwd_block_px",
+                                        "bwd_visit_px", "bwd_blend_px", "bwd_contributing")})
     return roof, rooftab, work
 
 

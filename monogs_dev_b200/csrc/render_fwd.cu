@@ -49,7 +49,7 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
                   float* __restrict__ out_opacity, int* __restrict__ n_touched,
                   unsigned long long* __restrict__ counters, const __grid_constant__ B2gsFusedLoss fl) {
   __shared__ SplatRec s_rec[RF_BATCH];
-  unsigned c_visit = 0, c_full = 0, c_contrib = 0;
+  unsigned c_visit = 0, c_full = 0, c_contrib = 0, c_blocks = 0;
   __shared__ int s_cnt[RF_BATCH];
   pdl_wait();
 
@@ -130,7 +130,7 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
           const f2 quad = fma2(bc(dx), bc(adx), cdy2);
           const f2 power = fma2(quad, bc(-0.5f), mul2(dy, bc(nbdx)));
           bool actA = !doneA && !(power.x > 0.0f), actB = !doneB && !(power.y > 0.0f);
-          if (COUNT) ++c_visit;
+          if (COUNT) { ++c_visit; c_blocks += __popc(r.bm & wmask); }
           if (!__any_sync(RF_FULL, actA || actB)) continue;
           if (COUNT) ++c_full;
           const f2 og = mul2(bc(co.w), expf_pair(power));
@@ -178,6 +178,7 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
       atomicAdd(&counters[0], (unsigned long long)c_visit);
       atomicAdd(&counters[1], (unsigned long long)c_full);
       atomicAdd(&counters[2], (unsigned long long)c_contrib);
+      atomicAdd(&counters[3], (unsigned long long)c_blocks);   // (splat, 8x4 block) pairs among the visits
     }
   }
   const size_t plane = (size_t)H * W;

@@ -823,7 +823,7 @@ class MappingWindow:
         c = cnt.tolist()
         return dict(visible=int((pkg["radii"] > 0).sum().item()), instances=inst,
                     effective_pairs=int(nc.long().sum().item()),
-                    fwd_visit_px=64 * c[0], fwd_eval_px=64 * c[1], fwd_contributing=c[2],
+                    fwd_visit_px=64 * c[0], fwd_eval_px=64 * c[1], fwd_contributing=c[2], fwd_block_px=32 * c[3],
                     bwd_visit_px=64 * c[4], bwd_blend_px=64 * c[5], bwd_contributing=c[6])
 
 
