@@ -21,7 +21,7 @@
 
 namespace b2gs {
 
-constexpr int WF_THREADS = 256;
+constexpr int WF_THREADS = 1024;
 constexpr int WF_MAX_VIEWS = 32;
 constexpr int PS_MAX_CAMS = 24;
 
@@ -40,22 +40,39 @@ window_finalize_kernel(const __grid_constant__ FinalizeTable t, float* __restric
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   // r[0..3]: loss partial sums, r[4..10]: tau[6] + regulariser.  Every thread's share is summed in a
   // fixed order and the cross-thread reduction order is fixed too: deterministic given the partials.
+  // The kernel is pure latency (a few hundred KB, one CTA per view): every load of a thread is
+  // issued before the first add (WF_ROWS rows per trip, all in flight together).
   double r[11] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+  constexpr int WF_ROWS = 4;
   if (v.loss_partials) {
     const float4* lp = reinterpret_cast<const float4*>(v.loss_partials);
-#pragma unroll 4
-    for (int i = threadIdx.x; i < v.loss_rows; i += WF_THREADS) {
-      const float4 p = __ldcg(lp + i);
-      r[0] += p.x; r[1] += p.y; r[2] += p.z; r[3] += p.w;
+    for (int i0 = threadIdx.x; i0 < v.loss_rows; i0 += WF_ROWS * WF_THREADS) {
+      float4 p[WF_ROWS];
+#pragma unroll
+      for (int u = 0; u < WF_ROWS; ++u) {
+        const int i = i0 + u * WF_THREADS;
+        p[u] = i < v.loss_rows ? __ldcg(lp + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+#pragma unroll
+      for (int u = 0; u < WF_ROWS; ++u) { r[0] += p[u].x; r[1] += p[u].y; r[2] += p[u].z; r[3] += p[u].w; }
     }
   }
   if (v.tau_partials) {
     const float4* tp = reinterpret_cast<const float4*>(v.tau_partials);
-#pragma unroll 4
-    for (int i = threadIdx.x; i < v.tau_rows; i += WF_THREADS) {
-      const float4 a = __ldcg(tp + 2 * i), b = __ldcg(tp + 2 * i + 1);
-      r[4] += a.x; r[5] += a.y; r[6] += a.z; r[7] += a.w;
-      r[8] += b.x; r[9] += b.y; r[10] += b.z;
+    for (int i0 = threadIdx.x; i0 < v.tau_rows; i0 += WF_ROWS * WF_THREADS) {
+      float4 a[WF_ROWS], b[WF_ROWS];
+#pragma unroll
+      for (int u = 0; u < WF_ROWS; ++u) {
+        const int i = i0 + u * WF_THREADS;
+        const bool ok = i < v.tau_rows;
+        a[u] = ok ? __ldcg(tp + 2 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
+        b[u] = ok ? __ldcg(tp + 2 * i + 1) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+#pragma unroll
+      for (int u = 0; u < WF_ROWS; ++u) {
+        r[4] += a[u].x; r[5] += a[u].y; r[6] += a[u].z; r[7] += a[u].w;
+        r[8] += b[u].x; r[9] += b[u].y; r[10] += b[u].z;
+      }
     }
   }
 #pragma unroll
