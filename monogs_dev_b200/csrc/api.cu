@@ -208,8 +208,7 @@ static int forward_front(const B2gsScene& s, const B2gsWorkspace* ws, const B2gs
     return B2GS_ERR_WORKSPACE;
   }
   const size_t tiles = (size_t)((s.W + TILE - 1) / TILE) * ((s.H + TILE - 1) / TILE);
-  // tile counters and the status block (visible-Gaussian count) in one fill: status follows cursor
-  B2GS_CUDA(cudaMemsetAsync(im.cursor, 0, (size_t)((char*)(im.status + 8) - (char*)im.cursor), st));
+  B2GS_CUDA(cudaMemsetAsync(im.cursor, 0, sizeof(uint32_t) * tiles * CURSOR_STRIDE, st));
   float* acc_zero = nullptr;
   if (out->bwd_scratch) {
     if (out->bwd_scratch_bytes < b2gs_backward_scratch_bytes(s.P)) {
@@ -389,7 +388,7 @@ extern "C" int b2gs_backward(const B2gsScene* scene, const B2gsWorkspace* ws, in
     rc = launch_render_bwd(s, g, im, b, *io, acc, st);
     if (rc) return rc;
   }
-  return launch_preprocess_bwd(s, g, *io, acc, im.status + 2, st);
+  return launch_preprocess_bwd(s, g, *io, acc, st);
 }
 
 namespace b2gs {

@@ -33,7 +33,6 @@ GeomWS carve_geom(void* base, int32_t P, size_t* total) {
   g.rect = c.take<ushort4>(n);
   g.tiles_touched = c.take<uint32_t>(n);
   g.clamped = c.take<uint8_t>(n);
-  g.vis_list = c.take<uint32_t>(n);
   if (total) *total = c.total();
   return g;
 }
@@ -200,22 +199,16 @@ scatter_instances_kernel(int P, uint32_t gx, const uint32_t* __restrict__ tiles_
                          const ushort4* __restrict__ rect, const float2* __restrict__ xy,
                          const float4* __restrict__ conic_o, const float4* __restrict__ rgbd,
                          uint32_t* __restrict__ cursor, const uint32_t* __restrict__ status,
-                         uint64_t* __restrict__ keys, const uint32_t* __restrict__ vis_list) {
+                         uint64_t* __restrict__ keys) {
   __shared__ WarpRects s_rects[8];
   __shared__ SplatCullBox s_cull[8][32];
   __shared__ uint32_t s_depth[8][32];
-  __shared__ uint32_t s_id[8][32];
   pdl_wait();
   if (status[1]) return;  // overflow: nothing may be written
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  // thread t takes the t-th VISIBLE Gaussian (GeomWS::vis_list): every lane of a warp has work
-  const int t = blockIdx.x * blockDim.x + threadIdx.x;
-  const int nvis = (int)status[2];
-  if (blockIdx.x * blockDim.x >= nvis) return;   // block-uniform
-  const int i = t < nvis ? (int)vis_list[t] : P;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
   uint32_t touched = 0, org = 0, w = 1;
   if (i < P) {
-    s_id[warp][lane] = (uint32_t)i;
     touched = tiles_touched[i];
     if (touched) {
       const ushort4 r = rect[i];
@@ -225,13 +218,14 @@ scatter_instances_kernel(int P, uint32_t gx, const uint32_t* __restrict__ tiles_
       s_cull[warp][lane] = splat_cull_setup(xy[i], conic_o[i]);
     }
   }
+  const uint32_t id0 = (uint32_t)(blockIdx.x * blockDim.x + warp * 32);   // id of lane 0's Gaussian
   warp_expand_rects<4>(
       s_rects[warp], lane, touched, org, w, gx,
       [&](uint32_t tile) { return atomicAdd(&cursor[tile * CURSOR_STRIDE], 1u); },
       [&](uint32_t slot, uint32_t tile, int owner) {
         const uint32_t ty = tile / gx, tx = tile - ty * gx;
         const uint32_t bm = splat_block_mask(s_cull[warp][owner], (float)(tx * TILE), (float)(ty * TILE));
-        keys[slot] = ((uint64_t)s_depth[warp][owner] << 32) | (s_id[warp][owner] << 8) | bm;
+        keys[slot] = ((uint64_t)s_depth[warp][owner] << 32) | ((id0 + (uint32_t)owner) << 8) | bm;
       });
 }
 
@@ -373,7 +367,7 @@ int launch_binning(const B2gsScene& s, const GeomWS& g, const ImageWS& im, const
     B2GS_LAUNCH(scatter_instances_kernel, (s.P + 255) / 256, 256, st, s.P, (uint32_t)gx, (const uint32_t*)g.tiles_touched,
                                                                g.rect, g.xy, g.conic_o, g.rgbd, im.cursor,
                                                                im.status,
-                                                               b.keys, (const uint32_t*)g.vis_list);
+                                                               b.keys);
     B2GS_LAUNCH_CHECK(st, s.debug);
   }
   B2GS_PROF("tile_sort", st);

@@ -125,10 +125,7 @@ __device__ __forceinline__ V3 sh_backward(int deg, int M, const float* __restric
   return dnormvdv3(dir_orig, V3{ddir[0], ddir[1], ddir[2]});
 }
 
-// COMPACT (accumulate mode): thread t works on the t-th VISIBLE Gaussian (GeomWS::vis_list) instead of
-// Gaussian t — culled rows need nothing in accumulate mode, and a warp of 32 consecutive ids would
-// spend its issue slots on its live lanes all the same (31 % of the rows are culled at cfg3).
-template <bool RAW, bool COMPACT>
+template <bool RAW>
 __global__ void __launch_bounds__(128, 6)
 preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
                       const int32_t* __restrict__ radii, const float* __restrict__ shs,
@@ -146,8 +143,7 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
                       const float* __restrict__ shs_rest, const float* __restrict__ opacities,
                       int accumulate, float* __restrict__ dL_dsh_rest,
                       float* __restrict__ st_grad_accum, float* __restrict__ st_denom,
-                      float* __restrict__ st_max_radii, float iso_w, int iso_stride, int iso_offset,
-                      const uint32_t* __restrict__ vis_list, const uint32_t* __restrict__ vis_count) {
+                      float* __restrict__ st_max_radii, float iso_w, int iso_stride, int iso_offset) {
   __shared__ float s_view[16], s_proj[16];
   __shared__ float s_tau[4][7];
   pdl_wait();
@@ -157,9 +153,7 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
   const float* view = s_view;
   const float* proj = s_proj;
 
-  const int tix = blockIdx.x * blockDim.x + threadIdx.x;
-  int idx = tix;
-  if (COMPACT) idx = tix < (int)*vis_count ? (int)vis_list[tix] : P;
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   float tau[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   // all per-Gaussian inputs are requested before the first dependent use (radius -> accumulator row
   // -> mean -> rotation / scale -> opacity ... would otherwise be a chain of DRAM round trips; the
@@ -491,10 +485,7 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
   // ---- isotropic-scale regulariser (utils/slam_backend.py:229-231), every Gaussian, visible or
   // not: value partial + gradient wrt the raw log-scales added to the gradient arena ----
   float reg = 0.f;
-  // (the regulariser covers EVERY Gaussian: it goes by the thread's own index, not the list's)
-  if (RAW && iso_w != 0.f && tix < P && (iso_stride <= 1 || tix % iso_stride == iso_offset)) {
-    const int idx = tix;
-    if (COMPACT) s_in = {scales[3 * idx], scales[3 * idx + 1], scales[3 * idx + 2]};
+  if (RAW && iso_w != 0.f && idx < P && (iso_stride <= 1 || idx % iso_stride == iso_offset)) {
     const float s0 = expf(s_in.x), s1 = expf(s_in.y), s2 = expf(s_in.z);
     const float m = (s0 + s1 + s2) / 3.0f;
     const float d0 = s0 - m, d1 = s1 - m, d2 = s2 - m;
@@ -552,15 +543,13 @@ __global__ void __launch_bounds__(256) tau_finalize_kernel(int blocks, const flo
 }
 
 int launch_preprocess_bwd(const B2gsScene& s, const GeomWS& g, const B2gsBackwardIO& io,
-                          const float* acc, const uint32_t* vis_count, cudaStream_t st) {
+                          const float* acc, cudaStream_t st) {
   const float focal_y = s.H / (2.0f * s.tan_fovy);
   const float focal_x = s.W / (2.0f * s.tan_fovx);
   const int blocks = (s.P + 127) / 128;
   float* partials = const_cast<float*>(acc) + (size_t)s.P * ACC_STRIDE;  // scratch tail
   B2GS_PROF("preprocess_bwd", st);
-  const bool compact = io.accumulate != 0;
-  auto kern = s.raw_params ? (compact ? preprocess_bwd_kernel<true, true> : preprocess_bwd_kernel<true, false>)
-                           : (compact ? preprocess_bwd_kernel<false, true> : preprocess_bwd_kernel<false, false>);
+  auto kern = s.raw_params ? preprocess_bwd_kernel<true> : preprocess_bwd_kernel<false>;
   B2GS_LAUNCH(kern, blocks, 128, st,
       s.P, s.D, s.M, s.means3D, io.radii, s.shs, g.clamped, s.scales, s.rotations, s.scale_modifier,
       s.cov3D_precomp, s.viewmatrix, s.projmatrix, s.projmatrix_raw, s.campos, focal_x, focal_y,
@@ -569,7 +558,7 @@ int launch_preprocess_bwd(const B2gsScene& s, const GeomWS& g, const B2gsBackwar
       s.shs_rest, s.opacities, io.accumulate, io.dL_dsh_rest, io.densify_grad_accum,
       io.densify_denom, io.max_radii2D,
       io.iso_reg_weight != 0.f ? io.iso_reg_weight / (3.0f * (float)s.P) : 0.f, io.iso_reg_stride,
-      io.iso_reg_offset, (const uint32_t*)g.vis_list, (const uint32_t*)vis_count);
+      io.iso_reg_offset);
   B2GS_LAUNCH_CHECK(st, s.debug);
   if (io.dL_dtau) {   // defer_tau callers hand the partial rows to b2gs_window_finalize instead
     tau_finalize_kernel<<<1, 256, 0, st>>>(blocks, partials, io.dL_dtau);

@@ -68,7 +68,7 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
                       int gy, int prefiltered,
                       const float* __restrict__ shs_rest, int32_t* __restrict__ radii,
                       int32_t* __restrict__ n_touched, uint32_t* __restrict__ tile_count, GeomWS g,
-                      float* __restrict__ acc_zero, uint32_t* __restrict__ vis_count) {
+                      float* __restrict__ acc_zero) {
   __shared__ float s_view[16], s_proj[16];
   __shared__ WarpRects s_rects[8];
   pdl_wait();
@@ -194,19 +194,6 @@ preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
     }
   }
 
-  // compacted list of the visible Gaussians (warp-aggregated append; order is arbitrary)
-  {
-    const int ln = threadIdx.x & 31;
-    const unsigned vm = __ballot_sync(0xffffffffu, visible);
-    if (vm) {
-      const int leader = __ffs(vm) - 1;
-      uint32_t base = 0;
-      if (ln == leader) base = atomicAdd(vis_count, (uint32_t)__popc(vm));
-      base = __shfl_sync(0xffffffffu, base, leader);
-      if (visible) g.vis_list[base + __popc(vm & ((1u << ln) - 1u))] = (uint32_t)idx;
-    }
-  }
-
   // instances per tile: the T counters become the tile ranges (binning.cu) — replaces the
   // P-wide InclusiveSum + identifyTileRanges (CR/rasterizer_impl.cu:280,116-138)
   const int lane = threadIdx.x & 31;
@@ -240,7 +227,7 @@ int launch_preprocess_fwd(const B2gsScene& s, const GeomWS& g, const ImageWS& im
       s.P, s.D, s.M, s.means3D, s.scales, s.scale_modifier, s.rotations, s.opacities, s.shs,
       s.cov3D_precomp, s.colors_precomp, s.viewmatrix, s.projmatrix, s.campos, s.W, s.H,
       s.tan_fovx, s.tan_fovy, focal_x, focal_y, gx, gy, s.prefiltered, s.shs_rest, radii,
-      n_touched, im.cursor, g, acc_zero, im.status + 2);
+      n_touched, im.cursor, g, acc_zero);
   B2GS_LAUNCH_CHECK(st, s.debug);
   return B2GS_OK;
 }
