@@ -342,9 +342,20 @@ B2GS_API int b2gs_pose_step(const B2gsPoseCam* cams, int32_t n_cams, int64_t* st
  *                        the update, e.g. b2gs_pose_step(extra_tick)) — saves the 1-thread tick launch. */
 #define B2GS_ADAM_ZERO_GRAD 1
 #define B2GS_ADAM_NO_TICK 2
+/* b2gs_adam_step_peer_fused only: */
+#define B2GS_ADAM_TICK_LATE 4         /* with NO_TICK: the SECOND barrier advances the counter (nothing else
+                                       * on the stream has to: the camera step can run beside the exchange) */
+#define B2GS_ADAM_NO_ZERO 8           /* leave this rank's gradient arena as it is: the caller clears it
+                                       * (b2gs_memset_async) off the critical path, before the next backward */
+#define B2GS_ADAM_NO_FIRST_BARRIER 16 /* the caller has already run b2gs_peer_barrier on this stream */
 B2GS_API int b2gs_adam_step_fused(const B2gsAdamSegment* segments, int32_t num_segments,
                          int64_t* step_counter, float beta1, float beta2, float eps, int32_t flags,
                          void* stream);
+/* The first of the two barriers of b2gs_adam_step_peer on its own: all ranks' streams meet, and the
+ * update guard of the calling thread (b2gs_set_update_guard) becomes the OR over all ranks. */
+B2GS_API int b2gs_peer_barrier(const B2gsPeerArena* peers, void* stream);
+/* cudaMemsetAsync through the C ABI (a step built from libb2gs calls only needs no framework kernel). */
+B2GS_API int b2gs_memset_async(void* device_ptr, int value, size_t bytes, void* stream);
 B2GS_API int b2gs_adam_step_peer_fused(const B2gsAdamSegment* segments, int32_t num_segments,
                               int64_t* step_counter, float beta1, float beta2, float eps,
                               const B2gsPeerArena* peers, int32_t flags, void* stream);

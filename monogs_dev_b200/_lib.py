@@ -183,6 +183,8 @@ SYMBOLS = {
     "b2gs_densify_apply": (C.c_int, [C.POINTER(B2gsDensifyArgs), C.c_void_p, C.POINTER(C.c_int64), C.c_void_p,
                                      C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
                                      C.POINTER(C.c_void_p), C.c_void_p]),
+    "b2gs_peer_barrier": (C.c_int, [C.POINTER(B2gsPeerArena), C.c_void_p]),
+    "b2gs_memset_async": (C.c_int, [C.c_void_p, C.c_int, C.c_size_t, C.c_void_p]),
     "b2gs_window_finalize": (C.c_int, [C.POINTER(B2gsViewFinalize), C.c_int32, C.c_void_p, C.c_void_p,
                                        C.c_void_p, C.c_void_p]),
     "b2gs_pose_step": (C.c_int, [C.POINTER(B2gsPoseCam), C.c_int32, C.c_void_p, C.c_void_p, C.c_float,

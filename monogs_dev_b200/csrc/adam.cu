@@ -147,7 +147,8 @@ __device__ __forceinline__ void multimem_st(float* mc_addr, float4 v) {
 // arriving, and leaves the OR over all ranks in its own guard word — the ranks then agree on
 // whether this step's update is discarded.
 __global__ void peer_barrier_kernel(const __grid_constant__ PeerTable pt, uint32_t* __restrict__ fail,
-                                    int32_t* __restrict__ guard) {
+                                    int32_t* __restrict__ guard, long long* __restrict__ tick,
+                                    const int32_t* __restrict__ tick_guard) {
   pdl_wait();
   const int t = threadIdx.x;
   const bool peer = t < pt.world && t != pt.rank;
@@ -177,6 +178,8 @@ __global__ void peer_barrier_kernel(const __grid_constant__ PeerTable pt, uint32
     any |= *(volatile uint32_t*)fail;
     *guard = (int32_t)any;
   }
+  // B2GS_ADAM_TICK_LATE: the step counter advances here, after every block of the update has read it
+  if (tick && t == 0 && !(tick_guard && *tick_guard) && !*(volatile uint32_t*)fail) *tick += 1;
 }
 
 constexpr int PEER_CHUNK = 1024;   // floats per ownership chunk = one float4 per thread of a block
@@ -395,8 +398,11 @@ extern "C" int b2gs_adam_step_peer_fused(const B2gsAdamSegment* segments, int32_
   t.num = num_segments;
   // every rank's gradients are final ...  (the barrier also leaves the OR of all ranks' guard words
   // in *guard, and sets it when a peer timed out: the update below is then skipped on every rank)
-  B2GS_LAUNCH(peer_barrier_kernel, 1, 32, st, pt, peers->fail_flag, guard);
-  B2GS_LAUNCH_CHECK(st, 0);
+  if (!(flags & B2GS_ADAM_NO_FIRST_BARRIER)) {
+    B2GS_LAUNCH(peer_barrier_kernel, 1, 32, st, pt, peers->fail_flag, guard, (long long*)nullptr,
+                (const int32_t*)nullptr);
+    B2GS_LAUNCH_CHECK(st, 0);
+  }
   // ... and only now may the step counter advance: with the rank-local guard value a rank whose own
   // forward did not overflow would tick while an overflowed rank does not, and the replicas' bias
   // corrections would diverge for good
@@ -414,8 +420,11 @@ extern "C" int b2gs_adam_step_peer_fused(const B2gsAdamSegment* segments, int32_
     B2GS_LAUNCH_CHECK(st, 0);
   }
   // ... and every replica has been written, every gradient arena read, by all of its chunk owners
-  B2GS_LAUNCH(peer_barrier_kernel, 1, 32, st, pt, peers->fail_flag, (int32_t*)nullptr);
+  B2GS_LAUNCH(peer_barrier_kernel, 1, 32, st, pt, peers->fail_flag, (int32_t*)nullptr,
+              (flags & B2GS_ADAM_TICK_LATE) ? reinterpret_cast<long long*>(step_counter) : (long long*)nullptr,
+              (const int32_t*)guard);
   B2GS_LAUNCH_CHECK(st, 0);
+  if (flags & B2GS_ADAM_NO_ZERO) return B2GS_OK;
   // zero_grad: every rank clears ITS OWN gradient arena (local HBM writes) now that all owners have
   // read it — clearing it through the owners' remote stores would put a second arena's worth of
   // zeros on every rank's NVLink ingress next to the parameter broadcast
@@ -439,5 +448,37 @@ extern "C" int b2gs_adam_step_peer_fused(const B2gsAdamSegment* segments, int32_
           B2GS_CUDA(cudaMemsetAsync(const_cast<float*>(segments[k].grad), 0, (size_t)segments[k].n * sizeof(float), st));
     }
   }
+  return B2GS_OK;
+}
+
+static int peer_table(const B2gsPeerArena* peers, b2gs::PeerTable* pt) {
+  if (!peers || peers->world < 1 || peers->world > b2gs::PEER_MAX || peers->rank < 0 || peers->rank >= peers->world ||
+      !peers->signal || !peers->fail_flag) {
+    b2gs::set_error("bad peer table");
+    return B2GS_ERR_INVALID;
+  }
+  memset(pt, 0, sizeof(*pt));
+  pt->world = peers->world; pt->rank = peers->rank;
+  for (int r = 0; r < pt->world; ++r) {
+    pt->signal[r] = peers->signal[r];
+    if (!pt->signal[r]) { b2gs::set_error("NULL signal pad"); return B2GS_ERR_INVALID; }
+  }
+  return B2GS_OK;
+}
+
+extern "C" int b2gs_peer_barrier(const B2gsPeerArena* peers, void* stream) {
+  b2gs::PeerTable pt;
+  int rc = peer_table(peers, &pt);
+  if (rc) return rc;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  B2GS_LAUNCH(b2gs::peer_barrier_kernel, 1, 32, st, pt, peers->fail_flag, const_cast<int32_t*>(b2gs::update_guard()),
+              (long long*)nullptr, (const int32_t*)nullptr);
+  B2GS_LAUNCH_CHECK(st, 0);
+  return B2GS_OK;
+}
+
+extern "C" int b2gs_memset_async(void* device_ptr, int value, size_t bytes, void* stream) {
+  if (!device_ptr && bytes) { b2gs::set_error("b2gs_memset_async: NULL pointer"); return B2GS_ERR_INVALID; }
+  B2GS_CUDA(cudaMemsetAsync(device_ptr, value, bytes, reinterpret_cast<cudaStream_t>(stream)));
   return B2GS_OK;
 }

@@ -29,7 +29,7 @@ from . import _lib
 from ._lib import lib, check, ptr
 from .losses import MAPPING_RGBD
 
-ADAM_ZERO_GRAD, ADAM_NO_TICK = 1, 2
+ADAM_ZERO_GRAD, ADAM_NO_TICK, ADAM_TICK_LATE, ADAM_NO_ZERO, ADAM_NO_FIRST_BARRIER = 1, 2, 4, 8, 16
 HEADROOM = 1.5
 
 
@@ -71,6 +71,12 @@ class LeanWindow:
         self.views = {}
         self._arena_key = None
         self.launches_fb = self.launches_up = 0
+        # peer mode: the gradient arena of a step is cleared at the START of the next one, on a side
+        # branch under the forward kernels (it is first needed by the backward), and the camera step
+        # runs beside the exchange: neither sits on the critical path of a one-view rank
+        self._aux_stream = None
+        self._zero_pending = False
+        self._zero_event = None
 
     # -- (re)build: the argument structs hold raw pointers into the arenas ------------------------
     def reset_camera_optimizer(self):
@@ -272,6 +278,12 @@ class LeanWindow:
             side = list(side) if len(self.local) > 1 else []
             for s in side:
                 s.wait_stream(main)
+            if self._zero_pending and not self.pose_only:
+                aux = self._aux()
+                aux.wait_stream(main)
+                g = self.g
+                check(lib.b2gs_memset_async(g.flat_grad.data_ptr(), 0, 4 * g.flat_grad.numel(), aux.cuda_stream))
+                self._zero_event.record(aux)
             prev_ev = None
             for i, v in enumerate(self.local):
                 V = self.views[v]
@@ -288,14 +300,24 @@ class LeanWindow:
                 else:
                     V.out.event_after_binning = None
                 check(lib.b2gs_forward(C.byref(V.scene), C.byref(V.ws), C.byref(V.out), st))
+                if self._zero_pending and not self.pose_only:
+                    stream.wait_event(self._zero_event)      # the arena is clear before anything is added
                 check(lib.b2gs_backward(C.byref(V.scene), C.byref(V.ws), V.cap_real, C.byref(V.io), st))
             for s in side:
                 main.wait_stream(s)
+            if self._zero_pending and not self.pose_only and not self.local:
+                main.wait_event(self._zero_event)
             if self.local:
                 check(lib.b2gs_window_finalize(self._fin_arr, len(self.local), self.loss_total.data_ptr(),
                                                self.guard.data_ptr(), self.tickets.data_ptr(), main.cuda_stream))
         self.launches_fb = lib.b2gs_kernel_launches() - n0
         return self.loss_total
+
+    def _aux(self):
+        if self._aux_stream is None:
+            self._aux_stream = torch.cuda.Stream(self.dev)
+            self._zero_event = torch.cuda.Event()
+        return self._aux_stream
 
     def update(self, peer=None, world=1, group=None, gaussians=True):
         """[gradient exchange ->] Adam + zero_grad -> camera Adam + pose updates + step ticks, every
@@ -314,10 +336,28 @@ class LeanWindow:
             lib.b2gs_set_update_guard(self.guard.data_ptr())
             try:
                 tick = None
+                if gaussians and peer is not None:
+                    # barrier (ORs the guard over the ranks) -> camera step on a side branch || gradient
+                    # sum + Adam + parameter broadcast -> second barrier (advances the step counter);
+                    # this rank's gradient arena is cleared at the start of the next step
+                    main = torch.cuda.current_stream()
+                    aux = self._aux()
+                    check(lib.b2gs_peer_barrier(peer.struct(), st))
+                    aux.wait_stream(main)
+                    check(lib.b2gs_pose_step(self._pose_arr, len(self.local), self.kf_step.data_ptr(), None, 0.9, 0.999,
+                                             1e-8, self.tickets.data_ptr() + 4, aux.cuda_stream))
+                    check(lib.b2gs_adam_step_peer_fused(
+                        self._segs, len(self._segs), opt._step_dev.data_ptr(), b1, b2, self._eps, peer.struct(),
+                        ADAM_NO_TICK | ADAM_TICK_LATE | ADAM_NO_ZERO | ADAM_NO_FIRST_BARRIER, st))
+                    main.wait_stream(aux)
+                    self._zero_pending = True
+                    for v in self.local:
+                        self.views[v].cam._host_RT = None
+                    self.launches_up = lib.b2gs_kernel_launches() - n0
+                    return
                 if gaussians:
                     if peer is not None:
-                        check(lib.b2gs_adam_step_peer_fused(self._segs, len(self._segs), opt._step_dev.data_ptr(), b1, b2,
-                                                            self._eps, peer.struct(), ADAM_NO_TICK, st))
+                        pass
                     else:
                         check(lib.b2gs_adam_step_fused(self._segs, len(self._segs), opt._step_dev.data_ptr(), b1, b2,
                                                        self._eps, ADAM_ZERO_GRAD | ADAM_NO_TICK, st))
