@@ -127,6 +127,11 @@ typedef struct B2gsForwardOut {
    * start the NEXT view's HBM-bound front end when this view's issue-bound render begins, instead
    * of all front ends first and all renders after (window.py: the views form a software pipeline). */
   void* event_after_binning;
+  /* b2gs_forward only: the caller promises that the tile counters inside ws->image are zero — they
+   * are after a zero-filled allocation and after every completed b2gs_forward on that workspace
+   * (the per-tile sort clears its tile's counter once the scatter is done with it) — so the call
+   * skips its own fill of them (one node less at the head of every view's chain). */
+  int32_t tile_counters_clean;
 } B2gsForwardOut;
 
 typedef struct B2gsBackwardIO {

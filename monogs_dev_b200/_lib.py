@@ -38,7 +38,7 @@ class B2gsForwardOut(C.Structure):
         ("color", C.c_void_p), ("depth", C.c_void_p), ("opacity", C.c_void_p),
         ("radii", C.c_void_p), ("n_touched", C.c_void_p), ("status", C.c_void_p),
         ("fused_loss", C.c_void_p), ("bwd_scratch", C.c_void_p), ("bwd_scratch_bytes", C.c_size_t),
-        ("event_after_binning", C.c_void_p),
+        ("event_after_binning", C.c_void_p), ("tile_counters_clean", C.c_int32),
     ]
 
 

@@ -208,7 +208,8 @@ static int forward_front(const B2gsScene& s, const B2gsWorkspace* ws, const B2gs
     return B2GS_ERR_WORKSPACE;
   }
   const size_t tiles = (size_t)((s.W + TILE - 1) / TILE) * ((s.H + TILE - 1) / TILE);
-  B2GS_CUDA(cudaMemsetAsync(im.cursor, 0, sizeof(uint32_t) * tiles * CURSOR_STRIDE, st));
+  if (!(cap >= 0 && out->tile_counters_clean))
+    B2GS_CUDA(cudaMemsetAsync(im.cursor, 0, sizeof(uint32_t) * tiles * CURSOR_STRIDE, st));
   float* acc_zero = nullptr;
   if (out->bwd_scratch) {
     if (out->bwd_scratch_bytes < b2gs_backward_scratch_bytes(s.P)) {

@@ -320,10 +320,15 @@ __device__ __forceinline__ void merge_level(const uint64_t* __restrict__ in, uin
 
 __global__ void __launch_bounds__(SORT_THREADS)
 tile_sort_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ order,
-                 uint64_t* __restrict__ keys, uint32_t* __restrict__ point_list) {
+                 uint64_t* __restrict__ keys, uint32_t* __restrict__ point_list,
+                 uint32_t* __restrict__ cursor) {
   __shared__ uint64_t s_keys[SORT_SMEM_KEYS];
   pdl_wait();
-  const uint2 r = ranges[order[blockIdx.x]];
+  const uint32_t tile = order[blockIdx.x];
+  // the scatter is done with this tile's cursor: leave it zero for the next forward on this workspace
+  // (B2gsForwardOut::tile_counters_clean)
+  if (threadIdx.x == 0) cursor[tile * CURSOR_STRIDE] = 0u;
+  const uint2 r = ranges[tile];
   const uint32_t n = r.y - r.x;
   if (n == 0) return;
   uint64_t* seg = keys + r.x;
@@ -361,7 +366,10 @@ tile_sort_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
 int launch_binning(const B2gsScene& s, const GeomWS& g, const ImageWS& im, const BinWS& b,
                    int64_t cap, cudaStream_t st) {
   const int gx = (s.W + TILE - 1) / TILE, gy = (s.H + TILE - 1) / TILE;
-  if (cap <= 0 || s.P == 0) return B2GS_OK;
+  if (cap <= 0 || s.P == 0) {   // no sort will run: clear the tile counters here
+    B2GS_CUDA(cudaMemsetAsync(im.cursor, 0, sizeof(uint32_t) * (size_t)gx * gy * CURSOR_STRIDE, st));
+    return B2GS_OK;
+  }
   {
     B2GS_PROF("scatter_instances", st);
     B2GS_LAUNCH(scatter_instances_kernel, (s.P + 255) / 256, 256, st, s.P, (uint32_t)gx, (const uint32_t*)g.tiles_touched,
@@ -372,7 +380,7 @@ int launch_binning(const B2gsScene& s, const GeomWS& g, const ImageWS& im, const
   }
   B2GS_PROF("tile_sort", st);
   B2GS_LAUNCH(tile_sort_kernel, gx * gy, SORT_THREADS, st, (const uint2*)im.ranges, (const uint32_t*)im.order, b.keys,
-              b.point_list);
+              b.point_list, im.cursor);
   B2GS_LAUNCH_CHECK(st, s.debug);
   return B2GS_OK;
 }

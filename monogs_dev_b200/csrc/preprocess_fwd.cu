@@ -57,7 +57,7 @@ __device__ __forceinline__ float3 sh_to_rgb(int deg, const float* __restrict__ d
 // RAW is a template parameter so that the RAW=false instantiation is, instruction for
 // instruction, the kernel whose roundings are bit-identical to the reference's.
 template <bool RAW>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 5)
 preprocess_fwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
                       const float* __restrict__ scales, float scale_modifier,
                       const float* __restrict__ rotations, const float* __restrict__ opacities,

@@ -120,7 +120,7 @@ class LeanWindow:
                     setattr(V, a, getattr(old, a))
             else:
                 V.color, V.depth, V.opacity = torch.empty(3, H, W, **f32), torch.empty(1, H, W, **f32), torch.empty(1, H, W, **f32)
-                V.image_ws = torch.empty(lib.b2gs_image_bytes(W, H), **u8)
+                V.image_ws = torch.zeros(lib.b2gs_image_bytes(W, H), **u8)
                 V.dL_dimage, V.dL_ddepth = torch.empty(3, H, W, **f32), torch.empty(1, H, W, **f32)
                 V.partials = torch.empty(tiles, 4, **f32)
             V.radii = torch.empty(P, dtype=torch.int32, device=dev)
@@ -155,7 +155,7 @@ class LeanWindow:
             V.out = _lib.B2gsForwardOut(V.color.data_ptr(), V.depth.data_ptr(), V.opacity.data_ptr(),
                                         V.radii.data_ptr(), V.n_touched.data_ptr(),
                                         self.status_all[i].data_ptr(), C.addressof(fl), V.scratch.data_ptr(),
-                                        V.scratch.numel())
+                                        V.scratch.numel(), None, 1)     # tile counters: zero-filled, kept clean
             io = _lib.B2gsBackwardIO()
             io.dL_dcolor, io.dL_ddepth, io.radii = V.dL_dimage.data_ptr(), V.dL_ddepth.data_ptr(), V.radii.data_ptr()
             if sinks is not None:
@@ -249,6 +249,7 @@ class LeanWindow:
                 out = _lib.B2gsForwardOut(None, None, None, V.radii.data_ptr(), V.n_touched.data_ptr(), None)
                 R = C.c_int64(0)
                 check(lib.b2gs_forward_plan(C.byref(V.scene), C.byref(ws), C.byref(out), st, C.byref(R)))
+                V.image_ws.zero_()         # the plan leaves scan offsets in the tile counters
             cap = int(R.value * HEADROOM) + 4096
         self.cap[v] = int(cap)
         V.binning = torch.empty(lib.b2gs_binning_bytes(self.cap[v], V.W, V.H), dtype=torch.uint8, device=self.dev)
