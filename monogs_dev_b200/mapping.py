@@ -469,6 +469,8 @@ class MappingWindow:
                                     lambda v: bool(self.kfs[v].get("optimize_exposure", True)),
                                     densify_stats=self.densify_stats, regulariser=self.regulariser,
                                     rank=self.rank, world=self.world)
+            if self.peer is not None:
+                self.peer.set_fail_word(self._lean.fail)
         self.last = {}
         self._g1 = self._g2 = None
         self._ovf = self._status_all = None
@@ -654,9 +656,7 @@ class MappingWindow:
                 self._update(set_to_none=False)
             self._status_all, self._ovf, self._gstates = self._lean.status_all, self._lean.guard, None
             self.graph_launches = self._lean.launches_fb + self._lean.launches_up
-            self._flag_host = [(torch.empty(self._status_all.shape, dtype=torch.int32).pin_memory(),
-                                torch.empty(1, dtype=torch.int32).pin_memory(),
-                                torch.zeros(1, dtype=torch.int32).pin_memory()) for _ in range(3)]
+            self._flag_host = [torch.zeros(self._lean.flags.shape, dtype=torch.int32).pin_memory() for _ in range(3)]
             return
         l0 = lib.b2gs_kernel_launches()
         self._g1 = torch.cuda.CUDAGraph()
@@ -696,7 +696,16 @@ class MappingWindow:
         self._g1.replay()
         if self._g2 is not None:
             self._g2.replay()
-        if self._status_all is not None:
+        if self._lean is not None:
+            # ONE read-back per step: per-view (instances, overflow), the guard (after the exchange: the OR
+            # over all ranks), the peer barrier's time-out word
+            h = self._flag_host[self._launched % 3]
+            h.copy_(self._lean.flags, non_blocking=True)
+            n = self._status_all.shape[0]
+            ev = torch.cuda.Event()
+            ev.record()
+            self._pending.append((ev, h[:2 * n].view(n, 2), h[2 * n:2 * n + 1], h[2 * n + 1:2 * n + 2]))
+        elif self._status_all is not None:
             st, ov, fl = self._flag_host[self._launched % 3]
             st.copy_(self._status_all, non_blocking=True)      # this rank's views: sizes the retry
             ov.copy_(self._ovf, non_blocking=True)             # after G2: the OR over all ranks

@@ -63,6 +63,13 @@ class PeerArena:
                                           mc if mc else None, (mc + 4 * n) if mc else None)
         return self._arena[:total], self._arena[n:n + total]
 
+    def set_fail_word(self, word):
+        """let the barrier's time-out flag live in caller memory (one int32 device word), e.g. next to
+        the overflow flags a window reads back every step"""
+        self.fail = word
+        if self._struct is not None:
+            self._struct.fail_flag = word.data_ptr()
+
     def struct(self):
         if self._struct is None:
             raise RuntimeError("PeerArena.alloc() has not been called")

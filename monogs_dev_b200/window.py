@@ -58,8 +58,13 @@ class LeanWindow:
         self.dev = bg.device
         n = max(len(self.local), 1)
         i32 = dict(dtype=torch.int32, device=self.dev)
-        self.status_all = torch.zeros(n, 2, **i32)           # (instances, overflow) per local view
-        self.guard = torch.zeros(1, **i32)                   # OR of the overflow flags (window_finalize)
+        # one block of flag words, read back by the host with ONE async copy per step:
+        # (instances, overflow) per local view | the guard (OR of the overflow flags, window_finalize)
+        # | the peer barrier's time-out word (MappingWindow points PeerArena.fail at it)
+        self.flags = torch.zeros(2 * n + 2, **i32)
+        self.status_all = self.flags[:2 * n].view(n, 2)
+        self.guard = self.flags[2 * n:2 * n + 1]
+        self.fail = self.flags[2 * n + 1:2 * n + 2]
         self.tickets = torch.zeros(4, **i32)                 # [0] finalize, [1] pose step
         self.losses = torch.zeros(n, device=self.dev)
         self.loss_total = torch.zeros((), device=self.dev)
