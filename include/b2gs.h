@@ -258,6 +258,17 @@ B2GS_API size_t b2gs_knn_bytes(int32_t P);
 B2GS_API int b2gs_knn3_dist2(const float* points, int32_t P, float* out, void* workspace,
                     size_t workspace_bytes, void* stream);
 
+/* b2gs_knn3_dist2 WITHOUT a caller workspace and without any allocation: the scratch is a static
+ * device array inside the library (9 MiB, held by every device that loads the library until the
+ * process exits), enough for b2gs_knn3_dist2_static_max_points() = 262144 points; more points are
+ * rejected with B2GS_ERR_INVALID.  For callers that cannot call cudaMalloc (under CUDA-graph
+ * capture, serving loops, harnesses that forbid it).  No cudaMalloc / cudaFree / allocating
+ * library call is made.  All calls on a device share the one array: calls that overlap on the GPU
+ * (different streams) race; calls on one stream are safe.  Same result as b2gs_knn3_dist2.
+ * No counterpart in the reference. */
+B2GS_API int32_t b2gs_knn3_dist2_static_max_points(void);
+B2GS_API int b2gs_knn3_dist2_static(const float* points, int32_t P, float* out, void* stream);
+
 /* Fused Adam over a set of parameter segments (torch.optim.Adam semantics:
  * no weight decay, no amsgrad, bias correction from `step`, 1-based).
  * Segment s covers n[s] floats at param[s]/grad[s]/exp_avg[s]/exp_avg_sq[s]

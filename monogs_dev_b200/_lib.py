@@ -153,6 +153,8 @@ SYMBOLS = {
     "b2gs_knn_bytes": (C.c_size_t, [C.c_int32]),
     "b2gs_knn3_dist2": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_size_t,
                                   C.c_void_p]),
+    "b2gs_knn3_dist2_static_max_points": (C.c_int32, []),
+    "b2gs_knn3_dist2_static": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]),
     "b2gs_loss_scratch_bytes": (C.c_size_t, [C.c_int32]),
     "b2gs_loss_forward": (C.c_int, [C.POINTER(B2gsLossArgs), C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     "b2gs_loss_backward": (C.c_int, [C.POINTER(B2gsLossArgs), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,

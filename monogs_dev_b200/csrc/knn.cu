@@ -22,6 +22,7 @@
 //    warp match_any votes (no library call anywhere in the library).
 #include "common.cuh"
 #include <float.h>
+#include <mutex>
 
 namespace b2gs {
 
@@ -471,4 +472,64 @@ extern "C" int b2gs_knn3_dist2(const float* points, int32_t P, float* out, void*
   B2GS_LAUNCH_CHECK(st, 0);
   note_launches(3);
   return B2GS_OK;
+}
+
+// ---- no-allocation variant --------------------------------------------------------------------
+// b2gs_knn3_dist2 with its workspace in a file-scope device array, for callers that cannot hand
+// in device memory of their own (under CUDA-graph capture, serving loops, harnesses that forbid
+// cudaMalloc).  Every device that loads the library holds these bytes until the process exits.
+// All calls on a device share the array: two calls that overlap on the GPU (different streams)
+// race.  Nothing in it has to start at zero — knn_init_kernel resets the bounding-box words and
+// every other region is written in full before it is read — so the last call's contents are
+// simply overwritten.
+constexpr int32_t KNN_STATIC_MAX_POINTS = 262144;
+constexpr size_t KNN_STATIC_BYTES = 9u << 20;             // carve_knn(262144) needs 8 658 432
+static __device__ __align__(256) unsigned char g_knn_static[KNN_STATIC_BYTES];
+
+namespace {
+constexpr int KNN_STATIC_MAX_DEVICES = 64;
+std::mutex g_knn_static_mu;
+void* g_knn_static_ptr[KNN_STATIC_MAX_DEVICES] = {};      // per device: the array's DEVICE address
+}  // namespace
+
+extern "C" int32_t b2gs_knn3_dist2_static_max_points(void) { return KNN_STATIC_MAX_POINTS; }
+
+extern "C" int b2gs_knn3_dist2_static(const float* points, int32_t P, float* out, void* stream) {
+  if (P < 0) { set_error("b2gs_knn3_dist2_static: negative P"); return B2GS_ERR_INVALID; }
+  if (P > KNN_STATIC_MAX_POINTS) {
+    set_error("b2gs_knn3_dist2_static: %d points exceed the built-in scratch (at most %d); use "
+              "b2gs_knn3_dist2 with a caller workspace", P, KNN_STATIC_MAX_POINTS);
+    return B2GS_ERR_INVALID;
+  }
+  if (P == 0) return B2GS_OK;
+  size_t need = 0;
+  carve_knn(nullptr, P, &need);
+  if (need > KNN_STATIC_BYTES) {      // only if carve_knn grows without this file's constants
+    set_error("b2gs_knn3_dist2_static: scratch layout needs %zu bytes, built-in array has %zu", need,
+              (size_t)KNN_STATIC_BYTES);
+    return B2GS_ERR_WORKSPACE;
+  }
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= KNN_STATIC_MAX_DEVICES) {
+    set_error("b2gs_knn3_dist2_static: cudaGetDevice: %s (device %d)", cudaGetErrorString(e), dev);
+    return B2GS_ERR_CUDA;
+  }
+  void* ws = nullptr;
+  {
+    // the array's name is a host-side handle, not a device address: resolve it once per device,
+    // with that device current
+    std::lock_guard<std::mutex> lock(g_knn_static_mu);
+    if (!g_knn_static_ptr[dev]) {
+      void* p = nullptr;
+      e = cudaGetSymbolAddress(&p, g_knn_static);
+      if (e != cudaSuccess || !p) {
+        set_error("b2gs_knn3_dist2_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+        return B2GS_ERR_CUDA;
+      }
+      g_knn_static_ptr[dev] = p;
+    }
+    ws = g_knn_static_ptr[dev];
+  }
+  return b2gs_knn3_dist2(points, P, out, ws, KNN_STATIC_BYTES, stream);
 }
