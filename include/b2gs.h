@@ -174,6 +174,15 @@ typedef struct B2gsBackwardIO {
    * the call then covers only the Gaussians i with i % stride == offset (stride 0 means all). */
   float iso_reg_weight;
   int32_t iso_reg_stride, iso_reg_offset;
+  /* optional device words read when the call RUNS (graph replays included): the densification
+   * statistics above are left untouched if any non-NULL word is non-zero.  The sync-free mapping
+   * window points them at: the view's own overflow flag (B2gsForwardOut.status + 1: a
+   * background-only pass must not count as "seen"), the update guard (still holding the
+   * previous step's verdict: the replays after a discarded step repeat it), and a per-view host
+   * mask set for the re-run of a discarded step (the views that did fit were counted already).
+   * Keeps xyz_gradient_accum / denom exact under GS/scene/gaussian_model.py:691-695 when a
+   * step is discarded and repeated. */
+  const int32_t* stats_gate[3];
 } B2gsBackwardIO;
 
 B2GS_API int b2gs_version(void);

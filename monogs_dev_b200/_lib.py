@@ -53,6 +53,7 @@ class B2gsBackwardIO(C.Structure):
         ("densify_denom", C.c_void_p), ("max_radii2D", C.c_void_p),
         ("scratch_zeroed", C.c_int32), ("defer_tau", C.c_int32), ("iso_reg_weight", C.c_float),
         ("iso_reg_stride", C.c_int32), ("iso_reg_offset", C.c_int32),
+        ("stats_gate", C.c_void_p * 3),
     ]
 
 

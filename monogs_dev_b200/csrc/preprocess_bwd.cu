@@ -143,10 +143,18 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
                       const float* __restrict__ shs_rest, const float* __restrict__ opacities,
                       int accumulate, float* __restrict__ dL_dsh_rest,
                       float* __restrict__ st_grad_accum, float* __restrict__ st_denom,
-                      float* __restrict__ st_max_radii, float iso_w, int iso_stride, int iso_offset) {
+                      float* __restrict__ st_max_radii, float iso_w, int iso_stride, int iso_offset,
+                      const int32_t* __restrict__ gate0, const int32_t* __restrict__ gate1,
+                      const int32_t* __restrict__ gate2, const float4* __restrict__ conic_o, float half_w,
+                      float half_h) {
   __shared__ float s_view[16], s_proj[16];
   __shared__ float s_tau[4][7];
   pdl_wait();
+  // statistics gates (B2gsBackwardIO.stats_gate): this view overflowed / the previous step was
+  // discarded / the host has already counted this view for the step being re-run
+  if ((gate0 && *gate0) || (gate1 && *gate1) || (gate2 && *gate2)) {
+    st_grad_accum = nullptr; st_denom = nullptr; st_max_radii = nullptr;
+  }
   if (threadIdx.x < 16) s_view[threadIdx.x] = viewmatrix[threadIdx.x];
   else if (threadIdx.x < 32) s_proj[threadIdx.x - 16] = projmatrix[threadIdx.x - 16];
   __syncthreads();
@@ -159,12 +167,14 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
   // -> mean -> rotation / scale -> opacity ... would otherwise be a chain of DRAM round trips; the
   // kernel is latency-bound).  Rows of culled Gaussians are fetched in vain: ~30 % of 100 B.
   int radius_in = 0;
+  float4 co_in = {0.f, 0.f, 0.f, 0.f};
   float4 a0 = {0.f, 0.f, 0.f, 0.f}, a1 = a0, a2 = a0, q_in = make_float4(1.f, 0.f, 0.f, 0.f);
   float3 mean = {0.f, 0.f, 0.f}, s_in = {0.f, 0.f, 0.f};
   float op_raw = 0.f;
   uint8_t clamp_in = 0;
   if (idx < P) {
     radius_in = radii[idx];
+    co_in = conic_o[idx];
     const float4* arow = reinterpret_cast<const float4*>(acc + (size_t)idx * ACC_STRIDE);
     a0 = arow[0]; a1 = arow[1]; a2 = arow[2];
     mean = {means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]};
@@ -194,8 +204,13 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
   }
 
   if (live) {
-    const float dmean2D_x = a0.x, dmean2D_y = a0.y;
-    const float3 dL_dconic = {a0.z, a0.w, a1.x};
+    // render_bwd leaves the moments of q = G * dL_dalpha about the splat centre (render_bwd.cu,
+    // accumulator row layout); the factors CR/backward.cu:735-757 applies per pixel — conic,
+    // opacity, the viewport scale — are applied to the sums here
+    const float dmean2D_x = half_w * co_in.w * -fmaf(co_in.x, a0.x, co_in.y * a0.y);
+    const float dmean2D_y = half_h * co_in.w * -fmaf(co_in.z, a0.y, co_in.y * a0.x);
+    const float nho = -0.5f * co_in.w;
+    const float3 dL_dconic = {nho * a0.z, nho * a0.w, nho * a1.x};
     const float dL_dop = a1.y;
     const V3 dL_dcol = {a1.z, a1.w, a2.x};
     const float dL_ddepth = a2.y;
@@ -558,7 +573,8 @@ int launch_preprocess_bwd(const B2gsScene& s, const GeomWS& g, const B2gsBackwar
       s.shs_rest, s.opacities, io.accumulate, io.dL_dsh_rest, io.densify_grad_accum,
       io.densify_denom, io.max_radii2D,
       io.iso_reg_weight != 0.f ? io.iso_reg_weight / (3.0f * (float)s.P) : 0.f, io.iso_reg_stride,
-      io.iso_reg_offset);
+      io.iso_reg_offset, io.stats_gate[0], io.stats_gate[1], io.stats_gate[2], g.conic_o,
+      0.5f * (float)s.W, 0.5f * (float)s.H);
   B2GS_LAUNCH_CHECK(st, s.debug);
   if (io.dL_dtau) {   // defer_tau callers hand the partial rows to b2gs_window_finalize instead
     tau_finalize_kernel<<<1, 256, 0, st>>>(blocks, partials, io.dL_dtau);

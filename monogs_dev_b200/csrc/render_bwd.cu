@@ -29,9 +29,10 @@ namespace b2gs {
 constexpr int RB_BATCH = 256;
 constexpr unsigned FULL = 0xffffffffu;
 
-// accumulator row layout (ACC_STRIDE floats):
-// 0 dmean2D.x  1 dmean2D.y  2 dconic.x  3 dconic.y  4 dconic.w
-// 5 dopacity   6 dcolor.r   7 dcolor.g  8 dcolor.b  9 ddepth   10,11 pad
+// accumulator row layout (ACC_STRIDE floats), q = G * dL_dalpha per pixel, d = mean2D - pixel:
+// 0 sum q dx   1 sum q dy   2 sum q dx^2   3 sum q dx dy   4 sum q dy^2
+// 5 sum q (= dL_dopacity)   6 dcolor.r   7 dcolor.g  8 dcolor.b  9 ddepth   10,11 pad
+// (preprocess_bwd.cu turns 0..4 into dL_dmean2D / dL_dconic)
 
 // 1/x for x in [0.01, 1] (x = 1 - alpha, alpha <= 0.99): MUFU.RCP + one Newton step, <= 1 ulp,
 // without the range / denormal handling of a full-range reciprocal.
@@ -39,6 +40,14 @@ __device__ __forceinline__ float rcp_unit_range(float x) {
   float r;
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
   return fmaf(r, fmaf(-x, r, 1.0f), r);
+}
+
+__device__ __forceinline__ float2 rcp_unit_range2(float2 x) {   // both pixels, Newton step packed
+  float2 r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r.x) : "f"(x.x));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r.y) : "f"(x.y));
+  const float2 e = __ffma2_rn(make_float2(-x.x, -x.y), r, make_float2(1.0f, 1.0f));
+  return __ffma2_rn(r, e, r);
 }
 
 __device__ __forceinline__ float xchg_add(bool upper, float lo_val, float hi_val, int offset) {
@@ -127,15 +136,14 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   f2 T = T_final;
   const int lastA = insideA ? (int)n_contrib[pixA] : 0, lastB = insideB ? (int)n_contrib[pixB] : 0;
 
-  // accum_c: blended colour behind the current splat; diff_c: (colour - accum) of the previous list
-  // entry.  The reference's replay  accum = last_alpha * last_colour + (1 - last_alpha) * accum
-  // (CR/backward.cu:716-727) is written as  accum += last_alpha * (last_colour - accum): the
-  // difference is the one the previous contributor already formed for its dL_dalpha.  A pixel that
-  // skips a splat runs the same recurrences with alpha = 0 — a transparent contributor: it applies
-  // the pending update, leaves T alone (T * 1/(1 - 0), exact) and parks last_alpha at 0 — so the
-  // two pixels of a lane need no divergent state updates.
+  // accum_c: blended colour behind the current splat.  The reference's replay  accum = last_alpha *
+  // last_colour + (1 - last_alpha) * accum  (CR/backward.cu:716-727), done when the NEXT contributor
+  // is visited, is applied as  accum += alpha * (colour - accum)  at the end of the visit that
+  // formed that difference for its own dL_dalpha (same operands, no carried last_alpha /
+  // last_colour).  A pixel that skips a splat runs the same recurrences with alpha = 0 — a
+  // transparent contributor: accum + 0 * diff, T * 1/(1 - 0), both exact — so the two pixels of a
+  // lane need no divergent state updates.
   f2 accum0 = bc(0.f), accum1 = bc(0.f), accum2 = bc(0.f), accumd = bc(0.f);
-  f2 diff0 = bc(0.f), diff1 = bc(0.f), diff2 = bc(0.f), diffd = bc(0.f);
   f2 dLp0 = bc(0.f), dLp1 = bc(0.f), dLp2 = bc(0.f), dLpd = bc(0.f);
   {
     const size_t plane = (size_t)H * W;
@@ -152,15 +160,12 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
       dLpd.y = dL_dpixels_depth[pixB];
     }
   }
-  f2 last_alpha = bc(0.f);
   f2 bg_dot = mul2(bc(bg[0]), dLp0);
   bg_dot = fma2(bc(bg[1]), dLp1, bg_dot);
   bg_dot = fma2(bc(bg[2]), dLp2, bg_dot);
   // dL_dalpha += (-T_final / (1 - alpha)) * bg . dL_dpixel
   const f2 neg_Tf_bg = mul2(make_float2(-T_final.x, -T_final.y), bg_dot);
 
-  const float ddelx_dx = 0.5f * W;
-  const float ddely_dy = 0.5f * H;
   const int slot = fold10_slot(lane);
   float* const slot_row = slot >= 0 ? acc + slot : nullptr;
 
@@ -190,7 +195,10 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     }
     __syncthreads();
 
-    // entry j is at position tile_max-1-(base+j); this warp needs pos < warp_max
+    // entry j is at position pos = tile_max-1-(base+j); a pixel is past its last contributor
+    // unless pos < last  <=>  j > tile_max-1-base-last
+    const int behindA = tile_max - 1 - base - lastA, behindB = tile_max - 1 - base - lastB;
+    // this warp needs pos < warp_max
     int j0 = tile_max - base - warp_max;
     if (j0 < 0) j0 = 0;
     for (int c0 = j0 & ~31; c0 < cnt; c0 += 32) {
@@ -202,7 +210,6 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
         const int k = __ffs(mask) - 1;
         mask &= mask - 1;
         const int j = c0 + k;
-        const int pos = tile_max - 1 - (base + j);
         const SplatRec& r = s_rec[j];
         const float2 p = r.xy;
         const float4 co = r.co;
@@ -217,8 +224,8 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
         const f2 G = expf_pair(power);
         const f2 og = mul2(bc(co.w), G);
         const float alphaA = fminf(0.99f, og.x), alphaB = fminf(0.99f, og.y);
-        const bool skipA = !(pos < lastA) || power.x > 0.0f || alphaA < 1.0f / 255.0f;
-        const bool skipB = !(pos < lastB) || power.y > 0.0f || alphaB < 1.0f / 255.0f;
+        const bool skipA = j <= behindA || power.x > 0.0f || alphaA < 1.0f / 255.0f;
+        const bool skipB = j <= behindB || power.y > 0.0f || alphaB < 1.0f / 255.0f;
         if (COUNT) ++c_visit;
         if (__all_sync(FULL, skipA && skipB)) continue;
         if (COUNT) { ++c_full; c_contrib += (unsigned)!skipA + (unsigned)!skipB; }
@@ -227,41 +234,41 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
         const f2 Gs = make_float2(skipA ? 0.f : G.x, skipB ? 0.f : G.y);
         const float4 cd = r.cd;
         const f2 oma = add2(bc(1.f), make_float2(-alpha.x, -alpha.y));
-        const f2 inv1ma = make_float2(rcp_unit_range(oma.x), rcp_unit_range(oma.y));
+        const f2 inv1ma = rcp_unit_range2(oma);
         T = mul2(T, inv1ma);  // reference: T / (1 - alpha); differs by <= 1 ulp
         const f2 dchannel_dcolor = mul2(alpha, T);
 
-        accum0 = fma2(last_alpha, diff0, accum0);
-        accum1 = fma2(last_alpha, diff1, accum1);
-        accum2 = fma2(last_alpha, diff2, accum2);
-        accumd = fma2(last_alpha, diffd, accumd);
-        diff0 = fma2(accum0, bc(-1.f), bc(cd.x));
-        diff1 = fma2(accum1, bc(-1.f), bc(cd.y));
-        diff2 = fma2(accum2, bc(-1.f), bc(cd.z));
-        diffd = fma2(accumd, bc(-1.f), bc(cd.w));
+        const f2 diff0 = fma2(accum0, bc(-1.f), bc(cd.x));
+        const f2 diff1 = fma2(accum1, bc(-1.f), bc(cd.y));
+        const f2 diff2 = fma2(accum2, bc(-1.f), bc(cd.z));
+        const f2 diffd = fma2(accumd, bc(-1.f), bc(cd.w));
         f2 d = mul2(diff0, dLp0);
         d = fma2(diff1, dLp1, d);
         d = fma2(diff2, dLp2, d);
         d = fma2(diffd, dLpd, d);
-        last_alpha = alpha;
+        accum0 = fma2(alpha, diff0, accum0);   // what lies behind the NEXT entry (skipping pixel: + 0)
+        accum1 = fma2(alpha, diff1, accum1);
+        accum2 = fma2(alpha, diff2, accum2);
+        accumd = fma2(alpha, diffd, accumd);
         const f2 dL_dalpha = fma2(inv1ma, neg_Tf_bg, mul2(d, T));
 
-        // per-pixel partials -> the lane's two pixels are summed before the warp fold; a skipping
-        // pixel contributes exact zeros (every partial is a product with Gs or alpha = 0)
-        const f2 dL_dG = mul2(bc(co.w), dL_dalpha);
-        const f2 gdx = mul2(Gs, bc(dx));
-        const f2 gdy = mul2(Gs, dy);
-        const f2 dG_ddelx = fma2(gdx, bc(-co.x), mul2(gdy, bc(-co.y)));
-        const f2 dG_ddely = fma2(gdy, bc(-co.z), mul2(gdx, bc(-co.y)));
-        const f2 hg = mul2(dL_dG, bc(-0.5f));
-        const f2 hgdx = mul2(hg, gdx);
+        // per-splat sums over the pixels.  The conic, the opacity and the viewport factors do not
+        // depend on the pixel, so what is folded are the moments of q = G * dL_dalpha about the
+        // splat centre (d = mean - pixel):  S0 = sum q,  Sx = sum q dx,  Sy = sum q dy,  Sxx, Sxy,
+        // Syy; preprocess_bwd forms dL_dmean2D = o * (-a Sx - b Sy) * W/2, ...,  dL_dconic =
+        // -o/2 * (Sxx, Sxy, Syy) from them (CR/backward.cu:735-757 distributes the same factors
+        // over every pixel).  Both pixels of a lane share dx, so the x moments are dx times the
+        // lane's sums.  A skipping pixel contributes exact zeros (q carries Gs = 0, the colour
+        // terms alpha = 0).
+        const f2 q = mul2(Gs, dL_dalpha);
+        const f2 qy = mul2(q, dy);
         float v[10];
-        v[0] = hsum(mul2(dL_dG, dG_ddelx)) * ddelx_dx;
-        v[1] = hsum(mul2(dL_dG, dG_ddely)) * ddely_dy;
-        v[2] = hsum(hgdx) * dx;
-        v[3] = hsum(mul2(hgdx, dy));
-        v[4] = hsum(mul2(mul2(hg, gdy), dy));
-        v[5] = hsum(mul2(Gs, dL_dalpha));
+        v[5] = hsum(q);
+        v[1] = hsum(qy);
+        v[4] = hsum(mul2(qy, dy));
+        v[0] = v[5] * dx;
+        v[2] = v[0] * dx;
+        v[3] = v[1] * dx;
         v[6] = hsum(mul2(dchannel_dcolor, dLp0));
         v[7] = hsum(mul2(dchannel_dcolor, dLp1));
         v[8] = hsum(mul2(dchannel_dcolor, dLp2));

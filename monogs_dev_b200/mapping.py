@@ -607,11 +607,14 @@ class MappingWindow:
         if self._lean is not None:
             for attempt in range(3):
                 loss, stats = self._forward_backward()
-                if not self._lean.note_overflow(self._lean.status_all.tolist()):    # one host sync per step
+                vals = self._lean.status_all.tolist()      # one host sync per step
+                if not self._lean.note_overflow(vals):
                     break
                 self.g.zero_grad()              # discard the background-only pass, redo it with more room
+                self._lean.begin_rerun(vals)    # the views that fitted are not counted a second time
                 if attempt == 2:
                     raise RuntimeError("binning capacity overflow persisted after two retries")
+            self._lean.end_rerun()
             self.last = stats
             return loss
         loss, stats = self._forward_backward()
@@ -722,7 +725,7 @@ class MappingWindow:
         guard word made every Adam / pose kernel return, on every rank — the word is the OR over
         all ranks, so all ranks take this path together)."""
         from . import rasterizer as rz
-        over = False
+        over, first = False, None
         while len(self._pending) > keep:
             ev, st, ov, fl = self._pending.pop(0)
             ev.synchronize()
@@ -730,6 +733,8 @@ class MappingWindow:
                 raise RuntimeError("libb2gs peer barrier timed out: a rank died or fell out of step; the "
                                    "replicas were left untouched by that step but the window cannot continue")
             self._note(st.tolist())
+            if int(ov[0]) and first is None:
+                first = st.tolist()             # which local views fitted in the first discarded step
             over = over or bool(int(ov[0]))
         if not over:
             return
@@ -738,10 +743,18 @@ class MappingWindow:
         for ev, st, ov, fl in self._pending:
             self._note(st.tolist())
         self._pending.clear()
-        for _ in range(lost):
+        for k in range(lost):
             self.g.zero_grad()
             self._zero_kf_grads(False)
             self._g1 = None
+            if self._lean is not None:
+                # densification statistics: the first discarded step counted the views that fitted
+                # (the replays after it counted nothing: B2gsBackwardIO.stats_gate), so the first
+                # repeat, still at the same parameters, counts only the views that did not
+                if k == 0:
+                    self._lean.begin_rerun(first)
+                else:
+                    self._lean.end_rerun()
             self._capture()                     # larger capacities are now in rz._SyncFree.cap
             self._launch()
             torch.cuda.synchronize()
@@ -749,6 +762,8 @@ class MappingWindow:
             self._note(st.tolist())
             if int(ov[0]):
                 raise RuntimeError("binning capacity overflow persisted after re-capture")
+        if self._lean is not None:
+            self._lean.end_rerun()
 
     def _note(self, vals):
         from . import rasterizer as rz

@@ -66,6 +66,9 @@ class LeanWindow:
         self.guard = self.flags[2 * n:2 * n + 1]
         self.fail = self.flags[2 * n + 1:2 * n + 2]
         self.tickets = torch.zeros(4, **i32)                 # [0] finalize, [1] pose step
+        # per view: "already counted in the densification statistics of the step being re-run"
+        # (B2gsBackwardIO.stats_gate[2]; see begin_rerun)
+        self.stats_mask = torch.zeros(n, **i32)
         self.losses = torch.zeros(n, device=self.dev)
         self.loss_total = torch.zeros((), device=self.dev)
         self.kf_grads = torch.zeros(n, 8, device=self.dev)   # per view: dL_dtau[6], dL_dexposure[2]
@@ -169,6 +172,13 @@ class LeanWindow:
                 io.dL_dscales, io.dL_drotations = sinks.scaling.data_ptr(), sinks.rotation.data_ptr()
                 io.densify_grad_accum, io.densify_denom = ptr(sinks.xyz_gradient_accum), ptr(sinks.denom)
                 io.max_radii2D = ptr(sinks.max_radii2D)
+                if self.densify_stats:
+                    # a discarded step must not be counted twice (GS/scene/gaussian_model.py:691-695
+                    # counts every applied iteration once): own overflow flag | the guard, which
+                    # still holds the previous step's verdict here | the host's re-run mask
+                    io.stats_gate[0] = self.status_all[i].data_ptr() + 4
+                    io.stats_gate[1] = self.guard.data_ptr()
+                    io.stats_gate[2] = self.stats_mask[i:i + 1].data_ptr()
             io.scratch, io.scratch_bytes = V.scratch.data_ptr(), V.scratch.numel()
             io.accumulate, io.scratch_zeroed, io.defer_tau = int(sinks is not None), 1, 1
             io.iso_reg_weight = 10.0 if v == reg_view else 0.0
@@ -271,6 +281,17 @@ class LeanWindow:
                 over = True
                 self._alloc_binning(v, max(self.cap[v], int(inst * HEADROOM) + 4096))
         return over
+
+    def begin_rerun(self, vals):
+        """before the FIRST repeat of a discarded step (parameters unchanged since): the views
+        that did fit have added their densification statistics already, the ones that overflowed
+        have not (stats_gate[0]); the replays after it added nothing (stats_gate[1])."""
+        self.guard.zero_()
+        self.stats_mask.copy_(torch.tensor([0 if flag else 1 for _, flag in vals] or [0],
+                                           dtype=torch.int32))
+
+    def end_rerun(self):
+        self.stats_mask.zero_()
 
     # -- the step --------------------------------------------------------------------------------
     def forward_backward(self, side=()):
