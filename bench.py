@@ -57,8 +57,9 @@ METRIC = "fwd+bwd render iters/s @1200x680, 500k Gaussians (8-keyframe map-windo
 POSE_LR = (0.0015, 0.0005, 0.01, 0.01)
 # executed flop per pixel of the render kernels' inner loops, counted on the source
 FWD_POWER, FWD_BLEND = 9.5, 24.0     # power tree | expf (11) + alpha/test_T (4) + 4 FMA blend + weight (9)
-BWD_HEAD, BWD_BLEND = 22.5, 52.0     # power + expf + alpha | rcp, replay, dL_dalpha, 6 moments + 4 colour sums, 12-shuffle fold
-#                                      (67.0 until the kernel folded moments instead of finished conic / mean gradients)
+BWD_HEAD, BWD_BLEND = 22.5, 39.0     # power + expf + alpha | rcp, colour . dL_dpixel, dL_dalpha, 6 moments + 4 colour sums, 12-shuffle fold
+#                                      (67.0 until the kernel folded moments instead of finished conic / mean gradients, 52.0
+#                                      until it carried accum . dL_dpixel as one scalar instead of four blended channels)
 GRAPH_WARMUP = 4   # native graph mode: 3 eager sizing steps + the capture; the reference arm runs them too
 
 

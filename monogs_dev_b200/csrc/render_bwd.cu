@@ -4,8 +4,8 @@
 // Per-pixel arithmetic follows the reference recurrences (CR/backward.cu:700-757) with two
 // algebraic rewrites that stay within the 1e-4 gradient tolerance but are NOT operation for
 // operation: T / (1 - alpha) is T * rcp(1 - alpha) (MUFU.RCP + one Newton step, <= 1 ulp), and the
-// replay accum = last_alpha * last_colour + (1 - last_alpha) * accum is kept in the incremental
-// form accum += last_alpha * (last_colour - accum).  `power` / exp / the skip tests ARE the
+// replay accum = last_alpha * last_colour + (1 - last_alpha) * accum is carried as the one number
+// that is used of it, accum . dL_dpixel (see `behind` below).  `power` / exp / the skip tests ARE the
 // forward's operation tree bit for bit, so both passes take the same decisions.  What is
 // redesigned is the reduction of the 10 per-splat partials:
 //   reference: per splat per tile 3 block barriers + a 256-wide, 8-level shared
@@ -136,14 +136,17 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   f2 T = T_final;
   const int lastA = insideA ? (int)n_contrib[pixA] : 0, lastB = insideB ? (int)n_contrib[pixB] : 0;
 
-  // accum_c: blended colour behind the current splat.  The reference's replay  accum = last_alpha *
-  // last_colour + (1 - last_alpha) * accum  (CR/backward.cu:716-727), done when the NEXT contributor
-  // is visited, is applied as  accum += alpha * (colour - accum)  at the end of the visit that
-  // formed that difference for its own dL_dalpha (same operands, no carried last_alpha /
-  // last_colour).  A pixel that skips a splat runs the same recurrences with alpha = 0 — a
-  // transparent contributor: accum + 0 * diff, T * 1/(1 - 0), both exact — so the two pixels of a
+  // behind = accum . dL_dpixel, accum_c being the colour / depth blended behind the current splat.
+  // The reference replays  accum_c = last_alpha * last_colour_c + (1 - last_alpha) * accum_c  per
+  // channel when the NEXT contributor is visited and then forms  sum_c (colour_c - accum_c) *
+  // dL_dpixel_c  (CR/backward.cu:716-732).  Only that dot product is ever used, and the replay is
+  // linear, so the dot product itself is carried:  d = colour . dL_dpixel - behind,  behind +=
+  // alpha * d  — one scalar per pixel instead of four channels, 6 instead of 12 packed
+  // instructions per visit; the rounding error is of the same order (eps * |accum . dL_dpixel|
+  // either way).  A pixel that skips a splat runs the same recurrences with alpha = 0 — a
+  // transparent contributor: behind + 0 * d, T * 1/(1 - 0), both exact — so the two pixels of a
   // lane need no divergent state updates.
-  f2 accum0 = bc(0.f), accum1 = bc(0.f), accum2 = bc(0.f), accumd = bc(0.f);
+  f2 behind = bc(0.f);
   f2 dLp0 = bc(0.f), dLp1 = bc(0.f), dLp2 = bc(0.f), dLpd = bc(0.f);
   {
     const size_t plane = (size_t)H * W;
@@ -238,18 +241,12 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
         T = mul2(T, inv1ma);  // reference: T / (1 - alpha); differs by <= 1 ulp
         const f2 dchannel_dcolor = mul2(alpha, T);
 
-        const f2 diff0 = fma2(accum0, bc(-1.f), bc(cd.x));
-        const f2 diff1 = fma2(accum1, bc(-1.f), bc(cd.y));
-        const f2 diff2 = fma2(accum2, bc(-1.f), bc(cd.z));
-        const f2 diffd = fma2(accumd, bc(-1.f), bc(cd.w));
-        f2 d = mul2(diff0, dLp0);
-        d = fma2(diff1, dLp1, d);
-        d = fma2(diff2, dLp2, d);
-        d = fma2(diffd, dLpd, d);
-        accum0 = fma2(alpha, diff0, accum0);   // what lies behind the NEXT entry (skipping pixel: + 0)
-        accum1 = fma2(alpha, diff1, accum1);
-        accum2 = fma2(alpha, diff2, accum2);
-        accumd = fma2(alpha, diffd, accumd);
+        // d = sum_c (colour_c - accum_c) * dL_dpixel_c = colour . dL_dpixel - behind
+        f2 d = fma2(bc(cd.x), dLp0, make_float2(-behind.x, -behind.y));
+        d = fma2(bc(cd.y), dLp1, d);
+        d = fma2(bc(cd.z), dLp2, d);
+        d = fma2(bc(cd.w), dLpd, d);
+        behind = fma2(alpha, d, behind);   // what lies behind the NEXT entry (skipping pixel: + 0)
         const f2 dL_dalpha = fma2(inv1ma, neg_Tf_bg, mul2(d, T));
 
         // per-splat sums over the pixels.  The conic, the opacity and the viewport factors do not
