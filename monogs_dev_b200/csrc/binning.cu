@@ -20,6 +20,7 @@
 #include "common.cuh"
 #include "expand.cuh"
 #include "cull.cuh"
+#include <cooperative_groups.h>
 
 namespace b2gs {
 
@@ -63,10 +64,16 @@ BinWS carve_bin(void* base, int64_t cap, size_t* total) {
 }
 
 // ---- counters -> ranges ------------------------------------------------------------
-// One CTA.  Exclusive scan of the T per-tile instance counts.  Writes ranges (the
-// reference leaves empty tiles at (0,0), CR/rasterizer_impl.cu:313-321), turns the
-// counters into scatter cursors, publishes num_rendered and the overflow flag.
-constexpr int SCAN_THREADS = 1024;
+// Exclusive scan of the T per-tile instance counts.  Writes ranges (the reference leaves empty
+// tiles at (0,0), CR/rasterizer_impl.cu:313-321), turns the counters into scatter cursors,
+// publishes num_rendered and the overflow flag, and lists the tiles longest list first (`order`,
+// half-octave length classes) for the render kernels.
+// One thread-block CLUSTER of 8 CTAs: as a single 1024-thread CTA the kernel was issue-bound on
+// one SM (32 warps x ~1400 instructions = 8 us in the middle of every view's dependent chain).
+// Each CTA scans an eighth of the tiles; chunk totals and class censuses cross the cluster
+// through distributed shared memory between two cluster barriers.
+constexpr int SCAN_CTAS = 8;
+constexpr int SCAN_THREADS = 512;
 constexpr int SCAN_CLASSES = 64;
 // length class of a tile: half octaves of its instance count, LONGEST = class 0
 __device__ __forceinline__ uint32_t length_class(uint32_t c) {
@@ -77,23 +84,44 @@ __device__ __forceinline__ uint32_t length_class(uint32_t c) {
   return (uint32_t)(SCAN_CLASSES - 2 - min(k, SCAN_CLASSES - 2));
 }
 
-__global__ void __launch_bounds__(SCAN_THREADS)
+// Position of a tile inside its length class (phase 2), or just the class census (phase 1), with ONE
+// shared atomic per (warp, class present in the warp): neighbouring tiles mostly share a class.
+// Inactive lanes pass class SCAN_CLASSES (a dump slot).  Inside a warp the order is by lane.
+__device__ __forceinline__ uint32_t class_take(uint32_t* s_class, uint32_t cls, int lane) {
+  const unsigned peers = __match_any_sync(0xffffffffu, cls);
+  const int leader = __ffs(peers) - 1;
+  uint32_t base = 0;
+  if (lane == leader) base = atomicAdd(&s_class[cls], (uint32_t)__popc(peers));
+  base = __shfl_sync(0xffffffffu, base, leader);
+  return base + (uint32_t)__popc(peers & ((1u << lane) - 1u));
+}
+
+__global__ void __cluster_dims__(SCAN_CTAS, 1, 1) __launch_bounds__(SCAN_THREADS)
 tile_scan_kernel(uint32_t tiles, long long cap, uint32_t* __restrict__ cursor,
                  uint2* __restrict__ ranges, uint32_t* __restrict__ status,
                  uint32_t* __restrict__ status_out, uint32_t* __restrict__ order) {
-  __shared__ uint32_t s_total;
-  __shared__ uint32_t s_class[SCAN_CLASSES];   // tiles per length class, then the class cursors
+  namespace cg = cooperative_groups;
+  __shared__ uint32_t s_class[SCAN_CLASSES + 1];     // census of this CTA's tiles (+ dump slot), then the class cursors
+  __shared__ uint32_t s_pub[SCAN_CLASSES];           // the census as the peers read it
+  __shared__ unsigned long long s_total;             // instances of this CTA's tiles (read by the peers)
+  __shared__ unsigned long long s_w64[SCAN_THREADS / 32];
+  __shared__ uint32_t s_all[SCAN_CTAS][SCAN_CLASSES];
+  __shared__ unsigned long long s_tot[SCAN_CTAS];
   pdl_wait();
-  if (threadIdx.x < SCAN_CLASSES) s_class[threadIdx.x] = 0u;
-  __syncthreads();
+  cg::cluster_group cluster = cg::this_cluster();
+  const uint32_t rank = cluster.block_rank();
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const uint32_t per = (tiles + SCAN_THREADS - 1) / SCAN_THREADS;
-  const uint32_t lo = min(tiles, (uint32_t)tid * per), hi = min(tiles, lo + per);
-  // up to SCAN_REG counters per thread stay in registers: their loads are issued together and the
-  // second pass does not read them again (8 x 1024 tiles covers 1920x1080; beyond: the loops)
-  constexpr uint32_t SCAN_REG = 8;
+  if (tid <= SCAN_CLASSES) s_class[tid] = 0u;
+  __syncthreads();
+  const uint32_t chunk = (tiles + SCAN_CTAS - 1) / SCAN_CTAS;
+  const uint32_t c_lo = min(tiles, rank * chunk), c_hi = min(tiles, c_lo + chunk);
+  const uint32_t per = (chunk + SCAN_THREADS - 1) / SCAN_THREADS;      // the same in every CTA
+  const uint32_t lo = min(c_hi, c_lo + (uint32_t)tid * per), hi = min(c_hi, lo + per);
+  // up to SCAN_REG counters per thread stay in registers (2 x 512 x 8 tiles covers 1920x1080);
+  // beyond that the second pass reads them again
+  constexpr uint32_t SCAN_REG = 2;
   const bool in_regs = per <= SCAN_REG;
-  uint32_t cnt[SCAN_REG];
+  uint32_t cnt[SCAN_REG], cls[SCAN_REG];
   unsigned long long mine = 0;
   if (in_regs) {
 #pragma unroll
@@ -101,79 +129,115 @@ tile_scan_kernel(uint32_t tiles, long long cap, uint32_t* __restrict__ cursor,
 #pragma unroll
     for (uint32_t k = 0; k < SCAN_REG; ++k) {
       mine += cnt[k];
-      if (lo + k < hi) atomicAdd(&s_class[length_class(cnt[k])], 1u);
+      cls[k] = lo + k < hi ? length_class(cnt[k]) : (uint32_t)SCAN_CLASSES;
+      class_take(s_class, cls[k], lane);
     }
   } else {
-    for (uint32_t t = lo; t < hi; ++t) {
-      const uint32_t c = cursor[t * CURSOR_STRIDE];
+    for (uint32_t k = 0; k < per; ++k) {       // uniform trip count: class_take is a warp operation
+      const uint32_t t = lo + k;
+      const uint32_t c = t < hi ? cursor[t * CURSOR_STRIDE] : 0u;
       mine += c;
-      atomicAdd(&s_class[length_class(c)], 1u);
+      class_take(s_class, t < hi ? length_class(c) : (uint32_t)SCAN_CLASSES, lane);
     }
   }
-  // block-wide exclusive scan of `mine` (64-bit: the total may exceed 2^32)
+  // CTA-wide exclusive scan of `mine` (64-bit: the total may exceed 2^32)
   unsigned long long incl = mine;
 #pragma unroll
   for (int d = 1; d < 32; d <<= 1) {
     const unsigned long long n = __shfl_up_sync(0xffffffffu, incl, d);
     if (lane >= d) incl += n;
   }
-  __shared__ unsigned long long s_w64[32];
   if (lane == 31) s_w64[warp] = incl;
   __syncthreads();
   if (warp == 0) {
-    unsigned long long w = s_w64[lane];
+    const unsigned long long w = lane < SCAN_THREADS / 32 ? s_w64[lane] : 0ull;
     unsigned long long wi = w;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
       const unsigned long long n = __shfl_up_sync(0xffffffffu, wi, d);
       if (lane >= d) wi += n;
     }
-    s_w64[lane] = wi - w;  // exclusive prefix of the warp
-    // class histogram -> class start offsets (two values per lane)
-    {
-      const uint32_t a = s_class[2 * lane], b = s_class[2 * lane + 1];
-      uint32_t incl2 = a + b;
+    if (lane < SCAN_THREADS / 32) s_w64[lane] = wi - w;  // exclusive prefix of the warp
+    if (lane == 31) s_total = wi;
+  } else if (warp == 1 || warp == 2) {
+    const int k = (warp - 1) * 32 + lane;
+    s_pub[k] = s_class[k];
+  }
+  cluster.sync();        // every CTA's s_total / s_pub is in place (also a CTA barrier)
+
+  // gather the cluster's totals and censuses (distributed shared memory), then a second cluster
+  // barrier: nobody reads a peer's shared memory after it, so CTAs may finish independently
+  {
+    const int c = tid >> 6, k = tid & 63;                 // SCAN_THREADS == SCAN_CTAS * SCAN_CLASSES
+    s_all[c][k] = *cluster.map_shared_rank(&s_pub[k], c);
+    if (tid < SCAN_CTAS) s_tot[tid] = *cluster.map_shared_rank(&s_total, tid);
+  }
+  cluster.sync();
+
+  unsigned long long before = 0, grand = 0;
 #pragma unroll
-      for (int d = 1; d < 32; d <<= 1) {
-        const uint32_t n = __shfl_up_sync(0xffffffffu, incl2, d);
-        if (lane >= d) incl2 += n;
-      }
-      s_class[2 * lane] = incl2 - a - b;
-      s_class[2 * lane + 1] = incl2 - b;
-    }
-    if (lane == 31) {
-      const bool over = wi >= (1ull << 31) || (cap >= 0 && wi > (unsigned long long)cap);
-      status[0] = (uint32_t)min(wi, 0xffffffffull);
-      status[1] = over ? 1u : 0u;
-      if (status_out) {
-        status_out[0] = (uint32_t)min(wi, 0xffffffffull);
-        status_out[1] = over ? 1u : 0u;
-      }
-      s_total = over ? 0xffffffffu : 0u;
+  for (int c = 0; c < SCAN_CTAS; ++c) {
+    const unsigned long long v = s_tot[c];
+    if ((uint32_t)c < rank) before += v;
+    grand += v;
+  }
+  const bool over = grand >= (1ull << 31) || (cap >= 0 && grand > (unsigned long long)cap);
+  if (rank == 0 && tid == 0) {
+    status[0] = (uint32_t)min(grand, 0xffffffffull);
+    status[1] = over ? 1u : 0u;
+    if (status_out) {
+      status_out[0] = (uint32_t)min(grand, 0xffffffffull);
+      status_out[1] = over ? 1u : 0u;
     }
   }
+  if (warp == 0) {
+    // class start offsets over the whole image (two classes per lane) + the share of the CTAs
+    // before this one inside each class -> this CTA's class cursors
+    uint32_t tot[2] = {0u, 0u}, mineoff[2] = {0u, 0u};
+#pragma unroll
+    for (int c = 0; c < SCAN_CTAS; ++c) {
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const uint32_t v = s_all[c][2 * lane + h];
+        tot[h] += v;
+        if ((uint32_t)c < rank) mineoff[h] += v;
+      }
+    }
+    uint32_t incl2 = tot[0] + tot[1];
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t n = __shfl_up_sync(0xffffffffu, incl2, d);
+      if (lane >= d) incl2 += n;
+    }
+    s_class[2 * lane] = incl2 - tot[0] - tot[1] + mineoff[0];
+    s_class[2 * lane + 1] = incl2 - tot[1] + mineoff[1];
+  }
   __syncthreads();
-  const bool over = s_total != 0u;
-  uint32_t run = (uint32_t)(s_w64[warp] + incl - mine);
+  uint32_t run = (uint32_t)(before + s_w64[warp] + incl - mine);
   if (in_regs) {
 #pragma unroll
     for (uint32_t k = 0; k < SCAN_REG; ++k) {
       const uint32_t t = lo + k, c = cnt[k];
+      const uint32_t at = class_take(s_class, cls[k], lane);
       if (t < hi) {
         ranges[t] = (c && !over) ? make_uint2(run, run + c) : make_uint2(0u, 0u);
         cursor[t * CURSOR_STRIDE] = run;
-        order[atomicAdd(&s_class[length_class(c)], 1u)] = t;
+        order[at] = t;
       }
       run += c;
     }
     return;
   }
-  for (uint32_t t = lo; t < hi; ++t) {
-    const uint32_t c = cursor[t * CURSOR_STRIDE];
-    // on overflow every tile is rendered empty; the caller sees status[1] and retries
-    ranges[t] = (c && !over) ? make_uint2(run, run + c) : make_uint2(0u, 0u);
-    cursor[t * CURSOR_STRIDE] = run;
-    order[atomicAdd(&s_class[length_class(c)], 1u)] = t;
+  for (uint32_t k = 0; k < per; ++k) {
+    const uint32_t t = lo + k;
+    const uint32_t c = t < hi ? cursor[t * CURSOR_STRIDE] : 0u;
+    const uint32_t at = class_take(s_class, t < hi ? length_class(c) : (uint32_t)SCAN_CLASSES, lane);
+    if (t < hi) {
+      // on overflow every tile is rendered empty; the caller sees status[1] and retries
+      ranges[t] = (c && !over) ? make_uint2(run, run + c) : make_uint2(0u, 0u);
+      cursor[t * CURSOR_STRIDE] = run;
+      order[at] = t;
+    }
     run += c;
   }
 }
@@ -182,8 +246,8 @@ int launch_tile_scan(const B2gsScene& s, const ImageWS& im, int64_t cap, uint32_
                      cudaStream_t st) {
   const int gx = (s.W + TILE - 1) / TILE, gy = (s.H + TILE - 1) / TILE;
   B2GS_PROF("tile_scan", st);
-  B2GS_LAUNCH(tile_scan_kernel, 1, SCAN_THREADS, st, (uint32_t)(gx * gy), (long long)cap, im.cursor, im.ranges,
-              im.status, status_out, im.order);
+  B2GS_LAUNCH(tile_scan_kernel, SCAN_CTAS, SCAN_THREADS, st, (uint32_t)(gx * gy), (long long)cap, im.cursor,
+              im.ranges, im.status, status_out, im.order);
   B2GS_LAUNCH_CHECK(st, s.debug);
   return B2GS_OK;
 }
