@@ -26,6 +26,14 @@ __device__ __forceinline__ float4 load_gt(const B2gsLossArgs& a, int i) {
                      (a.mode & 2) ? 0.f : a.gt_depth[i]);
 }
 
+__device__ __forceinline__ void prefetch_gt(const B2gsLossArgs& a, int i) {
+  const size_t N = (size_t)a.N;
+  asm volatile("prefetch.global.L2 [%0];" ::"l"(a.gt_image + i));
+  asm volatile("prefetch.global.L2 [%0];" ::"l"(a.gt_image + N + i));
+  asm volatile("prefetch.global.L2 [%0];" ::"l"(a.gt_image + 2 * N + i));
+  if (!(a.mode & 2)) asm volatile("prefetch.global.L2 [%0];" ::"l"(a.gt_depth + i));
+}
+
 __device__ __forceinline__ PixelTerms pixel_terms_of(const B2gsLossArgs& a, float ea, float eb, int i,
                                                     float c0, float c1, float c2, float dep, float op_in,
                                                     float4 gt) {

@@ -230,7 +230,8 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
         const bool skipA = j <= behindA || power.x > 0.0f || alphaA < 1.0f / 255.0f;
         const bool skipB = j <= behindB || power.y > 0.0f || alphaB < 1.0f / 255.0f;
         if (COUNT) ++c_visit;
-        if (__all_sync(FULL, skipA && skipB)) continue;
+        // no warp vote on "every pixel skips" (0.8 % of the visits of the benched view: the block
+        // mask is tight); such a visit adds exact zeros to the splat's row
         if (COUNT) { ++c_full; c_contrib += (unsigned)!skipA + (unsigned)!skipB; }
 
         const f2 alpha = make_float2(skipA ? 0.f : alphaA, skipB ? 0.f : alphaB);

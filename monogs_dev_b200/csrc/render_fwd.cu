@@ -70,13 +70,15 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   const uint2 range = ranges[tile];
   const int n = (int)(range.y - range.x);
 
-  // fused loss: this lane's two ground-truth pixels, requested now, consumed in the epilogue
-  float4 gtA = make_float4(0.f, 0.f, 0.f, 0.f), gtB = gtA;
+  // fused loss: this lane's two ground-truth pixels are pulled into L2 now (prefetch: no register is
+  // held across the blend loop — as register prefetches they cost the kernel a CTA per SM) and
+  // loaded in the epilogue
   if (LOSS) {
-    if (insideA) gtA = load_gt(fl.args, pixA);
-    if (insideB) gtB = load_gt(fl.args, pixB);
+    if (insideA) prefetch_gt(fl.args, pixA);
+    if (insideB) prefetch_gt(fl.args, pixB);
   }
-  const uint32_t cnt_base = (uint32_t)__cvta_generic_to_shared(s_cnt);
+  uint32_t cnt_base = (uint32_t)__cvta_generic_to_shared(s_cnt);
+  asm volatile("" : "+r"(cnt_base));   // keep it in its register (else re-derived from %cluster_ctaid per visit)
   bool doneA = !insideA, doneB = !insideB;
   f2 T = bc(1.0f);
   f2 C0 = bc(0.f), C1 = bc(0.f), C2 = bc(0.f), D = bc(0.f);
@@ -131,7 +133,10 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
           const f2 power = fma2(quad, bc(-0.5f), mul2(dy, bc(nbdx)));
           bool actA = !doneA && !(power.x > 0.0f), actB = !doneB && !(power.y > 0.0f);
           if (COUNT) { ++c_visit; c_blocks += __popc(r.bm & wmask); }
-          if (!__any_sync(RF_FULL, actA || actB)) continue;
+          // no warp vote on (actA || actB) here: the block mask already says that the splat reaches
+          // this quadrant, so "no live pixel with power <= 0" never happened in 1.6 M visits of the
+          // benched view (ncu source counters), and the vote + branch were 6 of 88 instructions per
+          // visit.  A visit that no pixel takes blends alpha = 0 everywhere: exact no-ops.
           if (COUNT) ++c_full;
           const f2 og = mul2(bc(co.w), expf_pair(power));
           const float alphaA = fminf(0.99f, og.x), alphaB = fminf(0.99f, og.y);
@@ -154,11 +159,11 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
           lastB = actB ? here : lastB;
           // n_touched: how many pixels saw this splat with T still above 0.5
           if (hot) {
-            const unsigned ta = __ballot_sync(RF_FULL, actA && test_T.x > 0.5f);
-            const unsigned tb = __ballot_sync(RF_FULL, actB && test_T.y > 0.5f);
-            if ((ta | tb) != 0u && lane == 0) {   // plain red.shared: one lane, nothing to aggregate
-              asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(cnt_base + 4u * (uint32_t)j),
-                           "r"(__popc(ta) + __popc(tb)) : "memory");
+            // one warp-wide integer add (REDUX) instead of two ballots + two popcounts
+            const unsigned mine = (unsigned)(actA && test_T.x > 0.5f) + (unsigned)(actB && test_T.y > 0.5f);
+            const unsigned tot = __reduce_add_sync(RF_FULL, mine);
+            if (tot != 0u && lane == 0) {   // plain red.shared: one lane, nothing to aggregate
+              asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(cnt_base + 4u * (uint32_t)j), "r"(tot) : "memory");
             }
           }
         }
@@ -211,14 +216,14 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     float red[4] = {0.f, 0.f, 0.f, 0.f};
     if (insideA) {
       const PixelLoss r = pixel_loss(fl.args, ea, eb, w_rgb, w_dep, pixA, C0.x + T.x * bg[0], C1.x + T.x * bg[1],
-                                     C2.x + T.x * bg[2], D.x, 1 - T.x, gtA);
+                                     C2.x + T.x * bg[2], D.x, 1 - T.x, load_gt(fl.args, pixA));
       fl.dL_dimage[0 * plane + pixA] = r.g[0]; fl.dL_dimage[1 * plane + pixA] = r.g[1];
       fl.dL_dimage[2 * plane + pixA] = r.g[2]; fl.dL_ddepth[pixA] = r.gd;
       red[0] += r.rgb; red[1] += r.dep; red[2] += r.ga; red[3] += r.gb;
     }
     if (insideB) {
       const PixelLoss r = pixel_loss(fl.args, ea, eb, w_rgb, w_dep, pixB, C0.y + T.y * bg[0], C1.y + T.y * bg[1],
-                                     C2.y + T.y * bg[2], D.y, 1 - T.y, gtB);
+                                     C2.y + T.y * bg[2], D.y, 1 - T.y, load_gt(fl.args, pixB));
       fl.dL_dimage[0 * plane + pixB] = r.g[0]; fl.dL_dimage[1 * plane + pixB] = r.g[1];
       fl.dL_dimage[2 * plane + pixB] = r.g[2]; fl.dL_ddepth[pixB] = r.gd;
       red[0] += r.rgb; red[1] += r.dep; red[2] += r.ga; red[3] += r.gb;
