@@ -379,6 +379,13 @@ B2GS_API int b2gs_adam_step_fused(const B2gsAdamSegment* segments, int32_t num_s
 /* The first of the two barriers of b2gs_adam_step_peer on its own: all ranks' streams meet, and the
  * update guard of the calling thread (b2gs_set_update_guard) becomes the OR over all ranks. */
 B2GS_API int b2gs_peer_barrier(const B2gsPeerArena* peers, void* stream);
+/* The same, but this rank's contribution to the guard is the OR of status[2 i + 1], i < n_views — the
+ * overflow flags its forward passes left in B2gsForwardOut.status ((instances, overflow) pairs, one
+ * per view, contiguous) — instead of the guard word's current value: the barrier then depends on the
+ * views' backward passes only, and b2gs_window_finalize (called with guard = NULL) can run beside it.
+ * No counterpart in the reference (its loop is single-GPU). */
+B2GS_API int b2gs_peer_barrier_status(const B2gsPeerArena* peers, const uint32_t* status, int32_t n_views,
+                             void* stream);
 /* cudaMemsetAsync through the C ABI (a step built from libb2gs calls only needs no framework kernel). */
 B2GS_API int b2gs_memset_async(void* device_ptr, int value, size_t bytes, void* stream);
 B2GS_API int b2gs_adam_step_peer_fused(const B2gsAdamSegment* segments, int32_t num_segments,

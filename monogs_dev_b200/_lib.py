@@ -187,6 +187,7 @@ SYMBOLS = {
                                      C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
                                      C.POINTER(C.c_void_p), C.c_void_p]),
     "b2gs_peer_barrier": (C.c_int, [C.POINTER(B2gsPeerArena), C.c_void_p]),
+    "b2gs_peer_barrier_status": (C.c_int, [C.POINTER(B2gsPeerArena), C.c_void_p, C.c_int32, C.c_void_p]),
     "b2gs_memset_async": (C.c_int, [C.c_void_p, C.c_int, C.c_size_t, C.c_void_p]),
     "b2gs_window_finalize": (C.c_int, [C.POINTER(B2gsViewFinalize), C.c_int32, C.c_void_p, C.c_void_p,
                                        C.c_void_p, C.c_void_p]),

@@ -146,15 +146,25 @@ __device__ __forceinline__ void multimem_st(float* mc_addr, float4 v) {
 // With a guard word: every rank also posts its guard value on all pads (slots 16 + src) before
 // arriving, and leaves the OR over all ranks in its own guard word — the ranks then agree on
 // whether this step's update is discarded.
+// With status words (b2gs_peer_barrier_status): this rank's guard value is not read from *guard but
+// formed here as the OR of status[2 i + 1], the overflow flags the forward passes of the rank's
+// n_status views left (B2gsForwardOut.status) — the caller need not wait for b2gs_window_finalize.
 __global__ void peer_barrier_kernel(const __grid_constant__ PeerTable pt, uint32_t* __restrict__ fail,
                                     int32_t* __restrict__ guard, long long* __restrict__ tick,
-                                    const int32_t* __restrict__ tick_guard) {
+                                    const int32_t* __restrict__ tick_guard,
+                                    const uint32_t* __restrict__ status, int n_status) {
   pdl_wait();
   const int t = threadIdx.x;
   const bool peer = t < pt.world && t != pt.rank;
   if (guard && t < pt.world) {
+    uint32_t mine = 0;
+    if (status) {
+      for (int i = 0; i < n_status; ++i) mine |= status[2 * i + 1];
+    } else {
+      mine = (uint32_t)*guard;
+    }
     volatile uint32_t* slot = pt.signal[t] + PEER_MAX + pt.rank;
-    *slot = (uint32_t)(*guard != 0);
+    *slot = (uint32_t)(mine != 0);
   }
   if (peer) {
     __threadfence_system();
@@ -400,7 +410,7 @@ extern "C" int b2gs_adam_step_peer_fused(const B2gsAdamSegment* segments, int32_
   // in *guard, and sets it when a peer timed out: the update below is then skipped on every rank)
   if (!(flags & B2GS_ADAM_NO_FIRST_BARRIER)) {
     B2GS_LAUNCH(peer_barrier_kernel, 1, 32, st, pt, peers->fail_flag, guard, (long long*)nullptr,
-                (const int32_t*)nullptr);
+                (const int32_t*)nullptr, (const uint32_t*)nullptr, 0);
     B2GS_LAUNCH_CHECK(st, 0);
   }
   // ... and only now may the step counter advance: with the rank-local guard value a rank whose own
@@ -422,7 +432,7 @@ extern "C" int b2gs_adam_step_peer_fused(const B2gsAdamSegment* segments, int32_
   // ... and every replica has been written, every gradient arena read, by all of its chunk owners
   B2GS_LAUNCH(peer_barrier_kernel, 1, 32, st, pt, peers->fail_flag, (int32_t*)nullptr,
               (flags & B2GS_ADAM_TICK_LATE) ? reinterpret_cast<long long*>(step_counter) : (long long*)nullptr,
-              (const int32_t*)guard);
+              (const int32_t*)guard, (const uint32_t*)nullptr, 0);
   B2GS_LAUNCH_CHECK(st, 0);
   if (flags & B2GS_ADAM_NO_ZERO) return B2GS_OK;
   // zero_grad: every rank clears ITS OWN gradient arena (local HBM writes) now that all owners have
@@ -472,7 +482,21 @@ extern "C" int b2gs_peer_barrier(const B2gsPeerArena* peers, void* stream) {
   if (rc) return rc;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   B2GS_LAUNCH(b2gs::peer_barrier_kernel, 1, 32, st, pt, peers->fail_flag, const_cast<int32_t*>(b2gs::update_guard()),
-              (long long*)nullptr, (const int32_t*)nullptr);
+              (long long*)nullptr, (const int32_t*)nullptr, (const uint32_t*)nullptr, 0);
+  B2GS_LAUNCH_CHECK(st, 0);
+  return B2GS_OK;
+}
+
+extern "C" int b2gs_peer_barrier_status(const B2gsPeerArena* peers, const uint32_t* status, int32_t n_views,
+                                        void* stream) {
+  if (!status || n_views < 1) { b2gs::set_error("b2gs_peer_barrier_status: status words of >= 1 view needed"); return B2GS_ERR_INVALID; }
+  if (!b2gs::update_guard()) { b2gs::set_error("b2gs_peer_barrier_status: no update guard set (b2gs_set_update_guard)"); return B2GS_ERR_INVALID; }
+  b2gs::PeerTable pt;
+  int rc = peer_table(peers, &pt);
+  if (rc) return rc;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  B2GS_LAUNCH(b2gs::peer_barrier_kernel, 1, 32, st, pt, peers->fail_flag, const_cast<int32_t*>(b2gs::update_guard()),
+              (long long*)nullptr, (const int32_t*)nullptr, status, (int)n_views);
   B2GS_LAUNCH_CHECK(st, 0);
   return B2GS_OK;
 }

@@ -471,6 +471,7 @@ class MappingWindow:
                                     rank=self.rank, world=self.world)
             if self.peer is not None:
                 self.peer.set_fail_word(self._lean.fail)
+                self._lean.defer_finalize = bool(self.local)
         self.last = {}
         self._g1 = self._g2 = None
         self._ovf = self._status_all = None

@@ -79,6 +79,9 @@ class LeanWindow:
         self.views = {}
         self._arena_key = None
         self.launches_fb = self.launches_up = 0
+        # peer mode (MappingWindow sets it): forward_backward leaves b2gs_window_finalize to update()
+        self.defer_finalize = False
+        self._fin_pending = False
         # peer mode: the gradient arena of a step is cleared at the START of the next one, on a side
         # branch under the forward kernels (it is first needed by the backward), and the camera step
         # runs beside the exchange: neither sits on the critical path of a one-view rank
@@ -335,8 +338,11 @@ class LeanWindow:
             if self._zero_pending and not self.pose_only and not self.local:
                 main.wait_event(self._zero_event)
             if self.local:
-                check(lib.b2gs_window_finalize(self._fin_arr, len(self.local), self.loss_total.data_ptr(),
-                                               self.guard.data_ptr(), self.tickets.data_ptr(), main.cuda_stream))
+                if self.defer_finalize:
+                    self._fin_pending = True       # update() runs it beside the first peer barrier
+                else:
+                    check(lib.b2gs_window_finalize(self._fin_arr, len(self.local), self.loss_total.data_ptr(),
+                                                   self.guard.data_ptr(), self.tickets.data_ptr(), main.cuda_stream))
         self.launches_fb = lib.b2gs_kernel_launches() - n0
         return self.loss_total
 
@@ -369,8 +375,18 @@ class LeanWindow:
                     # this rank's gradient arena is cleared at the start of the next step
                     main = torch.cuda.current_stream()
                     aux = self._aux()
-                    check(lib.b2gs_peer_barrier(peer.struct(), st))
-                    aux.wait_stream(main)
+                    if self._fin_pending:
+                        # the barrier forms this rank's guard from the views' overflow flags itself, so
+                        # the finalize kernel (losses, camera gradients) leaves the critical path too
+                        self._fin_pending = False
+                        aux.wait_stream(main)
+                        check(lib.b2gs_window_finalize(self._fin_arr, len(self.local), self.loss_total.data_ptr(),
+                                                       None, self.tickets.data_ptr(), aux.cuda_stream))
+                        check(lib.b2gs_peer_barrier_status(peer.struct(), self.status_all.data_ptr(),
+                                                           len(self.local), st))
+                    else:
+                        check(lib.b2gs_peer_barrier(peer.struct(), st))
+                    aux.wait_stream(main)          # the camera step needs the OR'd guard
                     check(lib.b2gs_pose_step(self._pose_arr, len(self.local), self.kf_step.data_ptr(), None, 0.9, 0.999,
                                              1e-8, self.tickets.data_ptr() + 4, aux.cuda_stream))
                     check(lib.b2gs_adam_step_peer_fused(
@@ -382,6 +398,10 @@ class LeanWindow:
                         self.views[v].cam._host_RT = None
                     self.launches_up = lib.b2gs_kernel_launches() - n0
                     return
+                if self._fin_pending:              # deferred, but this update has no exchange to hide it under
+                    self._fin_pending = False
+                    check(lib.b2gs_window_finalize(self._fin_arr, len(self.local), self.loss_total.data_ptr(),
+                                                   self.guard.data_ptr(), self.tickets.data_ptr(), st))
                 if gaussians:
                     if peer is not None:
                         pass
