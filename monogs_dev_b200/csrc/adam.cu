@@ -60,12 +60,20 @@ adam_kernel(const __grid_constant__ AdamTable t, float w1, float beta2, float w2
   float neg_step = t.neg_step_size[s];
   if (step_dev != nullptr) {
     // CUDA-graph capturable form: the step count lives on the device (incremented by
-    // adam_tick_kernel just before); same double-precision scalar prep as the host path
-    const double step = (double)(*step_dev + ((flags & B2GS_ADAM_NO_TICK) ? 1 : 0));
-    const double bc1 = 1.0 - pow((double)beta1, step);
-    bc2_sqrt = (float)sqrt(1.0 - pow((double)beta2, step));
-    const float lr = t.lr_dev[s] ? t.lr_dev[s][0] : t.lr[s];
-    neg_step = (float)(-((double)lr / bc1));
+    // adam_tick_kernel just before); same double-precision scalar prep as the host path.
+    // Once per block, not once per thread: the two double-precision pow() are ~500 instructions,
+    // more than a thread's whole share of the update (4 float4 trips).
+    __shared__ float s_bc[2];
+    if (threadIdx.x == 0) {
+      const double step = (double)(*step_dev + ((flags & B2GS_ADAM_NO_TICK) ? 1 : 0));
+      const double bc1 = 1.0 - pow((double)beta1, step);
+      const float lr = t.lr_dev[s] ? t.lr_dev[s][0] : t.lr[s];
+      s_bc[0] = (float)sqrt(1.0 - pow((double)beta2, step));
+      s_bc[1] = (float)(-((double)lr / bc1));
+    }
+    __syncthreads();
+    bc2_sqrt = s_bc[0];
+    neg_step = s_bc[1];
   }
 
   const bool vec = ((((uintptr_t)p | (uintptr_t)g | (uintptr_t)m | (uintptr_t)v) & 15) == 0);

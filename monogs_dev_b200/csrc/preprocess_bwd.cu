@@ -55,12 +55,28 @@ __device__ __forceinline__ V3 sh_backward(int deg, int M, const float* __restric
   dL_dRGB.z *= (clamp_bits & 4) ? 0.f : 1.f;
   const float g[3] = {dL_dRGB.x, dL_dRGB.y, dL_dRGB.z};
 
+  float ddir[3] = {0.f, 0.f, 0.f};  // dL/d(dir)
+  // the constant (DC) basis function on its own: degree 0 — the mapping configuration — then never
+  // touches the run-time indexed basis table below (a 64 B local-memory array)
+  if (d_dc != nullptr) {
+    if (accumulate) {
+      atomicAdd(d_dc, B2GS_SH_C0 * g[0]); atomicAdd(d_dc + 1, B2GS_SH_C0 * g[1]); atomicAdd(d_dc + 2, B2GS_SH_C0 * g[2]);
+    } else {
+      d_dc[0] = B2GS_SH_C0 * g[0]; d_dc[1] = B2GS_SH_C0 * g[1]; d_dc[2] = B2GS_SH_C0 * g[2];
+    }
+  }
+  if (deg == 0) {
+    for (int k = 1; d_dc != nullptr && !accumulate && k < M; ++k) {
+      float* o = d_rest + 3 * (k - 1);
+      o[0] = 0.f; o[1] = 0.f; o[2] = 0.f;
+    }
+    return dnormvdv3(dir_orig, V3{0.f, 0.f, 0.f});
+  }
   float basis[16];
 #pragma unroll
   for (int i = 0; i < 16; ++i) basis[i] = 0.f;
   basis[0] = B2GS_SH_C0;
-  float ddir[3] = {0.f, 0.f, 0.f};  // dL/d(dir)
-  if (deg > 0) {
+  {
     basis[1] = -B2GS_SH_C1 * y;
     basis[2] = B2GS_SH_C1 * z;
     basis[3] = -B2GS_SH_C1 * x;
@@ -113,9 +129,9 @@ __device__ __forceinline__ V3 sh_backward(int deg, int M, const float* __restric
     }
   }
   const int active = (deg + 1) * (deg + 1);
-  for (int k = 0; d_dc != nullptr && k < M; ++k) {
+  for (int k = 1; d_dc != nullptr && k < M; ++k) {
     const float bk = (k < active && k < 16) ? basis[k] : 0.f;
-    float* o = k == 0 ? d_dc : d_rest + 3 * (k - 1);
+    float* o = d_rest + 3 * (k - 1);
     if (accumulate) {
       if (bk != 0.f) { atomicAdd(o, bk * g[0]); atomicAdd(o + 1, bk * g[1]); atomicAdd(o + 2, bk * g[2]); }
     } else {
