@@ -110,7 +110,8 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
                   const float4* __restrict__ conic_o, const float4* __restrict__ rgbd,
                   const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib,
                   const float* __restrict__ dL_dpixels, const float* __restrict__ dL_dpixels_depth,
-                  float* __restrict__ acc, unsigned long long* __restrict__ counters) {
+                  float* __restrict__ acc, unsigned long long* __restrict__ counters, float expf_k,
+                  float expf_252) {
   __shared__ SplatRec s_rec[RB_BATCH];
   __shared__ int s_max;
   unsigned c_visit = 0, c_full = 0, c_contrib = 0;
@@ -224,7 +225,7 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
         const f2 cdy2 = mul2(dy, mul2(bc(co.z), dy));
         const f2 quad = fma2(bc(dx), bc(adx), cdy2);
         const f2 power = fma2(quad, bc(-0.5f), mul2(dy, bc(nbdx)));
-        const f2 G = expf_pair(power);
+        const f2 G = expf_pair(power, expf_k, expf_252);
         const f2 og = mul2(bc(co.w), G);
         const float alphaA = fminf(0.99f, og.x), alphaB = fminf(0.99f, og.y);
         const bool skipA = j <= behindA || power.x > 0.0f || alphaA < 1.0f / 255.0f;
@@ -293,11 +294,11 @@ int launch_render_bwd(const B2gsScene& s, const GeomWS& g, const ImageWS& im, co
   if (cnt)
     B2GS_LAUNCH(render_bwd_kernel<true>, gx * gy, RB_THREADS, st, im.ranges, im.order, b.point_list, s.W, s.H, gx, s.bg, g.xy,
                                                             g.conic_o, g.rgbd, im.final_T, im.n_contrib,
-                                                            io.dL_dcolor, io.dL_ddepth, acc, cnt);
+                                                            io.dL_dcolor, io.dL_ddepth, acc, cnt, expf_k_host(), 252.0f);
   else
     B2GS_LAUNCH(render_bwd_kernel<false>, gx * gy, RB_THREADS, st, im.ranges, im.order, b.point_list, s.W, s.H, gx, s.bg, g.xy,
                                                              g.conic_o, g.rgbd, im.final_T, im.n_contrib,
-                                                             io.dL_dcolor, io.dL_ddepth, acc, nullptr);
+                                                             io.dL_dcolor, io.dL_ddepth, acc, nullptr, expf_k_host(), 252.0f);
   B2GS_LAUNCH_CHECK(st, s.debug);
   return B2GS_OK;
 }

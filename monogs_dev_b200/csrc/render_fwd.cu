@@ -47,7 +47,8 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
                   float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
                   float* __restrict__ out_color, float* __restrict__ out_depth,
                   float* __restrict__ out_opacity, int* __restrict__ n_touched,
-                  unsigned long long* __restrict__ counters, const __grid_constant__ B2gsFusedLoss fl) {
+                  unsigned long long* __restrict__ counters, const __grid_constant__ B2gsFusedLoss fl,
+                  float expf_k, float expf_252) {
   __shared__ SplatRec s_rec[RF_BATCH];
   unsigned c_visit = 0, c_full = 0, c_contrib = 0, c_blocks = 0;
   __shared__ int s_cnt[RF_BATCH];
@@ -106,6 +107,7 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     __syncthreads();
 
     if (!__all_sync(RF_FULL, doneA && doneB)) {
+      int lastjA = -1, lastjB = -1;
       for (int c0 = 0; c0 < cnt; c0 += 32) {
         // can the splat reach this warp's quadrant at all?  (bits computed once by the binning
         // stage, cull.cuh: splat_block_mask)
@@ -138,7 +140,7 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
           // benched view (ncu source counters), and the vote + branch were 6 of 88 instructions per
           // visit.  A visit that no pixel takes blends alpha = 0 everywhere: exact no-ops.
           if (COUNT) ++c_full;
-          const f2 og = mul2(bc(co.w), expf_pair(power));
+          const f2 og = mul2(bc(co.w), expf_pair(power, expf_k, expf_252));
           const float alphaA = fminf(0.99f, og.x), alphaB = fminf(0.99f, og.y);
           actA = actA && !(alphaA < 1.0f / 255.0f);
           actB = actB && !(alphaB < 1.0f / 255.0f);
@@ -154,9 +156,9 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
           D = fma2(bc(cd.w), w, D);
           T = make_float2(actA ? test_T.x : T.x, actB ? test_T.y : T.y);
           if (COUNT) c_contrib += (unsigned)actA + (unsigned)actB;
-          const uint32_t here = (uint32_t)(base + j + 1);
-          lastA = actA ? here : lastA;
-          lastB = actB ? here : lastB;
+          // last contributor inside this batch (list position = base + j + 1, formed after the batch)
+          lastjA = actA ? j : lastjA;
+          lastjB = actB ? j : lastjB;
           // n_touched: how many pixels saw this splat with T still above 0.5
           if (hot) {
             // one warp-wide integer add (REDUX) instead of two ballots + two popcounts
@@ -169,6 +171,8 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
         }
         if (__all_sync(RF_FULL, doneA && doneB)) break;  // warp-level early termination
       }
+      if (lastjA >= 0) lastA = (uint32_t)(base + lastjA + 1);
+      if (lastjB >= 0) lastB = (uint32_t)(base + lastjB + 1);
     }
     __syncthreads();
     for (int t = tid; t < cnt; t += RF_THREADS) {
@@ -256,7 +260,7 @@ int launch_render_fwd(const B2gsScene& s, const GeomWS& g, const ImageWS& im, co
   B2GS_LAUNCH((render_fwd_kernel<C_, L_>), gx * gy, RF_THREADS, st,                                  \
       im.ranges, im.order, b.point_list, s.W, s.H, gx, g.xy, g.conic_o, g.rgbd, s.bg, im.final_T,     \
       im.n_contrib,                                                                                  \
-      out.color, out.depth, out.opacity, out.n_touched, cnt, fl)
+      out.color, out.depth, out.opacity, out.n_touched, cnt, fl, expf_k_host(), 252.0f)
   if (out.fused_loss) {
     if (cnt) B2GS_RF_LAUNCH(true, true); else B2GS_RF_LAUNCH(false, true);
   } else {
