@@ -1011,6 +1011,10 @@ class TrackingLoop:
                     break
             return self.pkg
         rz.set_sync_free(True, rz._SyncFree.headroom)
+        # the frame as loaded: an overflow anywhere in the loop restores THIS state (pose, exposure,
+        # fresh optimizer) and runs all iterations again — not the state after the warm-up iterations
+        # with zeroed moments (advisor finding)
+        snap = self.cam.state.clone(), [p.detach().clone() for g in self.opt.param_groups for p in g["params"]]
         done = 0
         if self._graph is None:
             s = torch.cuda.Stream()
@@ -1026,7 +1030,6 @@ class TrackingLoop:
             with torch.cuda.graph(self._graph):
                 self.pkg, self.loss, _ = self._iteration()
             self.graph_launches = lib.b2gs_kernel_launches() - l0
-        snap = self.cam.state.clone(), [p.detach().clone() for g in self.opt.param_groups for p in g["params"]]
         for _ in range(iters - done):
             self._graph.replay()
         from types import SimpleNamespace
@@ -1042,5 +1045,5 @@ class TrackingLoop:
                     p.copy_(q)
             self._reset_optimizer()
             self._graph = None
-            return self.track(iters - done, check_converged)
+            return self.track(iters, check_converged)
         return self.pkg
