@@ -46,7 +46,8 @@ __device__ __forceinline__ V3 dnormvdv3(V3 v, V3 dv) {
 __device__ __forceinline__ V3 sh_backward(int deg, int M, const float* __restrict__ dc,
                                           const float* __restrict__ rest, V3 pos, V3 campos,
                                           uint8_t clamp_bits, V3 dL_dRGB, float* __restrict__ d_dc,
-                                          float* __restrict__ d_rest, bool accumulate) {
+                                          float* __restrict__ d_rest, bool accumulate,
+                                          float* __restrict__ stage_row = nullptr) {
   V3 dir_orig = {pos.x - campos.x, pos.y - campos.y, pos.z - campos.z};
   float len = sqrtf(dir_orig.x * dir_orig.x + dir_orig.y * dir_orig.y + dir_orig.z * dir_orig.z);
   const float x = dir_orig.x / len, y = dir_orig.y / len, z = dir_orig.z / len;
@@ -60,12 +61,13 @@ __device__ __forceinline__ V3 sh_backward(int deg, int M, const float* __restric
   // touches the run-time indexed basis table below (a 64 B local-memory array)
   if (d_dc != nullptr) {
     if (accumulate) {
-      atomicAdd(d_dc, B2GS_SH_C0 * g[0]); atomicAdd(d_dc + 1, B2GS_SH_C0 * g[1]); atomicAdd(d_dc + 2, B2GS_SH_C0 * g[2]);
+      red_add3(d_dc, B2GS_SH_C0 * g[0], B2GS_SH_C0 * g[1], B2GS_SH_C0 * g[2]);
     } else {
       d_dc[0] = B2GS_SH_C0 * g[0]; d_dc[1] = B2GS_SH_C0 * g[1]; d_dc[2] = B2GS_SH_C0 * g[2];
     }
   }
   if (deg == 0) {
+    for (int k = 0; stage_row != nullptr && k < 3 * (M - 1); ++k) stage_row[k] = 0.f;
     for (int k = 1; d_dc != nullptr && !accumulate && k < M; ++k) {
       float* o = d_rest + 3 * (k - 1);
       o[0] = 0.f; o[1] = 0.f; o[2] = 0.f;
@@ -132,8 +134,10 @@ __device__ __forceinline__ V3 sh_backward(int deg, int M, const float* __restric
   for (int k = 1; d_dc != nullptr && k < M; ++k) {
     const float bk = (k < active && k < 16) ? basis[k] : 0.f;
     float* o = d_rest + 3 * (k - 1);
-    if (accumulate) {
-      if (bk != 0.f) { atomicAdd(o, bk * g[0]); atomicAdd(o + 1, bk * g[1]); atomicAdd(o + 2, bk * g[2]); }
+    if (stage_row != nullptr) {      // the warp adds its 32 rows to the arena together (kernel tail)
+      stage_row[3 * (k - 1)] = bk * g[0]; stage_row[3 * (k - 1) + 1] = bk * g[1]; stage_row[3 * (k - 1) + 2] = bk * g[2];
+    } else if (accumulate) {
+      if (bk != 0.f) red_add3(o, bk * g[0], bk * g[1], bk * g[2]);
     } else {
       o[0] = bk * g[0]; o[1] = bk * g[1]; o[2] = bk * g[2];
     }
@@ -165,6 +169,12 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
                       float half_h) {
   __shared__ float s_view[16], s_proj[16];
   __shared__ float s_tau[4][7];
+  // accumulate mode, SH degree > 0: the dL_dsh_rest rows of a warp's 32 Gaussians are one contiguous,
+  // 16-byte aligned span of the arena, so they are staged here and added with red.v4 by the whole
+  // warp — 11 reduction lane-operations per Gaussian at degree 3 instead of 45 scalar ones (the
+  // kernel was bound by their number at cfg5: 0.98 -> 0.78 ms with v2 triplets alone)
+  constexpr int SH_STAGE_MAX = 45;       // 3 * (16 - 1) floats per Gaussian
+  __shared__ __align__(16) float s_rest[RAW ? 128 * SH_STAGE_MAX : 4];
   pdl_wait();
   // statistics gates (B2gsBackwardIO.stats_gate): this view overflowed / the previous step was
   // discarded / the host has already counted this view for the step being re-run
@@ -202,6 +212,13 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
     if (shs != nullptr) clamp_in = clamped[idx];
   }
   const bool live = radius_in > 0;
+  const int R3 = 3 * (M - 1);
+  const bool coop = RAW && accumulate && dL_dsh != nullptr && dL_dsh_rest != nullptr && shs != nullptr && M > 1 &&
+                    M <= 16 && D > 0 && blockDim.x == 128 && (reinterpret_cast<uintptr_t>(dL_dsh_rest) & 15u) == 0;
+  float* const stage_row = coop ? s_rest + threadIdx.x * R3 : nullptr;
+  if (coop && !live) {
+    for (int k = 0; k < R3; ++k) stage_row[k] = 0.f;
+  }
 
   if (idx < P && !live && !accumulate) {
     // culled: every gradient row is zero (reference: torch::zeros, DGR/rasterize_points.cu:160-170)
@@ -400,7 +417,7 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
         d_rest = RAW ? dL_dsh_rest + (size_t)idx * (M - 1) * 3 : d_dc + 3;
       }
       const V3 dm = sh_backward(D, M, dc, rest, V3{mean.x, mean.y, mean.z}, campos, clamp_in,
-                                dL_dcol, d_dc, d_rest, accumulate != 0);
+                                dL_dcol, d_dc, d_rest, accumulate != 0, stage_row);
       dmean.x += dm.x; dmean.y += dm.y; dmean.z += dm.z;
       tau[0] += -dm.x; tau[1] += -dm.y; tau[2] += -dm.z;
       if (dL_dcolors) { dL_dcolors[3 * idx] = dL_dcol.x; dL_dcolors[3 * idx + 1] = dL_dcol.y; dL_dcolors[3 * idx + 2] = dL_dcol.z; }
@@ -435,8 +452,7 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
         if (accumulate) {
           // red.global.add: fire-and-forget, no load latency at the tail of the kernel (rows are
           // private to this thread, so there is no contention)
-          atomicAdd(&dL_dscales[3 * idx + 0], ds0); atomicAdd(&dL_dscales[3 * idx + 1], ds1);
-          atomicAdd(&dL_dscales[3 * idx + 2], ds2);
+          red_add3(&dL_dscales[3 * (size_t)idx], ds0, ds1, ds2);
         } else {
           dL_dscales[3 * idx + 0] = ds0; dL_dscales[3 * idx + 1] = ds1; dL_dscales[3 * idx + 2] = ds2;
         }
@@ -464,7 +480,11 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
         }
         if (accumulate) {
           float* out = dL_drots + 4 * (size_t)idx;
-          atomicAdd(out, dq.x); atomicAdd(out + 1, dq.y); atomicAdd(out + 2, dq.z); atomicAdd(out + 3, dq.w);
+          if ((reinterpret_cast<uintptr_t>(out) & 15u) == 0) {      // uniform: rows are 16 B
+            red_add_v4(out, dq.x, dq.y, dq.z, dq.w);
+          } else {
+            atomicAdd(out, dq.x); atomicAdd(out + 1, dq.y); atomicAdd(out + 2, dq.z); atomicAdd(out + 3, dq.w);
+          }
         } else {
           reinterpret_cast<float4*>(dL_drots)[idx] = dq;
         }
@@ -486,9 +506,7 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
     // (pose-only callers — tracking — pass NULL for the per-Gaussian outputs they do not want)
     if (accumulate) {
       if (dL_dmeans3D) {
-        atomicAdd(&dL_dmeans3D[3 * idx], dmean.x);
-        atomicAdd(&dL_dmeans3D[3 * idx + 1], dmean.y);
-        atomicAdd(&dL_dmeans3D[3 * idx + 2], dmean.z);
+        red_add3(&dL_dmeans3D[3 * (size_t)idx], dmean.x, dmean.y, dmean.z);
       }
       if (dL_dopacity) atomicAdd(&dL_dopacity[idx], d_op);
     } else {
@@ -513,6 +531,27 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
     if (st_max_radii) atomicMax(reinterpret_cast<int*>(st_max_radii) + idx, __float_as_int((float)radius_in));
   }
 
+  if (coop) {
+    __syncwarp();
+    const int wl = threadIdx.x & 31, ww = threadIdx.x >> 5;
+    const size_t span0 = (size_t)(blockIdx.x * 128 + ww * 32) * (size_t)R3;   // the warp's first float in dL_dsh_rest
+    const size_t total = (size_t)P * (size_t)R3;
+    const float4* src = reinterpret_cast<const float4*>(s_rest + ww * 32 * R3);
+    for (int q = wl; q < 8 * R3; q += 32) {
+      const float4 v = src[q];
+      if (v.x != 0.f || v.y != 0.f || v.z != 0.f || v.w != 0.f) {
+        const size_t f = span0 + 4 * (size_t)q;
+        if (f + 4 <= total) {
+          red_add_v4(dL_dsh_rest + f, v.x, v.y, v.z, v.w);
+        } else {                        // the last chunk of the array: stay inside it
+          const float e[4] = {v.x, v.y, v.z, v.w};
+          for (int k = 0; k < 4; ++k)
+            if (f + k < total && e[k] != 0.f) atomicAdd(dL_dsh_rest + f + k, e[k]);
+        }
+      }
+    }
+  }
+
   // ---- isotropic-scale regulariser (utils/slam_backend.py:229-231), every Gaussian, visible or
   // not: value partial + gradient wrt the raw log-scales added to the gradient arena ----
   float reg = 0.f;
@@ -524,9 +563,8 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
     const float g0 = (float)(d0 > 0.f) - (float)(d0 < 0.f), g1 = (float)(d1 > 0.f) - (float)(d1 < 0.f),
                 g2 = (float)(d2 > 0.f) - (float)(d2 < 0.f);
     const float gm = (g0 + g1 + g2) / 3.0f;          // through the mean
-    atomicAdd(&dL_dscales[3 * idx], iso_w * (g0 - gm) * s0);   // d exp(x) = exp(x) dx
-    atomicAdd(&dL_dscales[3 * idx + 1], iso_w * (g1 - gm) * s1);
-    atomicAdd(&dL_dscales[3 * idx + 2], iso_w * (g2 - gm) * s2);
+    // d exp(x) = exp(x) dx
+    red_add3(&dL_dscales[3 * (size_t)idx], iso_w * (g0 - gm) * s0, iso_w * (g1 - gm) * s1, iso_w * (g2 - gm) * s2);
   }
 
   // ---- dL_dtau (+ the regulariser partial): warp -> block -> one partial row per block ----
