@@ -412,7 +412,7 @@ def run_native(args):
     kfs = build_window(device, sc)
     gm = mapping.GaussianModel(sc.xyz, sc.f_dc, sc.f_rest, sc.opacity, sc.scaling, sc.rotation,
                                sh_degree=sc.sh_degree)
-    win = mapping.MappingWindow(gm, kfs, sc.bg, pose_lr=POSE_LR, cuda_graph=graph, view_streams=args.view_streams,
+    win = mapping.MappingWindow(gm, kfs, sc.bg, pose_lr=POSE_LR, cuda_graph=graph, view_streams=(args.view_streams or None),
                                 peer_adam=(args.peer_mode if args.peer_mode == "nomc" else True)
                                 if (world > 1 and not args.no_peer_adam) else False)
     local_views = win.local
@@ -482,8 +482,8 @@ def run_native(args):
                        if getattr(win, "peer", None) is not None else ""),
                    "launch": ("cuda graphs (no host sync inside a step: overflow flags are read back "
                               "asynchronously, flush() inside the timed region)" if graph else "eager") +
-                             ("" if args.view_streams < 2 else
-                              ", views issued on %d forked streams" % args.view_streams),
+                             ("" if win.view_streams < 2 else
+                              ", views issued on %d forked streams" % win.view_streams),
                    **work},
         "clocks": clocks,
         "state_check": check,
@@ -690,8 +690,9 @@ def main():
     ap.add_argument("--peer-mode", default="mc", choices=["mc", "nomc"],
                     help="native arm, N>1: peer-memory Adam over NVLS multicast (multimem.ld_reduce / multimem.st) "
                          "where available, or plain peer loads / stores")
-    ap.add_argument("--view-streams", type=int, default=8,
-                    help="native arm: side streams the window's views are issued on (1 = serial)")
+    ap.add_argument("--view-streams", type=int, default=0,
+                    help="native arm: side streams the window's views are issued on (1 = serial; 0 = the "
+                         "library's choice, mapping.auto_view_streams: 8 unless one view's working set exceeds L2)")
     args = ap.parse_args()
     if not torch.cuda.is_available():
         if args.impl == "reference":
