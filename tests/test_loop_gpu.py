@@ -569,3 +569,52 @@ def test_peer_adam_two_ranks_on_one_gpu_matches_allreduce_plus_adam():
     assert not bool((own0 & own1).any())
     assert bool(own0.any()) and bool(own1.any())
     assert torch.equal(ms[0] + ms[1], me) and torch.equal(vs[0] + vs[1], ve)
+
+
+def test_peer_barrier_status_ors_the_overflow_flags_of_all_ranks():
+    """b2gs_peer_barrier_status through the C ABI, two 'ranks' on one device: each rank's guard word
+    ends up as the OR over ALL ranks of the overflow flags in their (instances, overflow) status
+    pairs — whatever the guard words held before (b2gs_window_finalize need not have run)."""
+    import ctypes as C
+    from monogs_dev_b200 import _lib
+    lib = _lib.lib
+    W = 2
+    dummy = [torch.zeros(16, device=DEV) for _ in range(W)]
+    sig = [torch.zeros(64, dtype=torch.int32, device=DEV) for _ in range(W)]
+    fail = [torch.zeros(1, dtype=torch.int32, device=DEV) for _ in range(W)]
+    guard = [torch.full((1,), 7, dtype=torch.int32, device=DEV) for _ in range(W)]     # stale values
+    status = [torch.zeros(3, 2, dtype=torch.int32, device=DEV) for _ in range(W)]      # 3 views per rank
+    streams = [torch.cuda.Stream() for _ in range(W)]
+    one = (C.c_void_p * 1)
+    try:
+        # world = 1 warm-up call: loads the kernel while no other barrier is spinning (see the test above)
+        pa1 = _lib.B2gsPeerArena(1, 0, one(dummy[0].data_ptr()), one(dummy[0].data_ptr()), one(sig[0].data_ptr()),
+                                 fail[0].data_ptr())
+        lib.b2gs_set_update_guard(guard[0].data_ptr())
+        _lib.check(lib.b2gs_peer_barrier_status(C.byref(pa1), status[0].data_ptr(), 3,
+                                                torch.cuda.current_stream().cuda_stream))
+        torch.cuda.synchronize()
+        assert int(guard[0]) == 0
+        for flags, want in (((0, 0), 0), ((0, 1), 1), ((1, 0), 1), ((0, 0), 0)):
+            keep = []
+            for r in range(W):
+                status[r].zero_()
+                status[r][:, 0] = 1000 + r
+                status[r][2, 1] = flags[r]              # the LAST view of rank r overflowed (or not)
+                guard[r].fill_(5)
+            torch.cuda.synchronize()
+            for r in range(W):
+                pb = (C.c_void_p * W)(*[t.data_ptr() for t in dummy])
+                sb = (C.c_void_p * W)(*[t.data_ptr() for t in sig])
+                pa = _lib.B2gsPeerArena(W, r, pb, pb, sb, fail[r].data_ptr())
+                keep.append((pb, sb, pa))
+                lib.b2gs_set_update_guard(guard[r].data_ptr())
+                _lib.check(lib.b2gs_peer_barrier_status(C.byref(pa), status[r].data_ptr(), 3, streams[r].cuda_stream))
+            torch.cuda.synchronize()
+            assert int(fail[0]) == 0 and int(fail[1]) == 0, "peer barrier timed out"
+            assert int(guard[0]) == want and int(guard[1]) == want, (flags, int(guard[0]), int(guard[1]))
+        # without a guard word the call is refused
+        lib.b2gs_set_update_guard(None)
+        assert lib.b2gs_peer_barrier_status(C.byref(pa1), status[0].data_ptr(), 3, None) != 0
+    finally:
+        lib.b2gs_set_update_guard(None)
