@@ -52,7 +52,9 @@ needs_ref = pytest.mark.skipif(not ref_ext.available(), reason="oracle/_ref not 
     ("cfg2_tracking", "sh", {}), ("cfg3_replica", "sh", {}),
     ("cfg5_large", "sh", dict(P=400_000)), ("cfg5_large", "sh", {}),      # BASELINE config 5 at its full 4M / SH3 / 1080p
     # few tiles, very long lists: the > 2048-key (smem bitonic) and > 4096-key (global) sort paths
-    ("tiny", "sh", dict(P=30_000, W=48, H=32)), ("tiny", "sh", dict(P=9_000, W=64, H=48))])
+    ("tiny", "sh", dict(P=30_000, W=48, H=32)), ("tiny", "sh", dict(P=9_000, W=64, H=48)),
+    # 32 640 tiles: more than the 8192 the cluster tile scan keeps in registers (its loop path)
+    ("cfg1_plumbing", "sh", dict(P=20_000, W=3840, H=2176))])
 def test_native_vs_reference_ext(name, mode, kw):
     bg = (0.0, 0.0, 0.0) if name.startswith("cfg") else (0.2, 0.4, 0.1)
     sc, rs, inp, gc, gd = build_case(name, device=DEV, mode=mode, bg=bg, **kw)
