@@ -73,17 +73,23 @@ __device__ __forceinline__ int fold10_slot(int lane) {
 __device__ __forceinline__ void warp_fold10_and_red(const float v[10], int lane,
                                                     float* __restrict__ slot_row, size_t row_off) {
   const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4, b1 = lane & 2;
-  float w0 = xchg_add(b4, v[0], v[5], 16);
-  float w1 = xchg_add(b4, v[1], v[6], 16);
-  float w2 = xchg_add(b4, v[2], v[7], 16);
-  float w3 = xchg_add(b4, v[3], v[8], 16);
-  float w4 = xchg_add(b4, v[4], v[9], 16);
-  float u0 = xchg_add(b3, w0, w3, 8);
-  float u1 = xchg_add(b3, w1, w4, 8);
-  float u2 = xchg_add(b3, w2, 0.f, 8);
-  float t0 = xchg_add(b2, u0, u2, 4);
-  float t1 = xchg_add(b2, u1, 0.f, 4);
-  float s = xchg_add(b1, t0, t1, 2);
+  // the adds of a level are issued in pairs where two run side by side (FADD2: keep.x + recv.x,
+  // keep.y + recv.y) — 3 issue slots fewer per fold
+#define B2GS_KEEP(up, lo, hi) ((up) ? (hi) : (lo))
+#define B2GS_RECV(up, lo, hi, off) __shfl_xor_sync(FULL, (up) ? (lo) : (hi), off)
+  const float2 w01 = __fadd2_rn(make_float2(B2GS_KEEP(b4, v[0], v[5]), B2GS_KEEP(b4, v[1], v[6])),
+                                make_float2(B2GS_RECV(b4, v[0], v[5], 16), B2GS_RECV(b4, v[1], v[6], 16)));
+  const float2 w23 = __fadd2_rn(make_float2(B2GS_KEEP(b4, v[2], v[7]), B2GS_KEEP(b4, v[3], v[8])),
+                                make_float2(B2GS_RECV(b4, v[2], v[7], 16), B2GS_RECV(b4, v[3], v[8], 16)));
+  const float w4 = xchg_add(b4, v[4], v[9], 16);
+  const float2 u01 = __fadd2_rn(make_float2(B2GS_KEEP(b3, w01.x, w23.y), B2GS_KEEP(b3, w01.y, w4)),
+                                make_float2(B2GS_RECV(b3, w01.x, w23.y, 8), B2GS_RECV(b3, w01.y, w4, 8)));
+  const float u2 = xchg_add(b3, w23.x, 0.f, 8);
+  const float2 t01 = __fadd2_rn(make_float2(B2GS_KEEP(b2, u01.x, u2), B2GS_KEEP(b2, u01.y, 0.f)),
+                                make_float2(B2GS_RECV(b2, u01.x, u2, 4), B2GS_RECV(b2, u01.y, 0.f, 4)));
+#undef B2GS_KEEP
+#undef B2GS_RECV
+  float s = xchg_add(b1, t01.x, t01.y, 2);
   s += __shfl_xor_sync(FULL, s, 1);
   if (slot_row) atomicAdd(slot_row + row_off, s);
 }
