@@ -244,3 +244,13 @@ def test_render_pipeline_switches(monkeypatch):
                                 torch.randn(4, 1), torch.randn(4, 4))
     mapping.render(cam, iso, None, torch.zeros(3))
     assert seen["scales"].shape == (4, 3) and torch.equal(seen["scales"][:, 0], seen["scales"][:, 2])
+
+
+def test_auto_view_streams_is_serial_without_a_gpu_and_bounded():
+    """mapping.auto_view_streams: one stream for anything that is not a CUDA arena; the GPU rule
+    (8 streams unless one view's working set exceeds L2) is exercised by bench.py's default run."""
+    from types import SimpleNamespace
+    from monogs_dev_b200 import mapping
+    g = SimpleNamespace(flat=torch.zeros(10), get_xyz=torch.zeros(5, 3))
+    assert mapping.auto_view_streams(g, 8) == 1
+    assert mapping.auto_view_streams(SimpleNamespace(), 8) == 1
