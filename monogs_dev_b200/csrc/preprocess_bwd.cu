@@ -166,15 +166,17 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
                       float* __restrict__ st_max_radii, float iso_w, int iso_stride, int iso_offset,
                       const int32_t* __restrict__ gate0, const int32_t* __restrict__ gate1,
                       const int32_t* __restrict__ gate2, const float4* __restrict__ conic_o, float half_w,
-                      float half_h) {
+                      float half_h, int stage_floats) {
   __shared__ float s_view[16], s_proj[16];
   __shared__ float s_tau[4][7];
   // accumulate mode, SH degree > 0: the dL_dsh_rest rows of a warp's 32 Gaussians are one contiguous,
   // 16-byte aligned span of the arena, so they are staged here and added with red.v4 by the whole
   // warp — 11 reduction lane-operations per Gaussian at degree 3 instead of 45 scalar ones (the
   // kernel was bound by their number at cfg5: 0.98 -> 0.78 ms with v2 triplets alone)
-  constexpr int SH_STAGE_MAX = 45;       // 3 * (16 - 1) floats per Gaussian
-  __shared__ __align__(16) float s_rest[RAW ? 128 * SH_STAGE_MAX : 4];
+  // DYNAMIC shared memory, 128 * 3 (M - 1) floats, handed over by the launch only when this path
+  // runs: as a static 23 KB array it took the L1 carve-out of six resident blocks at degree 0 too
+  // and cost the benched SH0 configuration 2 us per view.
+  extern __shared__ __align__(16) float s_rest[];
   pdl_wait();
   // statistics gates (B2gsBackwardIO.stats_gate): this view overflowed / the previous step was
   // discarded / the host has already counted this view for the step being re-run
@@ -213,8 +215,9 @@ preprocess_bwd_kernel(int P, int D, int M, const float* __restrict__ means3D,
   }
   const bool live = radius_in > 0;
   const int R3 = 3 * (M - 1);
-  const bool coop = RAW && accumulate && dL_dsh != nullptr && dL_dsh_rest != nullptr && shs != nullptr && M > 1 &&
-                    M <= 16 && D > 0 && blockDim.x == 128 && (reinterpret_cast<uintptr_t>(dL_dsh_rest) & 15u) == 0;
+  const bool coop = stage_floats >= 128 * R3 && RAW && accumulate && dL_dsh != nullptr && dL_dsh_rest != nullptr &&
+                    shs != nullptr && M > 1 && D > 0 && blockDim.x == 128 &&
+                    (reinterpret_cast<uintptr_t>(dL_dsh_rest) & 15u) == 0;
   float* const stage_row = coop ? s_rest + threadIdx.x * R3 : nullptr;
   if (coop && !live) {
     for (int k = 0; k < R3; ++k) stage_row[k] = 0.f;
@@ -619,7 +622,10 @@ int launch_preprocess_bwd(const B2gsScene& s, const GeomWS& g, const B2gsBackwar
   float* partials = const_cast<float*>(acc) + (size_t)s.P * ACC_STRIDE;  // scratch tail
   B2GS_PROF("preprocess_bwd", st);
   auto kern = s.raw_params ? preprocess_bwd_kernel<true> : preprocess_bwd_kernel<false>;
-  B2GS_LAUNCH(kern, blocks, 128, st,
+  // staging buffer of the dL_dsh_rest rows (kernel: `coop`): only where that path can run
+  const int stage_floats = (s.raw_params && io.accumulate && io.dL_dsh && io.dL_dsh_rest && s.shs && s.M > 1 &&
+                            s.M <= 16 && s.D > 0) ? 128 * 3 * (s.M - 1) : 0;
+  B2GS_LAUNCH_SMEM(kern, blocks, 128, sizeof(float) * (size_t)stage_floats, st,
       s.P, s.D, s.M, s.means3D, io.radii, s.shs, g.clamped, s.scales, s.rotations, s.scale_modifier,
       s.cov3D_precomp, s.viewmatrix, s.projmatrix, s.projmatrix_raw, s.campos, focal_x, focal_y,
       s.tan_fovx, s.tan_fovy, acc, io.dL_dmeans3D, io.dL_dmeans2D, io.dL_dopacity, io.dL_dcolors,
@@ -628,7 +634,7 @@ int launch_preprocess_bwd(const B2gsScene& s, const GeomWS& g, const B2gsBackwar
       io.densify_denom, io.max_radii2D,
       io.iso_reg_weight != 0.f ? io.iso_reg_weight / (3.0f * (float)s.P) : 0.f, io.iso_reg_stride,
       io.iso_reg_offset, io.stats_gate[0], io.stats_gate[1], io.stats_gate[2], g.conic_o,
-      0.5f * (float)s.W, 0.5f * (float)s.H);
+      0.5f * (float)s.W, 0.5f * (float)s.H, stage_floats);
   B2GS_LAUNCH_CHECK(st, s.debug);
   if (io.dL_dtau) {   // defer_tau callers hand the partial rows to b2gs_window_finalize instead
     tau_finalize_kernel<<<1, 256, 0, st>>>(blocks, partials, io.dL_dtau);
