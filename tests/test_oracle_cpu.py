@@ -207,3 +207,65 @@ def test_oracle_matches_reference_golden(path):
             assert frac_bad(bw[k][sel], g[k], 2e-2, 2e-3 * scale) < 1e-2, k
     tau_scale = float(g["dL_dtau"].abs().max())
     assert float((bw["dL_dtau"] - g["dL_dtau"]).abs().max()) < 5e-3 * tau_scale
+
+
+def test_backward_moment_and_carried_dot_rewrites_equal_the_reference_recurrences():
+    """The two algebraic rewrites of render_bwd.cu / preprocess_bwd.cu, checked in float64 against
+    the reference's per-pixel recurrences (CR/backward.cu:700-757) on a random pixel block:
+    (1) per splat, dL_dmean2D / dL_dconic / dL_dopacity from the six moments of q = G * dL_dalpha
+    about the splat centre with the conic / opacity / viewport factors applied once;
+    (2) the blended colour behind a splat carried as ONE number per pixel, accum . dL_dpixel."""
+    import numpy as np
+    rng = np.random.default_rng(11)
+    npx, nsp, W, H = 64, 12, 1200, 680
+    px = np.stack([rng.uniform(100, 108, npx), rng.uniform(200, 208, npx)], 1)      # pixel centres
+    mean = np.stack([rng.uniform(98, 110, nsp), rng.uniform(198, 210, nsp)], 1)
+    a, c = rng.uniform(0.05, 0.3, nsp), rng.uniform(0.05, 0.3, nsp)
+    b = rng.uniform(-0.04, 0.04, nsp)
+    op = rng.uniform(0.2, 0.95, nsp)
+    col = rng.uniform(0, 1, (nsp, 4))                                             # rgb + depth
+    dLp = rng.normal(size=(npx, 4))
+    bg = np.array([0.1, 0.2, 0.3])
+    # forward, front to back
+    T = np.ones(npx)
+    alpha = np.zeros((nsp, npx)); G = np.zeros((nsp, npx)); Tbefore = np.zeros((nsp, npx))
+    for i in range(nsp):
+        d = mean[i] - px
+        power = -0.5 * (a[i] * d[:, 0] ** 2 + c[i] * d[:, 1] ** 2) - b[i] * d[:, 0] * d[:, 1]
+        G[i] = np.exp(power)
+        al = np.minimum(0.99, op[i] * G[i])
+        al[(power > 0) | (al < 1 / 255)] = 0.0
+        alpha[i], Tbefore[i] = al, T
+        T = T * (1 - al)
+    T_final = T
+    # reference recurrences, back to front
+    ref = np.zeros((nsp, 10)); new = np.zeros((nsp, 10))
+    accum = np.zeros((npx, 4)); last_alpha = np.zeros(npx); last_col = np.zeros((npx, 4))
+    behind = np.zeros(npx)
+    bg_dot = dLp[:, :3] @ bg
+    for i in reversed(range(nsp)):
+        d = mean[i] - px
+        al, Ti, on = alpha[i], Tbefore[i], alpha[i] > 0
+        # --- reference form
+        accum = np.where(on[:, None], last_alpha[:, None] * last_col + (1 - last_alpha[:, None]) * accum, accum)
+        dL_dalpha = ((col[i] - accum) * dLp).sum(1) * Ti - T_final / (1 - al) * bg_dot
+        last_alpha = np.where(on, al, last_alpha); last_col = np.where(on[:, None], col[i], last_col)
+        dL_dG = op[i] * dL_dalpha
+        gdx, gdy = G[i] * d[:, 0], G[i] * d[:, 1]
+        dG_ddelx, dG_ddely = -gdx * a[i] - gdy * b[i], -gdy * c[i] - gdx * b[i]
+        ref[i] = [(dL_dG * dG_ddelx * 0.5 * W)[on].sum(), (dL_dG * dG_ddely * 0.5 * H)[on].sum(),
+                  (-0.5 * gdx * d[:, 0] * dL_dG)[on].sum(), (-0.5 * gdx * d[:, 1] * dL_dG)[on].sum(),
+                  (-0.5 * gdy * d[:, 1] * dL_dG)[on].sum(), (G[i] * dL_dalpha)[on].sum(),
+                  *[((al * Ti) * dLp[:, k])[on].sum() for k in range(4)]]
+        # --- rewritten form: carried dot product + moments
+        dd = col[i] @ dLp.T - behind
+        dLda2 = dd * Ti - T_final / (1 - al) * bg_dot
+        behind = behind + al * dd                       # alpha = 0 for a skipping pixel: unchanged
+        q = np.where(on, G[i] * dLda2, 0.0)
+        S0, Sx, Sy = q.sum(), (q * d[:, 0]).sum(), (q * d[:, 1]).sum()
+        Sxx, Sxy, Syy = (q * d[:, 0] ** 2).sum(), (q * d[:, 0] * d[:, 1]).sum(), (q * d[:, 1] ** 2).sum()
+        new[i] = [0.5 * W * op[i] * -(a[i] * Sx + b[i] * Sy), 0.5 * H * op[i] * -(c[i] * Sy + b[i] * Sx),
+                  -0.5 * op[i] * Sxx, -0.5 * op[i] * Sxy, -0.5 * op[i] * Syy, S0,
+                  *[((al * Ti) * dLp[:, k]).sum() for k in range(4)]]
+    assert np.abs(alpha).sum() > 0 and (alpha == 0).any(), "the block must mix taken and skipped pairs"
+    np.testing.assert_allclose(new, ref, rtol=1e-9, atol=1e-12 * np.abs(ref).max())
